@@ -1,0 +1,221 @@
+/*
+ * lynx_b200.h -- C ABI of the B200-native beam-tracking hot path.
+ *
+ * The reference (jank324/lynx) has NO plugin / FFI seam: its hot path is the Python
+ * method surface Segment.track / Element.transfer_map / Screen.reading / BPM.reading
+ * (SURVEY.md section 8b).  These entry points are what a binding for that surface
+ * (XLA FFI custom call, ctypes, torch extension) calls.  Each one cites the reference
+ * code it replaces.  Plain pointers and sizes only; no torch / XLA types.
+ *
+ * Conventions
+ *   - all `d_*` / device pointers are device memory owned by the caller; every launcher
+ *     only ENQUEUES work on `stream` and returns; no allocation, no synchronisation,
+ *     no global mutable state (a program handle is immutable after creation).
+ *   - return value: 0 = LYNX_OK, negative = lynx_status error.  No exceptions.
+ *   - coordinates are (x, xp, y, yp, s, p); the constant-1 seventh coordinate of the
+ *     reference (lynx/accelerator/element.py:41-54) is never stored.
+ *   - particles are SoA: six float planes of N_pad floats per beam row;
+ *     plane k of beam row r starts at  soa + (r*6 + k)*ld  (ld >= N, multiple of 4,
+ *     base 16-byte aligned).  AoS (..,N,7) <-> SoA converters are provided.
+ *   - B = number of settings (product of the reference's leading batch dims).
+ */
+#ifndef LYNX_B200_H
+#define LYNX_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* lynx_stream_t; /* == cudaStream_t */
+
+typedef enum {
+  LYNX_OK = 0,
+  LYNX_E_BADARG = -1,     /* null / misaligned pointer, negative size            */
+  LYNX_E_BADPROGRAM = -2, /* unknown opcode, column out of range, bad slot        */
+  LYNX_E_LAUNCH = -3,     /* CUDA reported an error while enqueueing              */
+  LYNX_E_NOMEM = -4,      /* handle / workspace allocation failed                 */
+  LYNX_E_NODEVICE = -5    /* no CUDA device: there is NO CPU fallback             */
+} lynx_status;
+
+/* Lattice program.  One op per reference element, in beam order.
+ * `col` = index of the op's first parameter column; columns are consecutive.     */
+typedef enum {
+  LYNX_OP_MARKER = 0,    /* marker.py:33-36 identity; no columns                         */
+  LYNX_OP_DRIFT = 1,     /* drift.py:44-62              cols: length                     */
+  LYNX_OP_QUAD = 2,      /* quadrupole.py:66-80         cols: length,k1,mis_x,mis_y,tilt */
+  LYNX_OP_HCOR = 3,      /* horizontal_corrector.py:52-67  cols: length,angle            */
+  LYNX_OP_VCOR = 4,      /* vertical_corrector.py:52-66    cols: length,angle            */
+  LYNX_OP_DIPOLE = 5,    /* dipole.py:112-181  cols: length,angle,e1,e2,tilt,fint,fint_exit,gap
+                            flag LYNX_F_RBEND adds angle/2 to e1,e2 (rbend.py:79-80)     */
+  LYNX_OP_CAVITY = 6,    /* cavity.py:97-325   cols: length,voltage,phase_deg,frequency
+                            flag LYNX_F_ACTIVE: non-linear energy-changing track
+                            (cavity.py:97-246); without it the linear map only
+                            (is_skippable case, cavity.py:68-70)                         */
+  LYNX_OP_SOLENOID = 7,  /* solenoid.py:61-105          cols: length,k,mis_x,mis_y       */
+  LYNX_OP_UNDULATOR = 8, /* undulator.py:48-60          cols: length                     */
+  LYNX_OP_CUSTOM = 9,    /* custom_transfer_map.py:87-88  cols: 42 = rows 0..5 of the 7x7,
+                            row-major (row 6 must be 0,..,0,1)                           */
+  LYNX_OP_BPM = 10,      /* bpm.py:48-58 ACTIVE bpm: aux = reading slot; no columns      */
+  LYNX_OP_SCREEN = 11,   /* screen.py:126-141 ACTIVE screen: aux = slot; cols: mis_x,mis_y;
+                            terminal: nothing after it is tracked (returns Beam.empty)   */
+  LYNX_OP__COUNT = 12
+} lynx_opcode;
+
+enum {
+  LYNX_F_ACTIVE = 1,       /* CAVITY: voltage != 0 somewhere in the batch          */
+  LYNX_F_RBEND = 2,        /* DIPOLE: rectangular bend                             */
+  LYNX_F_SCREEN_Y_FIX = 4  /* SCREEN: subtract mis_y from y (physically meant) instead
+                              of from xp as the reference writes it (screen.py:135) */
+};
+
+typedef struct {
+  int32_t opcode; /* lynx_opcode */
+  int32_t col;    /* first parameter column, -1 if none */
+  int32_t flags;
+  int32_t aux;    /* BPM / SCREEN slot */
+} lynx_op_t;
+
+/* Parameter table.  Value of column c for setting b:
+ *     params[col_offset[c] + b * col_stride[c]]      col_stride in {0 (shared), 1}
+ * so "vectorised element parameters" (tests/test_vectorized.py) are a stride-1 column
+ * and Element.broadcast (e.g. drift.py:64-65) is a stride-0 column: nothing is tiled. */
+typedef struct lynx_program lynx_program_t;
+
+int lynx_version(void);
+const char* lynx_status_str(int status);
+
+/* Builds an immutable program handle (copies ops / column descriptors to the device).
+ * Replaces the Python-side structure of Segment (segment.py:40-54) + the run grouping
+ * of Segment.track (segment.py:344-351), which is decided here once per lattice.     */
+int lynx_program_create(const lynx_op_t* ops, int32_t n_ops, const int64_t* col_offset,
+                        const int32_t* col_stride, int32_t n_cols, lynx_program_t** out);
+void lynx_program_destroy(lynx_program_t* prog);
+
+/* Introspection of the compiled plan. */
+int32_t lynx_program_num_stages(const lynx_program_t*);  /* affine stages (merged runs) */
+int32_t lynx_program_num_bpm(const lynx_program_t*);
+int32_t lynx_program_num_screens(const lynx_program_t*);
+int32_t lynx_program_is_terminal(const lynx_program_t*); /* ends in an active screen    */
+int64_t lynx_program_record_floats(const lynx_program_t*);
+
+/* Bytes of caller-supplied workspace needed by the particle launchers for B settings. */
+size_t lynx_workspace_bytes(const lynx_program_t*, int64_t B);
+
+/* K1 -- per-setting map composer.  Replaces Segment.transfer_map (segment.py:329-338),
+ * CustomTransferMap.from_merging_elements (custom_transfer_map.py:48-85) and every
+ * element's transfer_map (track_methods.py:14-122 and the element files cited above).
+ * Writes one record per setting into `records` ([B][record_floats]): the merged affine
+ * stage maps (rows 0..5 of each 7x7, row-major 6x7), the per-setting cavity scalars and
+ * the moment-shift centres.  `maps_out` (nullable, [B][n_stages][7][7]) receives the
+ * full 7x7 of every stage in the reference's layout.  `seed_soa` (nullable) is the
+ * incoming beam (used only to seed the moment-shift centre with particle 0).          */
+int lynx_compose_maps(const lynx_program_t*, const float* d_params, int64_t B,
+                      const float* d_energy_in /*[B]*/, const float* d_seed_soa,
+                      int64_t seed_row_stride /*0 = shared beam*/, int64_t seed_ld,
+                      float* d_records, float* d_maps_out, float* d_energy_out /*[B]*/,
+                      lynx_stream_t stream);
+
+/* K2 (+K4 histogram, K5 moments, BPM snapshots fused) -- fused particle tracker.
+ * Replaces Segment.track / Element.track for ParticleBeam (segment.py:340-356,
+ * element.py:83-92), Cavity._track_beam (cavity.py:97-246), BPM.track (bpm.py:48-58),
+ * Screen.track + Screen.reading (screen.py:126-141,195-211) and the ParticleBeam
+ * moment properties (particle_beam.py:736-836).
+ *   in_soa    [Bb][6][ld_in]   Bb = B, or 1 with in_row_stride = 0 (one beam, B settings)
+ *   out_soa   [B][6][ld_out]   nullable (terminal screen or moments-only)
+ *   bpm_sums  [n_bpm][B][2]    double, sums of x and y at each active BPM (ZEROED by the
+ *                              call); reading = sums / N
+ *   screen_img [B][H][W] float, image layout of the reference (row 0 = max y,
+ *                              flipud(hist.T), screen.py:208); ZEROED by the call;
+ *                              integer-valued, exact below 2^24 per pixel
+ *   edges_x [W+1], edges_y [H+1] float bin edges (screen.py:105-118), device memory
+ *   moment_sums [B][28] double  (ZEROED by the call): [0]=N, [1..6]=sum v_i,
+ *                              [7..27]=sum v_i v_j (i<=j, row-major upper triangle) of the
+ *                              OUTGOING beam (for a terminal screen: the beam at the screen)
+ *   moment_mode 0 = none, 1 = diagonal+xxp+yyp only (others left 0), 2 = all 21
+ *   workspace   lynx_workspace_bytes() bytes, device; holds the K1 records (K1 is run
+ *               inside this call)                                                      */
+int lynx_track_particles_fwd(const lynx_program_t*, const float* d_params, int64_t B,
+                             const float* d_in_soa, int64_t in_row_stride, int64_t ld_in,
+                             int64_t N, float* d_out_soa, int64_t ld_out,
+                             double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H,
+                             const float* d_edges_x, const float* d_edges_y,
+                             double* d_moment_sums, int32_t moment_mode,
+                             const float* d_energy_in, float* d_energy_out,
+                             void* d_workspace, lynx_stream_t stream);
+
+/* K3 -- adjoint of lynx_track_particles_fwd w.r.t. every parameter column and
+ * (optionally) the incoming particles.  The reference has no custom_vjp; this is the
+ * vjp of segment.py:340-356 that the array framework would derive op by op.
+ *   g_out_soa     [B][6][ld_g]  cotangent of the outgoing particles, nullable
+ *   g_moment_sums [B][28]       cotangent of moment_sums, nullable
+ *   g_bpm_sums    [n_bpm][B][2] cotangent of bpm_sums, nullable
+ *   g_params      float, same layout as params (shared columns reduced over B); ZEROED
+ *   g_in_soa      [Bb][6][ld_gin] nullable (for Bb == 1 < B reduced over settings)
+ *   g_energy_in   [B] nullable                                                          */
+int lynx_track_particles_bwd(const lynx_program_t*, const float* d_params, int64_t B,
+                             const float* d_in_soa, int64_t in_row_stride, int64_t ld_in,
+                             int64_t N, const float* d_g_out_soa, int64_t ld_g,
+                             const double* d_g_moment_sums, const double* d_g_bpm_sums,
+                             const float* d_energy_in, float* d_g_params,
+                             float* d_g_in_soa, int64_t ld_gin, void* d_workspace,
+                             lynx_stream_t stream);
+size_t lynx_bwd_workspace_bytes(const lynx_program_t*, int64_t B);
+
+/* K6 -- ParameterBeam step.  Replaces Element.track for ParameterBeam
+ * (element.py:71-82), the ParameterBeam branches of Cavity._track_beam
+ * (cavity.py:134-140,202-218), BPM.track and Screen.track.
+ *   mu_in [Bm][7], cov_in [Bm][7][7]  Bm = B or 1 (beam_stride 0: one beam, B settings)
+ *   mu_out [B][7], cov_out [B][7][7]  (for a terminal screen: the beam AT the screen,
+ *                                      misalignment already subtracted)
+ *   bpm_out [n_bpm][B][2] float readings                                                 */
+int lynx_parambeam_fwd(const lynx_program_t*, const float* d_params, int64_t B,
+                       const float* d_mu_in, const float* d_cov_in, int64_t beam_stride,
+                       const float* d_energy_in, float* d_mu_out, float* d_cov_out,
+                       float* d_bpm_out, float* d_energy_out, lynx_stream_t stream);
+int lynx_parambeam_bwd(const lynx_program_t*, const float* d_params, int64_t B,
+                       const float* d_mu_in, const float* d_cov_in, int64_t beam_stride,
+                       const float* d_energy_in, const float* d_g_mu, const float* d_g_cov,
+                       const float* d_g_bpm, float* d_g_params, float* d_g_mu_in,
+                       float* d_g_cov_in, lynx_stream_t stream);
+
+/* Layout converters between the reference's AoS (..,N,7) ParticleBeam.particles
+ * (particle_beam.py:24-45) and the SoA-6 device layout. */
+int lynx_aos7_to_soa6(const float* d_aos /*[R][N][7]*/, int64_t R, int64_t N,
+                      float* d_soa /*[R][6][ld]*/, int64_t ld, lynx_stream_t stream);
+int lynx_soa6_to_aos7(const float* d_soa, int64_t R, int64_t N, int64_t ld,
+                      float* d_aos /*[R][N][7], column 6 := 1*/, lynx_stream_t stream);
+
+/* Launch counter (kernels enqueued by this library since load / last reset). */
+int64_t lynx_launch_count(void);
+void lynx_launch_count_reset(void);
+
+/* ---- host-buffer entry points (what a NumPy / host-array binding calls) ------------
+ * Same semantics as the device launchers, but every pointer is HOST memory (pinned for
+ * full copy speed, pageable accepted).  Copies in, runs, copies out, synchronises.
+ * Device scratch is cached on a context handle.                                        */
+typedef struct lynx_host_ctx lynx_host_ctx_t;
+int lynx_host_ctx_create(int device, lynx_host_ctx_t** out);
+void lynx_host_ctx_destroy(lynx_host_ctx_t*);
+
+int lynx_host_track_particles(lynx_host_ctx_t*, const lynx_program_t*, const float* params,
+                              int64_t n_param_floats, int64_t B, const float* in_soa,
+                              int64_t Bb, int64_t N, const float* energy_in,
+                              float* out_soa /*nullable [B][6][N]*/,
+                              double* bpm_sums /*nullable*/, float* screen_img /*nullable*/,
+                              int32_t W, int32_t H, const float* edges_x,
+                              const float* edges_y, double* moment_sums /*nullable*/,
+                              int32_t moment_mode, float* energy_out /*nullable*/);
+
+int lynx_host_parambeam(lynx_host_ctx_t*, const lynx_program_t*, const float* params,
+                        int64_t n_param_floats, int64_t B, const float* mu_in,
+                        const float* cov_in, int64_t Bm, const float* energy_in,
+                        float* mu_out, float* cov_out, float* bpm_out /*nullable*/,
+                        float* energy_out /*nullable*/);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LYNX_B200_H */

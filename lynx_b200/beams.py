@@ -1,0 +1,295 @@
+"""Beam state (host-side mirror of lynx/particles/*).
+
+``ParticleBeam`` keeps the reference's constructor / property surface
+(particle_beam.py:24-45, 720-843) but stores particles as SoA-6 device planes
+``(*batch, 6, ld)``; ``.particles`` materialises the reference's AoS ``(*batch, N, 7)``
+view on demand.  Moments come from the fused double-precision sums of the tracking
+kernel (or one extra streaming pass when a beam was not produced by ``track``).
+``ParameterBeam`` mirrors parameter_beam.py:25-45, 371-433.
+"""
+
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+
+ELECTRON_MASS_EV = 510998.95069  # lynx/particles/beam.py:7
+
+
+class Beam:
+    """Base class; ``Beam.empty`` is the reference's sentinel (beam.py:12)."""
+
+    empty = "I'm an empty beam!"
+
+    # ---- derived quantities shared by both beam kinds (beam.py:241-310)
+    @property
+    def relativistic_gamma(self):
+        return self.energy / ELECTRON_MASS_EV
+
+    @property
+    def relativistic_beta(self):
+        g = self.relativistic_gamma
+        return torch.where(g.abs() > 0, torch.sqrt(1 - 1 / (g * g)), torch.ones_like(g))
+
+    @property
+    def emittance_x(self):
+        v = self.sigma_x**2 * self.sigma_xp**2 - self.sigma_xxp**2
+        return torch.sqrt(torch.clamp_min(v, torch.finfo(v.dtype).tiny))
+
+    @property
+    def emittance_y(self):
+        v = self.sigma_y**2 * self.sigma_yp**2 - self.sigma_yyp**2
+        return torch.sqrt(torch.clamp_min(v, torch.finfo(v.dtype).tiny))
+
+    @property
+    def normalized_emittance_x(self):
+        return self.emittance_x * self.relativistic_beta * self.relativistic_gamma
+
+    @property
+    def normalized_emittance_y(self):
+        return self.emittance_y * self.relativistic_beta * self.relativistic_gamma
+
+    @property
+    def beta_x(self):
+        return self.sigma_x**2 / self.emittance_x
+
+    @property
+    def alpha_x(self):
+        return -self.sigma_xxp / self.emittance_x
+
+    @property
+    def beta_y(self):
+        return self.sigma_y**2 / self.emittance_y
+
+    @property
+    def alpha_y(self):
+        return -self.sigma_yyp / self.emittance_y
+
+    @property
+    def parameters(self) -> dict:
+        names = ["mu_x", "mu_xp", "mu_y", "mu_yp", "sigma_x", "sigma_xp", "sigma_y",
+                 "sigma_yp", "sigma_s", "sigma_p", "energy"]
+        return {n: getattr(self, n) for n in names}
+
+
+_COORD = {"x": 0, "xp": 1, "y": 2, "yp": 3, "s": 4, "p": 5}
+
+
+def _tri(i: int, j: int) -> int:
+    return i * 6 - i * (i - 1) // 2 + (j - i)
+
+
+class ParticleBeam(Beam):
+    """Beam of individually tracked particles.
+
+    :param particles: ``(*batch, N, 7)`` as in the reference (seventh column 1), on any
+        device; converted once to the SoA-6 device layout.
+    :param energy: ``(*batch)`` reference energy in eV.
+    :param particle_charges: ``(*batch, N)``, passed through untouched.
+    """
+
+    def __init__(self, particles, energy, particle_charges=None, device=None,
+                 dtype=torch.float32):
+        assert dtype == torch.float32, "device path is fp32 (SURVEY.md section 5)"
+        assert particles.shape[-2] > 0 and particles.shape[-1] == 7, (
+            "Particle vectors must be 7-dimensional."
+        )
+        device = torch.device(device if device is not None else "cuda")
+        aos = particles.to(device=device, dtype=torch.float32).contiguous()
+        batch = tuple(aos.shape[:-2])
+        N = aos.shape[-2]
+        R = 1
+        for s in batch:
+            R *= s
+        ld = (N + 3) & ~3
+        soa = torch.empty((*batch, 6, ld), device=device, dtype=torch.float32)
+        if ld != N:
+            soa[..., N:] = 0
+        L.check(L.lib().lynx_aos7_to_soa6(aos.data_ptr(), R, N, soa.data_ptr(), ld,
+                                          L.current_stream()), "lynx_aos7_to_soa6")
+        self._init_soa(soa, N, torch.as_tensor(energy, dtype=torch.float32, device=device),
+                       particle_charges)
+
+    def _init_soa(self, soa, N, energy, particle_charges):
+        self._soa = soa
+        self._n = int(N)
+        self.energy = energy
+        self.particle_charges = (
+            particle_charges.to(device=soa.device, dtype=torch.float32)
+            if particle_charges is not None
+            else None
+        )
+        self._sums = None  # (*batch, 28) float64 raw moment sums
+
+    @classmethod
+    def from_soa(cls, soa, num_particles, energy, particle_charges=None, moment_sums=None):
+        """Wrap existing SoA-6 planes ``(*batch, 6, ld)`` (no copy)."""
+        self = cls.__new__(cls)
+        self._init_soa(soa, num_particles, energy, particle_charges)
+        self._sums = moment_sums
+        return self
+
+    # ---- storage views
+    @property
+    def soa(self) -> torch.Tensor:
+        return self._soa
+
+    @property
+    def ld(self) -> int:
+        return self._soa.shape[-1]
+
+    @property
+    def batch_shape(self):
+        return tuple(self._soa.shape[:-2])
+
+    @property
+    def num_particles(self) -> int:
+        return self._n
+
+    def __len__(self) -> int:
+        return self._n
+
+    @property
+    def particles(self) -> torch.Tensor:
+        """AoS ``(*batch, N, 7)`` view of the reference (particle_beam.py:35-39)."""
+        R = 1
+        for s in self.batch_shape:
+            R *= s
+        aos = torch.empty((*self.batch_shape, self._n, 7), device=self._soa.device,
+                          dtype=torch.float32)
+        L.check(L.lib().lynx_soa6_to_aos7(self._soa.data_ptr(), R, self._n, self.ld,
+                                          aos.data_ptr(), L.current_stream()),
+                "lynx_soa6_to_aos7")
+        return aos
+
+    @property
+    def total_charge(self):
+        if self.particle_charges is None:
+            return torch.zeros(self.batch_shape, device=self._soa.device)
+        return self.particle_charges.sum(dim=-1)
+
+    def _plane(self, k):
+        return self._soa[..., k, : self._n]
+
+    xs = property(lambda self: self._plane(0))
+    xps = property(lambda self: self._plane(1))
+    ys = property(lambda self: self._plane(2))
+    yps = property(lambda self: self._plane(3))
+    ss = property(lambda self: self._plane(4))
+    ps = property(lambda self: self._plane(5))
+
+    # ---- moments (particle_beam.py:736-836)
+    def moment_sums(self) -> torch.Tensor:
+        """``(*batch, 28)`` float64: N, sum v_i, sum v_i v_j (i<=j)."""
+        if self._sums is None:
+            from .segment import beam_moment_sums
+
+            self._sums = beam_moment_sums(self)
+        return self._sums
+
+    def _mean(self, i):
+        s = self.moment_sums()
+        return (s[..., 1 + i] / s[..., 0]).to(torch.float32)
+
+    def _std(self, i):  # torch.std default: unbiased, N-1 (particle_beam.py:742)
+        s = self.moment_sums()
+        n = s[..., 0]
+        var = (s[..., 7 + _tri(i, i)] - s[..., 1 + i] ** 2 / n) / (n - 1)
+        return torch.sqrt(torch.clamp_min(var, 0.0)).to(torch.float32)
+
+    def _cross(self, i, j):  # biased mean of centred products (particle_beam.py:824-836)
+        s = self.moment_sums()
+        n = s[..., 0]
+        return ((s[..., 7 + _tri(i, j)] - s[..., 1 + i] * s[..., 1 + j] / n) / n).to(
+            torch.float32
+        )
+
+    sigma_xxp = property(lambda self: self._cross(0, 1))
+    sigma_yyp = property(lambda self: self._cross(2, 3))
+
+    def broadcast(self, shape: tuple) -> "ParticleBeam":
+        """particle_beam.py:838-843 -- tiled by stride-0 views, nothing is copied."""
+        soa = self._soa.expand(*shape, *self._soa.shape[-2:]) if self.batch_shape in ((), (1,)) \
+            else self._soa.repeat(*shape, 1, 1)
+        energy = self.energy.expand(shape) if self.energy.numel() == 1 else self.energy.repeat(shape)
+        pc = self.particle_charges
+        if pc is not None:
+            pc = pc.expand(*shape, pc.shape[-1]) if pc.shape[:-1] in ((), (1,)) else pc.repeat(*shape, 1)
+        return ParticleBeam.from_soa(soa, self._n, energy, pc)
+
+    def __repr__(self) -> str:
+        return f"ParticleBeam(n={self._n}, batch={self.batch_shape}, energy={self.energy})"
+
+
+for _name, _i in _COORD.items():
+    setattr(ParticleBeam, f"mu_{_name}", property(lambda self, i=_i: self._mean(i)))
+    setattr(ParticleBeam, f"sigma_{_name}", property(lambda self, i=_i: self._std(i)))
+
+
+class ParameterBeam(Beam):
+    """Beam described by ``mu (*batch, 7)`` and ``cov (*batch, 7, 7)``
+    (parameter_beam.py:25-45)."""
+
+    def __init__(self, mu, cov, energy, total_charge=None, device=None, dtype=torch.float32):
+        assert dtype == torch.float32
+        device = torch.device(device if device is not None else "cuda")
+        kw = {"device": device, "dtype": torch.float32}
+        self._mu = torch.as_tensor(mu, **kw)
+        self._cov = torch.as_tensor(cov, **kw)
+        self.total_charge = torch.as_tensor(
+            total_charge if total_charge is not None else [0.0], **kw
+        )
+        self.energy = torch.as_tensor(energy, **kw)
+
+    @classmethod
+    def from_parameters(cls, mu_x=None, mu_xp=None, mu_y=None, mu_yp=None, sigma_x=None,
+                        sigma_xp=None, sigma_y=None, sigma_yp=None, sigma_s=None,
+                        sigma_p=None, cor_x=None, cor_y=None, cor_s=None, energy=None,
+                        total_charge=None, device=None, dtype=torch.float32):
+        """parameter_beam.py:47-146 (same defaults)."""
+        given = [a for a in (mu_x, mu_xp, mu_y, mu_yp, sigma_x, sigma_xp, sigma_y, sigma_yp,
+                             sigma_s, sigma_p, cor_x, cor_y, cor_s, energy, total_charge)
+                 if a is not None]
+        shape = tuple(given[0].shape) if given else (1,)
+        assert all(tuple(a.shape) == shape for a in given), "Arguments must have the same shape."
+        d = lambda a, v: (torch.as_tensor(a, dtype=torch.float64).cpu() if a is not None  # noqa: E731
+                          else torch.full(shape, v, dtype=torch.float64))
+        mu_x, mu_xp, mu_y, mu_yp = d(mu_x, 0.0), d(mu_xp, 0.0), d(mu_y, 0.0), d(mu_yp, 0.0)
+        sig = [d(sigma_x, 175e-9), d(sigma_xp, 2e-7), d(sigma_y, 175e-9), d(sigma_yp, 2e-7),
+               d(sigma_s, 1e-6), d(sigma_p, 1e-6)]
+        cor = [d(cor_x, 0.0), d(cor_y, 0.0), d(cor_s, 0.0)]
+        mu = torch.stack([mu_x, mu_xp, mu_y, mu_yp, torch.zeros(shape, dtype=torch.float64),
+                          torch.zeros(shape, dtype=torch.float64),
+                          torch.ones(shape, dtype=torch.float64)], dim=-1).float()
+        cov = torch.zeros(*shape, 7, 7)
+        for i in range(6):
+            cov[..., i, i] = (sig[i].float()) ** 2
+        for n, (i, j) in enumerate(((0, 1), (2, 3), (4, 5))):
+            cov[..., i, j] = cov[..., j, i] = cor[n].float()
+        return cls(mu, cov, d(energy, 1e8).float(), d(total_charge, 0.0).float(), device=device)
+
+    def _sigma(self, i):  # parameter_beam.py:375-417
+        return torch.sqrt(torch.clamp_min(self._cov[..., i, i], 1e-20))
+
+    sigma_xxp = property(lambda self: self._cov[..., 0, 1])
+    sigma_yyp = property(lambda self: self._cov[..., 2, 3])
+
+    def broadcast(self, shape: tuple) -> "ParameterBeam":
+        """parameter_beam.py:427-433 (stride-0 views instead of ``repeat``)."""
+        one = self._mu.shape[:-1] in ((), (1,))
+        mu = self._mu.reshape(7).expand(*shape, 7) if one else self._mu.repeat(*shape, 1)
+        cov = self._cov.reshape(7, 7).expand(*shape, 7, 7) if one else self._cov.repeat(*shape, 1, 1)
+        e = self.energy.reshape(()).expand(shape) if one else self.energy.repeat(shape)
+        q = self.total_charge.reshape(()).expand(shape) if one else self.total_charge.repeat(shape)
+        out = ParameterBeam.__new__(ParameterBeam)
+        out._mu, out._cov, out.energy, out.total_charge = mu, cov, e, q
+        return out
+
+    def __repr__(self) -> str:
+        return f"ParameterBeam(mu_x={self.mu_x}, sigma_x={self.sigma_x}, energy={self.energy})"
+
+
+for _name, _i in _COORD.items():
+    setattr(ParameterBeam, f"mu_{_name}", property(lambda self, i=_i: self._mu[..., i]))
+    setattr(ParameterBeam, f"sigma_{_name}", property(lambda self, i=_i: self._sigma(i)))

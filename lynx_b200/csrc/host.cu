@@ -1,0 +1,165 @@
+// Host-buffer entry points: the call a NumPy / host-array binding of
+// Segment.track makes.  Copies inputs host->device on the context's stream, runs the
+// device launchers, copies results back, synchronises.  Device scratch is cached on the
+// context and only grows.
+#include <cstring>
+#include <new>
+
+#include "common.cuh"
+
+struct lynx_host_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  struct Buf {
+    void* p = nullptr;
+    size_t cap = 0;
+  };
+  Buf params, in, out, energy_in, energy_out, bpm, img, ex, ey, mom, ws, mu_in, cov_in, mu_out,
+      cov_out, bpm_f;
+  bool grow(Buf& b, size_t bytes) {
+    if (bytes <= b.cap) return true;
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+    size_t cap = (bytes + 255) & ~(size_t)255;
+    if (cudaMalloc(&b.p, cap) != cudaSuccess) return false;
+    b.cap = cap;
+    return true;
+  }
+  void release(Buf& b) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+  }
+};
+
+extern "C" int lynx_host_ctx_create(int device, lynx_host_ctx_t** out) {
+  if (!out) return LYNX_E_BADARG;
+  *out = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) return LYNX_E_NODEVICE;
+  if (device < 0 || device >= n) return LYNX_E_BADARG;
+  if (cudaSetDevice(device) != cudaSuccess) return LYNX_E_LAUNCH;
+  lynx_host_ctx* c = new (std::nothrow) lynx_host_ctx();
+  if (!c) return LYNX_E_NOMEM;
+  c->device = device;
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete c;
+    return LYNX_E_LAUNCH;
+  }
+  *out = c;
+  return LYNX_OK;
+}
+
+extern "C" void lynx_host_ctx_destroy(lynx_host_ctx_t* c) {
+  if (!c) return;
+  lynx_host_ctx::Buf* all[] = {&c->params, &c->in,  &c->out,   &c->energy_in, &c->energy_out,
+                               &c->bpm,    &c->img, &c->ex,    &c->ey,        &c->mom,
+                               &c->ws,     &c->mu_in, &c->cov_in, &c->mu_out, &c->cov_out,
+                               &c->bpm_f};
+  for (auto* b : all) c->release(*b);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+#define H2D(buf, src, bytes)                                                          \
+  do {                                                                                \
+    if (!c->grow(buf, bytes)) return LYNX_E_NOMEM;                                    \
+    LYNX_CUDA_OK(cudaMemcpyAsync(buf.p, src, bytes, cudaMemcpyHostToDevice, st));      \
+  } while (0)
+#define D2H(dst, buf, bytes) \
+  LYNX_CUDA_OK(cudaMemcpyAsync(dst, buf.p, bytes, cudaMemcpyDeviceToHost, st))
+
+extern "C" int lynx_host_track_particles(
+    lynx_host_ctx_t* c, const lynx_program_t* p, const float* params, int64_t n_param_floats,
+    int64_t B, const float* in_soa, int64_t Bb, int64_t N, const float* energy_in,
+    float* out_soa, double* bpm_sums, float* screen_img, int32_t W, int32_t H,
+    const float* edges_x, const float* edges_y, double* moment_sums, int32_t moment_mode,
+    float* energy_out) {
+  if (!c || !p || !params || !in_soa || !energy_in || B <= 0 || N <= 0 || n_param_floats <= 0 ||
+      (Bb != 1 && Bb != B))
+    return LYNX_E_BADARG;
+  if (screen_img && (!edges_x || !edges_y)) return LYNX_E_BADARG;
+  LYNX_CUDA_OK(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int64_t ld = (N + 3) & ~(int64_t)3;
+  const int n_bpm = lynx_program_num_bpm(p);
+  const bool has_screen = screen_img && lynx_program_num_screens(p) > 0;
+
+  H2D(c->params, params, sizeof(float) * n_param_floats);
+  H2D(c->energy_in, energy_in, sizeof(float) * B);
+  if (!c->grow(c->in, sizeof(float) * Bb * 6 * ld)) return LYNX_E_NOMEM;
+  if (ld == N) {
+    LYNX_CUDA_OK(cudaMemcpyAsync(c->in.p, in_soa, sizeof(float) * Bb * 6 * N,
+                                 cudaMemcpyHostToDevice, st));
+  } else {
+    LYNX_CUDA_OK(cudaMemcpy2DAsync(c->in.p, sizeof(float) * ld, in_soa, sizeof(float) * N,
+                                   sizeof(float) * N, Bb * 6, cudaMemcpyHostToDevice, st));
+  }
+  if (out_soa && !c->grow(c->out, sizeof(float) * B * 6 * ld)) return LYNX_E_NOMEM;
+  if (!c->grow(c->energy_out, sizeof(float) * B)) return LYNX_E_NOMEM;
+  if (n_bpm > 0 && !c->grow(c->bpm, sizeof(double) * 2 * n_bpm * B)) return LYNX_E_NOMEM;
+  if (has_screen) {
+    if (!c->grow(c->img, sizeof(float) * (size_t)W * H * B)) return LYNX_E_NOMEM;
+    H2D(c->ex, edges_x, sizeof(float) * (W + 1));
+    H2D(c->ey, edges_y, sizeof(float) * (H + 1));
+  }
+  if (moment_mode && !c->grow(c->mom, sizeof(double) * 28 * B)) return LYNX_E_NOMEM;
+  if (!c->grow(c->ws, lynx_workspace_bytes(p, B))) return LYNX_E_NOMEM;
+
+  int rc = lynx_track_particles_fwd(
+      p, (const float*)c->params.p, B, (const float*)c->in.p, (Bb == B) ? 1 : 0,
+      ld, N, out_soa ? (float*)c->out.p : nullptr, ld, (double*)c->bpm.p,
+      has_screen ? (float*)c->img.p : nullptr, W, H, (const float*)c->ex.p,
+      (const float*)c->ey.p, moment_mode ? (double*)c->mom.p : nullptr, moment_mode,
+      (const float*)c->energy_in.p, (float*)c->energy_out.p, c->ws.p, (lynx_stream_t)st);
+  if (rc != LYNX_OK) return rc;
+
+  if (out_soa) {
+    if (ld == N) {
+      D2H(out_soa, c->out, sizeof(float) * B * 6 * N);
+    } else {
+      LYNX_CUDA_OK(cudaMemcpy2DAsync(out_soa, sizeof(float) * N, c->out.p, sizeof(float) * ld,
+                                     sizeof(float) * N, B * 6, cudaMemcpyDeviceToHost, st));
+    }
+  }
+  if (n_bpm > 0 && bpm_sums) D2H(bpm_sums, c->bpm, sizeof(double) * 2 * n_bpm * B);
+  if (has_screen) D2H(screen_img, c->img, sizeof(float) * (size_t)W * H * B);
+  if (moment_mode && moment_sums) D2H(moment_sums, c->mom, sizeof(double) * 28 * B);
+  if (energy_out) D2H(energy_out, c->energy_out, sizeof(float) * B);
+  LYNX_CUDA_OK(cudaStreamSynchronize(st));
+  return LYNX_OK;
+}
+
+extern "C" int lynx_host_parambeam(lynx_host_ctx_t* c, const lynx_program_t* p,
+                                   const float* params, int64_t n_param_floats, int64_t B,
+                                   const float* mu_in, const float* cov_in, int64_t Bm,
+                                   const float* energy_in, float* mu_out, float* cov_out,
+                                   float* bpm_out, float* energy_out) {
+  if (!c || !p || !params || !mu_in || !cov_in || !energy_in || !mu_out || !cov_out || B <= 0 ||
+      n_param_floats <= 0 || (Bm != 1 && Bm != B))
+    return LYNX_E_BADARG;
+  LYNX_CUDA_OK(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int n_bpm = lynx_program_num_bpm(p);
+  H2D(c->params, params, sizeof(float) * n_param_floats);
+  H2D(c->energy_in, energy_in, sizeof(float) * B);
+  H2D(c->mu_in, mu_in, sizeof(float) * 7 * Bm);
+  H2D(c->cov_in, cov_in, sizeof(float) * 49 * Bm);
+  if (!c->grow(c->mu_out, sizeof(float) * 7 * B)) return LYNX_E_NOMEM;
+  if (!c->grow(c->cov_out, sizeof(float) * 49 * B)) return LYNX_E_NOMEM;
+  if (!c->grow(c->energy_out, sizeof(float) * B)) return LYNX_E_NOMEM;
+  if (n_bpm > 0 && !c->grow(c->bpm_f, sizeof(float) * 2 * n_bpm * B)) return LYNX_E_NOMEM;
+  int rc = lynx_parambeam_fwd(p, (const float*)c->params.p, B, (const float*)c->mu_in.p,
+                              (const float*)c->cov_in.p, (Bm == B) ? 1 : 0,
+                              (const float*)c->energy_in.p, (float*)c->mu_out.p,
+                              (float*)c->cov_out.p, (float*)c->bpm_f.p,
+                              (float*)c->energy_out.p, (lynx_stream_t)st);
+  if (rc != LYNX_OK) return rc;
+  D2H(mu_out, c->mu_out, sizeof(float) * 7 * B);
+  D2H(cov_out, c->cov_out, sizeof(float) * 49 * B);
+  if (n_bpm > 0 && bpm_out) D2H(bpm_out, c->bpm_f, sizeof(float) * 2 * n_bpm * B);
+  if (energy_out) D2H(energy_out, c->energy_out, sizeof(float) * B);
+  LYNX_CUDA_OK(cudaStreamSynchronize(st));
+  return LYNX_OK;
+}

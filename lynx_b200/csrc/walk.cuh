@@ -1,0 +1,99 @@
+// Walks one setting through the compiled program, composing merged affine stages
+// (Segment.transfer_map, segment.py:329-338; run grouping of segment.py:344-351) and
+// handing them to a Sink.  Shared by K1 (records for the particle kernels) and K6
+// (ParameterBeam propagation).
+#pragma once
+#include "maps.cuh"
+
+namespace lynx {
+
+struct ParamView {
+  const float* params;
+  const int64_t* col_offset;
+  const int32_t* col_stride;
+  int64_t b;
+  __device__ __forceinline__ float operator()(int col) const {
+    return __ldg(params + __ldg(col_offset + col) + b * (int64_t)__ldg(col_stride + col));
+  }
+};
+
+// Sink concept:
+//   void stage(const Map& M, int stage_idx);                 merged run finished
+//   void cavity(const Map& C, const CavityOut& co, int stage_idx, int cav_idx);
+//   void bpm(int slot, int snap_idx);
+//   void screen(int slot, int screen_idx, float mis_x, float mis_y, int flags);
+template <typename Sink>
+__device__ __forceinline__ void walk_program(const DevOp* __restrict__ ops, int n_ops,
+                                             int final_stage, const ParamView& P,
+                                             float& energy, Sink& sink) {
+  Map M;
+  map_identity(M);
+  Rel rel = make_rel(energy);
+  for (int i = 0; i < n_ops; ++i) {
+    const DevOp op = ops[i];
+    if (op.flush_stage >= 0) {
+      sink.stage(M, op.flush_stage);
+      map_identity(M);
+    }
+    const int c = op.col;
+    switch (op.opcode) {
+      case LYNX_OP_MARKER:
+        break;
+      case LYNX_OP_DRIFT: {
+        float L = P(c);
+        lm_drift(M, L, drift_r56(L, rel));
+      } break;
+      case LYNX_OP_QUAD:
+        lm_quad(M, P(c), P(c + 1), P(c + 2), P(c + 3), P(c + 4), rel);
+        break;
+      case LYNX_OP_HCOR: {
+        float L = P(c);
+        lm_drift(M, L, drift_r56(L, rel));
+        M.m[1][6] += P(c + 1);  // horizontal_corrector.py:63
+      } break;
+      case LYNX_OP_VCOR: {
+        float L = P(c);
+        lm_drift(M, L, drift_r56(L, rel));
+        M.m[3][6] += P(c + 1);  // vertical_corrector.py:63
+      } break;
+      case LYNX_OP_DIPOLE:
+        lm_dipole(M, P(c), P(c + 1), P(c + 2), P(c + 3), P(c + 4), P(c + 5), P(c + 6),
+                  P(c + 7), (op.flags & LYNX_F_RBEND) != 0, rel);
+        break;
+      case LYNX_OP_CAVITY: {
+        Map C;
+        CavityOut co;
+        cavity_setting(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
+        if (op.flags & LYNX_F_ACTIVE) {
+          sink.cavity(C, co, op.self_stage, op.cav_idx);
+          energy += co.dE;  // cavity.py:130
+          rel = make_rel(energy);
+        } else {
+          // skippable cavity (voltage == 0 everywhere): linear map merged into the run
+          lm_custom(M, [&](int r, int k) { return C.m[r][k]; });
+        }
+      } break;
+      case LYNX_OP_SOLENOID:
+        lm_solenoid(M, P(c), P(c + 1), P(c + 2), P(c + 3), rel);
+        break;
+      case LYNX_OP_UNDULATOR: {
+        float L = P(c);
+        lm_drift(M, L, L * rel.igamma2_drift);  // undulator.py:52-58 (quirk B4)
+      } break;
+      case LYNX_OP_CUSTOM:
+        lm_custom(M, [&](int r, int k) { return P(c + r * 7 + k); });
+        break;
+      case LYNX_OP_BPM:
+        sink.bpm(op.aux, op.snap_idx);
+        break;
+      case LYNX_OP_SCREEN:
+        sink.screen(op.aux, op.snap_idx, P(c), P(c + 1), op.flags);
+        break;
+      default:
+        break;
+    }
+  }
+  if (final_stage >= 0) sink.stage(M, final_stage);
+}
+
+}  // namespace lynx

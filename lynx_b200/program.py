@@ -1,0 +1,144 @@
+"""Encode a flat list of elements into the C-ABI lattice program + parameter table.
+
+Host-side logic only (runs without a GPU up to ``Program.handle``): decides, from
+Python values at call time, which elements are active / skippable -- exactly the
+decisions the reference takes in ``is_skippable`` (cavity.py:68-70, bpm.py:40-42,
+screen.py:82-84) and ``Segment.track`` (segment.py:344-351) -- and lays the element
+parameters out as columns: a one-element tensor becomes a shared (stride-0) column, a
+batch-shaped tensor a per-setting (stride-1) column.  ``Element.broadcast`` therefore
+never materialises copies.
+"""
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Tuple
+
+import torch
+
+from . import _lib as L
+
+
+@dataclass
+class Encoded:
+    ops: List[Tuple[int, int, int, int]]  # (opcode, col, flags, aux)
+    columns: List[torch.Tensor]  # each numel()==1 (shared) or batch-shaped (per setting)
+    batch_shape: Tuple[int, ...]
+    bpm_elements: list  # active BPM elements, index == slot
+    screen_element: Optional[object]  # the terminal active screen, if any
+
+    @property
+    def B(self) -> int:
+        n = 1
+        for s in self.batch_shape:
+            n *= s
+        return n
+
+
+def _batch_shape(shapes) -> Tuple[int, ...]:
+    shape: Tuple[int, ...] = ()
+    for s in shapes:
+        shape = tuple(torch.broadcast_shapes(shape, tuple(s)))
+    return shape
+
+
+def encode(elements, energy_shape=()) -> Encoded:
+    """elements: flat list of lynx_b200 elements (no nested Segments)."""
+    ops, cols = [], []
+    bpms, screen = [], None
+    shapes = [tuple(energy_shape)]
+    for el in elements:
+        op = el._encode()  # (opcode, [tensors], flags) or None for identity elements
+        if op is None:
+            continue
+        opcode, tensors, flags = op
+        aux = 0
+        if opcode == L.OP_BPM:
+            aux = len(bpms)
+            bpms.append(el)
+        elif opcode == L.OP_SCREEN:
+            screen = el
+        col = len(cols) if tensors else -1
+        for t in tensors:
+            cols.append(t)
+            shapes.append(t.shape)
+        ops.append((opcode, col, flags, aux))
+        if opcode == L.OP_SCREEN:
+            break  # terminal: the reference returns Beam.empty from here on (screen.py:139)
+    if not ops:
+        ops.append((L.OP_MARKER, -1, 0, 0))
+    return Encoded(ops, cols, _batch_shape(shapes), bpms, screen)
+
+
+def layout(enc: Encoded):
+    """Column offsets / strides of the packed parameter buffer: shared scalars first,
+    then the per-setting columns, each B contiguous floats."""
+    B = enc.B
+    shared = [i for i, t in enumerate(enc.columns) if t.numel() == 1]
+    varying = [i for i, t in enumerate(enc.columns) if t.numel() != 1]
+    n_shared = len(shared)
+    # keep the per-setting block 16-byte aligned
+    base = (n_shared + 3) & ~3
+    off = [0] * len(enc.columns)
+    stride = [0] * len(enc.columns)
+    for k, i in enumerate(shared):
+        off[i] = k
+    for k, i in enumerate(varying):
+        off[i] = base + k * B
+        stride[i] = 1
+    total = base + len(varying) * B
+    return off, stride, shared, varying, max(total, 1)
+
+
+def pack_params(enc: Encoded, device) -> torch.Tensor:
+    """One fp32 device buffer holding every column (differentiable w.r.t. the columns)."""
+    off, stride, shared, varying, total = layout(enc)
+    B = enc.B
+    parts = []
+    n_shared = len(shared)
+    base = (n_shared + 3) & ~3
+    if base:
+        sh = [enc.columns[i].reshape(1).to(device=device, dtype=torch.float32) for i in shared]
+        if base > n_shared:
+            sh.append(torch.zeros(base - n_shared, device=device, dtype=torch.float32))
+        parts.extend(sh)
+    for i in varying:
+        t = enc.columns[i].to(device=device, dtype=torch.float32)
+        parts.append(t.expand(enc.batch_shape).reshape(B))
+    if not parts:
+        return torch.zeros(1, device=device, dtype=torch.float32)
+    return torch.cat(parts)
+
+
+class Program:
+    """Immutable device-side program handle (``lynx_program_create``), cached by
+    structure."""
+
+    _cache = {}
+
+    def __init__(self, ops, off, stride):
+        lib = L.lib()
+        n = len(ops)
+        arr = (L.OpT * n)(*[L.OpT(*o) for o in ops])
+        nc = len(off)
+        offs = (C.c_int64 * max(nc, 1))(*off)
+        strs = (C.c_int32 * max(nc, 1))(*stride)
+        h = C.c_void_p()
+        L.check(lib.lynx_program_create(arr, n, offs, strs, nc, C.byref(h)), "lynx_program_create")
+        self.handle = h
+        self.n_stages = lib.lynx_program_num_stages(h)
+        self.n_bpm = lib.lynx_program_num_bpm(h)
+        self.n_screens = lib.lynx_program_num_screens(h)
+        self.terminal = bool(lib.lynx_program_is_terminal(h))
+
+    def workspace_bytes(self, B: int) -> int:
+        return L.lib().lynx_workspace_bytes(self.handle, B)
+
+    @classmethod
+    def get(cls, enc: Encoded) -> "Program":
+        off, stride, _, _, _ = layout(enc)
+        key = (tuple(enc.ops), tuple(off), tuple(stride), torch.cuda.current_device())
+        prog = cls._cache.get(key)
+        if prog is None:
+            prog = cls(enc.ops, off, stride)
+            cls._cache[key] = prog
+        return prog

@@ -1,0 +1,339 @@
+"""``Segment`` and the launch glue between the element objects and the C ABI.
+
+Mirror of lynx/accelerator/segment.py:32-368 (container, name registry, subcell,
+flattened, transfer_map, track, broadcast, the ``transfer_maps_merged`` family).
+Plotting and file I/O are out of scope.
+"""
+
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+from .beams import Beam, ParameterBeam, ParticleBeam
+from .elements import BPM, CustomTransferMap, Drift, Element, Marker, Screen
+from .program import Program, encode, pack_params
+
+
+def _flatten(elements):
+    flat = []
+    for e in elements:
+        if isinstance(e, Segment):
+            flat.extend(_flatten(e.elements))
+        else:
+            flat.append(e)
+    return flat
+
+
+def _numel(shape) -> int:
+    n = 1
+    for s in shape:
+        n *= s
+    return n
+
+
+def _require_cuda(device):
+    if device.type != "cuda":
+        raise L.LynxError(
+            "lynx_b200 tracks on a CUDA device only (sm_100a kernels, no CPU fallback); "
+            f"got a beam on {device}"
+        )
+
+
+def _is_shared(t: torch.Tensor, nbatch_dims: int) -> bool:
+    """True if the leading batch dims hold one logical row (size 1 or stride 0)."""
+    return all(t.shape[d] == 1 or t.stride(d) == 0 for d in range(nbatch_dims))
+
+
+# --------------------------------------------------------------------------- K1
+def compose_transfer_map(elements, energy: torch.Tensor) -> Optional[torch.Tensor]:
+    """Segment.transfer_map (segment.py:329-338): product of the elements' maps."""
+    flat = _flatten(elements)
+    if not all(e.is_skippable for e in flat):
+        return None
+    energy = torch.as_tensor(energy, dtype=torch.float32)
+    device = energy.device if energy.device.type == "cuda" else torch.device("cuda")
+    _require_cuda(device)
+    energy = energy.to(device)
+    enc = encode(flat, energy.shape)
+    prog = Program.get(enc)
+    B = enc.B
+    bshape = enc.batch_shape
+    if prog.n_stages == 0:
+        return torch.eye(7, device=device).expand(*bshape, 7, 7).clone()
+    params = pack_params(enc, device)
+    e_in = energy.expand(bshape).reshape(B).contiguous()
+    rec = torch.empty(prog.workspace_bytes(B), dtype=torch.uint8, device=device)
+    maps = torch.empty((B, prog.n_stages, 7, 7), dtype=torch.float32, device=device)
+    L.check(L.lib().lynx_compose_maps(prog.handle, params.data_ptr(), B, e_in.data_ptr(), None,
+                                      0, 0, rec.data_ptr(), maps.data_ptr(), None,
+                                      L.current_stream()), "lynx_compose_maps")
+    return maps[:, 0].reshape(*bshape, 7, 7)
+
+
+# --------------------------------------------------------------------------- K2
+def launch_track_particles(prog: Program, params, B, soa, shared, ld, N, energy_in, *,
+                           want_out, moment_mode, screen: Optional[Screen], batch_shape):
+    """One call of ``lynx_track_particles_fwd``; returns the raw device outputs."""
+    device = soa.device
+    out = (torch.empty((*batch_shape, 6, ld), dtype=torch.float32, device=device)
+           if want_out else None)
+    bpm = (torch.empty((prog.n_bpm, B, 2), dtype=torch.float64, device=device)
+           if prog.n_bpm else None)
+    img = ex = ey = None
+    W = H = 0
+    if screen is not None:
+        ex, ey = screen._device_edges(device)
+        W, H = ex.numel() - 1, ey.numel() - 1
+        img = torch.empty((*batch_shape, H, W), dtype=torch.float32, device=device)
+    mom = (torch.empty((*batch_shape, 28), dtype=torch.float64, device=device)
+           if moment_mode else None)
+    e_out = torch.empty(batch_shape, dtype=torch.float32, device=device)
+    ws = torch.empty(prog.workspace_bytes(B), dtype=torch.uint8, device=device)
+    L.check(L.lib().lynx_track_particles_fwd(
+        prog.handle, params.data_ptr(), B, soa.data_ptr(), 0 if shared else 1, ld, N,
+        L.ptr(out), ld, L.ptr(bpm), L.ptr(img), W, H, L.ptr(ex), L.ptr(ey), L.ptr(mom),
+        moment_mode, energy_in.data_ptr(), e_out.data_ptr(), ws.data_ptr(),
+        L.current_stream()), "lynx_track_particles_fwd")
+    return out, bpm, img, mom, e_out
+
+
+def _prep_particle_beam(beam: ParticleBeam, batch_shape):
+    soa = beam.soa
+    nb = soa.dim() - 2
+    if _is_shared(soa, nb):
+        return soa[(0,) * nb].contiguous(), True
+    return soa.expand(*batch_shape, *soa.shape[-2:]).contiguous(), False
+
+
+def track_elements(elements, incoming, *, particles: bool = True, moments: int = 1):
+    """Segment.track (segment.py:340-356) for a flat or nested element list.
+
+    :param particles: write the outgoing particles (48 B/particle) or only the fused
+        readings / moments (24 B/particle).
+    :param moments: 0 none, 1 diagonal + xxp + yyp (all the ParticleBeam API exposes),
+        2 all 21 second moments.
+    """
+    if incoming is Beam.empty:
+        return incoming
+    flat = _flatten(elements)
+    if isinstance(incoming, ParameterBeam):
+        return _track_parameter_beam(flat, incoming)
+    if not isinstance(incoming, ParticleBeam):
+        raise TypeError(f"Parameter incoming is of invalid type {type(incoming)}")
+    device = incoming.soa.device
+    _require_cuda(device)
+    enc = encode(flat, incoming.energy.shape)
+    bshape = tuple(torch.broadcast_shapes(enc.batch_shape, incoming.batch_shape))
+    enc.batch_shape = bshape
+    B = enc.B
+    prog = Program.get(enc)
+    params = pack_params(enc, device)
+    e_in = incoming.energy.to(device).expand(bshape).reshape(B).contiguous()
+    soa, shared = _prep_particle_beam(incoming, bshape)
+    N, ld = incoming.num_particles, incoming.ld
+    want_out = particles and not prog.terminal
+    out, bpm, img, mom, e_out = launch_track_particles(
+        prog, params, B, soa, shared, ld, N, e_in, want_out=want_out, moment_mode=moments,
+        screen=enc.screen_element, batch_shape=bshape)
+    for slot, el in enumerate(enc.bpm_elements):  # bpm.py:54
+        el.reading = (bpm[slot] / N).to(torch.float32).T.reshape(2, *bshape)
+    if enc.screen_element is not None:
+        scr = enc.screen_element
+        upto = flat[: flat.index(scr)]
+        scr._read = lambda: _beam_at_screen(upto, incoming, scr)
+        scr.cached_reading = img
+        return Beam.empty
+    if not want_out:
+        return _MomentsOnly(mom, e_out, N)
+    pc = incoming.particle_charges
+    return ParticleBeam.from_soa(out, N, e_out, pc, moment_sums=mom)
+
+
+class _MomentsOnly(ParticleBeam):
+    """Outgoing beam of ``track(..., particles=False)``: moments and energy only."""
+
+    def __init__(self, sums, energy, n):
+        self._soa, self._n, self.energy, self.particle_charges, self._sums = None, n, energy, None, sums
+
+    @property
+    def batch_shape(self):
+        return tuple(self.energy.shape)
+
+
+def _beam_at_screen(upto, incoming, scr: Screen):
+    """The beam ``Screen.track`` would have stashed (screen.py:126-139)."""
+    beam = track_elements(upto, incoming, moments=0) if upto else incoming
+    soa = beam.soa.clone()
+    mis = scr.misalignment.to(soa.device)
+    soa[..., 0, :] -= mis[..., 0].reshape(*mis.shape[:-1], 1)
+    col = 2 if scr.y_misalignment_fix else 1  # quirk B1: y offset lands on xp as written
+    soa[..., col, :] -= mis[..., 1].reshape(*mis.shape[:-1], 1)
+    return ParticleBeam.from_soa(soa, beam.num_particles, beam.energy, beam.particle_charges)
+
+
+def beam_moment_sums(beam: ParticleBeam) -> torch.Tensor:
+    """One streaming pass (24 B/particle): all 28 raw moment sums of a beam."""
+    bshape = beam.batch_shape
+    B = max(_numel(bshape), 1)
+    device = beam.soa.device
+    _require_cuda(device)
+    enc = encode([], ())
+    enc.batch_shape = bshape
+    prog = Program.get(enc)
+    params = pack_params(enc, device)
+    e_in = torch.as_tensor(beam.energy, device=device, dtype=torch.float32).expand(bshape).reshape(B).contiguous()
+    soa, shared = _prep_particle_beam(beam, bshape)
+    _, _, _, mom, _ = launch_track_particles(
+        prog, params, B, soa, shared, beam.ld, beam.num_particles, e_in,
+        want_out=False, moment_mode=2, screen=None, batch_shape=bshape)
+    return mom
+
+
+# --------------------------------------------------------------------------- K6
+def _track_parameter_beam(flat, incoming: ParameterBeam):
+    device = incoming._mu.device
+    _require_cuda(device)
+    enc = encode(flat, incoming.energy.shape)
+    bshape = tuple(torch.broadcast_shapes(enc.batch_shape, tuple(incoming._mu.shape[:-1])))
+    enc.batch_shape = bshape
+    B = enc.B
+    prog = Program.get(enc)
+    params = pack_params(enc, device)
+    e_in = incoming.energy.to(device).expand(bshape).reshape(B).contiguous()
+    mu, cov = incoming._mu, incoming._cov
+    nb = mu.dim() - 1
+    shared = _is_shared(mu, nb) and _is_shared(cov, nb)
+    if shared:
+        mu_in, cov_in = mu[(0,) * nb].contiguous(), cov[(0,) * nb].contiguous()
+    else:
+        mu_in = mu.expand(*bshape, 7).contiguous()
+        cov_in = cov.expand(*bshape, 7, 7).contiguous()
+    mu_out = torch.empty((*bshape, 7), dtype=torch.float32, device=device)
+    cov_out = torch.empty((*bshape, 7, 7), dtype=torch.float32, device=device)
+    bpm = (torch.empty((prog.n_bpm, B, 2), dtype=torch.float32, device=device)
+           if prog.n_bpm else None)
+    e_out = torch.empty(bshape, dtype=torch.float32, device=device)
+    L.check(L.lib().lynx_parambeam_fwd(
+        prog.handle, params.data_ptr(), B, mu_in.data_ptr(), cov_in.data_ptr(),
+        0 if shared else 1, e_in.data_ptr(), mu_out.data_ptr(), cov_out.data_ptr(), L.ptr(bpm),
+        e_out.data_ptr(), L.current_stream()), "lynx_parambeam_fwd")
+    for slot, el in enumerate(enc.bpm_elements):
+        el.reading = bpm[slot].T.reshape(2, *bshape)
+    out = ParameterBeam.__new__(ParameterBeam)
+    out._mu, out._cov, out.energy = mu_out, cov_out, e_out
+    out.total_charge = incoming.total_charge
+    if enc.screen_element is not None:
+        enc.screen_element.set_read_beam(out)
+        return Beam.empty
+    return out
+
+
+# --------------------------------------------------------------------------- Segment
+class Segment(Element):
+    """segment.py:32-368."""
+
+    def __init__(self, elements, name: Optional[str] = None) -> None:
+        super().__init__(name=name)
+        self.elements = list(elements)
+        for element in self.elements:  # name registry, segment.py:45-54
+            if element.name in self.__dict__:
+                cur = self.__dict__[element.name]
+                if isinstance(cur, list):
+                    cur.append(element)
+                else:
+                    self.__dict__[element.name] = [cur, element]
+            else:
+                self.__dict__[element.name] = element
+
+    def subcell(self, start: str, end: str) -> "Segment":
+        sub, inside = [], False
+        for element in self.elements:
+            if element.name == start:
+                inside = True
+            if inside:
+                sub.append(element)
+            if element.name == end:
+                break
+        return self.__class__(sub)
+
+    def flattened(self) -> "Segment":
+        return Segment(_flatten(self.elements), name=self.name)
+
+    @property
+    def is_skippable(self) -> bool:
+        return all(e.is_skippable for e in self.elements)
+
+    @property
+    def length(self) -> torch.Tensor:
+        total = 0
+        for e in self.elements:
+            total = total + e.length.cpu()
+        return total
+
+    @length.setter
+    def length(self, value):  # Element.__init__ probes the attribute
+        pass
+
+    def transfer_map(self, energy):
+        return compose_transfer_map(self.elements, energy)
+
+    def track(self, incoming, **kw):
+        return track_elements(self.elements, incoming, **kw)
+
+    def broadcast(self, shape):
+        return self.__class__([e.broadcast(shape) for e in self.elements], name=self.name)
+
+    def split(self, resolution):
+        return [s for e in self.elements for s in e.split(resolution)]
+
+    def _encode(self):
+        raise TypeError("nested Segments are flattened before encoding")
+
+    # ---- speed optimisations of the reference (segment.py:84-218)
+    def transfer_maps_merged(self, incoming_beam, except_for=None) -> "Segment":
+        except_for = except_for or []
+        merged, run = [], []
+        beam = incoming_beam
+
+        def close(beam):
+            if len(run) == 1:
+                merged.append(run[0])
+                beam = run[0].track(beam)
+            elif len(run) > 1:
+                merged.append(CustomTransferMap.from_merging_elements(list(run), beam))
+                beam = merged[-1].track(beam)
+            run.clear()
+            return beam
+
+        for element in self.elements:
+            if element.is_skippable and element.name not in except_for:
+                run.append(element)
+            else:
+                beam = close(beam)
+                merged.append(element)
+                beam = element.track(beam)
+        if run:
+            merged.append(CustomTransferMap.from_merging_elements(list(run), beam))
+        return Segment(merged, name=self.name)
+
+    def without_inactive_markers(self, except_for=None) -> "Segment":
+        except_for = except_for or []
+        return Segment([e for e in self.elements
+                        if not isinstance(e, Marker) or e.name in except_for], name=self.name)
+
+    def without_inactive_zero_length_elements(self, except_for=None) -> "Segment":
+        except_for = except_for or []
+        return Segment([e for e in self.elements
+                        if bool((e.length > 0.0).any()) or getattr(e, "is_active", False)
+                        or e.name in except_for], name=self.name)
+
+    def inactive_elements_as_drifts(self, except_for=None) -> "Segment":
+        except_for = except_for or []
+        return Segment([
+            e if getattr(e, "is_active", False) or bool((e.length == 0.0).all())
+            or e.name in except_for else Drift(e.length)
+            for e in self.elements], name=self.name)
+
+    def __repr__(self) -> str:
+        return f"Segment(elements={self.elements!r}, name={self.name!r})"

@@ -1,0 +1,359 @@
+"""GPU parity: the CUDA path (through the C ABI) against the restatement oracle on the
+same seeded inputs.  Tolerances (north star): coordinates / moments within 1e-5
+relative in fp32 -- measured per SURVEY 7.3-3 against the fp64 oracle with the fp32
+oracle's own distance from it allowed on top; screen bins exact for the kernel's own
+coordinates, and vs. the oracle exact except particles within a few ulp of an edge.
+"""
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import aos_from_soa, assert_close_scaled, oracle_elements
+
+pytestmark = pytest.mark.gpu
+
+import lynx_b200 as lx  # noqa: E402
+from lynx_b200 import fixtures as F  # noqa: E402
+from oracle import lattice as O  # noqa: E402
+from oracle import screen_bin_edges, screen_reading_particles, segment_map  # noqa: E402
+
+
+def _oracle_track(spec, soa, energy, dtype, **kw):
+    els = oracle_elements(spec, dtype)
+    beam = O.ParticleBeamO(aos_from_soa(soa, dtype), torch.tensor([energy], dtype=dtype))
+    out = O.track(els, beam, **kw)
+    return els, out
+
+
+def _planes(beam_o):
+    return beam_o.particles[0, :, :6].T.numpy()
+
+
+def _gpu_beam(soa, energy):
+    t = torch.from_numpy(F.soa_to_aos7(soa)).unsqueeze(0)
+    return lx.ParticleBeam(t, torch.tensor([energy]))
+
+
+# ------------------------------------------------------------------ K1 maps
+def _rand(rng, lo, hi, n):
+    return torch.tensor(rng.uniform(lo, hi, n), dtype=torch.float32)
+
+
+def _check_maps(got, els, energy):
+    t64 = segment_map([_cast(e, torch.float64) for e in els], energy.double()).numpy()
+    t32 = segment_map(els, energy).numpy()
+    g = got.cpu().numpy().astype(np.float64)
+    # entries of a 7x7 live on very different scales: scale = max(|entry|, row scale*1e-3)
+    tol = 1e-5 * np.abs(t64) + np.abs(t32 - t64) + 1e-5 * 1e-3 * np.abs(t64).max(axis=-1, keepdims=True)
+    err = np.abs(g - t64)
+    assert (err <= tol).all(), f"worst {np.max(err / (np.abs(t64) + 1e-30)):.3e}"
+
+
+def _cast(el, dtype):
+    return O.El(el.kind, el.name, {k: (v.to(dtype) if torch.is_tensor(v) else v)
+                                   for k, v in el.p.items()}, el.is_active)
+
+
+def test_k1_element_maps_vs_oracle():
+    rng = np.random.default_rng(11)
+    B = 257
+    energy = _rand(rng, 5e6, 2e8, B)
+    z = torch.zeros(B)
+    cases = []
+    L_ = _rand(rng, 0.05, 2.0, B)
+    cases.append(([lx.Drift(L_)], [O.El("drift", "d", {"length": L_})]))
+    k1 = _rand(rng, -30, 30, B)
+    k1[:5] = 0.0
+    mis = torch.stack([_rand(rng, -1e-3, 1e-3, B), _rand(rng, -1e-3, 1e-3, B)], dim=-1)
+    tilt = _rand(rng, -1.5, 1.5, B)
+    tilt[::3] = 0.0
+    cases.append(([lx.Quadrupole(L_, k1, mis, tilt)],
+                  [O.El("quadrupole", "q", {"length": L_, "k1": k1, "misalignment": mis,
+                                            "tilt": tilt})]))
+    ang = _rand(rng, -6e-3, 6e-3, B)
+    cases.append(([lx.HorizontalCorrector(L_, ang)], [O.El("hcor", "h", {"length": L_, "angle": ang})]))
+    cases.append(([lx.VerticalCorrector(L_, ang)], [O.El("vcor", "v", {"length": L_, "angle": ang})]))
+    bang = _rand(rng, -0.4, 0.4, B)
+    e1, e2 = _rand(rng, -0.3, 0.3, B), _rand(rng, -0.3, 0.3, B)
+    fi, fe, gap = _rand(rng, 0, 0.5, B), _rand(rng, 0, 0.5, B), _rand(rng, 0, 0.05, B)
+    dp = {"length": L_, "angle": bang, "e1": e1, "e2": e2, "tilt": tilt, "fringe_integral": fi,
+          "fringe_integral_exit": fe, "gap": gap}
+    cases.append(([lx.Dipole(L_, bang, e1, e2, tilt, fi, fe, gap)], [O.El("dipole", "b", dp)]))
+    cases.append(([lx.RBend(L_, bang, e1, e2, tilt, fi, fe, gap)], [O.El("rbend", "b", dp)]))
+    ks = _rand(rng, -3, 3, B)
+    ks[:3] = 0.0
+    cases.append(([lx.Solenoid(L_, ks, mis)],
+                  [O.El("solenoid", "s", {"length": L_, "k": ks, "misalignment": mis})]))
+    cases.append(([lx.Undulator(L_)], [O.El("undulator", "u", {"length": L_})]))
+    for gpu_els, o_els in cases:
+        got = lx.Segment(gpu_els).transfer_map(energy.cuda())
+        _check_maps(got, o_els, energy)
+
+
+def test_k1_ares_segment_map_batched():
+    """Segment.transfer_map over 4096 random settings (config 3 ranges)."""
+    B = 4096
+    k1, ang = F.random_settings(B)
+    seg = F.build_segment(F.ares_ea())
+    seg.AREAMQZM1.k1 = torch.from_numpy(k1[:, 0])
+    seg.AREAMQZM2.k1 = torch.from_numpy(k1[:, 1])
+    seg.AREAMQZM3.k1 = torch.from_numpy(k1[:, 2])
+    seg.AREAMCVM1.angle = torch.from_numpy(ang[:, 0])
+    seg.AREAMCHM1.angle = torch.from_numpy(ang[:, 1])
+    energy = torch.full((B,), F.ASTRA_ENERGY)
+    got = seg.transfer_map(energy.cuda())
+    ov = {("AREAMQZM1", "k1"): k1[:, 0], ("AREAMQZM2", "k1"): k1[:, 1],
+          ("AREAMQZM3", "k1"): k1[:, 2], ("AREAMCVM1", "angle"): ang[:, 0],
+          ("AREAMCHM1", "angle"): ang[:, 1]}
+    els = oracle_elements(F.ares_ea(), torch.float32, (B,), ov)
+    _check_maps(got, els, energy)
+
+
+# ------------------------------------------------------------------ K2 particles
+@pytest.mark.parametrize("n", [1, 5, 1000, 100_003])
+def test_ares_ea_particles(n):
+    """Config 2 lattice (k1 = 5,-5,5; kicks 1e-3,-2e-3: tests/test_compare_ocelot.py:254-258),
+    ragged particle counts."""
+    spec = F.ares_ea(k1=(5.0, -5.0, 5.0), vkick=1e-3, hkick=-2e-3)
+    soa = F.gaussian_beam_soa(n, seed=1002)
+    _, t64 = _oracle_track(spec, soa, F.ASTRA_ENERGY, torch.float64)
+    _, t32 = _oracle_track(spec, soa, F.ASTRA_ENERGY, torch.float32)
+    out = F.build_segment(spec).track(_gpu_beam(soa, F.ASTRA_ENERGY))
+    assert out.particles.shape == (1, n, 7)
+    got = out.soa[0, :, :n].cpu().numpy()
+    if n >= 1000:
+        assert_close_scaled(got, _planes(t64), _planes(t32), what="ARES EA particles")
+    else:
+        np.testing.assert_allclose(got, _planes(t64), rtol=2e-4, atol=1e-9)
+    assert torch.all(out.particles[..., 6] == 1)
+    np.testing.assert_allclose(out.energy.cpu().numpy(), [F.ASTRA_ENERGY], rtol=1e-7)
+
+
+def test_smatch_bpms_and_moments():
+    """Config 1: README SMATCH with the three BPMs active, 100k particles."""
+    spec = F.smatch(bpms_active=True, angles=(1e-4, -2e-4, 1.5e-4))
+    sig = (175e-9, 2e-7, 175e-9, 2e-7, 1e-6, 1e-6)
+    soa = F.gaussian_beam_soa(100_000, mu=(0.0,) * 6, sigma=sig, seed=1001)
+    els, t64 = _oracle_track(spec, soa, 1e8, torch.float64)
+    seg = F.build_segment(spec)
+    out = seg.track(_gpu_beam(soa, 1e8))
+    _, t32 = _oracle_track(spec, soa, 1e8, torch.float32)
+    assert_close_scaled(out.soa[0, :, :100_000].cpu().numpy(), _planes(t64), _planes(t32),
+                        what="SMATCH particles")
+    for name in ("BPM1SMATCH", "BPM6SMATCH", "BPM13SMATCH"):
+        want = next(e for e in els if e.name == name).reading.numpy()  # (2, 1)
+        got = getattr(seg, name).reading.cpu().numpy()
+        assert got.shape == (2, 1)
+        scale = np.abs(_planes(t64)[[0, 2]]).max()
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6 * scale)
+    for i, nm in enumerate(("x", "xp", "y", "yp", "s", "p")):
+        np.testing.assert_allclose(getattr(out, f"mu_{nm}").cpu().numpy(), t64.mu(i).numpy(),
+                                   rtol=1e-5, atol=1e-6 * t64.sigma(i).item())
+        np.testing.assert_allclose(getattr(out, f"sigma_{nm}").cpu().numpy(),
+                                   t64.sigma(i).numpy(), rtol=1e-5)
+    np.testing.assert_allclose(out.sigma_xxp.cpu().numpy(), t64.sigma_xxp.numpy(), rtol=1e-5)
+    np.testing.assert_allclose(out.sigma_yyp.cpu().numpy(), t64.sigma_yyp.numpy(), rtol=1e-5)
+
+
+def test_screen_histogram_exact_and_vs_oracle():
+    """Config 2 with AREABSCR1 active (tests/test_screen.py:78-98 geometry)."""
+    n = 200_000
+    spec = F.ares_ea(k1=(5.0, -5.0, 5.0), vkick=1e-3, hkick=-2e-3, screen_active=True,
+                     screen=F.TEST_SCREEN)
+    soa = F.gaussian_beam_soa(n, seed=1002)
+    seg = F.build_segment(spec)
+    beam = _gpu_beam(soa, F.ASTRA_ENERGY)
+    assert seg.track(beam) is lx.Beam.empty
+    img = seg.AREABSCR1.reading
+    assert img.shape == (1, 2040, 2448)
+    assert img.sum().item() <= n and img.sum().item() > 0.5 * n
+    # (a) bit-exact vs torch.histogramdd on the kernel's OWN coordinates
+    read = seg.AREABSCR1.get_read_beam()
+    ex, ey = screen_bin_edges(F.TEST_SCREEN["resolution"], F.TEST_SCREEN["pixel_size"])
+    own = screen_reading_particles(read.xs.cpu(), read.ys.cpu(), ex, ey)
+    assert torch.equal(img.cpu(), own)
+    # (b) vs the oracle end to end: only particles within a few ulp of an edge may move
+    els, _ = _oracle_track(spec, soa, F.ASTRA_ENERGY, torch.float32)
+    rb = els[-1].read_beam
+    want = screen_reading_particles(rb.col(0), rb.col(2), ex, ey)
+    moved = (img.cpu() - want).abs().sum().item() / 2
+    assert img.sum().item() == want.sum().item() or moved <= 1e-3 * n
+    assert moved <= 2e-3 * n, moved
+
+
+def test_screen_edge_semantics_device():
+    """Left-closed bins, right-closed last bin, out-of-range dropped -- on the device."""
+    scr = lx.Screen(resolution=torch.tensor([4.0, 2.0]), pixel_size=torch.tensor([1.0, 1.0]),
+                    is_active=True, name="s")
+    seg = lx.Segment([scr])
+    xs = [-2.0, -1.0, 1.999, 2.0, 2.1, -2.1, 0.5]
+    ys = [-1.0, 0.0, 0.999, 1.0, 0.0, 0.0, -0.5]
+    p = torch.zeros(1, len(xs), 7)
+    p[0, :, 0] = torch.tensor(xs)
+    p[0, :, 2] = torch.tensor(ys)
+    p[0, :, 6] = 1
+    seg.track(lx.ParticleBeam(p, torch.tensor([1e8])))
+    expect = torch.tensor([[[0.0, 1.0, 0.0, 2.0], [1.0, 0.0, 1.0, 0.0]]])
+    assert torch.equal(scr.reading.cpu(), expect)
+
+
+def test_cavity_dipole_line_particles():
+    """Config 4 lattice: non-linear cavity + dipole, 50k particles."""
+    n = 50_000
+    spec = F.cavity_dipole_line(screen_active=False)
+    soa = F.cfg4_beam_soa(n)
+    _, t64 = _oracle_track(spec, soa, F.CFG4_ENERGY, torch.float64)
+    _, t32 = _oracle_track(spec, soa, F.CFG4_ENERGY, torch.float32)
+    out = F.build_segment(spec).track(_gpu_beam(soa, F.CFG4_ENERGY))
+    assert_close_scaled(out.soa[0, :, :n].cpu().numpy(), _planes(t64), _planes(t32),
+                        what="cavity line particles")
+    np.testing.assert_allclose(out.energy.cpu().numpy(), t64.energy.numpy(), rtol=1e-6)
+
+
+def test_vectorized_shapes_and_broadcast_equivalence():
+    """tests/test_vectorized.py:54,88,324-366: batch dims (2,) and (3,2); broadcast then
+    track == track."""
+    n = 4096
+    spec = F.ares_ea(k1=(4.2, -3.0, 1.0), vkick=2e-4)
+    soa = F.gaussian_beam_soa(n, seed=5)
+    seg = F.build_segment(spec)
+    beam = _gpu_beam(soa, F.ASTRA_ENERGY)
+    base = seg.track(beam)
+    for shape in [(2,), (3, 2)]:
+        out = seg.broadcast(shape).track(beam.broadcast(shape))
+        assert out.particles.shape == (*shape, n, 7)
+        assert out.mu_x.shape == shape and out.sigma_p.shape == shape
+        assert out.energy.shape == shape
+        flat = out.soa.reshape(-1, 6, out.ld)
+        for r in range(flat.shape[0]):
+            assert torch.equal(flat[r], base.soa[0])
+
+
+def test_per_setting_particles():
+    """Three settings with different k1, per-setting outputs match three oracle runs."""
+    n = 3000
+    soa = F.gaussian_beam_soa(n, seed=9)
+    k1s = [(-5.0, 2.0, 7.5), (0.0, 0.0, 0.0), (12.0, -20.0, 3.0)]
+    seg = F.build_segment(F.ares_ea())
+    for i, nm in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")):
+        getattr(seg, nm).k1 = torch.tensor([k[i] for k in k1s])
+    out = seg.track(_gpu_beam(soa, F.ASTRA_ENERGY))
+    assert out.particles.shape == (3, n, 7)
+    for b, k1 in enumerate(k1s):
+        _, t64 = _oracle_track(F.ares_ea(k1=k1), soa, F.ASTRA_ENERGY, torch.float64)
+        _, t32 = _oracle_track(F.ares_ea(k1=k1), soa, F.ASTRA_ENERGY, torch.float32)
+        assert_close_scaled(out.soa[b, :, :n].cpu().numpy(), _planes(t64), _planes(t32),
+                            what=f"setting {b}")
+
+
+# ------------------------------------------------------------------ K6 ParameterBeam
+def test_parameter_beam_4096_settings():
+    """Config 3: 4096 random settings x ParameterBeam through ARES EA."""
+    B = 4096
+    k1, ang = F.random_settings(B)
+    seg = F.build_segment(F.ares_ea())
+    names = ("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")
+    for i, nm in enumerate(names):
+        getattr(seg, nm).k1 = torch.from_numpy(k1[:, i])
+    seg.AREAMCVM1.angle = torch.from_numpy(ang[:, 0])
+    seg.AREAMCHM1.angle = torch.from_numpy(ang[:, 1])
+    kw = dict(zip(("mu_x", "mu_xp", "mu_y", "mu_yp"), (torch.tensor([v]) for v in F.ASTRA_MU[:4])))
+    kw.update(dict(zip(("sigma_x", "sigma_xp", "sigma_y", "sigma_yp", "sigma_s", "sigma_p"),
+                       (torch.tensor([v]) for v in F.ASTRA_SIGMA))))
+    beam = lx.ParameterBeam.from_parameters(energy=torch.tensor([F.ASTRA_ENERGY]), **kw)
+    out = seg.track(beam)
+    assert out._mu.shape == (B, 7) and out._cov.shape == (B, 7, 7)
+    ov = {(nm, "k1"): k1[:, i] for i, nm in enumerate(names)}
+    ov[("AREAMCVM1", "angle")] = ang[:, 0]
+    ov[("AREAMCHM1", "angle")] = ang[:, 1]
+    res = {}
+    for d in (torch.float32, torch.float64):
+        els = oracle_elements(F.ares_ea(), d, (B,), ov)
+        pb = O.ParameterBeamO.from_parameters(F.ASTRA_MU[:4], F.ASTRA_SIGMA, F.ASTRA_ENERGY, dtype=d)
+        pb = O.ParameterBeamO(pb.mu_.expand(B, 7).clone(), pb.cov_.expand(B, 7, 7).clone(),
+                              pb.energy.expand(B).clone())
+        res[d] = O.track(els, pb)
+    t64, t32 = res[torch.float64], res[torch.float32]
+    mu = out._mu.cpu().numpy().astype(np.float64)
+    cov = out._cov.cpu().numpy().astype(np.float64)
+    m64, m32 = t64.mu_.numpy(), t32.mu_.numpy().astype(np.float64)
+    c64, c32 = t64.cov_.numpy(), t32.cov_.numpy().astype(np.float64)
+    sd = np.sqrt(np.abs(np.einsum("bii->bi", c64)))
+    tol_mu = 1e-5 * (np.abs(m64) + sd) + np.abs(m32 - m64)
+    assert (np.abs(mu - m64) <= tol_mu).all()
+    tol_c = 1e-5 * (sd[:, :, None] * sd[:, None, :] + np.abs(c64)) + np.abs(c32 - c64)
+    assert (np.abs(cov - c64) <= tol_c).all()
+
+
+def test_parameter_beam_cavity_and_bpm():
+    spec = F.cavity_dipole_line(screen_active=False)
+    spec.insert(5, ("bpm", "BPMX", {"is_active": True}))
+    sx, sxp, cx = F.twiss_sigmas(5.91253677, 3.55631308, 3.494768647122823e-09)
+    sy, syp, cy = F.twiss_sigmas(5.91253677, 3.55631308, 3.497810737006068e-09)
+    t = lambda v: torch.tensor([v])  # noqa: E731
+    beam = lx.ParameterBeam.from_parameters(
+        mu_x=t(1e-4), mu_xp=t(-2e-5), sigma_x=t(sx), sigma_xp=t(sxp), sigma_y=t(sy),
+        sigma_yp=t(syp), cor_x=t(cx), cor_y=t(cy), energy=t(F.CFG4_ENERGY))
+    seg = F.build_segment(spec)
+    out = seg.track(beam)
+    d = torch.float64
+    els = oracle_elements(spec, d)
+    pb = O.ParameterBeamO.from_parameters((1e-4, -2e-5, 0.0, 0.0), (sx, sxp, sy, syp, 1e-6, 1e-6),
+                                          F.CFG4_ENERGY, cor=(cx, cy, 0.0), dtype=d)
+    want = O.track(els, pb)
+    sd = np.sqrt(np.abs(np.diag(want.cov_[0].numpy())))
+    np.testing.assert_allclose(out._mu[0].cpu().numpy(), want.mu_[0].numpy(), rtol=2e-5,
+                               atol=2e-5 * sd.max())
+    got_c, want_c = out._cov[0].cpu().numpy(), want.cov_[0].numpy()
+    tol = 3e-5 * (np.outer(sd, sd) + np.abs(want_c))
+    assert (np.abs(got_c - want_c) <= tol).all(), np.abs(got_c - want_c).max()
+    bp = next(e for e in els if e.name == "BPMX").reading.numpy()
+    np.testing.assert_allclose(seg.BPMX.reading.cpu().numpy(), bp, rtol=2e-5, atol=1e-9)
+    np.testing.assert_allclose(out.energy.cpu().numpy(), want.energy.numpy(), rtol=1e-6)
+
+
+# ------------------------------------------------------------------ layout + host ABI
+def test_aos_soa_roundtrip():
+    for n in (1, 255, 256, 257, 10_001):
+        p = torch.randn(2, n, 7)
+        p[..., 6] = 1
+        b = lx.ParticleBeam(p, torch.tensor([1e8, 1e8]))
+        assert torch.equal(b.particles.cpu(), p)
+        assert torch.equal(b.xs.cpu(), p[..., 0]) and torch.equal(b.ps.cpu(), p[..., 5])
+
+
+def test_host_buffer_abi_matches_device_path():
+    """lynx_host_track_particles with NumPy buffers == the torch-plumbed device path."""
+    import ctypes as C
+
+    from lynx_b200 import _lib as L
+    from lynx_b200.program import Program, encode, layout, pack_params
+
+    n = 10_001
+    spec = F.ares_ea(k1=(5.0, -5.0, 5.0), vkick=1e-3, hkick=-2e-3, screen_active=True,
+                     screen=F.TEST_SCREEN)
+    seg = F.build_segment(spec)
+    soa = F.gaussian_beam_soa(n, seed=3)
+    seg.track(_gpu_beam(soa, F.ASTRA_ENERGY))
+    want = seg.AREABSCR1.reading.cpu().numpy()
+    enc = encode(seg.elements, (1,))
+    prog = Program.get(enc)
+    params = pack_params(enc, "cpu").numpy()
+    ex, ey = seg.AREABSCR1.pixel_bin_edges
+    ex, ey = ex.numpy(), ey.numpy()
+    W, H = ex.size - 1, ey.size - 1
+    img = np.empty((1, H, W), dtype=np.float32)
+    mom = np.empty((1, 28), dtype=np.float64)
+    e_out = np.empty(1, dtype=np.float32)
+    e_in = np.array([F.ASTRA_ENERGY], dtype=np.float32)
+    ctx = C.c_void_p()
+    L.check(L.lib().lynx_host_ctx_create(0, C.byref(ctx)))
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    soa_c = np.ascontiguousarray(soa)
+    L.check(L.lib().lynx_host_track_particles(
+        ctx, prog.handle, vp(params), params.size, 1, vp(soa_c), 1, n, vp(e_in), None, None,
+        vp(img), W, H, vp(ex), vp(ey), vp(mom), 2, vp(e_out)))
+    L.lib().lynx_host_ctx_destroy(ctx)
+    assert np.array_equal(img, want)
+    assert mom[0, 0] == n
