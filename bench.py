@@ -1,0 +1,475 @@
+#!/usr/bin/env python
+"""Benchmark of the beam-tracking hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo, CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # reference arithmetic on CPU
+
+Workload (BASELINE.json configs[1]): ARES experimental-area segment (13 elements;
+AREAMQZM1-3 k1 = 5,-5,5; AREAMCVM1 = 1e-3, AREAMCHM1 = -2e-3; AREABSCR1 active,
+2448x2040) tracking a 1M-particle synthetic Astra-shaped ParticleBeam per GPU; one
+step = Segment.track + Screen.reading.  Metric: particle-element updates/s =
+particles * 13 / step time.  Secondary: ParameterBeam env-steps/s at 4096 settings
+(configs[2]) and the streaming roofline point at 32M particles.
+"""
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+E_ARES = 13
+K1 = (5.0, -5.0, 5.0)
+VKICK, HKICK = 1e-3, -2e-3
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--particles", type=int, default=1_000_000, help="per GPU")
+    ap.add_argument("--settings", type=int, default=4096)
+    ap.add_argument("--scale-particles", type=int, default=32_000_000)
+    ap.add_argument("--no-extras", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4)
+                          if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def oracle_workload(n, dtype=torch.float32, seed=1002):
+    from helpers import aos_from_soa, oracle_elements
+    from lynx_b200 import fixtures as F
+    from oracle import lattice as O
+    from oracle import screen_bin_edges
+
+    spec = F.ares_ea(k1=K1, vkick=VKICK, hkick=HKICK, screen_active=True, screen=F.TEST_SCREEN)
+    els = oracle_elements(spec, dtype)
+    beam = O.ParticleBeamO(aos_from_soa(F.gaussian_beam_soa(n, seed=seed), dtype),
+                           torch.tensor([F.ASTRA_ENERGY], dtype=dtype))
+    ex, ey = screen_bin_edges(F.TEST_SCREEN["resolution"], F.TEST_SCREEN["pixel_size"])
+    return els, beam, ex, ey
+
+
+def oracle_step(els, beam, ex, ey):
+    """Segment.track + Screen.reading in the restated reference arithmetic (torch CPU)."""
+    from oracle import lattice as O
+    from oracle import screen_reading_particles
+
+    O.track(els, beam)
+    rb = els[-1].read_beam
+    return screen_reading_particles(rb.col(0), rb.col(2), ex, ey)
+
+
+def time_cpu(n, steps, warmup):
+    els, beam, ex, ey = oracle_workload(n)
+    for _ in range(warmup):
+        oracle_step(els, beam, ex, ey)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        oracle_step(els, beam, ex, ey)
+    return (time.perf_counter() - t0) / steps
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    n = args.particles
+    torch.set_num_threads(os.cpu_count() or 1)
+    sec = time_cpu(n, args.steps, min(args.warmup, 2))
+    val = n * E_ARES / sec
+    line = {
+        "impl": "reference", "metric": "particle_element_updates_per_s", "value": val,
+        "unit": "particle-element updates/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "ares_ea_1M_particles_screen_2448x2040", "elements": E_ARES,
+                   "particles": n,
+                   "note": "torch-CPU restatement of the reference arithmetic (the "
+                           "reference itself cannot execute, SURVEY.md 0.1)"},
+        "cpu_baseline": {"value": val, "unit": "particle-element updates/s",
+                         "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": f"{args.steps} full steps of {n} particles"},
+        "e2e": {"value": val, "unit": "particle-element updates/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- GPU arm
+class ParticleWorkload:
+    """Pre-encoded Segment.track(ParticleBeam) (+ Screen.reading) on device buffers: what
+    a jit-compiled caller holds -- program handle, packed parameters, resident beam."""
+
+    def __init__(self, n, device, seed, screen=True, want_out=False, moments=0):
+        import lynx_b200 as lx
+        from lynx_b200 import _lib as L
+        from lynx_b200 import fixtures as F
+        from lynx_b200.program import Program, encode, pack_params
+
+        self.L, self.n, self.device = L, n, device
+        spec = F.ares_ea(k1=K1, vkick=VKICK, hkick=HKICK, screen_active=screen,
+                         screen=F.TEST_SCREEN)
+        self.seg = F.build_segment(spec)
+        self.enc = encode(self.seg.elements, (1,))
+        self.prog = Program.get(self.enc)
+        self.params = pack_params(self.enc, device)
+        self.params_host = self.params.cpu().pin_memory()
+        self.ld = (n + 3) & ~3
+        self.soa_host = torch.empty((6, self.ld), dtype=torch.float32).pin_memory()
+        self.soa_host[:, :n] = torch.from_numpy(F.gaussian_beam_soa(n, seed=seed))
+        self.soa = self.soa_host.to(device)
+        self.e_in = torch.tensor([F.ASTRA_ENERGY], device=device)
+        self.e_out = torch.empty(1, device=device)
+        self.ws = torch.empty(self.prog.workspace_bytes(1), dtype=torch.uint8, device=device)
+        self.out = torch.empty((6, self.ld), device=device) if want_out else None
+        self.mom = torch.empty((1, 28), dtype=torch.float64, device=device) if moments else None
+        self.moments = moments
+        self.img = self.ex = self.ey = None
+        self.W = self.H = 0
+        if screen:
+            scr = self.seg.AREABSCR1
+            self.ex, self.ey = scr._device_edges(device)
+            self.W, self.H = self.ex.numel() - 1, self.ey.numel() - 1
+            self.img = torch.empty((1, self.H, self.W), device=device)
+            self.exh, self.eyh = scr.pixel_bin_edges
+            self.img_host = torch.empty((1, self.H, self.W)).pin_memory()
+        self.lib = L.lib()
+
+    def step(self):
+        L = self.L
+        L.check(self.lib.lynx_track_particles_fwd(
+            self.prog.handle, self.params.data_ptr(), 1, self.soa.data_ptr(), 1, self.ld, self.n,
+            L.ptr(self.out), self.ld, None, L.ptr(self.img), self.W, self.H, L.ptr(self.ex),
+            L.ptr(self.ey), L.ptr(self.mom), self.moments, self.e_in.data_ptr(),
+            self.e_out.data_ptr(), self.ws.data_ptr(), L.current_stream()))
+
+    def algorithmic_bytes(self):
+        b = 24 * self.n
+        if self.out is not None:
+            b += 24 * self.n
+        if self.img is not None:
+            b += 4 * self.W * self.H
+        return b
+
+    def host_step(self, ctx):
+        """Through the host-buffer C ABI: H2D beam + params, kernels, D2H image."""
+        L = self.L
+        L.check(self.lib.lynx_host_track_particles(
+            ctx, self.prog.handle, self.params_host.data_ptr(), self.params_host.numel(), 1,
+            self.soa_host.data_ptr(), 1, self.n, self.e_in_host.data_ptr(), None, None,
+            self.img_host.data_ptr(), self.W, self.H, self.exh.data_ptr(), self.eyh.data_ptr(),
+            None, 0, None))
+
+    def prepare_host(self):
+        self.e_in_host = self.e_in.cpu().pin_memory()
+        self.exh, self.eyh = self.exh.pin_memory(), self.eyh.pin_memory()
+
+
+class ParamBeamWorkload:
+    """Config 3: B random (3 x k1, 2 x angle) settings x one ParameterBeam through ARES EA."""
+
+    def __init__(self, B, device, seed=1003):
+        from lynx_b200 import _lib as L
+        from lynx_b200 import fixtures as F
+        from lynx_b200.program import Program, encode, pack_params
+
+        self.L, self.B = L, B
+        k1, ang = F.random_settings(B, seed)
+        seg = F.build_segment(F.ares_ea())
+        for i, nm in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")):
+            getattr(seg, nm).k1 = torch.from_numpy(k1[:, i])
+        seg.AREAMCVM1.angle = torch.from_numpy(ang[:, 0])
+        seg.AREAMCHM1.angle = torch.from_numpy(ang[:, 1])
+        self.enc = encode(seg.elements, (1,))
+        self.prog = Program.get(self.enc)
+        self.params = pack_params(self.enc, device)
+        self.params_host = self.params.cpu().pin_memory()
+        mu = torch.tensor([*F.ASTRA_MU[:4], 0.0, 0.0, 1.0])
+        cov = torch.zeros(7, 7)
+        for i in range(6):
+            cov[i, i] = F.ASTRA_SIGMA[i] ** 2
+        self.mu_h, self.cov_h = mu.pin_memory(), cov.pin_memory()
+        self.mu, self.cov = mu.to(device), cov.to(device)
+        self.e_in = torch.full((B,), F.ASTRA_ENERGY, device=device)
+        self.e_in_h = self.e_in.cpu().pin_memory()
+        self.mu_out = torch.empty((B, 7), device=device)
+        self.cov_out = torch.empty((B, 7, 7), device=device)
+        self.e_out = torch.empty(B, device=device)
+        self.mu_out_h = torch.empty((B, 7)).pin_memory()
+        self.cov_out_h = torch.empty((B, 7, 7)).pin_memory()
+        self.lib = L.lib()
+
+    def step(self):
+        self.L.check(self.lib.lynx_parambeam_fwd(
+            self.prog.handle, self.params.data_ptr(), self.B, self.mu.data_ptr(),
+            self.cov.data_ptr(), 0, self.e_in.data_ptr(), self.mu_out.data_ptr(),
+            self.cov_out.data_ptr(), None, self.e_out.data_ptr(), self.L.current_stream()))
+
+    def host_step(self, ctx):
+        self.L.check(self.lib.lynx_host_parambeam(
+            ctx, self.prog.handle, self.params_host.data_ptr(), self.params_host.numel(), self.B,
+            self.mu_h.data_ptr(), self.cov_h.data_ptr(), 1, self.e_in_h.data_ptr(),
+            self.mu_out_h.data_ptr(), self.cov_out_h.data_ptr(), None, None))
+
+    def algorithmic_bytes(self):  # 20 B in + 228 B out per env-step, shared beam
+        return 248 * self.B
+
+
+def timed_steps(step, steps, warmup, flush, post=None):
+    """Per-step CUDA-event timing on the current stream with an L2 flush (outside the
+    events) before every step.  Returns the list of per-step milliseconds."""
+    for _ in range(warmup):
+        flush.zero_()
+        step()
+        if post:
+            post()
+    torch.cuda.synchronize()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(steps)]
+    for a, b in evs:
+        flush.zero_()
+        a.record()
+        step()
+        if post:
+            post()
+        b.record()
+    torch.cuda.synchronize()
+    return [a.elapsed_time(b) for a, b in evs]
+
+
+def kernel_ms(step, which, steps, flush, lib):
+    """Average device time of the dominant kernel alone (library event hooks)."""
+    lib.lynx_profile_enable(1)
+    acc = []
+    for _ in range(steps):
+        flush.zero_()
+        step()
+        ms = lib.lynx_profile_last_ms(which)
+        if ms >= 0:
+            acc.append(ms)
+    lib.lynx_profile_enable(0)
+    return float(np.mean(acc)) if acc else None
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch.distributed as dist
+
+    from lynx_b200 import _lib as L
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    assert args.particles % 4 == 0
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    lib = L.lib()
+    peak, peak_src = peaks()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+
+    wl = ParticleWorkload(args.particles, device, seed=1002 + rank, screen=True)
+    post = None
+    if world > 1:  # the one exchange step of the path: the screen image (north star)
+        post = lambda: dist.all_reduce(wl.img)  # noqa: E731
+
+    # ---- headline: device-resident steps, per-step events, max over ranks
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    lib.lynx_launch_count_reset()
+    ms = timed_steps(wl.step, args.steps, args.warmup, flush, post)
+    launches = lib.lynx_launch_count() - 0
+    launches_timed = launches * args.steps // (args.steps + args.warmup)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop() if sampler else None
+    total_ms = torch.tensor([sum(ms)], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    ms_per_step = total_ms.item() / args.steps
+    value = world * args.particles * E_ARES / (ms_per_step * 1e-3)
+
+    # ---- e2e through the host-buffer C ABI (H2D beam + params, D2H image), per rank
+    ctx = C.c_void_p()
+    L.check(lib.lynx_host_ctx_create(local_rank, C.byref(ctx)))
+    wl.prepare_host()
+    for _ in range(3):
+        wl.host_step(ctx)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        wl.host_step(ctx)
+    e2e_s = torch.tensor([(time.perf_counter() - t0) / args.steps], device=device,
+                         dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_val = world * args.particles * E_ARES / e2e_s.item()
+    h2d = 4 * (6 * wl.ld + wl.params_host.numel() + 1 + wl.W + 1 + wl.H + 1)
+    d2h = 4 * wl.W * wl.H
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (K2) on this workload, rank 0
+    k2_ms = kernel_ms(wl.step, 1, args.steps, flush, lib)
+    alg = wl.algorithmic_bytes()
+    ach = alg / (k2_ms * 1e-3) / 1e9 if k2_ms else None
+    roofline = {"bound": "hbm", "kernel": "track_fwd_kernel (K2)", "achieved": ach, "peak": peak,
+                "unit": "GB/s", "frac": (ach / peak) if ach else None, "traffic": None,
+                "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs, burst copy)",
+                "algorithmic_bytes_per_launch": alg, "kernel_ms": k2_ms,
+                "frac_of_8000": (ach / 8000.0) if ach else None,
+                "regime": "launch/latency-bound at 1M particles (44 MB per launch)"}
+    line = {
+        "metric": "particle_element_updates_per_s", "value": value,
+        "unit": "particle-element updates/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "ares_ea_1M_particles_screen_2448x2040", "elements": E_ARES,
+                   "particles_per_gpu": args.particles, "step": "Segment.track + Screen.reading",
+                   "l2": "256 MB flush write before every timed step (outside the events)",
+                   "parallelism": f"particle-sharded x{world}" + (
+                       ", image all-reduced (NCCL)" if world > 1 else "")},
+        "clocks": clocks, "gpu_launches": int(launches_timed),
+        "e2e": {"value": e2e_val, "unit": "particle-element updates/s",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": e2e_s.item() * 1e3,
+                "path": "lynx_host_track_particles (pinned host buffers)"},
+        "roofline": roofline,
+    }
+
+    if world == 1:
+        # ---- CPU baseline: the oracle port on this box's cores, bounded sample
+        torch.set_num_threads(os.cpu_count() or 1)
+        sec = time_cpu(args.particles, 8, 2)
+        line["cpu_baseline"] = {
+            "value": args.particles * E_ARES / sec, "unit": "particle-element updates/s",
+            "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"8 full steps of {args.particles} particles (torch-CPU restatement)",
+            "ms_per_step": sec * 1e3}
+
+    if world == 1 and not args.no_extras:
+        extras = {}
+        # ParameterBeam env-steps/s (configs[2])
+        pw = ParamBeamWorkload(args.settings, device)
+        pms = timed_steps(pw.step, args.steps, args.warmup, flush)
+        for _ in range(3):
+            pw.host_step(ctx)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            pw.host_step(ctx)
+        pe2e = (time.perf_counter() - t0) / args.steps
+        k6 = kernel_ms(pw.step, 2, args.steps, flush, lib)
+        extras["parameterbeam_env_steps"] = {
+            "settings": args.settings, "value": args.settings / (np.mean(pms) * 1e-3),
+            "unit": "env-steps/s", "ms_per_step": float(np.mean(pms)),
+            "e2e_value": args.settings / pe2e, "kernel_ms": k6,
+            "achieved_gbs": pw.algorithmic_bytes() / (k6 * 1e-3) / 1e9 if k6 else None,
+            "regime": "launch-latency-bound (1 MB per launch)"}
+        # large-B point where HBM is the limiter
+        bigB = 1 << 20
+        pw2 = ParamBeamWorkload(bigB, device)
+        k6b = kernel_ms(pw2.step, 2, 10, flush, lib)
+        extras["parameterbeam_at_scale"] = {
+            "settings": bigB, "value": bigB / (k6b * 1e-3), "unit": "env-steps/s",
+            "kernel_ms": k6b, "achieved_gbs": pw2.algorithmic_bytes() / (k6b * 1e-3) / 1e9,
+            "frac": pw2.algorithmic_bytes() / (k6b * 1e-3) / 1e9 / peak}
+        del pw2
+        # streaming roofline points at N = scale_particles
+        ns = args.scale_particles
+        for name, kw in (("track_out_48B", dict(screen=False, want_out=True)),
+                         ("track_out_moments_48B", dict(screen=False, want_out=True, moments=1)),
+                         ("screen_24B", dict(screen=True))):
+            w2 = ParticleWorkload(ns, device, seed=7, **kw)
+            km = kernel_ms(w2.step, 1, 10, flush, lib)
+            a2 = w2.algorithmic_bytes() / (km * 1e-3) / 1e9
+            extras[f"at_scale_{name}"] = {
+                "particles": ns, "kernel_ms": km, "achieved_gbs": a2, "frac": a2 / peak,
+                "frac_of_8000": a2 / 8000.0,
+                "particle_element_updates_per_s": ns * E_ARES / (km * 1e-3)}
+            del w2
+        line["extras"] = extras
+
+    lib.lynx_host_ctx_destroy(ctx)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -192,6 +192,14 @@ int lynx_soa6_to_aos7(const float* d_soa, int64_t R, int64_t N, int64_t ld,
 int64_t lynx_launch_count(void);
 void lynx_launch_count_reset(void);
 
+/* Measurement hooks (bench.py roofline): when enabled, the launchers bracket their
+ * dominant kernel with CUDA events on the launch stream.  lynx_profile_last_ms
+ * synchronises on the stop event and returns the device time of the last launch of
+ * kernel class `which` (0 = K1 composer, 1 = K2 tracker, 2 = K6 ParameterBeam,
+ * 3 = K3 adjoint), or a negative value if none was recorded. */
+void lynx_profile_enable(int on);
+float lynx_profile_last_ms(int which);
+
 /* ---- host-buffer entry points (what a NumPy / host-array binding calls) ------------
  * Same semantics as the device launchers, but every pointer is HOST memory (pinned for
  * full copy speed, pageable accepted).  Copies in, runs, copies out, synchronises.

@@ -61,6 +61,8 @@ SIGNATURES = {
     "lynx_soa6_to_aos7": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp]),
     "lynx_launch_count": (_i64, []),
     "lynx_launch_count_reset": (None, []),
+    "lynx_profile_enable": (None, [C.c_int]),
+    "lynx_profile_last_ms": (C.c_float, [C.c_int]),
     "lynx_host_ctx_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
     "lynx_host_ctx_destroy": (None, [_vp]),
     "lynx_host_track_particles": (

@@ -8,6 +8,26 @@
 namespace lynx {
 std::atomic<int64_t> g_launches{0};
 
+static std::atomic<int> g_profile{0};
+static cudaEvent_t g_ev[4][2];
+static bool g_ev_made[4] = {false, false, false, false};
+static bool g_ev_used[4] = {false, false, false, false};
+
+ProfileScope::ProfileScope(int w, cudaStream_t s) : which(w), st(s), on(g_profile.load() != 0) {
+  if (!on) return;
+  if (!g_ev_made[which]) {
+    cudaEventCreate(&g_ev[which][0]);
+    cudaEventCreate(&g_ev[which][1]);
+    g_ev_made[which] = true;
+  }
+  cudaEventRecord(g_ev[which][0], st);
+}
+ProfileScope::~ProfileScope() {
+  if (!on) return;
+  cudaEventRecord(g_ev[which][1], st);
+  g_ev_used[which] = true;
+}
+
 static int op_cols(int opcode) {
   switch (opcode) {
     case LYNX_OP_MARKER: return 0;
@@ -84,6 +104,15 @@ extern "C" const char* lynx_status_str(int s) {
     case LYNX_E_NODEVICE: return "no CUDA device (there is no CPU fallback)";
     default: return "unknown";
   }
+}
+
+extern "C" void lynx_profile_enable(int on) { g_profile.store(on); }
+extern "C" float lynx_profile_last_ms(int which) {
+  if (which < 0 || which > 3 || !g_ev_used[which]) return -1.f;
+  float ms = -1.f;
+  if (cudaEventSynchronize(g_ev[which][1]) != cudaSuccess) return -1.f;
+  if (cudaEventElapsedTime(&ms, g_ev[which][0], g_ev[which][1]) != cudaSuccess) return -1.f;
+  return ms;
 }
 
 extern "C" int64_t lynx_launch_count(void) { return g_launches.load(); }

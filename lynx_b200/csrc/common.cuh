@@ -72,6 +72,15 @@ namespace lynx {
 extern std::atomic<int64_t> g_launches;
 inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
+// optional event bracketing of the dominant kernels (bench roofline)
+struct ProfileScope {
+  int which;
+  cudaStream_t st;
+  bool on;
+  ProfileScope(int which, cudaStream_t st);
+  ~ProfileScope();
+};
+
 #define LYNX_CUDA_OK(expr)                                   \
   do {                                                       \
     cudaError_t _e = (expr);                                 \

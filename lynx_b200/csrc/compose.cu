@@ -281,7 +281,10 @@ extern "C" int lynx_compose_maps(const lynx_program_t* p, const float* d_params,
   a.energy_out = d_energy_out;
   const int threads = 128;
   const unsigned blocks = (unsigned)((B + threads - 1) / threads);
-  compose_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(a);
+  {
+    ProfileScope ps(0, (cudaStream_t)stream);
+    compose_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(a);
+  }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());
   return LYNX_OK;
@@ -313,7 +316,10 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
   a.bpm_out = d_bpm_out;
   a.energy_out = d_energy_out;
   const unsigned blocks = (unsigned)((B + kPBThreads - 1) / kPBThreads);
-  parambeam_fwd_kernel<<<blocks, kPBThreads, 0, (cudaStream_t)stream>>>(a);
+  {
+    ProfileScope ps(2, (cudaStream_t)stream);
+    parambeam_fwd_kernel<<<blocks, kPBThreads, 0, (cudaStream_t)stream>>>(a);
+  }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());
   return LYNX_OK;

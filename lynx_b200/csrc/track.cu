@@ -343,7 +343,10 @@ static int launch_track(const TrackArgs& a, dim3 grid, size_t smem, cudaStream_t
         cudaSuccess)
       return LYNX_E_BADPROGRAM;
   }
-  k<<<grid, kTPB, smem, st>>>(a);
+  {
+    ProfileScope ps(1, st);
+    k<<<grid, kTPB, smem, st>>>(a);
+  }
   count_launch();
   return cudaGetLastError() == cudaSuccess ? LYNX_OK : LYNX_E_LAUNCH;
 }

@@ -1,0 +1,35 @@
+"""Small, fixed launch sequence for ncu: python tools/prof_target.py --mode screen1m --steps 3"""
+import argparse
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--mode", default="screen1m")
+ap.add_argument("--steps", type=int, default=3)
+a = ap.parse_args()
+dev = torch.device("cuda", 0)
+torch.cuda.set_device(0)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+if a.mode == "screen1m":
+    w = bench.ParticleWorkload(1_000_000, dev, seed=1002, screen=True)
+elif a.mode == "screen32m":
+    w = bench.ParticleWorkload(32_000_000, dev, seed=7, screen=True)
+elif a.mode == "out32m":
+    w = bench.ParticleWorkload(32_000_000, dev, seed=7, screen=False, want_out=True)
+elif a.mode == "outmom32m":
+    w = bench.ParticleWorkload(32_000_000, dev, seed=7, screen=False, want_out=True, moments=1)
+elif a.mode == "pb4096":
+    w = bench.ParamBeamWorkload(4096, dev)
+elif a.mode == "pb1m":
+    w = bench.ParamBeamWorkload(1 << 20, dev)
+else:
+    raise SystemExit("unknown mode")
+ms = bench.timed_steps(w.step, a.steps, 2, flush)
+print(a.mode, "ms/step", sum(ms) / len(ms))
