@@ -72,6 +72,13 @@ namespace lynx {
 extern std::atomic<int64_t> g_launches;
 inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
+// K1 launcher shared by the public entry point and the particle launchers; the extra
+// blocks of the same launch zero `zero_ptr` (screen image), saving a memset node.
+int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
+                   const float* d_energy_in, const float* d_seed_soa, int64_t seed_row_stride,
+                   int64_t seed_ld, float* d_records, float* d_maps_out, float* d_energy_out,
+                   void* zero_ptr, size_t zero_bytes, cudaStream_t st);
+
 // optional event bracketing of the dominant kernels (bench roofline)
 struct ProfileScope {
   int which;

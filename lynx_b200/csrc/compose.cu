@@ -2,95 +2,47 @@
 // K6: ParameterBeam propagation (mu' = R mu, cov' = R cov R^T) fused with K1.
 // One thread owns one setting; parameters are read as columns (coalesced across the
 // warp for per-setting columns, broadcast for shared ones).
-#include "walk.cuh"
+#include <algorithm>
+
+#include "compose_common.cuh"
 
 namespace lynx {
 
-// ------------------------------------------------------------------ K1
-struct RecordSink {
-  float* rec;
-  float* maps_out;  // nullable, this setting's [n_stages][7][7]
-  int off_cav, off_centre, off_screen;
-  float ctr[6];
+// Stage the tile's ops and parameter columns in shared memory with ONE round of parallel
+// loads (a lone thread chasing col_offset -> params per column pays ~1 us of dependent
+// latency per column, which is the whole kernel at B = 1), then walk from shared memory.
+constexpr int kComposeTPB = 128;
 
-  __device__ __forceinline__ void write_map(const Map& M, int idx) {
-    float* d = rec + idx * kMapStride;
-#pragma unroll
-    for (int i = 0; i < 6; ++i)
-#pragma unroll
-      for (int j = 0; j < 7; ++j) d[i * 7 + j] = M.m[i][j];
-    if (maps_out) {
-      float* o = maps_out + idx * 49;
-#pragma unroll
-      for (int i = 0; i < 6; ++i)
-#pragma unroll
-        for (int j = 0; j < 7; ++j) o[i * 7 + j] = M.m[i][j];
-#pragma unroll
-      for (int j = 0; j < 7; ++j) o[42 + j] = (j == 6) ? 1.f : 0.f;
+template <bool STAGED>
+__global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int n_cols, int S) {
+  extern __shared__ __align__(16) float cs_smem[];
+  // blocks beyond the compose range only zero caller buffers (image / sums)
+  const int compose_blocks = (int)((a.B + S - 1) / S);
+  if ((int)blockIdx.x >= compose_blocks) {
+    const int zb = blockIdx.x - compose_blocks, nzb = gridDim.x - compose_blocks;
+    float4* z = reinterpret_cast<float4*>(a.zero_ptr);
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = (int64_t)zb * kComposeTPB + threadIdx.x; i < a.zero_vec4;
+         i += (int64_t)nzb * kComposeTPB)
+      z[i] = zero;
+    return;
+  }
+  const int64_t b0 = (int64_t)blockIdx.x * S;
+  const int ns = (int)min((int64_t)S, a.B - b0);
+  DevOp* s_ops = reinterpret_cast<DevOp*>(cs_smem);
+  float* s_vals = cs_smem + a.n_ops * (sizeof(DevOp) / sizeof(float));
+  if (STAGED) {
+    for (int i = threadIdx.x; i < a.n_ops * (int)(sizeof(DevOp) / 4); i += kComposeTPB)
+      cs_smem[i] = reinterpret_cast<const float*>(a.ops)[i];
+    for (int i = threadIdx.x; i < n_cols * ns; i += kComposeTPB) {
+      const int c = i / ns, sl = i - c * ns;
+      s_vals[c * S + sl] = __ldg(a.params + __ldg(a.col_offset + c) +
+                                 (b0 + sl) * (int64_t)__ldg(a.col_stride + c));
     }
+    __syncthreads();
   }
-  __device__ __forceinline__ void push_centre(const Map& M, float* lin) {
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-      float a = M.m[i][6];
-#pragma unroll
-      for (int j = 0; j < 6; ++j) a = fmaf(M.m[i][j], ctr[j], a);
-      lin[i] = a;
-    }
-  }
-  __device__ __forceinline__ void stage(const Map& M, int idx) {
-    write_map(M, idx);
-    float lin[6];
-    push_centre(M, lin);
-#pragma unroll
-    for (int i = 0; i < 6; ++i) ctr[i] = lin[i];
-  }
-  __device__ __forceinline__ void cavity(const Map& C, const CavityOut& co, int idx,
-                                         int cav_idx) {
-    write_map(C, idx);
-    float* d = rec + off_cav + cav_idx * kCavFloats;
-#pragma unroll
-    for (int i = 0; i < kCavFloats; ++i) d[i] = co.sc[i];
-    float lin[6];
-    push_centre(C, lin);
-    float s1, p1;
-    cavity_nonlinear(co.sc, ctr[4], ctr[5], lin[4], lin[5], s1, p1);
-    lin[4] = s1;
-    lin[5] = p1;
-#pragma unroll
-    for (int i = 0; i < 6; ++i) ctr[i] = lin[i];
-  }
-  __device__ __forceinline__ void bpm(int, int snap) {
-    float* d = rec + off_centre + snap * 6;
-#pragma unroll
-    for (int i = 0; i < 6; ++i) d[i] = ctr[i];
-  }
-  __device__ __forceinline__ void screen(int, int sidx, float mx, float my, int) {
-    rec[off_screen + sidx * 2 + 0] = mx;
-    rec[off_screen + sidx * 2 + 1] = my;
-  }
-};
-
-struct ComposeArgs {
-  const DevOp* ops;
-  int n_ops, final_stage;
-  const int64_t* col_offset;
-  const int32_t* col_stride;
-  const float* params;
-  int64_t B;
-  const float* energy_in;
-  const float* seed;
-  int64_t seed_row_stride, seed_ld;
-  float* records;
-  int rec_floats, off_cav, off_centre, off_screen, final_centre, n_stages;
-  float* maps_out;
-  float* energy_out;
-};
-
-__global__ void __launch_bounds__(128) compose_kernel(ComposeArgs a) {
-  int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= a.B) return;
-  ParamView P{a.params, a.col_offset, a.col_stride, b};
+  if ((int)threadIdx.x >= ns) return;
+  const int64_t b = b0 + threadIdx.x;
   RecordSink sink;
   sink.rec = a.records + b * a.rec_floats;
   sink.maps_out = a.maps_out ? a.maps_out + b * (int64_t)a.n_stages * 49 : nullptr;
@@ -101,119 +53,45 @@ __global__ void __launch_bounds__(128) compose_kernel(ComposeArgs a) {
   for (int i = 0; i < 6; ++i)
     sink.ctr[i] = a.seed ? __ldg(a.seed + b * a.seed_row_stride + i * a.seed_ld) : 0.f;
   float energy = a.energy_in[b];
-  walk_program(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+  if (STAGED) {
+    SmemParamView P{s_vals, S, (int)threadIdx.x};
+    walk_program(s_ops, a.n_ops, a.final_stage, P, energy, sink);
+  } else {
+    ParamView P{a.params, a.col_offset, a.col_stride, b};
+    walk_program(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+  }
   float* fc = sink.rec + a.final_centre;
 #pragma unroll
   for (int i = 0; i < 6; ++i) fc[i] = sink.ctr[i];
   if (a.energy_out) a.energy_out[b] = energy;
 }
 
-// ------------------------------------------------------------------ K6
-struct MomentSink {
-  float mu[7];
-  float cov[7][7];
-  float* bpm_out;
-  int64_t B, b;
-
-  // element.py:73-74 with R = [M; e6]
-  __device__ __forceinline__ void apply(const Map& M) {
-    float t[7];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-      float acc = 0.f;
-#pragma unroll
-      for (int j = 0; j < 7; ++j) acc = fmaf(M.m[i][j], mu[j], acc);
-      t[i] = acc;
-    }
-#pragma unroll
-    for (int i = 0; i < 6; ++i) mu[i] = t[i];
-    // cov <- R cov  (column by column, in place)
-#pragma unroll
-    for (int k = 0; k < 7; ++k) {
-#pragma unroll
-      for (int i = 0; i < 6; ++i) {
-        float acc = 0.f;
-#pragma unroll
-        for (int j = 0; j < 7; ++j) acc = fmaf(M.m[i][j], cov[j][k], acc);
-        t[i] = acc;
-      }
-#pragma unroll
-      for (int i = 0; i < 6; ++i) cov[i][k] = t[i];
-    }
-    // cov <- cov R^T  (row by row, in place)
-#pragma unroll
-    for (int i = 0; i < 7; ++i) {
-#pragma unroll
-      for (int l = 0; l < 6; ++l) {
-        float acc = 0.f;
-#pragma unroll
-        for (int k = 0; k < 7; ++k) acc = fmaf(cov[i][k], M.m[l][k], acc);
-        t[l] = acc;
-      }
-#pragma unroll
-      for (int l = 0; l < 6; ++l) cov[i][l] = t[l];
-    }
-  }
-  __device__ __forceinline__ void stage(const Map& M, int) { apply(M); }
-  // cavity.py:113-140, 202-218 (ParameterBeam branch; overwrites as written, quirk B5)
-  __device__ __forceinline__ void cavity(const Map& C, const CavityOut& co, int, int) {
-    const float mu4 = mu[4], mu5 = mu[5];
-    const float c44 = cov[4][4], c45 = cov[4][5], c55 = cov[5][5];
-    apply(C);
-    const float* sc = co.sc;
-    if (sc[CV_ON] != 0.f) {
-      float s1, p1;
-      cavity_nonlinear(sc, mu4, mu5, mu[4], mu[5], s1, p1);
-      mu[4] = s1;
-      mu[5] = p1;
-      cov[5][5] = c55;
-      float v = sc[CV_T566] * c55 * c55 + sc[CV_T556] * c45 * c55 + sc[CV_T555] * c44 * c44;
-      cov[4][4] = v;
-      cov[4][5] = v;
-      cov[5][4] = v;
-    }
-  }
-  __device__ __forceinline__ void bpm(int slot, int) {
-    if (bpm_out) {
-      bpm_out[(slot * B + b) * 2 + 0] = mu[0];  // bpm.py:52
-      bpm_out[(slot * B + b) * 2 + 1] = mu[2];
-    }
-  }
-  __device__ __forceinline__ void screen(int, int, float mx, float my, int) {
-    mu[0] -= mx;  // screen.py:131-132
-    mu[2] -= my;
-  }
-};
-
-struct ParamBeamArgs {
-  const DevOp* ops;
-  int n_ops, final_stage;
-  const int64_t* col_offset;
-  const int32_t* col_stride;
-  const float* params;
-  int64_t B;
-  const float* mu_in;
-  const float* cov_in;
-  int64_t beam_stride;  // 0 or 1 (in beams)
-  const float* energy_in;
-  float* mu_out;
-  float* cov_out;
-  float* bpm_out;
-  float* energy_out;
-};
-
 constexpr int kPBThreads = 64;
 
-__global__ void __launch_bounds__(kPBThreads) parambeam_fwd_kernel(ParamBeamArgs a) {
+template <bool STAGED>
+__global__ void __launch_bounds__(kPBThreads) parambeam_fwd_kernel(ParamBeamArgs a, int n_cols) {
   // staging tile so the [B][7] / [B][7][7] outputs leave the SM as full coalesced rows
-  __shared__ float tile[kPBThreads * 57];
+  __shared__ float tile[kPBThreads * 49];
+  extern __shared__ __align__(16) float pb_smem[];
   const int64_t b0 = (int64_t)blockIdx.x * kPBThreads;
   const int64_t b = b0 + threadIdx.x;
   const bool live = b < a.B;
+  DevOp* s_ops = reinterpret_cast<DevOp*>(pb_smem);
+  float* s_vals = pb_smem + a.n_ops * (sizeof(DevOp) / sizeof(float));
+  if (STAGED) {  // one parallel round of loads instead of a dependent chain per column
+    const int ns = (int)min((int64_t)kPBThreads, a.B - b0);
+    for (int i = threadIdx.x; i < a.n_ops * (int)(sizeof(DevOp) / 4); i += kPBThreads)
+      pb_smem[i] = reinterpret_cast<const float*>(a.ops)[i];
+    for (int i = threadIdx.x; i < n_cols * ns; i += kPBThreads) {
+      const int c = i / ns, sl = i - c * ns;
+      s_vals[c * kPBThreads + sl] = __ldg(a.params + __ldg(a.col_offset + c) +
+                                          (b0 + sl) * (int64_t)__ldg(a.col_stride + c));
+    }
+    __syncthreads();
+  }
   MomentSink sink;
   float energy = 0.f;
   if (live) {
-    ParamView P{a.params, a.col_offset, a.col_stride, b};
     const float* mi = a.mu_in + b * a.beam_stride * 7;
     const float* ci = a.cov_in + b * a.beam_stride * 49;
 #pragma unroll
@@ -226,7 +104,13 @@ __global__ void __launch_bounds__(kPBThreads) parambeam_fwd_kernel(ParamBeamArgs
     sink.B = a.B;
     sink.b = b;
     energy = a.energy_in[b];
-    walk_program(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+    if (STAGED) {
+      SmemParamView P{s_vals, kPBThreads, (int)threadIdx.x};
+      walk_program(s_ops, a.n_ops, a.final_stage, P, energy, sink);
+    } else {
+      ParamView P{a.params, a.col_offset, a.col_stride, b};
+      walk_program(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+    }
     if (a.energy_out) a.energy_out[b] = energy;
   }
   const int nb = (int)min((int64_t)kPBThreads, a.B - b0);
@@ -252,12 +136,13 @@ __global__ void __launch_bounds__(kPBThreads) parambeam_fwd_kernel(ParamBeamArgs
 
 using namespace lynx;
 
-extern "C" int lynx_compose_maps(const lynx_program_t* p, const float* d_params, int64_t B,
-                                 const float* d_energy_in, const float* d_seed_soa,
-                                 int64_t seed_row_stride, int64_t seed_ld, float* d_records,
-                                 float* d_maps_out, float* d_energy_out,
-                                 lynx_stream_t stream) {
+namespace lynx {
+int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
+                   const float* d_energy_in, const float* d_seed_soa, int64_t seed_row_stride,
+                   int64_t seed_ld, float* d_records, float* d_maps_out, float* d_energy_out,
+                   void* zero_ptr, size_t zero_bytes, cudaStream_t st) {
   if (!p || !d_params || !d_energy_in || !d_records || B <= 0) return LYNX_E_BADARG;
+  if (zero_bytes && (((uintptr_t)zero_ptr & 15) || (zero_bytes & 15))) return LYNX_E_BADARG;
   ComposeArgs a;
   a.ops = p->d_ops;
   a.n_ops = (int)p->dev_ops.size();
@@ -279,15 +164,42 @@ extern "C" int lynx_compose_maps(const lynx_program_t* p, const float* d_params,
   a.n_stages = p->n_stages;
   a.maps_out = d_maps_out;
   a.energy_out = d_energy_out;
-  const int threads = 128;
-  const unsigned blocks = (unsigned)((B + threads - 1) / threads);
+  a.zero_ptr = reinterpret_cast<float*>(zero_ptr);
+  a.zero_vec4 = (int64_t)(zero_bytes / 16);
+  const int n_cols = (int)p->col_offset.size();
+  const size_t budget = 40 * 1024;
+  const size_t ops_bytes = a.n_ops * sizeof(DevOp);
+  int S = kComposeTPB;
+  bool staged = false;
+  if (ops_bytes + (size_t)std::max(n_cols, 1) * 4 <= budget) {
+    staged = true;
+    if (n_cols > 0) S = (int)std::min<size_t>(kComposeTPB, (budget - ops_bytes) / (4 * (size_t)n_cols));
+    S = (int)std::min<int64_t>(S, std::max<int64_t>(B, 1));
+  }
+  const size_t smem = staged ? ops_bytes + (size_t)n_cols * S * 4 : 0;
+  unsigned blocks = (unsigned)((B + S - 1) / S);
+  if (a.zero_vec4 > 0)
+    blocks += (unsigned)std::min<int64_t>(2 * p->sm_count, (a.zero_vec4 + kComposeTPB - 1) / kComposeTPB);
   {
-    ProfileScope ps(0, (cudaStream_t)stream);
-    compose_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(a);
+    ProfileScope ps(0, st);
+    if (staged)
+      compose_kernel<true><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);
+    else
+      compose_kernel<false><<<blocks, kComposeTPB, 0, st>>>(a, n_cols, S);
   }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());
   return LYNX_OK;
+}
+}  // namespace lynx
+
+extern "C" int lynx_compose_maps(const lynx_program_t* p, const float* d_params, int64_t B,
+                                 const float* d_energy_in, const float* d_seed_soa,
+                                 int64_t seed_row_stride, int64_t seed_ld, float* d_records,
+                                 float* d_maps_out, float* d_energy_out,
+                                 lynx_stream_t stream) {
+  return compose_launch(p, d_params, B, d_energy_in, d_seed_soa, seed_row_stride, seed_ld,
+                        d_records, d_maps_out, d_energy_out, nullptr, 0, (cudaStream_t)stream);
 }
 
 extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params, int64_t B,
@@ -316,9 +228,14 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
   a.bpm_out = d_bpm_out;
   a.energy_out = d_energy_out;
   const unsigned blocks = (unsigned)((B + kPBThreads - 1) / kPBThreads);
+  const int n_cols = (int)p->col_offset.size();
+  const size_t smem = a.n_ops * sizeof(DevOp) + (size_t)n_cols * kPBThreads * 4;
   {
     ProfileScope ps(2, (cudaStream_t)stream);
-    parambeam_fwd_kernel<<<blocks, kPBThreads, 0, (cudaStream_t)stream>>>(a);
+    if (smem <= 32 * 1024)
+      parambeam_fwd_kernel<true><<<blocks, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols);
+    else
+      parambeam_fwd_kernel<false><<<blocks, kPBThreads, 0, (cudaStream_t)stream>>>(a, n_cols);
   }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());

@@ -1,0 +1,189 @@
+// Argument blocks and sinks shared by the thread-per-setting (compose.cu) and
+// warp-per-setting (compose_warp.cu) variants of K1 / K6.
+#pragma once
+#include "walk.cuh"
+
+namespace lynx {
+
+// ------------------------------------------------------------------ K1
+struct RecordSink {
+  float* rec;
+  float* maps_out;  // nullable, this setting's [n_stages][7][7]
+  int off_cav, off_centre, off_screen;
+  float ctr[6];
+
+  __device__ __forceinline__ void write_map(const Map& M, int idx) {
+    float* d = rec + idx * kMapStride;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = 0; j < 7; ++j) d[i * 7 + j] = M.m[i][j];
+    if (maps_out) {
+      float* o = maps_out + idx * 49;
+#pragma unroll
+      for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j < 7; ++j) o[i * 7 + j] = M.m[i][j];
+#pragma unroll
+      for (int j = 0; j < 7; ++j) o[42 + j] = (j == 6) ? 1.f : 0.f;
+    }
+  }
+  __device__ __forceinline__ void push_centre(const Map& M, float* lin) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      float a = M.m[i][6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) a = fmaf(M.m[i][j], ctr[j], a);
+      lin[i] = a;
+    }
+  }
+  __device__ __forceinline__ void stage(const Map& M, int idx) {
+    write_map(M, idx);
+    float lin[6];
+    push_centre(M, lin);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) ctr[i] = lin[i];
+  }
+  __device__ __forceinline__ void cavity(const Map& C, const CavityOut& co, int idx,
+                                         int cav_idx) {
+    write_map(C, idx);
+    float* d = rec + off_cav + cav_idx * kCavFloats;
+#pragma unroll
+    for (int i = 0; i < kCavFloats; ++i) d[i] = co.sc[i];
+    float lin[6];
+    push_centre(C, lin);
+    float s1, p1;
+    cavity_nonlinear(co.sc, ctr[4], ctr[5], lin[4], lin[5], s1, p1);
+    lin[4] = s1;
+    lin[5] = p1;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) ctr[i] = lin[i];
+  }
+  __device__ __forceinline__ void bpm(int, int snap) {
+    float* d = rec + off_centre + snap * 6;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) d[i] = ctr[i];
+  }
+  __device__ __forceinline__ void screen(int, int sidx, float mx, float my, int) {
+    rec[off_screen + sidx * 2 + 0] = mx;
+    rec[off_screen + sidx * 2 + 1] = my;
+  }
+};
+
+struct ComposeArgs {
+  const DevOp* ops;
+  int n_ops, final_stage;
+  const int64_t* col_offset;
+  const int32_t* col_stride;
+  const float* params;
+  int64_t B;
+  const float* energy_in;
+  const float* seed;
+  int64_t seed_row_stride, seed_ld;
+  float* records;
+  int rec_floats, off_cav, off_centre, off_screen, final_centre, n_stages;
+  float* maps_out;
+  float* energy_out;
+  float* zero_ptr;     // optional buffer zeroed by the extra blocks of the same launch
+  int64_t zero_vec4;   // its size in float4
+};
+
+// ------------------------------------------------------------------ K6
+struct MomentSink {
+  float mu[7];
+  float cov[7][7];
+  float* bpm_out;
+  int64_t B, b;
+
+  // element.py:73-74 with R = [M; e6]
+  __device__ __forceinline__ void apply(const Map& M) {
+    float t[7];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < 7; ++j) acc = fmaf(M.m[i][j], mu[j], acc);
+      t[i] = acc;
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) mu[i] = t[i];
+    // cov <- R cov  (column by column, in place)
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 7; ++j) acc = fmaf(M.m[i][j], cov[j][k], acc);
+        t[i] = acc;
+      }
+#pragma unroll
+      for (int i = 0; i < 6; ++i) cov[i][k] = t[i];
+    }
+    // cov <- cov R^T  (row by row, in place)
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+#pragma unroll
+      for (int l = 0; l < 6; ++l) {
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) acc = fmaf(cov[i][k], M.m[l][k], acc);
+        t[l] = acc;
+      }
+#pragma unroll
+      for (int l = 0; l < 6; ++l) cov[i][l] = t[l];
+    }
+  }
+  __device__ __forceinline__ void stage(const Map& M, int) { apply(M); }
+  // cavity.py:113-140, 202-218 (ParameterBeam branch; overwrites as written, quirk B5)
+  __device__ __forceinline__ void cavity(const Map& C, const CavityOut& co, int, int) {
+    const float mu4 = mu[4], mu5 = mu[5];
+    const float c44 = cov[4][4], c45 = cov[4][5], c55 = cov[5][5];
+    apply(C);
+    const float* sc = co.sc;
+    if (sc[CV_ON] != 0.f) {
+      float s1, p1;
+      cavity_nonlinear(sc, mu4, mu5, mu[4], mu[5], s1, p1);
+      mu[4] = s1;
+      mu[5] = p1;
+      cov[5][5] = c55;
+      float v = sc[CV_T566] * c55 * c55 + sc[CV_T556] * c45 * c55 + sc[CV_T555] * c44 * c44;
+      cov[4][4] = v;
+      cov[4][5] = v;
+      cov[5][4] = v;
+    }
+  }
+  __device__ __forceinline__ void bpm(int slot, int) {
+    if (bpm_out) {
+      bpm_out[(slot * B + b) * 2 + 0] = mu[0];  // bpm.py:52
+      bpm_out[(slot * B + b) * 2 + 1] = mu[2];
+    }
+  }
+  __device__ __forceinline__ void screen(int, int, float mx, float my, int) {
+    mu[0] -= mx;  // screen.py:131-132
+    mu[2] -= my;
+  }
+};
+
+struct ParamBeamArgs {
+  const DevOp* ops;
+  int n_ops, final_stage;
+  const int64_t* col_offset;
+  const int32_t* col_stride;
+  const float* params;
+  int64_t B;
+  const float* mu_in;
+  const float* cov_in;
+  int64_t beam_stride;  // 0 or 1 (in beams)
+  const float* energy_in;
+  float* mu_out;
+  float* cov_out;
+  float* bpm_out;
+  float* energy_out;
+};
+
+// warp-per-setting variants (compose_warp.cu) for small B; return 1 if not applicable
+int compose_warp_launch(const lynx_program_t* p, const ComposeArgs& a, cudaStream_t st);
+int parambeam_warp_launch(const lynx_program_t* p, const ParamBeamArgs& a, cudaStream_t st);
+
+}  // namespace lynx

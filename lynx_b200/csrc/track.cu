@@ -9,7 +9,9 @@
 //
 // Algorithmic HBM bytes: 24 B/particle read (+24 B written when outgoing particles are
 // requested); the per-setting record (<1 KB) is read once per CTA into shared memory.
-#include "maps.cuh"
+#include <cstdlib>
+
+#include "track_common.cuh"
 
 namespace lynx {
 
@@ -19,93 +21,6 @@ constexpr int kUnroll = 2;         // 128-bit accesses per plane per thread per 
 constexpr int kNP = kVec * kUnroll;            // particles per thread per tile
 constexpr int kTile = kTPB * kNP;              // particles per CTA per tile
 
-struct TrackArgs {
-  const float* in;
-  int64_t in_row_stride;  // floats between beam rows of `in` (0: one beam for all settings)
-  int64_t ld_in, N;
-  float* out;
-  int64_t ld_out;
-  const float* records;
-  int rec_floats;
-  const PlanItem* plan;
-  int n_plan;
-  int n_snap;
-  int final_centre;
-  double* bpm_sums;
-  float* img;
-  int W, H;
-  const float* ex;
-  const float* ey;
-  double* mom;
-  int64_t B;
-};
-
-__device__ __forceinline__ float4 ld_stream(const float* p) {
-  return __ldg(reinterpret_cast<const float4*>(p));
-}
-__device__ __forceinline__ void st_stream(float* p, float4 v) {
-  __stcs(reinterpret_cast<float4*>(p), v);
-}
-
-// v <- A v + c for kNP particles; A|c = 6x7 row-major in shared memory (16-B aligned)
-__device__ __forceinline__ void apply_affine(const float* __restrict__ m, float (&v)[6][kNP]) {
-  float r[kMapStride];
-  const float4* m4 = reinterpret_cast<const float4*>(m);
-#pragma unroll
-  for (int i = 0; i < kMapStride / 4; ++i) {
-    float4 t = m4[i];
-    r[4 * i] = t.x;
-    r[4 * i + 1] = t.y;
-    r[4 * i + 2] = t.z;
-    r[4 * i + 3] = t.w;
-  }
-#pragma unroll
-  for (int j = 0; j < kNP; ++j) {
-    float n[6];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-      float acc = r[i * 7 + 6];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) acc = fmaf(r[i * 7 + k], v[k][j], acc);
-      n[i] = acc;
-    }
-#pragma unroll
-    for (int i = 0; i < 6; ++i) v[i][j] = n[i];
-  }
-}
-
-// Bin lookup against the reference's fp32 edge table: left-closed bins, last bin
-// right-closed, out-of-range dropped (torch.histogramdd semantics).
-__device__ __forceinline__ int find_bin(float x, const float* __restrict__ e, int n, float e0,
-                                        float en, float inv) {
-  if (!(x >= e0 && x <= en)) return -1;
-  int i = (int)((x - e0) * inv);
-  i = min(max(i, 0), n - 1);
-  while (i > 0 && x < __ldg(e + i)) --i;
-  while (i < n - 1 && x >= __ldg(e + i + 1)) ++i;
-  return i;
-}
-
-__device__ __forceinline__ double warp_sum(double v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-
-template <int MOM>
-struct MomAcc {
-  static constexpr int kN = (MOM == 2) ? 27 : (MOM == 1 ? 14 : 1);
-  float a[kN];
-};
-
-// index of (i,j), i<=j in the 21-entry upper triangle, row-major
-__host__ __device__ constexpr int tri(int i, int j) { return i * 6 - i * (i - 1) / 2 + (j - i); }
-
 template <int MOM, bool HAS_OUT>
 __global__ void __launch_bounds__(kTPB, 2) track_fwd_kernel(TrackArgs a) {
   extern __shared__ __align__(16) float smem[];
@@ -113,7 +28,7 @@ __global__ void __launch_bounds__(kTPB, 2) track_fwd_kernel(TrackArgs a) {
   PlanItem* plan = reinterpret_cast<PlanItem*>(smem + a.rec_floats);  // n_plan
   double* s_bpm = reinterpret_cast<double*>(plan + a.n_plan);         // n_snap*2
   __shared__ double s_red[kTPB / 32][28];
-  __shared__ float s_hist[6];
+  __shared__ HistAxis s_hx, s_hy;
 
   const int tid = threadIdx.x;
   const int64_t b = blockIdx.y;
@@ -122,15 +37,10 @@ __global__ void __launch_bounds__(kTPB, 2) track_fwd_kernel(TrackArgs a) {
     for (int i = tid; i < a.rec_floats; i += kTPB) rec[i] = src[i];
     for (int i = tid; i < a.n_plan; i += kTPB) plan[i] = a.plan[i];
     for (int i = tid; i < a.n_snap * 2; i += kTPB) s_bpm[i] = 0.0;
-    if (tid == 0 && a.img) {
-      float x0 = a.ex[0], xn = a.ex[a.W], y0 = a.ey[0], yn = a.ey[a.H];
-      s_hist[0] = x0;
-      s_hist[1] = xn;
-      s_hist[2] = (float)a.W / (xn - x0);
-      s_hist[3] = y0;
-      s_hist[4] = yn;
-      s_hist[5] = (float)a.H / (yn - y0);
-    }
+  }
+  if (a.img) {
+    hist_axis_setup(a.ex, a.W, &s_hx, tid, kTPB);
+    hist_axis_setup(a.ey, a.H, &s_hy, tid, kTPB);
   }
   __syncthreads();
 
@@ -215,8 +125,8 @@ __global__ void __launch_bounds__(kTPB, 2) track_fwd_kernel(TrackArgs a) {
             if (live && img_b) {
               const float x = v[0][u * 4 + l] - mx;
               const float y = yfix ? v[2][u * 4 + l] - my : v[2][u * 4 + l];
-              const int ix = find_bin(x, a.ex, a.W, s_hist[0], s_hist[1], s_hist[2]);
-              const int iy = find_bin(y, a.ey, a.H, s_hist[3], s_hist[4], s_hist[5]);
+              const int ix = find_bin(x, a.ex, a.W, s_hx);
+              const int iy = find_bin(y, a.ey, a.H, s_hy);
               if (ix >= 0 && iy >= 0)
                 atomicAdd(img_b + (int64_t)(a.H - 1 - iy) * a.W + ix, 1.0f);
             }
@@ -381,14 +291,18 @@ extern "C" int lynx_track_particles_fwd(
   cudaStream_t st = (cudaStream_t)stream;
 
   float* records = reinterpret_cast<float*>(d_workspace);
-  int rc = lynx_compose_maps(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in,
-                             ld_in, records, nullptr, d_energy_out, stream);
+  // the screen image is zeroed by spare blocks of the K1 launch when its size allows
+  const bool has_img = d_screen_img && p->n_screen > 0;
+  const size_t img_bytes = has_img ? sizeof(float) * (size_t)W * H * B : 0;
+  const bool fuse_zero = has_img && !(img_bytes & 15) && !((uintptr_t)d_screen_img & 15);
+  int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
+                          records, nullptr, d_energy_out, fuse_zero ? d_screen_img : nullptr,
+                          fuse_zero ? img_bytes : 0, st);
   if (rc != LYNX_OK) return rc;
 
   if (p->n_bpm_slots > 0)
     LYNX_CUDA_OK(cudaMemsetAsync(d_bpm_sums, 0, sizeof(double) * 2 * p->n_bpm_slots * B, st));
-  if (d_screen_img && p->n_screen > 0)
-    LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, sizeof(float) * (size_t)W * H * B, st));
+  if (has_img && !fuse_zero) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
   if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
 
   TrackArgs a;
@@ -412,7 +326,18 @@ extern "C" int lynx_track_particles_fwd(
   a.ey = d_edges_y;
   a.mom = d_moment_sums;
   a.B = B;
+  static const int dbg = [] { const char* e = getenv("LYNX_DBG"); return e ? atoi(e) : 0; }();
+  a.dbg = dbg;
 
+  if (B > 65535) return LYNX_E_BADARG;
+  static const bool force_ldg = [] {
+    const char* e = getenv("LYNX_K2");
+    return e && e[0] == 'l';
+  }();
+  if (!force_ldg) {
+    const int r = launch_track_pipe(a, moment_mode, d_out_soa != nullptr, p->sm_count, st);
+    if (r <= 0) return r;
+  }
   const int64_t n_tiles = (N + kTile - 1) / kTile;
   int64_t per_b = (2LL * p->sm_count + B - 1) / B;
   if (per_b < 1) per_b = 1;

@@ -22,9 +22,69 @@ struct ParamView {
 //   void cavity(const Map& C, const CavityOut& co, int stage_idx, int cav_idx);
 //   void bpm(int slot, int snap_idx);
 //   void screen(int slot, int screen_idx, float mis_x, float mis_y, int flags);
-template <typename Sink>
+// Parameter columns of a tile of settings staged in shared memory: vals[col * S + s].
+struct SmemParamView {
+  const float* vals;
+  int S, s;
+  __device__ __forceinline__ float operator()(int col) const { return vals[col * S + s]; }
+};
+
+// Left-multiplies M by the map of one linear (skippable) op.  Returns false for ops that
+// are not part of a merged run (active cavity, BPM, screen).
+template <typename PV>
+__device__ __forceinline__ bool lm_linear_op(Map& M, const DevOp& op, const PV& P,
+                                             const Rel& rel, float energy) {
+  const int c = op.col;
+  switch (op.opcode) {
+    case LYNX_OP_MARKER:
+      return true;
+    case LYNX_OP_DRIFT: {
+      float L = P(c);
+      lm_drift(M, L, drift_r56(L, rel));
+    } return true;
+    case LYNX_OP_QUAD:
+      lm_quad(M, P(c), P(c + 1), P(c + 2), P(c + 3), P(c + 4), rel);
+      return true;
+    case LYNX_OP_HCOR: {
+      float L = P(c);
+      lm_drift(M, L, drift_r56(L, rel));
+      M.m[1][6] += P(c + 1);  // horizontal_corrector.py:63
+    } return true;
+    case LYNX_OP_VCOR: {
+      float L = P(c);
+      lm_drift(M, L, drift_r56(L, rel));
+      M.m[3][6] += P(c + 1);  // vertical_corrector.py:63
+    } return true;
+    case LYNX_OP_DIPOLE:
+      lm_dipole(M, P(c), P(c + 1), P(c + 2), P(c + 3), P(c + 4), P(c + 5), P(c + 6), P(c + 7),
+                (op.flags & LYNX_F_RBEND) != 0, rel);
+      return true;
+    case LYNX_OP_CAVITY: {
+      if (op.flags & LYNX_F_ACTIVE) return false;
+      // skippable cavity (voltage == 0 everywhere): linear map merged into the run
+      Map C;
+      CavityOut co;
+      cavity_setting(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
+      lm_custom(M, [&](int r, int k) { return C.m[r][k]; });
+    } return true;
+    case LYNX_OP_SOLENOID:
+      lm_solenoid(M, P(c), P(c + 1), P(c + 2), P(c + 3), rel);
+      return true;
+    case LYNX_OP_UNDULATOR: {
+      float L = P(c);
+      lm_drift(M, L, L * rel.igamma2_drift);  // undulator.py:52-58 (quirk B4)
+    } return true;
+    case LYNX_OP_CUSTOM:
+      lm_custom(M, [&](int r, int k) { return P(c + r * 7 + k); });
+      return true;
+    default:
+      return false;
+  }
+}
+
+template <typename Sink, typename PV>
 __device__ __forceinline__ void walk_program(const DevOp* __restrict__ ops, int n_ops,
-                                             int final_stage, const ParamView& P,
+                                             int final_stage, const PV& P,
                                              float& energy, Sink& sink) {
   Map M;
   map_identity(M);
@@ -35,62 +95,19 @@ __device__ __forceinline__ void walk_program(const DevOp* __restrict__ ops, int 
       sink.stage(M, op.flush_stage);
       map_identity(M);
     }
+    if (lm_linear_op(M, op, P, rel, energy)) continue;
     const int c = op.col;
-    switch (op.opcode) {
-      case LYNX_OP_MARKER:
-        break;
-      case LYNX_OP_DRIFT: {
-        float L = P(c);
-        lm_drift(M, L, drift_r56(L, rel));
-      } break;
-      case LYNX_OP_QUAD:
-        lm_quad(M, P(c), P(c + 1), P(c + 2), P(c + 3), P(c + 4), rel);
-        break;
-      case LYNX_OP_HCOR: {
-        float L = P(c);
-        lm_drift(M, L, drift_r56(L, rel));
-        M.m[1][6] += P(c + 1);  // horizontal_corrector.py:63
-      } break;
-      case LYNX_OP_VCOR: {
-        float L = P(c);
-        lm_drift(M, L, drift_r56(L, rel));
-        M.m[3][6] += P(c + 1);  // vertical_corrector.py:63
-      } break;
-      case LYNX_OP_DIPOLE:
-        lm_dipole(M, P(c), P(c + 1), P(c + 2), P(c + 3), P(c + 4), P(c + 5), P(c + 6),
-                  P(c + 7), (op.flags & LYNX_F_RBEND) != 0, rel);
-        break;
-      case LYNX_OP_CAVITY: {
-        Map C;
-        CavityOut co;
-        cavity_setting(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
-        if (op.flags & LYNX_F_ACTIVE) {
-          sink.cavity(C, co, op.self_stage, op.cav_idx);
-          energy += co.dE;  // cavity.py:130
-          rel = make_rel(energy);
-        } else {
-          // skippable cavity (voltage == 0 everywhere): linear map merged into the run
-          lm_custom(M, [&](int r, int k) { return C.m[r][k]; });
-        }
-      } break;
-      case LYNX_OP_SOLENOID:
-        lm_solenoid(M, P(c), P(c + 1), P(c + 2), P(c + 3), rel);
-        break;
-      case LYNX_OP_UNDULATOR: {
-        float L = P(c);
-        lm_drift(M, L, L * rel.igamma2_drift);  // undulator.py:52-58 (quirk B4)
-      } break;
-      case LYNX_OP_CUSTOM:
-        lm_custom(M, [&](int r, int k) { return P(c + r * 7 + k); });
-        break;
-      case LYNX_OP_BPM:
-        sink.bpm(op.aux, op.snap_idx);
-        break;
-      case LYNX_OP_SCREEN:
-        sink.screen(op.aux, op.snap_idx, P(c), P(c + 1), op.flags);
-        break;
-      default:
-        break;
+    if (op.opcode == LYNX_OP_CAVITY) {
+      Map C;
+      CavityOut co;
+      cavity_setting(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
+      sink.cavity(C, co, op.self_stage, op.cav_idx);
+      energy += co.dE;  // cavity.py:130
+      rel = make_rel(energy);
+    } else if (op.opcode == LYNX_OP_BPM) {
+      sink.bpm(op.aux, op.snap_idx);
+    } else if (op.opcode == LYNX_OP_SCREEN) {
+      sink.screen(op.aux, op.snap_idx, P(c), P(c + 1), op.flags);
     }
   }
   if (final_stage >= 0) sink.stage(M, final_stage);
