@@ -3,6 +3,7 @@
 // One thread owns one setting; parameters are read as columns (coalesced across the
 // warp for per-setting columns, broadcast for shared ones).
 #include <algorithm>
+#include <cstdlib>
 
 #include "compose_common.cuh"
 
@@ -16,6 +17,10 @@ constexpr int kComposeTPB = 128;
 template <bool STAGED>
 __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int n_cols, int S) {
   extern __shared__ __align__(16) float cs_smem[];
+  // Programmatic dependent launch: let the particle kernel start its prologue (barrier
+  // init, TMA requests for its first tiles) now; it waits (griddepcontrol.wait) for this
+  // grid to finish before it reads the records or touches the zeroed image.
+  asm volatile("griddepcontrol.launch_dependents;");
   // blocks beyond the compose range only zero caller buffers (image / sums)
   const int compose_blocks = (int)((a.B + S - 1) / S);
   if ((int)blockIdx.x >= compose_blocks) {
@@ -166,6 +171,17 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   a.energy_out = d_energy_out;
   a.zero_ptr = reinterpret_cast<float*>(zero_ptr);
   a.zero_vec4 = (int64_t)(zero_bytes / 16);
+  // The warp-per-setting variant (compose_warp.cu) is opt-in: on B200 it did not beat
+  // the thread-per-setting walk at any measured B (both are bound by single-warp
+  // instruction latency / fetch, not by instruction count) -- see DESIGN.md.
+  static const bool use_warp = [] {
+    const char* e = getenv("LYNX_K1");
+    return e && e[0] == 'w';
+  }();
+  if (use_warp) {
+    const int r = compose_warp_launch(p, a, st);
+    if (r <= 0) return r;
+  }
   const int n_cols = (int)p->col_offset.size();
   const size_t budget = 40 * 1024;
   const size_t ops_bytes = a.n_ops * sizeof(DevOp);
@@ -227,6 +243,14 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
   a.cov_out = d_cov_out;
   a.bpm_out = d_bpm_out;
   a.energy_out = d_energy_out;
+  static const bool use_warp = [] {
+    const char* e = getenv("LYNX_K1");
+    return e && e[0] == 'w';
+  }();
+  if (use_warp) {
+    const int r = parambeam_warp_launch(p, a, (cudaStream_t)stream);
+    if (r <= 0) return r;
+  }
   const unsigned blocks = (unsigned)((B + kPBThreads - 1) / kPBThreads);
   const int n_cols = (int)p->col_offset.size();
   const size_t smem = a.n_ops * sizeof(DevOp) + (size_t)n_cols * kPBThreads * 4;

@@ -295,15 +295,16 @@ extern "C" int lynx_track_particles_fwd(
   const bool has_img = d_screen_img && p->n_screen > 0;
   const size_t img_bytes = has_img ? sizeof(float) * (size_t)W * H * B : 0;
   const bool fuse_zero = has_img && !(img_bytes & 15) && !((uintptr_t)d_screen_img & 15);
-  int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
-                          records, nullptr, d_energy_out, fuse_zero ? d_screen_img : nullptr,
-                          fuse_zero ? img_bytes : 0, st);
-  if (rc != LYNX_OK) return rc;
-
+  // accumulators are cleared BEFORE K1 so that K1 -> K2 stay adjacent in the stream
+  // (programmatic dependent launch overlaps K2's prologue with K1)
   if (p->n_bpm_slots > 0)
     LYNX_CUDA_OK(cudaMemsetAsync(d_bpm_sums, 0, sizeof(double) * 2 * p->n_bpm_slots * B, st));
   if (has_img && !fuse_zero) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
   if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
+  int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
+                          records, nullptr, d_energy_out, fuse_zero ? d_screen_img : nullptr,
+                          fuse_zero ? img_bytes : 0, st);
+  if (rc != LYNX_OK) return rc;
 
   TrackArgs a;
   a.in = d_in_soa;

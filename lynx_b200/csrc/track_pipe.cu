@@ -154,16 +154,19 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
       issue_tile(it, t);
   }
 
-  // ---- everyone: per-setting record, plan, (edges) into shared memory
-  {
-    const float* src = a.records + b * a.rec_floats;
-    for (int i = tid; i < a.rec_floats; i += kPipeThreads) rec[i] = src[i];
-    for (int i = tid; i < a.n_plan; i += kPipeThreads) plan[i] = a.plan[i];
-    for (int i = tid; i < a.n_snap * 2; i += kPipeThreads) s_bpm[i] = 0.0;
-  }
+  // ---- everyone: plan and histogram geometry (independent of K1) ...
+  for (int i = tid; i < a.n_plan; i += kPipeThreads) plan[i] = a.plan[i];
+  for (int i = tid; i < a.n_snap * 2; i += kPipeThreads) s_bpm[i] = 0.0;
   if (a.img) {  // uniform over the CTA
     hist_axis_setup(a.ex, a.W, &s_hx, tid, kPipeThreads);
     hist_axis_setup(a.ey, a.H, &s_hy, tid, kPipeThreads);
+  }
+  // ... then wait for the K1 grid (records written, image zeroed) -- a no-op unless this
+  // kernel was launched with programmatic stream serialization
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  {
+    const float* src = a.records + b * a.rec_floats;
+    for (int i = tid; i < a.rec_floats; i += kPipeThreads) rec[i] = src[i];
   }
   __syncthreads();
 
@@ -358,12 +361,23 @@ static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, int edges_in_
       return LYNX_E_LAUNCH;
     attr_set = true;
   }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(kPipeThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t err;
   {
     ProfileScope ps(1, st);
-    k<<<grid, kPipeThreads, smem, st>>>(a, edges_in_smem);
+    err = cudaLaunchKernelEx(&cfg, k, a, edges_in_smem);
   }
   count_launch();
-  return cudaGetLastError() == cudaSuccess ? LYNX_OK : LYNX_E_LAUNCH;
+  return err == cudaSuccess ? LYNX_OK : LYNX_E_LAUNCH;
 }
 
 // Returns LYNX_OK after enqueueing, or 1 if this variant cannot take the problem (the

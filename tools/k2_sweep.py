@@ -12,7 +12,7 @@ from lynx_b200 import _lib as L  # noqa: E402
 
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(0)
-flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+flush = torch.empty((1 << 10) if os.environ.get("NOFLUSH") else (256 << 20), dtype=torch.uint8, device=dev)
 lib = L.lib()
 ns = [int(x) for x in (sys.argv[1].split(",") if len(sys.argv) > 1 else ["1000000"])]
 for n in ns:

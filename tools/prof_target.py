@@ -25,6 +25,8 @@ elif a.mode == "out32m":
     w = bench.ParticleWorkload(32_000_000, dev, seed=7, screen=False, want_out=True)
 elif a.mode == "outmom32m":
     w = bench.ParticleWorkload(32_000_000, dev, seed=7, screen=False, want_out=True, moments=1)
+elif a.mode == "none1m":
+    w = bench.ParticleWorkload(1_000_000, dev, seed=7, screen=False)
 elif a.mode == "pb4096":
     w = bench.ParamBeamWorkload(4096, dev)
 elif a.mode == "pb1m":
