@@ -59,12 +59,16 @@ struct RecordSink {
 #pragma unroll
     for (int i = 0; i < 6; ++i) ctr[i] = lin[i];
   }
-  __device__ __forceinline__ void bpm(int, int snap) {
+  __device__ __forceinline__ bool flush_before(const DevOp& op) const { return op.flush_stage >= 0; }
+  __device__ __forceinline__ void finish(const Map& M, int final_stage) {
+    if (final_stage >= 0) stage(M, final_stage);
+  }
+  __device__ __forceinline__ void bpm(const Map&, int, int snap) {
     float* d = rec + off_centre + snap * 6;
 #pragma unroll
     for (int i = 0; i < 6; ++i) d[i] = ctr[i];
   }
-  __device__ __forceinline__ void screen(int, int sidx, float mx, float my, int) {
+  __device__ __forceinline__ void screen(const Map&, int, int sidx, float mx, float my, int) {
     rec[off_screen + sidx * 2 + 0] = mx;
     rec[off_screen + sidx * 2 + 1] = my;
   }
@@ -89,20 +93,21 @@ struct ComposeArgs {
 };
 
 // ------------------------------------------------------------------ K6
-struct MomentSink {
-  float mu[7];
-  float cov[7][7];
-  float* bpm_out;
+template <typename T>
+struct MomentSinkT {
+  T mu[7];
+  T cov[7][7];
+  T* bpm_out;
   int64_t B, b;
 
   // element.py:73-74 with R = [M; e6]
-  __device__ __forceinline__ void apply(const Map& M) {
-    float t[7];
+  __device__ __forceinline__ void apply(const MapT<T>& M) {
+    T t[7];
 #pragma unroll
     for (int i = 0; i < 6; ++i) {
-      float acc = 0.f;
+      T acc = T(0.f);
 #pragma unroll
-      for (int j = 0; j < 7; ++j) acc = fmaf(M.m[i][j], mu[j], acc);
+      for (int j = 0; j < 7; ++j) acc = fma_(M.m[i][j], mu[j], acc);
       t[i] = acc;
     }
 #pragma unroll
@@ -112,9 +117,9 @@ struct MomentSink {
     for (int k = 0; k < 7; ++k) {
 #pragma unroll
       for (int i = 0; i < 6; ++i) {
-        float acc = 0.f;
+        T acc = T(0.f);
 #pragma unroll
-        for (int j = 0; j < 7; ++j) acc = fmaf(M.m[i][j], cov[j][k], acc);
+        for (int j = 0; j < 7; ++j) acc = fma_(M.m[i][j], cov[j][k], acc);
         t[i] = acc;
       }
 #pragma unroll
@@ -125,45 +130,50 @@ struct MomentSink {
     for (int i = 0; i < 7; ++i) {
 #pragma unroll
       for (int l = 0; l < 6; ++l) {
-        float acc = 0.f;
+        T acc = T(0.f);
 #pragma unroll
-        for (int k = 0; k < 7; ++k) acc = fmaf(cov[i][k], M.m[l][k], acc);
+        for (int k = 0; k < 7; ++k) acc = fma_(cov[i][k], M.m[l][k], acc);
         t[l] = acc;
       }
 #pragma unroll
       for (int l = 0; l < 6; ++l) cov[i][l] = t[l];
     }
   }
-  __device__ __forceinline__ void stage(const Map& M, int) { apply(M); }
+  __device__ __forceinline__ void stage(const MapT<T>& M, int) { apply(M); }
   // cavity.py:113-140, 202-218 (ParameterBeam branch; overwrites as written, quirk B5)
-  __device__ __forceinline__ void cavity(const Map& C, const CavityOut& co, int, int) {
-    const float mu4 = mu[4], mu5 = mu[5];
-    const float c44 = cov[4][4], c45 = cov[4][5], c55 = cov[5][5];
+  __device__ __forceinline__ void cavity(const MapT<T>& C, const CavityOutT<T>& co, int, int) {
+    const T mu4 = mu[4], mu5 = mu[5];
+    const T c44 = cov[4][4], c45 = cov[4][5], c55 = cov[5][5];
     apply(C);
-    const float* sc = co.sc;
-    if (sc[CV_ON] != 0.f) {
-      float s1, p1;
+    const T* sc = co.sc;
+    if (val(sc[CV_ON]) != 0.f) {
+      T s1, p1;
       cavity_nonlinear(sc, mu4, mu5, mu[4], mu[5], s1, p1);
       mu[4] = s1;
       mu[5] = p1;
       cov[5][5] = c55;
-      float v = sc[CV_T566] * c55 * c55 + sc[CV_T556] * c45 * c55 + sc[CV_T555] * c44 * c44;
+      T v = sc[CV_T566] * c55 * c55 + sc[CV_T556] * c45 * c55 + sc[CV_T555] * c44 * c44;
       cov[4][4] = v;
       cov[4][5] = v;
       cov[5][4] = v;
     }
   }
-  __device__ __forceinline__ void bpm(int slot, int) {
+  __device__ __forceinline__ bool flush_before(const DevOp& op) const { return op.flush_stage >= 0; }
+  __device__ __forceinline__ void finish(const MapT<T>& M, int final_stage) {
+    if (final_stage >= 0) apply(M);
+  }
+  __device__ __forceinline__ void bpm(const MapT<T>&, int slot, int) {
     if (bpm_out) {
       bpm_out[(slot * B + b) * 2 + 0] = mu[0];  // bpm.py:52
       bpm_out[(slot * B + b) * 2 + 1] = mu[2];
     }
   }
-  __device__ __forceinline__ void screen(int, int, float mx, float my, int) {
+  __device__ __forceinline__ void screen(const MapT<T>&, int, int, T mx, T my, int) {
     mu[0] -= mx;  // screen.py:131-132
     mu[2] -= my;
   }
 };
+using MomentSink = MomentSinkT<float>;
 
 struct ParamBeamArgs {
   const DevOp* ops;

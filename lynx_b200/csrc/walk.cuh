@@ -18,10 +18,16 @@ struct ParamView {
 };
 
 // Sink concept:
+//   bool flush_before(const DevOp&);   forward sinks: op.flush_stage >= 0 (the run grouping
+//                                      of segment.py:344-351); the adjoint sinks flush only
+//                                      before active cavities (they merge whole cavity-free
+//                                      segments, BPMs included)
+//   void finish(const Map& M, int final_stage);   end of program; forward sinks emit M as
+//                                      stage `final_stage` if it is >= 0
 //   void stage(const Map& M, int stage_idx);                 merged run finished
 //   void cavity(const Map& C, const CavityOut& co, int stage_idx, int cav_idx);
-//   void bpm(int slot, int snap_idx);
-//   void screen(int slot, int screen_idx, float mis_x, float mis_y, int flags);
+//   void bpm(const Map& M, int slot, int snap_idx);     M = map composed since the last flush
+//   void screen(const Map& M, int slot, int screen_idx, T mis_x, T mis_y, int flags);
 // Parameter columns of a tile of settings staged in shared memory: vals[col * S + s].
 struct SmemParamView {
   const float* vals;
@@ -31,27 +37,27 @@ struct SmemParamView {
 
 // Left-multiplies M by the map of one linear (skippable) op.  Returns false for ops that
 // are not part of a merged run (active cavity, BPM, screen).
-template <typename PV>
-__device__ __forceinline__ bool lm_linear_op(Map& M, const DevOp& op, const PV& P,
-                                             const Rel& rel, float energy) {
+template <typename T, typename PV>
+__device__ __forceinline__ bool lm_linear_op(MapT<T>& M, const DevOp& op, const PV& P,
+                                             const RelT<T>& rel, T energy) {
   const int c = op.col;
   switch (op.opcode) {
     case LYNX_OP_MARKER:
       return true;
     case LYNX_OP_DRIFT: {
-      float L = P(c);
+      T L = P(c);
       lm_drift(M, L, drift_r56(L, rel));
     } return true;
     case LYNX_OP_QUAD:
       lm_quad(M, P(c), P(c + 1), P(c + 2), P(c + 3), P(c + 4), rel);
       return true;
     case LYNX_OP_HCOR: {
-      float L = P(c);
+      T L = P(c);
       lm_drift(M, L, drift_r56(L, rel));
       M.m[1][6] += P(c + 1);  // horizontal_corrector.py:63
     } return true;
     case LYNX_OP_VCOR: {
-      float L = P(c);
+      T L = P(c);
       lm_drift(M, L, drift_r56(L, rel));
       M.m[3][6] += P(c + 1);  // vertical_corrector.py:63
     } return true;
@@ -62,16 +68,16 @@ __device__ __forceinline__ bool lm_linear_op(Map& M, const DevOp& op, const PV& 
     case LYNX_OP_CAVITY: {
       if (op.flags & LYNX_F_ACTIVE) return false;
       // skippable cavity (voltage == 0 everywhere): linear map merged into the run
-      Map C;
-      CavityOut co;
-      cavity_setting(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
+      MapT<T> C;
+      CavityOutT<T> co;
+      cavity_setting<T>(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
       lm_custom(M, [&](int r, int k) { return C.m[r][k]; });
     } return true;
     case LYNX_OP_SOLENOID:
       lm_solenoid(M, P(c), P(c + 1), P(c + 2), P(c + 3), rel);
       return true;
     case LYNX_OP_UNDULATOR: {
-      float L = P(c);
+      T L = P(c);
       lm_drift(M, L, L * rel.igamma2_drift);  // undulator.py:52-58 (quirk B4)
     } return true;
     case LYNX_OP_CUSTOM:
@@ -82,35 +88,35 @@ __device__ __forceinline__ bool lm_linear_op(Map& M, const DevOp& op, const PV& 
   }
 }
 
-template <typename Sink, typename PV>
+template <typename T, typename Sink, typename PV>
 __device__ __forceinline__ void walk_program(const DevOp* __restrict__ ops, int n_ops,
                                              int final_stage, const PV& P,
-                                             float& energy, Sink& sink) {
-  Map M;
+                                             T& energy, Sink& sink) {
+  MapT<T> M;
   map_identity(M);
-  Rel rel = make_rel(energy);
+  RelT<T> rel = make_rel(energy);
   for (int i = 0; i < n_ops; ++i) {
     const DevOp op = ops[i];
-    if (op.flush_stage >= 0) {
+    if (sink.flush_before(op)) {
       sink.stage(M, op.flush_stage);
       map_identity(M);
     }
     if (lm_linear_op(M, op, P, rel, energy)) continue;
     const int c = op.col;
     if (op.opcode == LYNX_OP_CAVITY) {
-      Map C;
-      CavityOut co;
-      cavity_setting(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
+      MapT<T> C;
+      CavityOutT<T> co;
+      cavity_setting<T>(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
       sink.cavity(C, co, op.self_stage, op.cav_idx);
       energy += co.dE;  // cavity.py:130
       rel = make_rel(energy);
     } else if (op.opcode == LYNX_OP_BPM) {
-      sink.bpm(op.aux, op.snap_idx);
+      sink.bpm(M, op.aux, op.snap_idx);
     } else if (op.opcode == LYNX_OP_SCREEN) {
-      sink.screen(op.aux, op.snap_idx, P(c), P(c + 1), op.flags);
+      sink.screen(M, op.aux, op.snap_idx, P(c), P(c + 1), op.flags);
     }
   }
-  if (final_stage >= 0) sink.stage(M, final_stage);
+  sink.finish(M, final_stage);
 }
 
 }  // namespace lynx

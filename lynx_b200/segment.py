@@ -10,6 +10,7 @@ from typing import Optional
 import torch
 
 from . import _lib as L
+from . import autograd as AG
 from .beams import Beam, ParameterBeam, ParticleBeam
 from .elements import BPM, CustomTransferMap, Drift, Element, Marker, Screen
 from .program import Program, encode, pack_params
@@ -74,28 +75,13 @@ def compose_transfer_map(elements, energy: torch.Tensor) -> Optional[torch.Tenso
 # --------------------------------------------------------------------------- K2
 def launch_track_particles(prog: Program, params, B, soa, shared, ld, N, energy_in, *,
                            want_out, moment_mode, screen: Optional[Screen], batch_shape):
-    """One call of ``lynx_track_particles_fwd``; returns the raw device outputs."""
-    device = soa.device
-    out = (torch.empty((*batch_shape, 6, ld), dtype=torch.float32, device=device)
-           if want_out else None)
-    bpm = (torch.empty((prog.n_bpm, B, 2), dtype=torch.float64, device=device)
-           if prog.n_bpm else None)
-    img = ex = ey = None
-    W = H = 0
-    if screen is not None:
-        ex, ey = screen._device_edges(device)
-        W, H = ex.numel() - 1, ey.numel() - 1
-        img = torch.empty((*batch_shape, H, W), dtype=torch.float32, device=device)
-    mom = (torch.empty((*batch_shape, 28), dtype=torch.float64, device=device)
-           if moment_mode else None)
-    e_out = torch.empty(batch_shape, dtype=torch.float32, device=device)
-    ws = torch.empty(prog.workspace_bytes(B), dtype=torch.uint8, device=device)
-    L.check(L.lib().lynx_track_particles_fwd(
-        prog.handle, params.data_ptr(), B, soa.data_ptr(), 0 if shared else 1, ld, N,
-        L.ptr(out), ld, L.ptr(bpm), L.ptr(img), W, H, L.ptr(ex), L.ptr(ey), L.ptr(mom),
-        moment_mode, energy_in.data_ptr(), e_out.data_ptr(), ws.data_ptr(),
-        L.current_stream()), "lynx_track_particles_fwd")
-    return out, bpm, img, mom, e_out
+    """One call of ``lynx_track_particles_fwd`` (through ``TrackParticlesFn`` when a
+    gradient is wanted); returns the raw device outputs."""
+    cfg = AG.TrackCfg(prog, B, shared, ld, N, energy_in, want_out, moment_mode, screen,
+                      tuple(batch_shape))
+    if AG.needs_grad(params, soa):
+        return AG.TrackParticlesFn.apply(params, soa, cfg)
+    return AG.track_particles_raw(cfg, params, soa)
 
 
 def _prep_particle_beam(beam: ParticleBeam, batch_shape):
@@ -209,15 +195,11 @@ def _track_parameter_beam(flat, incoming: ParameterBeam):
     else:
         mu_in = mu.expand(*bshape, 7).contiguous()
         cov_in = cov.expand(*bshape, 7, 7).contiguous()
-    mu_out = torch.empty((*bshape, 7), dtype=torch.float32, device=device)
-    cov_out = torch.empty((*bshape, 7, 7), dtype=torch.float32, device=device)
-    bpm = (torch.empty((prog.n_bpm, B, 2), dtype=torch.float32, device=device)
-           if prog.n_bpm else None)
-    e_out = torch.empty(bshape, dtype=torch.float32, device=device)
-    L.check(L.lib().lynx_parambeam_fwd(
-        prog.handle, params.data_ptr(), B, mu_in.data_ptr(), cov_in.data_ptr(),
-        0 if shared else 1, e_in.data_ptr(), mu_out.data_ptr(), cov_out.data_ptr(), L.ptr(bpm),
-        e_out.data_ptr(), L.current_stream()), "lynx_parambeam_fwd")
+    cfg = AG.ParamBeamCfg(prog, B, shared, e_in, tuple(bshape))
+    if AG.needs_grad(params, mu_in, cov_in):
+        mu_out, cov_out, bpm, e_out = AG.ParamBeamFn.apply(params, mu_in, cov_in, cfg)
+    else:
+        mu_out, cov_out, bpm, e_out = AG.parambeam_raw(cfg, params, mu_in, cov_in)
     for slot, el in enumerate(enc.bpm_elements):
         el.reading = bpm[slot].T.reshape(2, *bshape)
     out = ParameterBeam.__new__(ParameterBeam)
