@@ -37,8 +37,8 @@ VKICK, HKICK = 1e-3, -2e-3
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--particles", type=int, default=1_000_000, help="per GPU")
     ap.add_argument("--settings", type=int, default=4096)
@@ -56,43 +56,64 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+    """SM clock / throttle reasons DURING the timed region: an NVML polling thread (the
+    timed region is a few ms, far shorter than nvidia-smi's sampling period), with
+    nvidia-smi as the fallback."""
 
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    NAMES = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20,
+             "hw_thermal_slowdown": 0x40}
 
     def __init__(self, index):
-        self.rows, self.proc = [], None
+        self.sm, self.reasons, self.max_mhz = [], 0, None
+        self._stop = threading.Event()
+        self._nvml = None
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
+            import pynvml
+
+            pynvml.nvmlInit()
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            self._nvml = pynvml
+            self.t = threading.Thread(target=self._poll, daemon=True)
             self.t.start()
         except Exception:
-            self.proc = None
+            self._nvml = None
+            self._index = index
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+    def _poll(self):
+        nv = self._nvml
+        while not self._stop.is_set():
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                self.reasons |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+            except Exception:
+                try:
+                    self.reasons |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+                except Exception:
+                    pass
+            time.sleep(0.0002)
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
+        if self._nvml is not None:
+            self._stop.set()
+            self.t.join(timeout=2)
+            reasons = sorted(n for n, bit in self.NAMES.items() if self.reasons & bit)
+            return {"sm_mhz": float(np.median(self.sm)) if self.sm else None,
+                    "sm_max_mhz": self.max_mhz, "reasons": reasons, "samples": len(self.sm),
+                    "source": "nvml polled during the timed region"}
+        try:  # one nvidia-smi query right after the region
+            q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+                 "clocks_event_reasons.hw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+            out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                  "-i", str(self._index)], capture_output=True, text=True,
+                                 timeout=20).stdout.strip().split(",")
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            return {"sm_mhz": float(out[0]), "sm_max_mhz": float(out[1]),
+                    "reasons": [names[i] for i in range(4) if out[2 + i].strip().lower().startswith("active")],
+                    "samples": 1, "source": "nvidia-smi after the timed region"}
         except Exception:
-            self.proc.kill()
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4)
-                          if r[2 + i].lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None,
-                "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(sm)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock query unavailable"]}
 
 
 # ----------------------------------------------------------------------------- CPU arm
@@ -275,6 +296,63 @@ class ParamBeamWorkload:
         return 248 * self.B
 
 
+class GradWorkload:
+    """Config 5: one beam shared by B settings through ARES EA (screen off), loss on the
+    outgoing moments; a step = forward (moment sums) + backward (gradients w.r.t. every
+    parameter column, incl. 3 x k1 + 2 x angle per setting) through the C ABI."""
+
+    def __init__(self, n, B, device, seed=1005, per_particle=False):
+        from lynx_b200 import _lib as L
+        from lynx_b200 import fixtures as F
+        from lynx_b200.program import Program, encode, pack_params
+
+        self.L, self.n, self.B, self.per_particle = L, n, B, per_particle
+        k1, ang = F.random_settings(B, seed, k1_range=5.0)
+        seg = F.build_segment(F.ares_ea())
+        for i, nm in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")):
+            getattr(seg, nm).k1 = torch.from_numpy(k1[:, i])
+        seg.AREAMCVM1.angle = torch.from_numpy(ang[:, 0])
+        seg.AREAMCHM1.angle = torch.from_numpy(ang[:, 1])
+        self.enc = encode(seg.elements, (1,))
+        self.prog = Program.get(self.enc)
+        self.params = pack_params(self.enc, device)
+        self.ld = (n + 3) & ~3
+        self.soa = torch.zeros((6, self.ld), device=device)
+        self.soa[:, :n] = torch.from_numpy(F.gaussian_beam_soa(n, seed=seed)).to(device)
+        self.e_in = torch.full((B,), F.ASTRA_ENERGY, device=device)
+        self.e_out = torch.empty(B, device=device)
+        self.lib = L.lib()
+        self.ws = torch.empty(self.prog.workspace_bytes(B), dtype=torch.uint8, device=device)
+        self.bws = torch.empty(self.lib.lynx_bwd_workspace_bytes(self.prog.handle, B),
+                               dtype=torch.uint8, device=device)
+        self.mom = torch.empty((B, 28), dtype=torch.float64, device=device)
+        self.g_mom = torch.randn((B, 28), dtype=torch.float64, device=device)
+        self.g_params = torch.empty_like(self.params)
+        # per-particle cotangent variant (B must be 1): forces the streaming K3a pass
+        self.out = torch.empty((B, 6, self.ld), device=device) if per_particle else None
+        self.g_out = torch.randn((B, 6, self.ld), device=device) if per_particle else None
+        self.g_in = torch.empty((6, self.ld), device=device) if per_particle else None
+
+    def forward(self):
+        L = self.L
+        L.check(self.lib.lynx_track_particles_fwd(
+            self.prog.handle, self.params.data_ptr(), self.B, self.soa.data_ptr(), 0, self.ld,
+            self.n, L.ptr(self.out), self.ld, None, None, 0, 0, None, None, self.mom.data_ptr(), 1,
+            self.e_in.data_ptr(), self.e_out.data_ptr(), self.ws.data_ptr(), L.current_stream()))
+
+    def backward(self):
+        L = self.L
+        L.check(self.lib.lynx_track_particles_bwd(
+            self.prog.handle, self.params.data_ptr(), self.B, self.soa.data_ptr(), 0, self.ld,
+            self.n, L.ptr(self.g_out), self.ld, self.g_mom.data_ptr(), None,
+            self.e_in.data_ptr(), self.g_params.data_ptr(), L.ptr(self.g_in), self.ld,
+            self.bws.data_ptr(), L.current_stream()))
+
+    def step(self):
+        self.forward()
+        self.backward()
+
+
 def timed_steps(step, steps, warmup, flush, post=None):
     """Per-step CUDA-event timing on the current stream with an L2 flush (outside the
     events) before every step.  Returns the list of per-step milliseconds."""
@@ -452,6 +530,27 @@ def run_ours(args, rank, world, local_rank):
                 "frac_of_8000": a2 / 8000.0,
                 "particle_element_updates_per_s": ns * E_ARES / (km * 1e-3)}
             del w2
+        # config 5: gradients, one 1M-particle beam x 1024 settings (moment loss)
+        gw = GradWorkload(args.particles, 1024, device)
+        gms = timed_steps(gw.step, 20, 3, flush)
+        fms = timed_steps(gw.forward, 20, 3, flush)
+        extras["grad_1M_x_1024_settings"] = {
+            "particles": args.particles, "settings": 1024, "fwd_bwd_ms": float(np.mean(gms)),
+            "fwd_ms": float(np.mean(fms)),
+            "setting_gradients_per_s": 1024 / (np.mean(gms) * 1e-3),
+            "particle_setting_element_updates_per_s":
+                args.particles * 1024 * E_ARES / (np.mean(gms) * 1e-3),
+            "path": "moment collapse: the shared beam is streamed once per call, not per "
+                    "setting (DESIGN.md 4.1); K3b dual-number parameter gradients"}
+        del gw
+        # streaming adjoint K3a at scale: per-particle cotangent + g_in, B = 1
+        gw = GradWorkload(ns, 1, device, per_particle=True)
+        k3 = kernel_ms(gw.backward, 3, 10, flush, lib)
+        k3_bytes = 72 * ns  # x 24 B + g_out 24 B + g_in 24 B per particle
+        extras["at_scale_adjoint_K3a_72B"] = {
+            "particles": ns, "kernel_ms": k3, "achieved_gbs": k3_bytes / (k3 * 1e-3) / 1e9,
+            "frac": k3_bytes / (k3 * 1e-3) / 1e9 / peak}
+        del gw
         line["extras"] = extras
 
     lib.lynx_host_ctx_destroy(ctx)

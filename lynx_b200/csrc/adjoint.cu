@@ -730,6 +730,131 @@ __global__ void __launch_bounds__(64) parambeam_bwd_kernel(PBBwdArgs a) {
   }
 }
 
+// ------------------------------------------------------------------ forward moment collapse
+// One beam shared by B settings, no outgoing particles, no image, no active cavity: the
+// outgoing moment sums are the incoming ones pushed through each setting's total map,
+//   S1' = T S1,  S2' = T S2 T^T  (homogeneous 7x7),  bpm sums = (P_b S1)_{x,y},
+// so the beam is streamed ONCE (beam_moments_kernel), not once per setting.
+struct FwdCollapseArgs {
+  const float* arec;
+  AdjLayout L;
+  const double* in_sums;  // [28] of the shared beam
+  const PlanItem* plan;
+  int n_plan;
+  double* mom;            // [B][28] nullable
+  double* bpm_sums;       // [n_slots][B][2] nullable
+  const float* energy_in;
+  float* energy_out;
+  int64_t B;
+};
+
+__global__ void __launch_bounds__(128) fwd_collapse_kernel(FwdCollapseArgs a) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= a.B) return;
+  const float* rec = a.arec + b * a.L.rec_floats;
+  const double* S = a.in_sums;
+  const double n = S[0];
+  double S1[7], S2[7][7];
+  for (int i = 0; i < 6; ++i) {
+    S1[i] = S[1 + i];
+    S2[i][6] = S2[6][i] = S[1 + i];
+    for (int j = i; j < 6; ++j) S2[i][j] = S2[j][i] = S[7 + tri(i, j)];
+  }
+  S1[6] = n;
+  S2[6][6] = n;
+  if (a.mom) {
+    double* o = a.mom + b * 28;
+    double TS[6][7];
+    for (int l = 0; l < 6; ++l)
+      for (int j = 0; j < 7; ++j) {
+        double s = 0.0;
+        for (int m = 0; m < 7; ++m) s += (double)rec[l * 7 + m] * S2[m][j];
+        TS[l][j] = s;
+      }
+    o[0] = n;
+    for (int i = 0; i < 6; ++i) o[1 + i] = TS[i][6];
+    for (int i = 0; i < 6; ++i)
+      for (int j = i; j < 6; ++j) {
+        double s = 0.0;
+        for (int m = 0; m < 7; ++m) s += TS[i][m] * (double)rec[j * 7 + m];
+        o[7 + tri(i, j)] = s;
+      }
+  }
+  if (a.bpm_sums) {
+    for (int it = 0; it < a.n_plan; ++it) {
+      const PlanItem p = a.plan[it];
+      if (p.kind != P_BPM) continue;
+      const float* r = rec + a.L.off_bpm + p.c * kAdjBpm;
+      double sx = 0.0, sy = 0.0;
+      for (int j = 0; j < 7; ++j) {
+        sx += (double)r[j] * S1[j];
+        sy += (double)r[7 + j] * S1[j];
+      }
+      a.bpm_sums[((int64_t)p.a * a.B + b) * 2 + 0] = sx;
+      a.bpm_sums[((int64_t)p.a * a.B + b) * 2 + 1] = sy;
+    }
+  }
+  if (a.energy_out) a.energy_out[b] = a.energy_in[b];
+}
+
+static size_t align256_(size_t x) { return (x + 255) & ~(size_t)255; }
+
+size_t fwd_collapse_workspace_bytes(const lynx_program_t* p, int64_t B) {
+  const AdjLayout L = adj_layout(p->n_cav, p->n_snap);
+  return align256_(sizeof(float) * (size_t)B * L.rec_floats) + 256;
+}
+
+int fwd_collapse_launch(const lynx_program_t* p, const float* d_params, int64_t B,
+                        const float* d_in_soa, int64_t ld_in, int64_t N, double* d_bpm_sums,
+                        double* d_moment_sums, const float* d_energy_in, float* d_energy_out,
+                        void* d_workspace, cudaStream_t st) {
+  const AdjLayout L = adj_layout(p->n_cav, p->n_snap);
+  float* arec = reinterpret_cast<float*>(d_workspace);
+  double* in_sums = reinterpret_cast<double*>((char*)d_workspace +
+                                              align256_(sizeof(float) * (size_t)B * L.rec_floats));
+  AdjComposeArgs ca;
+  ca.ops = p->d_ops;
+  ca.n_ops = (int)p->dev_ops.size();
+  ca.final_stage = p->final_stage;
+  ca.col_offset = p->d_col_offset;
+  ca.col_stride = p->d_col_stride;
+  ca.params = d_params;
+  ca.B = B;
+  ca.energy_in = d_energy_in;
+  ca.seed = nullptr;
+  ca.seed_row_stride = 0;
+  ca.seed_ld = 0;
+  ca.arec = arec;
+  ca.L = L;
+  ca.g_bpm = nullptr;
+  ca.g_mom = nullptr;
+  adj_compose_kernel<<<(unsigned)((B + 127) / 128), 128, 0, st>>>(ca);
+  count_launch();
+  LYNX_CUDA_OK(cudaMemsetAsync(in_sums, 0, sizeof(double) * 28, st));
+  const int64_t per = (int64_t)kMomTPB * 4;
+  const int64_t gx = std::min<int64_t>((N + per - 1) / per, 4LL * p->sm_count);
+  {
+    ProfileScope ps(1, st);
+    beam_moments_kernel<<<dim3((unsigned)gx, 1), kMomTPB, 0, st>>>(d_in_soa, 0, ld_in, N, in_sums);
+  }
+  count_launch();
+  FwdCollapseArgs fa;
+  fa.arec = arec;
+  fa.L = L;
+  fa.in_sums = in_sums;
+  fa.plan = p->d_plan;
+  fa.n_plan = (int)p->plan.size();
+  fa.mom = d_moment_sums;
+  fa.bpm_sums = d_bpm_sums;
+  fa.energy_in = d_energy_in;
+  fa.energy_out = d_energy_out;
+  fa.B = B;
+  fwd_collapse_kernel<<<(unsigned)((B + 127) / 128), 128, 0, st>>>(fa);
+  count_launch();
+  LYNX_CUDA_OK(cudaGetLastError());
+  return LYNX_OK;
+}
+
 }  // namespace lynx
 
 using namespace lynx;

@@ -79,6 +79,14 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
                    int64_t seed_ld, float* d_records, float* d_maps_out, float* d_energy_out,
                    void* zero_ptr, size_t zero_bytes, cudaStream_t st);
 
+// forward moment collapse (adjoint.cu): one beam shared by B settings, moments / BPM sums
+// only, no active cavity -> the beam is streamed once instead of once per setting
+size_t fwd_collapse_workspace_bytes(const lynx_program_t* p, int64_t B);
+int fwd_collapse_launch(const lynx_program_t* p, const float* d_params, int64_t B,
+                        const float* d_in_soa, int64_t ld_in, int64_t N, double* d_bpm_sums,
+                        double* d_moment_sums, const float* d_energy_in, float* d_energy_out,
+                        void* d_workspace, cudaStream_t st);
+
 // optional event bracketing of the dominant kernels (bench roofline)
 struct ProfileScope {
   int which;

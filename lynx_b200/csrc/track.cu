@@ -9,6 +9,7 @@
 //
 // Algorithmic HBM bytes: 24 B/particle read (+24 B written when outgoing particles are
 // requested); the per-setting record (<1 KB) is read once per CTA into shared memory.
+#include <algorithm>
 #include <cstdlib>
 
 #include "track_common.cuh"
@@ -268,6 +269,7 @@ using namespace lynx;
 extern "C" size_t lynx_workspace_bytes(const lynx_program_t* p, int64_t B) {
   if (!p || B <= 0) return 0;
   size_t bytes = (size_t)B * p->rec_floats * sizeof(float);
+  bytes = std::max(bytes, fwd_collapse_workspace_bytes(p, B));
   return (bytes + 255) & ~(size_t)255;
 }
 
@@ -290,6 +292,15 @@ extern "C" int lynx_track_particles_fwd(
   if (p->terminal && d_out_soa) return LYNX_E_BADARG;  // Beam.empty after an active screen
   cudaStream_t st = (cudaStream_t)stream;
 
+  // one beam, B > 1 settings, only additive moment / BPM outputs, no cavity: stream the
+  // beam once and push its moment sums through every setting's map (adjoint.cu)
+  static const bool no_collapse = [] { const char* e = getenv("LYNX_NO_COLLAPSE"); return e && e[0] == '1'; }();
+  if (!no_collapse && in_row_stride == 0 && B > 1 && !d_out_soa && p->n_screen == 0 &&
+      p->n_cav == 0 && (moment_mode != 0 || p->n_bpm_slots > 0)) {
+    return fwd_collapse_launch(p, d_params, B, d_in_soa, ld_in, N, d_bpm_sums,
+                               moment_mode ? d_moment_sums : nullptr, d_energy_in, d_energy_out,
+                               d_workspace, st);
+  }
   float* records = reinterpret_cast<float*>(d_workspace);
   // the screen image is zeroed by spare blocks of the K1 launch when its size allows
   const bool has_img = d_screen_img && p->n_screen > 0;

@@ -123,6 +123,7 @@ def track_elements(elements, incoming, *, particles: bool = True, moments: int =
         prog, params, B, soa, shared, ld, N, e_in, want_out=want_out, moment_mode=moments,
         screen=enc.screen_element, batch_shape=bshape)
     for slot, el in enumerate(enc.bpm_elements):  # bpm.py:54
+        el._bpm_sums = bpm[slot]  # additive over particle shards (sharding.py)
         el.reading = (bpm[slot] / N).to(torch.float32).T.reshape(2, *bshape)
     if enc.screen_element is not None:
         scr = enc.screen_element

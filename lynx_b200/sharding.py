@@ -1,0 +1,103 @@
+"""Multi-GPU sharding of the tracking path (one process per GPU, ``torch.distributed``).
+
+The reference has no parallelism beyond leading batch dimensions; the
+path shards two ways:
+
+* particle axis -- rank r owns a contiguous slice of every SoA plane; parameters are
+  replicated; the ONE exchange step is an all-reduce (SUM) of the additive outputs: the
+  screen image (integer-valued counts < 2^24, so the fp32 sum is exact and
+  order-independent), the ``[B][28]`` double moment sums and the ``[slot][B][2]`` double
+  BPM sums.  Moments / BPM readings are then derived from the reduced sums with the
+  GLOBAL particle count.  Outgoing particles stay sharded.
+* settings axis -- rank r owns a contiguous slice of the B settings; the beam is
+  replicated; no collective at all (optional all-gather for a single consumer).
+
+Everything here is host logic over ``torch.distributed`` (NCCL on GPUs, gloo in the CPU
+tests); the device work is the unchanged single-GPU C ABI.
+"""
+
+from typing import Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(n: int, world: int, rank: int, multiple: int = 4) -> Tuple[int, int]:
+    """[lo, hi) of rank's slice of ``n`` items; every boundary except the last is a
+    multiple of ``multiple`` (128-bit aligned SoA planes), sizes differ by <= multiple."""
+    if world <= 0 or not 0 <= rank < world:
+        raise ValueError(f"bad rank {rank} of {world}")
+    blocks = (n + multiple - 1) // multiple
+    base, extra = divmod(blocks, world)
+    lo_b = rank * base + min(rank, extra)
+    hi_b = lo_b + base + (1 if rank < extra else 0)
+    return min(lo_b * multiple, n), min(hi_b * multiple, n)
+
+
+def shard_soa(soa: torch.Tensor, n: int, world: int, rank: int) -> Tuple[torch.Tensor, int]:
+    """Rank's slice of SoA planes ``(..., 6, ld)`` -> contiguous ``(..., 6, ld_r)``, n_r."""
+    lo, hi = shard_bounds(n, world, rank)
+    n_r = hi - lo
+    ld_r = (n_r + 3) & ~3
+    out = soa.new_zeros((*soa.shape[:-1], max(ld_r, 4)))
+    out[..., :n_r] = soa[..., lo:hi]
+    return out, n_r
+
+
+def shard_settings(B: int, world: int, rank: int) -> Tuple[int, int]:
+    """[lo, hi) of rank's slice of the B settings (no alignment requirement)."""
+    return shard_bounds(B, world, rank, multiple=1)
+
+
+def all_reduce_sums(tensors: Sequence[Optional[torch.Tensor]], group=None, async_op=False):
+    """The one exchange step of the particle-sharded path: SUM all-reduce, in place, of
+    every additive output (image, moment sums, BPM sums, adjoint H sums, g_params).
+    ``None`` entries are skipped.  Returns the work handles when ``async_op``."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return []
+    works = []
+    for t in tensors:
+        if t is None:
+            continue
+        w = dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+        if async_op:
+            works.append(w)
+    return works
+
+
+def moments_from_sums(sums: torch.Tensor):
+    """``[.., 28]`` raw double sums (N, sum v_i, sum v_i v_j i<=j) -> (mean[..,6],
+    sigma[..,6] unbiased as particle_beam.py:742, cov_biased[..,6,6] as :824-836)."""
+    n = sums[..., 0:1]
+    s1 = sums[..., 1:7]
+    mean = s1 / n
+    iu = torch.triu_indices(6, 6)
+    s2 = sums.new_zeros((*sums.shape[:-1], 6, 6))
+    s2[..., iu[0], iu[1]] = sums[..., 7:28]
+    s2 = s2 + s2.transpose(-1, -2) - torch.diag_embed(torch.diagonal(s2, dim1=-2, dim2=-1))
+    centred = s2 - s1.unsqueeze(-1) * s1.unsqueeze(-2) / n.unsqueeze(-1)
+    cov_biased = centred / n.unsqueeze(-1)
+    var_unbiased = torch.diagonal(centred, dim1=-2, dim2=-1) / (n - 1)
+    return mean, torch.sqrt(torch.clamp_min(var_unbiased, 0.0)), cov_biased
+
+
+def track_sharded(segment, soa_full: torch.Tensor, n: int, energy, *, world: int, rank: int,
+                  particles: bool = False, moments: int = 1, group=None):
+    """Particle-sharded ``Segment.track``: tracks this rank's slice on the current CUDA
+    device and all-reduces the additive outputs.  Returns (local outgoing beam or
+    Beam.empty, reduced image or None, reduced moment sums or None)."""
+    from .beams import Beam, ParticleBeam
+
+    local, n_r = shard_soa(soa_full, n, world, rank)
+    beam = ParticleBeam.from_soa(local.cuda(), n_r, torch.as_tensor(energy).cuda())
+    out = segment.track(beam, particles=particles, moments=moments)
+    img = None
+    screens = [e for e in segment.elements if getattr(e, "cached_reading", None) is not None]
+    if screens:
+        img = screens[-1].cached_reading
+    bpm_elems = [e for e in segment.elements if getattr(e, "_bpm_sums", None) is not None]
+    sums = None if out is Beam.empty else out._sums
+    all_reduce_sums([img, sums] + [e._bpm_sums for e in bpm_elems], group=group)
+    for e in bpm_elems:  # bpm.py:54 with the global particle count
+        e.reading = (e._bpm_sums / n).to(torch.float32).T.reshape(e.reading.shape)
+    return out, img, sums

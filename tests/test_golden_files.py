@@ -1,0 +1,129 @@
+"""Committed golden vectors (tests/golden/*.npz, generated from the fp64 oracle by
+tests/golden/make_golden.py -- NOT outputs of the reference, which cannot execute).
+
+CPU: the oracle still reproduces them (guards the checker against drift).
+GPU: the CUDA path, through the C ABI, against the fixed files (no oracle involved)."""
+
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from lynx_b200 import fixtures as F
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+QUADS = ("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")
+
+
+def _load(name):
+    return np.load(os.path.join(G, name))
+
+
+def test_oracle_reproduces_golden_particles():
+    from helpers import aos_from_soa, oracle_elements
+    from oracle import lattice as O
+
+    g = _load("ares_ea_particles.npz")
+    spec = F.ares_ea(k1=(5.0, -5.0, 5.0), vkick=1e-3, hkick=-2e-3)
+    beam = O.ParticleBeamO(aos_from_soa(g["in_soa"], torch.float64),
+                           torch.tensor([F.ASTRA_ENERGY], dtype=torch.float64))
+    out = O.track(oracle_elements(spec, torch.float64), beam)
+    np.testing.assert_allclose(out.particles[0, :, :6].T.numpy(), g["out_planes"], rtol=1e-12,
+                               atol=1e-20)
+    g4 = _load("cavity_dipole_line_particles.npz")
+    beam = O.ParticleBeamO(aos_from_soa(g4["in_soa"], torch.float64),
+                           torch.tensor([F.CFG4_ENERGY], dtype=torch.float64))
+    out = O.track(oracle_elements(F.cavity_dipole_line(False), torch.float64), beam)
+    np.testing.assert_allclose(out.particles[0, :, :6].T.numpy(), g4["out_planes"], rtol=1e-10,
+                               atol=1e-20)
+
+
+def test_golden_files_are_small_and_complete():
+    names = sorted(f for f in os.listdir(G) if f.endswith(".npz"))
+    assert names == ["ares_ea_gradients.npz", "ares_ea_parameter_beam.npz",
+                     "ares_ea_particles.npz", "cavity_dipole_line_particles.npz"]
+    assert all(os.path.getsize(os.path.join(G, n)) < 200_000 for n in names)
+
+
+def _rel(got, want, rtol, what):
+    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+    scale = np.sqrt(np.mean(want**2, axis=-1, keepdims=True)) + 1e-300
+    err = np.abs(got - want) / scale
+    assert err.max() <= rtol, f"{what}: worst err/rms {err.max():.3e} > {rtol}"
+
+
+@pytest.mark.gpu
+def test_gpu_particles_and_image_vs_golden():
+    import lynx_b200 as lx
+
+    g = _load("ares_ea_particles.npz")
+    n = g["in_soa"].shape[1]
+    beam = lx.ParticleBeam(torch.from_numpy(F.soa_to_aos7(g["in_soa"])).unsqueeze(0),
+                           torch.tensor([F.ASTRA_ENERGY]))
+    spec = F.ares_ea(k1=(5.0, -5.0, 5.0), vkick=1e-3, hkick=-2e-3)
+    seg = F.build_segment(spec)
+    out = seg.track(beam)
+    # 2e-5 of the plane rms: fp32 kernel vs the fp64 golden (fp32 input rounding included)
+    _rel(out.soa[0, :, :n].cpu().numpy(), g["out_planes"], 2e-5, "particles")
+    np.testing.assert_allclose(out.sigma_x.item(), g["sigma"][0], rtol=2e-5)
+    np.testing.assert_allclose(out.sigma_y.item(), g["sigma"][2], rtol=2e-5)
+    tm = seg.transfer_map(torch.tensor([F.ASTRA_ENERGY]).cuda())[0].cpu().numpy()
+    np.testing.assert_allclose(tm, g["transfer_map"], rtol=2e-5, atol=1e-9)
+
+    small = {"resolution": (64, 48), "pixel_size": (4e-5, 4e-5), "binning": 1}
+    seg_s = F.build_segment(F.ares_ea(k1=(5.0, -5.0, 5.0), vkick=1e-3, hkick=-2e-3,
+                                      screen_active=True, screen=small))
+    assert seg_s.track(beam) is lx.Beam.empty
+    img = seg_s.AREABSCR1.reading[0].cpu().numpy()
+    want = g["image"]
+    assert img.shape == want.shape and img.sum() == want.sum()
+    # bins exact except particles within 1 ulp-ish of an edge (fp32 kernel coordinates vs
+    # fp32-rounded fp64 oracle coordinates): at most a handful of unit moves
+    assert np.abs(img - want).sum() <= 8
+
+    g4 = _load("cavity_dipole_line_particles.npz")
+    beam4 = lx.ParticleBeam(torch.from_numpy(F.soa_to_aos7(g4["in_soa"])).unsqueeze(0),
+                            torch.tensor([F.CFG4_ENERGY]))
+    out4 = F.build_segment(F.cavity_dipole_line(False)).track(beam4)
+    _rel(out4.soa[0, :, :g4["in_soa"].shape[1]].cpu().numpy(), g4["out_planes"], 5e-5,
+         "cavity line particles")
+    np.testing.assert_allclose(out4.energy.cpu().numpy(), g4["energy_out"], rtol=1e-6)
+
+
+@pytest.mark.gpu
+def test_gpu_parameter_beam_and_gradients_vs_golden():
+    import lynx_b200 as lx
+
+    g = _load("ares_ea_parameter_beam.npz")
+    seg = F.build_segment(F.ares_ea())
+    for i, q in enumerate(QUADS):
+        getattr(seg, q).k1 = torch.from_numpy(g["k1"][:, i])
+    seg.AREAMCVM1.angle = torch.from_numpy(g["angles"][:, 0])
+    seg.AREAMCHM1.angle = torch.from_numpy(g["angles"][:, 1])
+    pb = lx.ParameterBeam(torch.from_numpy(g["mu_in"]).float().unsqueeze(0),
+                          torch.from_numpy(g["cov_in"]).float().unsqueeze(0),
+                          torch.tensor([F.ASTRA_ENERGY]))
+    out = seg.track(pb)
+    np.testing.assert_allclose(out._mu.cpu().numpy()[:, :4], g["mu_out"][:, :4], rtol=3e-5,
+                               atol=1e-9)
+    d = np.sqrt(np.abs(np.einsum("bii->bi", g["cov_out"])))
+    scale = d[:, :, None] * d[:, None, :] + 1e-300
+    assert (np.abs(out._cov.cpu().numpy() - g["cov_out"]) / scale)[:, :6, :6].max() < 3e-5
+
+    gg = _load("ares_ea_gradients.npz")
+    seg = F.build_segment(F.ares_ea())
+    k1 = torch.tensor(gg["k1"], requires_grad=True)
+    ang = torch.tensor(gg["angles"], requires_grad=True)
+    for i, q in enumerate(QUADS):
+        getattr(seg, q).k1 = k1[:, i]
+    seg.AREAMCVM1.angle, seg.AREAMCHM1.angle = ang[:, 0], ang[:, 1]
+    beam = lx.ParticleBeam(torch.from_numpy(F.soa_to_aos7(gg["in_soa"])).unsqueeze(0),
+                           torch.tensor([F.ASTRA_ENERGY]))
+    o = seg.track(beam)
+    loss = (o.mu_x**2 + o.sigma_x**2 + o.mu_y**2 + o.sigma_y**2).sum() / 4
+    loss.backward()
+    np.testing.assert_allclose(loss.item(), gg["loss"], rtol=3e-5)
+    for got, want, nm in ((k1.grad, gg["g_k1"], "g_k1"), (ang.grad, gg["g_angles"], "g_angles")):
+        err = np.abs(got.numpy() - want).max() / np.abs(want).max()
+        assert err < 3e-5, f"{nm}: {err:.3e}"

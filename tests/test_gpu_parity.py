@@ -392,3 +392,44 @@ def test_host_buffer_abi_matches_device_path():
     L.lib().lynx_host_ctx_destroy(ctx)
     assert np.array_equal(img, want)
     assert mom[0, 0] == n
+
+
+def test_forward_moment_collapse_matches_streaming():
+    """One beam shared by B settings, moments / BPM readings only: the collapse path
+    (beam streamed once, sums pushed through each setting's map) must agree with the
+    per-setting streaming pass and with the oracle."""
+    B, n = 12, 40_000
+    soa = F.gaussian_beam_soa(n, mu=(2e-4, 1e-5, -1e-4, -2e-5, 0, 0),
+                              sigma=(2e-4, 2e-5, 3e-4, 1e-5, 1e-5, 1e-3), seed=91)
+    beam = _gpu_beam(soa, 1e8)
+    rng = np.random.default_rng(5)
+    ang = torch.tensor(rng.uniform(-3e-4, 3e-4, (B, 3)), dtype=torch.float32)
+
+    def seg():
+        s = F.build_segment(F.smatch(bpms_active=True))
+        s.V7SMATCH.angle, s.H10SMATCH.angle, s.H12SMATCH.angle = ang[:, 0], ang[:, 1], ang[:, 2]
+        return s
+
+    s1, s2 = seg(), seg()
+    fast = s1.track(beam, particles=False, moments=2)   # collapse
+    slow = s2.track(beam, particles=True, moments=2)    # streaming, per-setting output
+    assert fast.soa is None and slow.soa.shape[0] == B
+    for nm in ("mu_x", "mu_y", "mu_xp", "sigma_x", "sigma_y", "sigma_xp", "sigma_s", "sigma_p",
+               "sigma_xxp", "sigma_yyp", "energy"):
+        np.testing.assert_allclose(getattr(fast, nm).cpu().numpy(), getattr(slow, nm).cpu().numpy(),
+                                   rtol=1e-5, atol=1e-12, err_msg=nm)
+    for a, b in ((s1.BPM1SMATCH, s2.BPM1SMATCH), (s1.BPM6SMATCH, s2.BPM6SMATCH),
+                 (s1.BPM13SMATCH, s2.BPM13SMATCH)):
+        assert a.reading.shape == (2, B)
+        np.testing.assert_allclose(a.reading.cpu().numpy(), b.reading.cpu().numpy(), rtol=1e-5,
+                                   atol=1e-10)
+    # oracle on setting 3
+    d = torch.float64
+    ov = {("V7SMATCH", "angle"): ang[3:4, 0], ("H10SMATCH", "angle"): ang[3:4, 1],
+          ("H12SMATCH", "angle"): ang[3:4, 2]}
+    els = oracle_elements(F.smatch(bpms_active=True), d, (1,), ov)
+    out = O.track(els, O.ParticleBeamO(aos_from_soa(soa, d), torch.tensor([1e8], dtype=d)))
+    np.testing.assert_allclose(fast.sigma_x[3].item(), out.sigma(0).item(), rtol=1e-5)
+    np.testing.assert_allclose(fast.mu_x[3].item(), out.mu(0).item(), rtol=1e-5, atol=1e-10)
+    np.testing.assert_allclose(s1.BPM13SMATCH.reading[:, 3].cpu().numpy(),
+                               els[-1].reading[:, 0].numpy(), rtol=1e-5, atol=1e-10)
