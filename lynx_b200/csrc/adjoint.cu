@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(128) adj_compose_kernel(AdjComposeArgs a) {
   }
   float energy = a.energy_in[b];
   ParamView P{a.params, a.col_offset, a.col_stride, b};
-  walk_program(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+  walk_program<kOpsAll>(a.ops, a.n_ops, a.final_stage, P, energy, sink);
   // final block: outgoing centre, moment cotangents re-centred on it
   float* f = sink.rec + a.L.off_final;
   double G2[6][6], gm1[6];
@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(128) adj_param_kernel(AdjParamArgs a) {
   sink.g = 0.0;
   DF energy(a.energy_in[b], 0.f);
   DualParamView P{a.params, a.col_offset, a.col_stride, b, c};
-  walk_program(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+  walk_program<kOpsAll>(a.ops, a.n_ops, a.final_stage, P, energy, sink);
   float* dst = a.g_params + a.col_offset[c];
   if (a.col_stride[c])
     dst[b] = (float)sink.g;
@@ -706,7 +706,7 @@ __global__ void __launch_bounds__(64) parambeam_bwd_kernel(PBBwdArgs a) {
   sink.gb = 0.f;
   DF energy(a.energy_in[b], 0.f);
   DualParamView P{a.params, a.col_offset, a.col_stride, b, dir < a.n_cols ? dir : -1};
-  walk_program(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+  walk_program<kOpsAll>(a.ops, a.n_ops, a.final_stage, P, energy, sink);
   float g = sink.gb;
   if (a.g_mu) {
 #pragma unroll

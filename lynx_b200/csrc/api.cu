@@ -153,6 +153,7 @@ extern "C" int lynx_program_create(const lynx_op_t* ops, int32_t n_ops,
       return LYNX_E_BADPROGRAM;
     }
     DevOp d{o.opcode, o.col, o.flags, o.aux, -1, -1, -1, -1};
+    p->op_mask |= 1 << o.opcode;
     auto flush = [&]() {
       if (pending) {
         d.flush_stage = S;

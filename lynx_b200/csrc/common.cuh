@@ -55,6 +55,7 @@ struct lynx_program {
   int32_t n_stages = 0, n_cav = 0, n_bpm_slots = 0, n_snap = 0, n_screen = 0;
   int32_t final_stage = -1;  // stage flushed after the last op (-1: none)
   int32_t terminal = 0;
+  int32_t op_mask = 0;       // bit per opcode present (kernel variant selection)
   // record layout (float offsets)
   int32_t off_cav = 0, off_centre = 0, off_screen = 0, rec_floats = 0;
   int32_t final_centre = 0;  // float offset of the outgoing-beam centre
@@ -77,7 +78,9 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
 int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
                    const float* d_energy_in, const float* d_seed_soa, int64_t seed_row_stride,
                    int64_t seed_ld, float* d_records, float* d_maps_out, float* d_energy_out,
-                   void* zero_ptr, size_t zero_bytes, cudaStream_t st);
+                   void* zero_ptr, size_t zero_bytes, cudaStream_t st,
+                   const float* hist_ex = nullptr, const float* hist_ey = nullptr, int hist_W = 0,
+                   int hist_H = 0, void* hist_out = nullptr);
 
 // forward moment collapse (adjoint.cu): one beam shared by B settings, moments / BPM sums
 // only, no active cavity -> the beam is streamed once instead of once per setting

@@ -6,6 +6,7 @@
 #include <cstdlib>
 
 #include "compose_common.cuh"
+#include "track_common.cuh"
 
 namespace lynx {
 
@@ -14,17 +15,25 @@ namespace lynx {
 // latency per column, which is the whole kernel at B = 1), then walk from shared memory.
 constexpr int kComposeTPB = 128;
 
-template <bool STAGED>
+template <bool STAGED, int OPS>
 __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int n_cols, int S) {
   extern __shared__ __align__(16) float cs_smem[];
   // Programmatic dependent launch: let the particle kernel start its prologue (barrier
   // init, TMA requests for its first tiles) now; it waits (griddepcontrol.wait) for this
   // grid to finish before it reads the records or touches the zeroed image.
   asm volatile("griddepcontrol.launch_dependents;");
+  // the last block validates the screen's edge tables and writes the bin-lookup geometry
+  const int hist_blocks = a.hist_out ? 1 : 0;
+  if (hist_blocks && blockIdx.x == gridDim.x - 1) {
+    HistAxis* h = reinterpret_cast<HistAxis*>(a.hist_out);
+    hist_axis_setup(a.hist_ex, a.hist_W, h, threadIdx.x, kComposeTPB);
+    hist_axis_setup(a.hist_ey, a.hist_H, h + 1, threadIdx.x, kComposeTPB);
+    return;
+  }
   // blocks beyond the compose range only zero caller buffers (image / sums)
   const int compose_blocks = (int)((a.B + S - 1) / S);
   if ((int)blockIdx.x >= compose_blocks) {
-    const int zb = blockIdx.x - compose_blocks, nzb = gridDim.x - compose_blocks;
+    const int zb = blockIdx.x - compose_blocks, nzb = gridDim.x - compose_blocks - hist_blocks;
     float4* z = reinterpret_cast<float4*>(a.zero_ptr);
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int64_t i = (int64_t)zb * kComposeTPB + threadIdx.x; i < a.zero_vec4;
@@ -60,10 +69,10 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
   float energy = a.energy_in[b];
   if (STAGED) {
     SmemParamView P{s_vals, S, (int)threadIdx.x};
-    walk_program(s_ops, a.n_ops, a.final_stage, P, energy, sink);
+    walk_program<OPS>(s_ops, a.n_ops, a.final_stage, P, energy, sink);
   } else {
     ParamView P{a.params, a.col_offset, a.col_stride, b};
-    walk_program(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+    walk_program<OPS>(a.ops, a.n_ops, a.final_stage, P, energy, sink);
   }
   float* fc = sink.rec + a.final_centre;
 #pragma unroll
@@ -73,7 +82,7 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
 
 constexpr int kPBThreads = 64;
 
-template <bool STAGED>
+template <bool STAGED, int OPS>
 __global__ void __launch_bounds__(kPBThreads) parambeam_fwd_kernel(ParamBeamArgs a, int n_cols) {
   // staging tile so the [B][7] / [B][7][7] outputs leave the SM as full coalesced rows
   __shared__ float tile[kPBThreads * 49];
@@ -111,10 +120,10 @@ __global__ void __launch_bounds__(kPBThreads) parambeam_fwd_kernel(ParamBeamArgs
     energy = a.energy_in[b];
     if (STAGED) {
       SmemParamView P{s_vals, kPBThreads, (int)threadIdx.x};
-      walk_program(s_ops, a.n_ops, a.final_stage, P, energy, sink);
+      walk_program<OPS>(s_ops, a.n_ops, a.final_stage, P, energy, sink);
     } else {
       ParamView P{a.params, a.col_offset, a.col_stride, b};
-      walk_program(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+      walk_program<OPS>(a.ops, a.n_ops, a.final_stage, P, energy, sink);
     }
     if (a.energy_out) a.energy_out[b] = energy;
   }
@@ -145,7 +154,8 @@ namespace lynx {
 int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
                    const float* d_energy_in, const float* d_seed_soa, int64_t seed_row_stride,
                    int64_t seed_ld, float* d_records, float* d_maps_out, float* d_energy_out,
-                   void* zero_ptr, size_t zero_bytes, cudaStream_t st) {
+                   void* zero_ptr, size_t zero_bytes, cudaStream_t st, const float* hist_ex,
+                   const float* hist_ey, int hist_W, int hist_H, void* hist_out) {
   if (!p || !d_params || !d_energy_in || !d_records || B <= 0) return LYNX_E_BADARG;
   if (zero_bytes && (((uintptr_t)zero_ptr & 15) || (zero_bytes & 15))) return LYNX_E_BADARG;
   ComposeArgs a;
@@ -171,6 +181,11 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   a.energy_out = d_energy_out;
   a.zero_ptr = reinterpret_cast<float*>(zero_ptr);
   a.zero_vec4 = (int64_t)(zero_bytes / 16);
+  a.hist_ex = hist_ex;
+  a.hist_ey = hist_ey;
+  a.hist_W = hist_W;
+  a.hist_H = hist_H;
+  a.hist_out = hist_out;
   // The warp-per-setting variant (compose_warp.cu) is opt-in: on B200 it did not beat
   // the thread-per-setting walk at any measured B (both are bound by single-warp
   // instruction latency / fetch, not by instruction count) -- see DESIGN.md.
@@ -178,7 +193,7 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
     const char* e = getenv("LYNX_K1");
     return e && e[0] == 'w';
   }();
-  if (use_warp) {
+  if (use_warp && !hist_out) {
     const int r = compose_warp_launch(p, a, st);
     if (r <= 0) return r;
   }
@@ -196,12 +211,16 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   unsigned blocks = (unsigned)((B + S - 1) / S);
   if (a.zero_vec4 > 0)
     blocks += (unsigned)std::min<int64_t>(2 * p->sm_count, (a.zero_vec4 + kComposeTPB - 1) / kComposeTPB);
+  if (hist_out) blocks += 1;
   {
     ProfileScope ps(0, st);
-    if (staged)
-      compose_kernel<true><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);
+    const bool light = (p->op_mask & ~kOpsLight) == 0;
+    if (staged && light)
+      compose_kernel<true, kOpsLight><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);
+    else if (staged)
+      compose_kernel<true, kOpsAll><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);
     else
-      compose_kernel<false><<<blocks, kComposeTPB, 0, st>>>(a, n_cols, S);
+      compose_kernel<false, kOpsAll><<<blocks, kComposeTPB, 0, st>>>(a, n_cols, S);
   }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());
@@ -215,7 +234,8 @@ extern "C" int lynx_compose_maps(const lynx_program_t* p, const float* d_params,
                                  float* d_maps_out, float* d_energy_out,
                                  lynx_stream_t stream) {
   return compose_launch(p, d_params, B, d_energy_in, d_seed_soa, seed_row_stride, seed_ld,
-                        d_records, d_maps_out, d_energy_out, nullptr, 0, (cudaStream_t)stream);
+                        d_records, d_maps_out, d_energy_out, nullptr, 0, (cudaStream_t)stream, nullptr,
+                        nullptr, 0, 0, nullptr);
 }
 
 extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params, int64_t B,
@@ -256,10 +276,13 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
   const size_t smem = a.n_ops * sizeof(DevOp) + (size_t)n_cols * kPBThreads * 4;
   {
     ProfileScope ps(2, (cudaStream_t)stream);
-    if (smem <= 32 * 1024)
-      parambeam_fwd_kernel<true><<<blocks, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols);
+    const bool light = (p->op_mask & ~kOpsLight) == 0;
+    if (smem <= 32 * 1024 && light)
+      parambeam_fwd_kernel<true, kOpsLight><<<blocks, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols);
+    else if (smem <= 32 * 1024)
+      parambeam_fwd_kernel<true, kOpsAll><<<blocks, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols);
     else
-      parambeam_fwd_kernel<false><<<blocks, kPBThreads, 0, (cudaStream_t)stream>>>(a, n_cols);
+      parambeam_fwd_kernel<false, kOpsAll><<<blocks, kPBThreads, 0, (cudaStream_t)stream>>>(a, n_cols);
   }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());

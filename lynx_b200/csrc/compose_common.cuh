@@ -90,6 +90,11 @@ struct ComposeArgs {
   float* energy_out;
   float* zero_ptr;     // optional buffer zeroed by the extra blocks of the same launch
   int64_t zero_vec4;   // its size in float4
+  // optional: screen edge tables checked / summarised by the LAST block of the launch
+  const float* hist_ex;
+  const float* hist_ey;
+  int hist_W, hist_H;
+  void* hist_out;      // HistAxis[2]
 };
 
 // ------------------------------------------------------------------ K6

@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(kCWThreads) compose_warp_kernel(CWArgs a) {
 #pragma unroll
         for (int i = 0; i < kCavFloats; ++i) w.cav[lane * kCavFloats + i] = co.sc[i];
       } else {
-        lm_linear_op(R, op, P, rel, e_before);
+        lm_linear_op<kOpsAll>(R, op, P, rel, e_before);
       }
       float* d = w.maps + lane * kCWMap;
 #pragma unroll

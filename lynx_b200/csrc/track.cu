@@ -270,7 +270,7 @@ extern "C" size_t lynx_workspace_bytes(const lynx_program_t* p, int64_t B) {
   if (!p || B <= 0) return 0;
   size_t bytes = (size_t)B * p->rec_floats * sizeof(float);
   bytes = std::max(bytes, fwd_collapse_workspace_bytes(p, B));
-  return (bytes + 255) & ~(size_t)255;
+  return ((bytes + 255) & ~(size_t)255) + 256;  // + HistAxis[2] written by K1
 }
 
 extern "C" int lynx_track_particles_fwd(
@@ -302,6 +302,7 @@ extern "C" int lynx_track_particles_fwd(
                                d_workspace, st);
   }
   float* records = reinterpret_cast<float*>(d_workspace);
+  void* hist_ws = (char*)d_workspace + lynx_workspace_bytes(p, B) - 256;
   // the screen image is zeroed by spare blocks of the K1 launch when its size allows
   const bool has_img = d_screen_img && p->n_screen > 0;
   const size_t img_bytes = has_img ? sizeof(float) * (size_t)W * H * B : 0;
@@ -314,7 +315,8 @@ extern "C" int lynx_track_particles_fwd(
   if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
   int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
                           records, nullptr, d_energy_out, fuse_zero ? d_screen_img : nullptr,
-                          fuse_zero ? img_bytes : 0, st);
+                          fuse_zero ? img_bytes : 0, st, has_img ? d_edges_x : nullptr,
+                          has_img ? d_edges_y : nullptr, W, H, has_img ? hist_ws : nullptr);
   if (rc != LYNX_OK) return rc;
 
   TrackArgs a;
@@ -336,6 +338,7 @@ extern "C" int lynx_track_particles_fwd(
   a.H = H;
   a.ex = d_edges_x;
   a.ey = d_edges_y;
+  a.hist = reinterpret_cast<const HistAxis*>(hist_ws);
   a.mom = d_moment_sums;
   a.B = B;
   static const int dbg = [] { const char* e = getenv("LYNX_DBG"); return e ? atoi(e) : 0; }();

@@ -5,6 +5,12 @@
 
 namespace lynx {
 
+// Per-axis histogram geometry (hist_axis_setup): prepared by K1 for the pipelined kernel,
+// per CTA by the LDG kernel.
+struct HistAxis {
+  float e0, en, inv, margin;  // margin >= 0.5: the table is always consulted
+};
+
 struct TrackArgs {
   const float* in;
   int64_t in_row_stride;  // floats between beam rows of `in` (0: one beam for all settings)
@@ -22,6 +28,7 @@ struct TrackArgs {
   int W, H;
   const float* ex;
   const float* ey;
+  const HistAxis* hist;  // [2] x, y geometry written by K1 (pipelined kernel)
   double* mom;
   int64_t B;
   int dbg;  // experiments only (LYNX_DBG): bit0 = skip the screen atomics
@@ -75,10 +82,6 @@ static __device__ __noinline__ int find_bin_table(float x, const float* __restri
   return i;
 }
 
-// Per-axis histogram geometry prepared once per CTA (hist_axis_setup).
-struct HistAxis {
-  float e0, en, inv, margin;  // margin >= 0.5: the table is always consulted
-};
 
 // Fast path: t = (x - e0) * n/(en - e0) names the bin outright unless its fractional
 // part is within `margin` of an edge; margin covers the fp32 error of t (<= ~3 eps n)

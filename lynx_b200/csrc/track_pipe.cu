@@ -11,19 +11,28 @@
 // registers x occupancy, so the whole 1M-particle beam is requested in the first
 // microsecond and large beams stream at copy speed.  SASS: UBLKCP (bulk copies),
 // SYNCS (mbarrier).  Same arithmetic and outputs as track_fwd_kernel (track.cu).
+//
+// Screen histogram (K4): global RED.ADD into the image runs at ~170 G updates/s for a
+// uniform footprint but collapses with focus (100 G/s at sigma = 100 px, 48 G/s at 20 px,
+// measured, tools/micro/atomic_bench.cu) because L2 serialises updates per line.  With an
+// active screen the ring shrinks to 2 stages and the freed shared memory holds a
+// CTA-private WINDOW of the image (16-bit counters, two per word) placed on the beam from
+// the moments of the CTA's first tile; in-window particles cost one shared-memory atomic,
+// the rest go to global REDs, and the window is flushed with coalesced REDs (32 lanes ->
+// 64 consecutive pixels) at the end / before a counter could overflow.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 
 #include "track_common.cuh"
 
 namespace lynx {
 
 constexpr int kPipeTile = 2048;                    // particles per stage
-constexpr int kPipeStages = 4;
 constexpr int kConsumerWarps = 16;
 constexpr int kConsumers = kConsumerWarps * 32;    // 512 threads x 4 particles = tile
 constexpr int kPipeThreads = kConsumers + 64;      // + producer warp + storer warp
 constexpr int kStageFloats = 6 * kPipeTile;
-constexpr size_t kStageBytes = sizeof(float) * kStageFloats * kPipeStages;  // 196608
 
 // ---- PTX wrappers ---------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -79,13 +88,13 @@ __device__ __forceinline__ void fence_mbar_init() {
 
 struct PipeSmemLayout {
   // byte offsets from the (128-B aligned) dynamic shared memory base
-  uint32_t rec, plan, bpm, edges_x, edges_y, bars, total;
+  uint32_t rec, plan, bpm, bars, win, total;
 };
 
-__host__ __device__ inline PipeSmemLayout pipe_layout(int rec_floats, int n_plan, int n_snap,
-                                                      int W, int H, bool edges_in_smem) {
+__host__ __device__ inline PipeSmemLayout pipe_layout(int stages, int rec_floats, int n_plan,
+                                                      int n_snap, uint32_t win_words) {
   PipeSmemLayout L;
-  uint32_t o = (uint32_t)kStageBytes;
+  uint32_t o = (uint32_t)(sizeof(float) * kStageFloats * stages);
   L.rec = o;
   o += 4u * rec_floats;
   o = (o + 15u) & ~15u;
@@ -93,31 +102,57 @@ __host__ __device__ inline PipeSmemLayout pipe_layout(int rec_floats, int n_plan
   o += 16u * n_plan;
   L.bpm = o;
   o += 16u * n_snap;
-  L.edges_x = o;
-  if (edges_in_smem) o += 4u * (W + 1);
-  L.edges_y = o;
-  if (edges_in_smem) o += 4u * (H + 1);
   o = (o + 7u) & ~7u;
   L.bars = o;
-  o += 8u * 3 * kPipeStages;
+  o += 8u * 3 * stages;
+  o = (o + 15u) & ~15u;
+  L.win = o;
+  o += 4u * win_words;
   L.total = o;
   return L;
 }
 
-template <int MOM, bool HAS_OUT>
-__global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a, int edges_in_smem) {
+// CTA-private image window (bin coordinates): [x0, x0+w) x [y0, y0+h), w even, two 16-bit
+// counters per word.
+struct HistWindow {
+  int x0, y0, w, h;
+};
+
+__device__ __forceinline__ void consumers_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory"); }
+
+// Flush the window into the image with coalesced REDs and clear it (consumer threads).
+__device__ __forceinline__ void window_flush(uint32_t* __restrict__ win, const HistWindow& hw,
+                                             float* __restrict__ img_b, int W, int H, int cid) {
+  const int wpr = hw.w >> 1;  // words per window row
+  const int n = wpr * hw.h;
+  for (int i = cid; i < n; i += kConsumers) {
+    const uint32_t v = win[i];
+    if (v) {
+      win[i] = 0u;
+      const int r = i / wpr, c = i - r * wpr;
+      float* p = img_b + (int64_t)(H - 1 - (hw.y0 + r)) * W + hw.x0 + 2 * c;
+      const uint32_t lo = v & 0xffffu, hi = v >> 16;
+      if (lo) atomicAdd(p, (float)lo);
+      if (hi) atomicAdd(p + 1, (float)hi);
+    }
+  }
+}
+
+template <int MOM, bool HAS_OUT, int STAGES>
+__global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a, uint32_t win_words) {
   extern __shared__ __align__(128) unsigned char psm[];
-  const PipeSmemLayout L =
-      pipe_layout(a.rec_floats, a.n_plan, a.n_snap, a.W, a.H, edges_in_smem != 0);
+  const PipeSmemLayout L = pipe_layout(STAGES, a.rec_floats, a.n_plan, a.n_snap, win_words);
   float* stages = reinterpret_cast<float*>(psm);
   float* rec = reinterpret_cast<float*>(psm + L.rec);
   PlanItem* plan = reinterpret_cast<PlanItem*>(psm + L.plan);
   double* s_bpm = reinterpret_cast<double*>(psm + L.bpm);
   uint64_t* full = reinterpret_cast<uint64_t*>(psm + L.bars);
-  uint64_t* empty = full + kPipeStages;
-  uint64_t* done = empty + kPipeStages;
+  uint64_t* empty = full + STAGES;
+  uint64_t* done = empty + STAGES;
+  uint32_t* win = reinterpret_cast<uint32_t*>(psm + L.win);
   __shared__ double s_red[kConsumerWarps][28];
-  __shared__ HistAxis s_hx, s_hy;
+  __shared__ float s_wstat[kConsumerWarps][5];
+  __shared__ HistWindow s_win;
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
@@ -126,7 +161,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   const float* in_b = a.in + b * a.in_row_stride;
 
   if (tid == 0) {
-    for (int s = 0; s < kPipeStages; ++s) {
+    for (int s = 0; s < STAGES; ++s) {
       mbar_init(full + s, 1);
       mbar_init(empty + s, HAS_OUT ? 1 : kConsumerWarps);
       mbar_init(done + s, kConsumerWarps);
@@ -136,7 +171,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   __syncthreads();
 
   auto issue_tile = [&](int it, int64_t t) {
-    const int s = it % kPipeStages;
+    const int s = it % STAGES;
     const int64_t p0 = t * kPipeTile;
     const uint32_t cnt = (uint32_t)min((int64_t)kPipeTile, a.N - p0);
     const uint32_t bytes = ((cnt + 3u) & ~3u) * 4u;
@@ -150,19 +185,17 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   // ---- prologue: request this CTA's first tiles before anything else touches memory
   if (tid == 0) {
     int it = 0;
-    for (int64_t t = blockIdx.x; t < n_tiles && it < kPipeStages; t += gridDim.x, ++it)
+    for (int64_t t = blockIdx.x; t < n_tiles && it < STAGES; t += gridDim.x, ++it)
       issue_tile(it, t);
   }
 
-  // ---- everyone: plan and histogram geometry (independent of K1) ...
+  // ---- everyone: plan, cleared window (independent of K1) ...
   for (int i = tid; i < a.n_plan; i += kPipeThreads) plan[i] = a.plan[i];
   for (int i = tid; i < a.n_snap * 2; i += kPipeThreads) s_bpm[i] = 0.0;
-  if (a.img) {  // uniform over the CTA
-    hist_axis_setup(a.ex, a.W, &s_hx, tid, kPipeThreads);
-    hist_axis_setup(a.ey, a.H, &s_hy, tid, kPipeThreads);
-  }
-  // ... then wait for the K1 grid (records written, image zeroed) -- a no-op unless this
-  // kernel was launched with programmatic stream serialization
+  for (uint32_t i = tid; i < win_words; i += kPipeThreads) win[i] = 0u;
+  if (tid == 0) s_win = HistWindow{0, 0, 0, 0};
+  // ... then wait for the K1 grid (records + histogram geometry written, image zeroed) --
+  // a no-op unless this kernel was launched with programmatic stream serialization
   asm volatile("griddepcontrol.wait;" ::: "memory");
   {
     const float* src = a.records + b * a.rec_floats;
@@ -183,9 +216,9 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
     if (lane == 0) {
       int it = 0;
       for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
-        if (it < kPipeStages) continue;  // issued in the prologue
-        const uint32_t u = (uint32_t)(it / kPipeStages);
-        mbar_wait(empty + (it % kPipeStages), (u - 1) & 1);
+        if (it < STAGES) continue;  // issued in the prologue
+        const uint32_t u = (uint32_t)(it / STAGES);
+        mbar_wait(empty + (it % STAGES), (u - 1) & 1);
         issue_tile(it, t);
       }
     }
@@ -195,8 +228,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
       float* out_b = a.out + b * 6 * a.ld_out;
       int it = 0, prev_s = -1;
       for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
-        const int s = it % kPipeStages;
-        const uint32_t u = (uint32_t)(it / kPipeStages);
+        const int s = it % STAGES;
+        const uint32_t u = (uint32_t)(it / STAGES);
         mbar_wait(done + s, u & 1);
         fence_proxy_async();
         const int64_t p0 = t * kPipeTile;
@@ -221,12 +254,21 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
     const int cid = tid - 64;
     const float* ex = a.ex;
     const float* ey = a.ey;
-    const HistAxis hx = s_hx, hy = s_hy;
+    HistAxis hx{0.f, 0.f, 0.f, 1.f}, hy{0.f, 0.f, 0.f, 1.f};
     float* img_b = a.img ? a.img + b * (int64_t)a.W * a.H : nullptr;
+    if (img_b) {
+      hx = a.hist[0];
+      hy = a.hist[1];
+    }
+    constexpr bool kWin = (STAGES == 2);  // window code only in the screen variants
+    const bool use_win = kWin && img_b && win_words > 0;
+    HistWindow hw{0, 0, 0, 0};
+    bool win_set = false;
+    int since_flush = 0;
     int it = 0;
     for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
-      const int s = it % kPipeStages;
-      const uint32_t u = (uint32_t)(it / kPipeStages);
+      const int s = it % STAGES;
+      const uint32_t u = (uint32_t)(it / STAGES);
       const int64_t p0 = t * kPipeTile;
       n_mine += min((int64_t)kPipeTile, a.N - p0);
       float* st = stages + s * kStageFloats + cid * 4;
@@ -286,21 +328,87 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
         } else if (img_b) {  // P_SCREEN, screen.py:126-141 + 195-211
           const float mx = rec[p.a], my = rec[p.a + 1];
           const bool yfix = (p.c & LYNX_F_SCREEN_Y_FIX) != 0;
-          int ix[4], iy[4];
+          int pk[4];  // ix | iy << 16, or -1 (dead lane / outside the screen)
+          float c = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, syy = 0.f;
 #pragma unroll
           for (int l = 0; l < 4; ++l) {
             const float x = v[0][l] - mx;
             const float y = yfix ? v[2][l] - my : v[2][l];
-            ix[l] = find_bin(x, ex, a.W, hx);
-            iy[l] = find_bin(y, ey, a.H, hy);
+            const int ix = find_bin(x, ex, a.W, hx);
+            const int iy = find_bin(y, ey, a.H, hy);
+            const bool ok = live[l] && ix >= 0 && iy >= 0;
+            pk[l] = ok ? (ix | (iy << 16)) : -1;
+            if (kWin && !win_set && ok) {
+              const float dx = (float)(ix - (a.W >> 1)), dy = (float)(iy - (a.H >> 1));
+              c += 1.f;
+              sx += dx;
+              sy += dy;
+              sxx = fmaf(dx, dx, sxx);
+              syy = fmaf(dy, dy, syy);
+            }
           }
+          if constexpr (kWin) {
+            if (use_win && !win_set) {
+              // place the window on the beam: mean +- k sigma of this CTA's first tile
+              c = warp_sum(c);
+              sx = warp_sum(sx);
+              sy = warp_sum(sy);
+              sxx = warp_sum(sxx);
+              syy = warp_sum(syy);
+              if (lane == 0) {
+                float* d = s_wstat[warp - 2];
+                d[0] = c; d[1] = sx; d[2] = sy; d[3] = sxx; d[4] = syy;
+              }
+              consumers_sync();
+              if (cid == 0) {
+                float tc = 0.f, tx = 0.f, ty = 0.f, txx = 0.f, tyy = 0.f;
+                for (int w = 0; w < kConsumerWarps; ++w) {
+                  tc += s_wstat[w][0]; tx += s_wstat[w][1]; ty += s_wstat[w][2];
+                  txx += s_wstat[w][3]; tyy += s_wstat[w][4];
+                }
+                HistWindow nw{0, 0, 0, 0};
+                const float cap = (float)(2u * win_words);
+                if (tc >= 32.f) {
+                  const float mxb = tx / tc, myb = ty / tc;
+                  const float sgx = fmaxf(sqrtf(fmaxf(txx / tc - mxb * mxb, 0.f)), 1.f);
+                  const float sgy = fmaxf(sqrtf(fmaxf(tyy / tc - myb * myb, 0.f)), 1.f);
+                  const float k = fminf(sqrtf(cap / (4.f * sgx * sgy)), 4.5f);
+                  int w2 = min(2 * ((int)ceilf(k * sgx) + 1), a.W & ~1);
+                  int h2 = min(2 * ((int)ceilf(k * sgy) + 1), a.H);
+                  if ((float)w2 * (float)h2 > cap) h2 = (int)(cap / (float)w2);
+                  if (h2 > 0 && w2 > 0) {
+                    nw.w = w2;
+                    nw.h = h2;
+                    nw.x0 = min(max((int)lrintf(mxb) + (a.W >> 1) - (w2 >> 1), 0), a.W - w2);
+                    nw.y0 = min(max((int)lrintf(myb) + (a.H >> 1) - (h2 >> 1), 0), a.H - h2);
+                  }
+                }
+                s_win = nw;
+              }
+              consumers_sync();
+              hw = s_win;
+              win_set = true;
+            }
+            if (use_win && since_flush + kPipeTile > 65535) {  // a 16-bit counter could overflow
+              consumers_sync();
+              window_flush(win, hw, img_b, a.W, a.H, cid);
+              consumers_sync();
+              since_flush = 0;
+            }
+            since_flush += kPipeTile;
+          }
+          const int wpr = hw.w >> 1;
 #pragma unroll
           for (int l = 0; l < 4; ++l)
-            if (live[l] && ix[l] >= 0 && iy[l] >= 0) {
+            if (pk[l] >= 0) {
+              const int ix = pk[l] & 0xffff, iy = pk[l] >> 16;
+              const unsigned dx = (unsigned)(ix - hw.x0), dy = (unsigned)(iy - hw.y0);
               if (a.dbg & 1) {
-                if (ix[l] + iy[l] == -12345) img_b[0] = 1.f;
+                if (ix + iy == -12345) img_b[0] = 1.f;
+              } else if (kWin && dx < (unsigned)hw.w && dy < (unsigned)hw.h) {
+                atomicAdd(win + dy * wpr + (dx >> 1), 1u << ((dx & 1u) * 16u));
               } else {
-                atomicAdd(img_b + (int64_t)(a.H - 1 - iy[l]) * a.W + ix[l], 1.0f);
+                atomicAdd(img_b + (int64_t)(a.H - 1 - iy) * a.W + ix, 1.0f);
               }
             }
         }
@@ -325,8 +433,13 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
         }
       }
     }
+    if constexpr (kWin) {
+      if (use_win && win_set) {
+        consumers_sync();
+        window_flush(win, hw, img_b, a.W, a.H, cid);
+      }
+    }
   }
-
   // ---- CTA epilogue
   if (MOM != 0) {
     mom_epilogue<MOM, kConsumerWarps>(acc, s_red, warp >= 2 ? warp - 2 : -1, lane, tid == 64,
@@ -350,10 +463,10 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   }
 }
 
-template <int MOM, bool HAS_OUT>
-static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, int edges_in_smem,
+template <int MOM, bool HAS_OUT, int STAGES>
+static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, uint32_t win_words,
                        cudaStream_t st) {
-  auto k = track_pipe_kernel<MOM, HAS_OUT>;
+  auto k = track_pipe_kernel<MOM, HAS_OUT, STAGES>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096) !=
@@ -374,7 +487,7 @@ static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, int edges_in_
   cudaError_t err;
   {
     ProfileScope ps(1, st);
-    err = cudaLaunchKernelEx(&cfg, k, a, edges_in_smem);
+    err = cudaLaunchKernelEx(&cfg, k, a, win_words);
   }
   count_launch();
   return err == cudaSuccess ? LYNX_OK : LYNX_E_LAUNCH;
@@ -384,25 +497,40 @@ static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, int edges_in_
 // caller then uses the LDG kernel).
 int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_count,
                       cudaStream_t st) {
-  const size_t cap = 227 * 1024 - 4096;  // static shared memory (s_red) takes the rest
-  int edges_in_smem = 0;  // the table is only consulted near bin edges: it stays in L1/L2
-  PipeSmemLayout L = pipe_layout(a.rec_floats, a.n_plan, a.n_snap, a.W, a.H, edges_in_smem != 0);
-  if (L.total > cap && edges_in_smem) {
-    edges_in_smem = 0;
-    L = pipe_layout(a.rec_floats, a.n_plan, a.n_snap, a.W, a.H, false);
-  }
+  const uint32_t cap = 227 * 1024 - 4096 - 1024;  // static shared memory takes the rest
+  const bool hist = a.img != nullptr && !has_out;
+  // The shared-memory window is OPT-IN (LYNX_WINDOW=1): measured on B200 it loses to plain
+  // global REDs unless the beam is focused below sigma ~ 10 px -- random scatter into shared
+  // memory costs ~7 cycles/lane/SM (bank conflicts) against 1.29 for REDG, so it only pays
+  // where L2 line contention pushes global REDs below ~40 G updates/s.
+  static const bool no_win = [] { const char* e = getenv("LYNX_WINDOW"); return !(e && e[0] == '1'); }();
+  const int stages = (hist && !no_win) ? 2 : 4;
+  PipeSmemLayout L = pipe_layout(stages, a.rec_floats, a.n_plan, a.n_snap, 0);
   if (L.total > cap) return 1;
+  uint32_t win_words = 0;
+  if (hist && !no_win) {
+    win_words = ((cap - L.total) / 4u) & ~3u;
+    if (win_words < 1024) win_words = 0;
+    L = pipe_layout(stages, a.rec_floats, a.n_plan, a.n_snap, win_words);
+  }
   const int64_t n_tiles = (a.N + kPipeTile - 1) / kPipeTile;
   int64_t per_b = (sm_count + a.B - 1) / a.B;
   if (per_b < 1) per_b = 1;
   dim3 grid((unsigned)std::min<int64_t>(n_tiles, per_b), (unsigned)a.B);
+  if (stages == 2) {
+    switch (moment_mode) {
+      case 0: return launch_pipe<0, false, 2>(a, grid, L.total, win_words, st);
+      case 1: return launch_pipe<1, false, 2>(a, grid, L.total, win_words, st);
+      default: return launch_pipe<2, false, 2>(a, grid, L.total, win_words, st);
+    }
+  }
   switch (moment_mode * 2 + (has_out ? 1 : 0)) {
-    case 0: return launch_pipe<0, false>(a, grid, L.total, edges_in_smem, st);
-    case 1: return launch_pipe<0, true>(a, grid, L.total, edges_in_smem, st);
-    case 2: return launch_pipe<1, false>(a, grid, L.total, edges_in_smem, st);
-    case 3: return launch_pipe<1, true>(a, grid, L.total, edges_in_smem, st);
-    case 4: return launch_pipe<2, false>(a, grid, L.total, edges_in_smem, st);
-    default: return launch_pipe<2, true>(a, grid, L.total, edges_in_smem, st);
+    case 0: return launch_pipe<0, false, 4>(a, grid, L.total, 0, st);
+    case 1: return launch_pipe<0, true, 4>(a, grid, L.total, 0, st);
+    case 2: return launch_pipe<1, false, 4>(a, grid, L.total, 0, st);
+    case 3: return launch_pipe<1, true, 4>(a, grid, L.total, 0, st);
+    case 4: return launch_pipe<2, false, 4>(a, grid, L.total, 0, st);
+    default: return launch_pipe<2, true, 4>(a, grid, L.total, 0, st);
   }
 }
 

@@ -37,7 +37,17 @@ struct SmemParamView {
 
 // Left-multiplies M by the map of one linear (skippable) op.  Returns false for ops that
 // are not part of a merged run (active cavity, BPM, screen).
-template <typename T, typename PV>
+// Opcode sets a kernel is compiled for.  The walk is bound by instruction fetch at small B
+// (one thread executes ~1.3k instructions once; the full switch is 64 KB of SASS), so
+// lattices made only of the cheap elements get a kernel without the dipole / cavity /
+// solenoid / dense-custom code.
+__host__ __device__ constexpr int op_bit(int opcode) { return 1 << opcode; }
+constexpr int kOpsAll = (1 << LYNX_OP__COUNT) - 1;
+constexpr int kOpsLight = op_bit(LYNX_OP_MARKER) | op_bit(LYNX_OP_DRIFT) | op_bit(LYNX_OP_QUAD) |
+                          op_bit(LYNX_OP_HCOR) | op_bit(LYNX_OP_VCOR) | op_bit(LYNX_OP_UNDULATOR) |
+                          op_bit(LYNX_OP_BPM) | op_bit(LYNX_OP_SCREEN);
+
+template <int OPS, typename T, typename PV>
 __device__ __forceinline__ bool lm_linear_op(MapT<T>& M, const DevOp& op, const PV& P,
                                              const RelT<T>& rel, T energy) {
   const int c = op.col;
@@ -62,33 +72,38 @@ __device__ __forceinline__ bool lm_linear_op(MapT<T>& M, const DevOp& op, const 
       M.m[3][6] += P(c + 1);  // vertical_corrector.py:63
     } return true;
     case LYNX_OP_DIPOLE:
-      lm_dipole(M, P(c), P(c + 1), P(c + 2), P(c + 3), P(c + 4), P(c + 5), P(c + 6), P(c + 7),
-                (op.flags & LYNX_F_RBEND) != 0, rel);
+      if constexpr ((OPS & op_bit(LYNX_OP_DIPOLE)) != 0)
+        lm_dipole(M, P(c), P(c + 1), P(c + 2), P(c + 3), P(c + 4), P(c + 5), P(c + 6), P(c + 7),
+                  (op.flags & LYNX_F_RBEND) != 0, rel);
       return true;
     case LYNX_OP_CAVITY: {
       if (op.flags & LYNX_F_ACTIVE) return false;
       // skippable cavity (voltage == 0 everywhere): linear map merged into the run
-      MapT<T> C;
-      CavityOutT<T> co;
-      cavity_setting<T>(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
-      lm_custom(M, [&](int r, int k) { return C.m[r][k]; });
+      if constexpr ((OPS & op_bit(LYNX_OP_CAVITY)) != 0) {
+        MapT<T> C;
+        CavityOutT<T> co;
+        cavity_setting<T>(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
+        lm_custom(M, [&](int r, int k) { return C.m[r][k]; });
+      }
     } return true;
     case LYNX_OP_SOLENOID:
-      lm_solenoid(M, P(c), P(c + 1), P(c + 2), P(c + 3), rel);
+      if constexpr ((OPS & op_bit(LYNX_OP_SOLENOID)) != 0)
+        lm_solenoid(M, P(c), P(c + 1), P(c + 2), P(c + 3), rel);
       return true;
     case LYNX_OP_UNDULATOR: {
       T L = P(c);
       lm_drift(M, L, L * rel.igamma2_drift);  // undulator.py:52-58 (quirk B4)
     } return true;
     case LYNX_OP_CUSTOM:
-      lm_custom(M, [&](int r, int k) { return P(c + r * 7 + k); });
+      if constexpr ((OPS & op_bit(LYNX_OP_CUSTOM)) != 0)
+        lm_custom(M, [&](int r, int k) { return P(c + r * 7 + k); });
       return true;
     default:
       return false;
   }
 }
 
-template <typename T, typename Sink, typename PV>
+template <int OPS, typename T, typename Sink, typename PV>
 __device__ __forceinline__ void walk_program(const DevOp* __restrict__ ops, int n_ops,
                                              int final_stage, const PV& P,
                                              T& energy, Sink& sink) {
@@ -101,15 +116,17 @@ __device__ __forceinline__ void walk_program(const DevOp* __restrict__ ops, int 
       sink.stage(M, op.flush_stage);
       map_identity(M);
     }
-    if (lm_linear_op(M, op, P, rel, energy)) continue;
+    if (lm_linear_op<OPS>(M, op, P, rel, energy)) continue;
     const int c = op.col;
     if (op.opcode == LYNX_OP_CAVITY) {
-      MapT<T> C;
-      CavityOutT<T> co;
-      cavity_setting<T>(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
-      sink.cavity(C, co, op.self_stage, op.cav_idx);
-      energy += co.dE;  // cavity.py:130
-      rel = make_rel(energy);
+      if constexpr ((OPS & op_bit(LYNX_OP_CAVITY)) != 0) {
+        MapT<T> C;
+        CavityOutT<T> co;
+        cavity_setting<T>(P(c), P(c + 1), P(c + 2), P(c + 3), energy, C, co);
+        sink.cavity(C, co, op.self_stage, op.cav_idx);
+        energy += co.dE;  // cavity.py:130
+        rel = make_rel(energy);
+      }
     } else if (op.opcode == LYNX_OP_BPM) {
       sink.bpm(M, op.aux, op.snap_idx);
     } else if (op.opcode == LYNX_OP_SCREEN) {
