@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--settings", type=int, default=4096)
     ap.add_argument("--scale-particles", type=int, default=32_000_000)
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="multi-GPU screen exchange: fused peer-memory kernel or dense NCCL")
     return ap.parse_args()
 
 
@@ -223,6 +225,18 @@ class ParticleWorkload:
             L.ptr(self.out), self.ld, None, L.ptr(self.img), self.W, self.H, L.ptr(self.ex),
             L.ptr(self.ey), L.ptr(self.mom), self.moments, self.e_in.data_ptr(),
             self.e_out.data_ptr(), self.ws.data_ptr(), L.current_stream()))
+
+    def sharded_step(self, exchange):
+        """N > 1: this rank's particle shard into the symmetric slot, then the ONE exchange
+        step of the path -- the fused bounding-box all-reduce over NVLink peers."""
+        L = self.L
+        img_ptr, bbox_ptr = exchange.slot_pointers()
+        L.check(self.lib.lynx_track_particles_fwd_bbox(
+            self.prog.handle, self.params.data_ptr(), 1, self.soa.data_ptr(), 1, self.ld, self.n,
+            None, self.ld, None, img_ptr, self.W, self.H, L.ptr(self.ex), L.ptr(self.ey), None, 0,
+            self.e_in.data_ptr(), self.e_out.data_ptr(), self.ws.data_ptr(), bbox_ptr,
+            L.current_stream()))
+        exchange.reduce()
 
     def algorithmic_bytes(self):
         b = 24 * self.n
@@ -406,8 +420,20 @@ def run_ours(args, rank, world, local_rank):
 
     wl = ParticleWorkload(args.particles, device, seed=1002 + rank, screen=True)
     post = None
+    step_fn = wl.step
+    exchange_kind = None
     if world > 1:  # the one exchange step of the path: the screen image (north star)
-        post = lambda: dist.all_reduce(wl.img)  # noqa: E731
+        from lynx_b200.sharding import ScreenExchange
+
+        if args.exchange == "nccl":
+            post = lambda: dist.all_reduce(wl.img)  # noqa: E731
+            exchange_kind = "dense NCCL all-reduce of the 20 MB image"
+        else:
+            exch = ScreenExchange(1, wl.W, wl.H, device)
+            step_fn = lambda: wl.sharded_step(exch)  # noqa: E731
+            exchange_kind = ("fused bounding-box all-reduce over NVLink peer memory "
+                             "(lynx_screen_allreduce)" if exch.fused
+                             else "dense NCCL all-reduce (symmetric memory unavailable)")
 
     # ---- headline: device-resident steps, per-step events, max over ranks
     if world > 1:
@@ -415,7 +441,7 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.synchronize()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     lib.lynx_launch_count_reset()
-    ms = timed_steps(wl.step, args.steps, args.warmup, flush, post)
+    ms = timed_steps(step_fn, args.steps, args.warmup, flush, post)
     launches = lib.lynx_launch_count() - 0
     launches_timed = launches * args.steps // (args.steps + args.warmup)
     torch.cuda.synchronize()
@@ -471,7 +497,7 @@ def run_ours(args, rank, world, local_rank):
                    "particles_per_gpu": args.particles, "step": "Segment.track + Screen.reading",
                    "l2": "256 MB flush write before every timed step (outside the events)",
                    "parallelism": f"particle-sharded x{world}" + (
-                       ", image all-reduced (NCCL)" if world > 1 else "")},
+                       f", {exchange_kind}" if world > 1 else "")},
         "clocks": clocks, "gpu_launches": int(launches_timed),
         "e2e": {"value": e2e_val, "unit": "particle-element updates/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -146,6 +146,39 @@ int lynx_track_particles_fwd(const lynx_program_t*, const float* d_params, int64
                              const float* d_energy_in, float* d_energy_out,
                              void* d_workspace, lynx_stream_t stream);
 
+/* Same, additionally recording the bounding box of the screen bins that were touched:
+ * d_screen_bbox[4] (int32, ZEROED by the call) = max(W - ix), max(ix + 1), max(H - iy),
+ * max(iy + 1) over the histogrammed particles (all 0 = none).  Used by the multi-GPU
+ * exchange below; pass the box that sits 64 bytes in front of the image of a symmetric
+ * buffer slot (lynx_screen_symm_image) to have box + image zeroed in one fused range.   */
+int lynx_track_particles_fwd_bbox(const lynx_program_t*, const float* d_params, int64_t B,
+                                  const float* d_in_soa, int64_t in_row_stride, int64_t ld_in,
+                                  int64_t N, float* d_out_soa, int64_t ld_out,
+                                  double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H,
+                                  const float* d_edges_x, const float* d_edges_y,
+                                  double* d_moment_sums, int32_t moment_mode,
+                                  const float* d_energy_in, float* d_energy_out,
+                                  void* d_workspace, int32_t* d_screen_bbox,
+                                  lynx_stream_t stream);
+
+/* Multi-GPU exchange step of the particle-sharded path (one process per GPU; the reference
+ * has no distributed code): all-reduce (SUM) of the screen image over
+ * NVLink peer memory, restricted to the union bounding box of the bins any rank touched.
+ *   - every rank allocates lynx_screen_symm_bytes(B, W, H) bytes of PEER-MAPPED symmetric
+ *     memory, zero-initialised once (e.g. torch symmetric memory; cudaMalloc + IPC handles),
+ *     and exchanges the base pointers: peer_bases[r] = rank r's buffer as mapped here
+ *   - step k tracks into slot = k & 1: image = lynx_screen_symm_image(base, slot, ..),
+ *     bbox = (int32_t*)image - 16, via lynx_track_particles_fwd_bbox
+ *   - lynx_screen_allreduce(.., slot, epoch = k + 1, ..) then runs ONE kernel: cross-GPU
+ *     barrier on epoch flags, union box, and d_out_img [B][H][W] = sum over ranks inside
+ *     the box (coalesced peer loads), zeros outside.  Exact (integer counts < 2^24).
+ *   epoch must increase by one per call on every rank; W % 4 == 0.                          */
+size_t lynx_screen_symm_bytes(int64_t B, int32_t W, int32_t H);
+float* lynx_screen_symm_image(void* d_symm_base, int32_t slot, int64_t B, int32_t W, int32_t H);
+int lynx_screen_allreduce(void* const* peer_bases /*host array [world]*/, int32_t world,
+                          int32_t rank, int32_t slot, uint32_t epoch, int64_t B, int32_t W,
+                          int32_t H, float* d_out_img, lynx_stream_t stream);
+
 /* K3 -- adjoint of lynx_track_particles_fwd w.r.t. every parameter column and
  * (optionally) the incoming particles.  The reference has no custom_vjp; this is the
  * vjp of segment.py:340-356 that the array framework would derive op by op.

@@ -279,6 +279,19 @@ extern "C" int lynx_track_particles_fwd(
     double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H, const float* d_edges_x,
     const float* d_edges_y, double* d_moment_sums, int32_t moment_mode,
     const float* d_energy_in, float* d_energy_out, void* d_workspace, lynx_stream_t stream) {
+  return lynx_track_particles_fwd_bbox(p, d_params, B, d_in_soa, in_row_stride, ld_in, N, d_out_soa,
+                                       ld_out, d_bpm_sums, d_screen_img, W, H, d_edges_x, d_edges_y,
+                                       d_moment_sums, moment_mode, d_energy_in, d_energy_out,
+                                       d_workspace, nullptr, stream);
+}
+
+extern "C" int lynx_track_particles_fwd_bbox(
+    const lynx_program_t* p, const float* d_params, int64_t B, const float* d_in_soa,
+    int64_t in_row_stride, int64_t ld_in, int64_t N, float* d_out_soa, int64_t ld_out,
+    double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H, const float* d_edges_x,
+    const float* d_edges_y, double* d_moment_sums, int32_t moment_mode,
+    const float* d_energy_in, float* d_energy_out, void* d_workspace, int32_t* d_screen_bbox,
+    lynx_stream_t stream) {
   if (!p || !d_params || !d_in_soa || !d_energy_in || !d_workspace || B <= 0 || N <= 0)
     return LYNX_E_BADARG;
   if ((ld_in & 3) || ld_in < N || ((uintptr_t)d_in_soa & 15)) return LYNX_E_BADARG;
@@ -307,6 +320,11 @@ extern "C" int lynx_track_particles_fwd(
   const bool has_img = d_screen_img && p->n_screen > 0;
   const size_t img_bytes = has_img ? sizeof(float) * (size_t)W * H * B : 0;
   const bool fuse_zero = has_img && !(img_bytes & 15) && !((uintptr_t)d_screen_img & 15);
+  // the bounding box sits right in front of the image in the symmetric exchange buffer
+  // (exchange.cu): one fused zeroing range covers both
+  const bool bbox_adjacent = d_screen_bbox && has_img && fuse_zero &&
+                             (char*)d_screen_bbox + 64 == (char*)d_screen_img;
+  if (d_screen_bbox && !bbox_adjacent) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_bbox, 0, 16, st));
   // accumulators are cleared BEFORE K1 so that K1 -> K2 stay adjacent in the stream
   // (programmatic dependent launch overlaps K2's prologue with K1)
   if (p->n_bpm_slots > 0)
@@ -314,8 +332,9 @@ extern "C" int lynx_track_particles_fwd(
   if (has_img && !fuse_zero) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
   if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
   int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
-                          records, nullptr, d_energy_out, fuse_zero ? d_screen_img : nullptr,
-                          fuse_zero ? img_bytes : 0, st, has_img ? d_edges_x : nullptr,
+                          records, nullptr, d_energy_out,
+                          fuse_zero ? (bbox_adjacent ? (void*)d_screen_bbox : (void*)d_screen_img) : nullptr,
+                          fuse_zero ? img_bytes + (bbox_adjacent ? 64 : 0) : 0, st, has_img ? d_edges_x : nullptr,
                           has_img ? d_edges_y : nullptr, W, H, has_img ? hist_ws : nullptr);
   if (rc != LYNX_OK) return rc;
 
@@ -339,6 +358,7 @@ extern "C" int lynx_track_particles_fwd(
   a.ex = d_edges_x;
   a.ey = d_edges_y;
   a.hist = reinterpret_cast<const HistAxis*>(hist_ws);
+  a.bbox = has_img ? d_screen_bbox : nullptr;
   a.mom = d_moment_sums;
   a.B = B;
   static const int dbg = [] { const char* e = getenv("LYNX_DBG"); return e ? atoi(e) : 0; }();
@@ -353,6 +373,7 @@ extern "C" int lynx_track_particles_fwd(
     const int r = launch_track_pipe(a, moment_mode, d_out_soa != nullptr, p->sm_count, st);
     if (r <= 0) return r;
   }
+  if (a.bbox) return LYNX_E_BADPROGRAM;  // bounding box is a feature of the pipelined kernel
   const int64_t n_tiles = (N + kTile - 1) / kTile;
   int64_t per_b = (2LL * p->sm_count + B - 1) / B;
   if (per_b < 1) per_b = 1;

@@ -29,6 +29,7 @@ struct TrackArgs {
   const float* ex;
   const float* ey;
   const HistAxis* hist;  // [2] x, y geometry written by K1 (pipelined kernel)
+  int* bbox;             // nullable: [4] max(W - ix), max(ix + 1), max(H - iy), max(iy + 1)
   double* mom;
   int64_t B;
   int dbg;  // experiments only (LYNX_DBG): bit0 = skip the screen atomics

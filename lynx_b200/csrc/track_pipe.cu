@@ -265,6 +265,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
     HistWindow hw{0, 0, 0, 0};
     bool win_set = false;
     int since_flush = 0;
+    int bb0 = 0, bb1 = 0, bb2 = 0, bb3 = 0;  // bounding box of the touched bins (exchange.cu)
     int it = 0;
     for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
       const int s = it % STAGES;
@@ -338,6 +339,12 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
             const int iy = find_bin(y, ey, a.H, hy);
             const bool ok = live[l] && ix >= 0 && iy >= 0;
             pk[l] = ok ? (ix | (iy << 16)) : -1;
+            if (ok) {
+              bb0 = max(bb0, a.W - ix);
+              bb1 = max(bb1, ix + 1);
+              bb2 = max(bb2, a.H - iy);
+              bb3 = max(bb3, iy + 1);
+            }
             if (kWin && !win_set && ok) {
               const float dx = (float)(ix - (a.W >> 1)), dy = (float)(iy - (a.H >> 1));
               c += 1.f;
@@ -437,6 +444,21 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
       if (use_win && win_set) {
         consumers_sync();
         window_flush(win, hw, img_b, a.W, a.H, cid);
+      }
+    }
+    if (a.bbox && img_b) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        bb0 = max(bb0, __shfl_xor_sync(0xffffffffu, bb0, o));
+        bb1 = max(bb1, __shfl_xor_sync(0xffffffffu, bb1, o));
+        bb2 = max(bb2, __shfl_xor_sync(0xffffffffu, bb2, o));
+        bb3 = max(bb3, __shfl_xor_sync(0xffffffffu, bb3, o));
+      }
+      if (lane == 0 && bb1 > 0) {
+        atomicMax(a.bbox + 0, bb0);
+        atomicMax(a.bbox + 1, bb1);
+        atomicMax(a.bbox + 2, bb2);
+        atomicMax(a.bbox + 3, bb3);
       }
     }
   }

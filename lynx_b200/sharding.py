@@ -101,3 +101,63 @@ def track_sharded(segment, soa_full: torch.Tensor, n: int, energy, *, world: int
     for e in bpm_elems:  # bpm.py:54 with the global particle count
         e.reading = (e._bpm_sums / n).to(torch.float32).T.reshape(e.reading.shape)
     return out, img, sums
+
+
+class ScreenExchange:
+    """The particle-sharded path's exchange step for the screen image over NVLink peer
+    memory (csrc/exchange.cu): every rank histograms into a slot of a peer-mapped symmetric
+    buffer, then ONE kernel per rank does the cross-GPU barrier and sums the union bounding
+    box of the touched bins over all peers.  Falls back to a dense NCCL all-reduce when
+    symmetric memory cannot be set up (``self.fused`` is False)."""
+
+    def __init__(self, B: int, W: int, H: int, device, group=None):
+        import ctypes as C
+
+        from . import _lib as L
+
+        self.B, self.W, self.H, self.device = B, W, H, device
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.step = 0
+        self.lib = L.lib()
+        self._L = L
+        self.fused = False
+        self.out = torch.zeros((B, H, W), dtype=torch.float32, device=device)
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            nbytes = self.lib.lynx_screen_symm_bytes(B, W, H)
+            self.buf = symm_mem.empty(nbytes // 4, dtype=torch.float32, device=device)
+            self.buf.zero_()
+            torch.cuda.synchronize(device)
+            self.hdl = symm_mem.rendezvous(self.buf, self.group)
+            ptrs = list(self.hdl.buffer_ptrs)
+            self._peers = (C.c_void_p * self.world)(*ptrs)
+            self.hdl.barrier()
+            torch.cuda.synchronize(device)
+            self.fused = W % 4 == 0 and self.world <= 16
+        except Exception as e:  # no P2P / symmetric memory: dense NCCL all-reduce
+            self.why = repr(e)
+            self.buf = torch.zeros((2, B, H, W), dtype=torch.float32, device=device)
+
+    def slot_pointers(self):
+        """(image pointer, bbox pointer) of the slot the NEXT step tracks into."""
+        slot = self.step & 1
+        if not self.fused:
+            return self.buf[slot].data_ptr(), None
+        img = self.lib.lynx_screen_symm_image(self.buf.data_ptr(), slot, self.B, self.W, self.H)
+        return img, img - 64
+
+    def reduce(self) -> torch.Tensor:
+        """All ranks' images of the current slot -> ``self.out`` (summed); advances the step."""
+        slot = self.step & 1
+        self.step += 1
+        if not self.fused:
+            self.out.copy_(self.buf[slot])
+            dist.all_reduce(self.out, group=self.group)
+            return self.out
+        self._L.check(self.lib.lynx_screen_allreduce(
+            self._peers, self.world, self.rank, slot, self.step, self.B, self.W, self.H,
+            self.out.data_ptr(), self._L.current_stream()), "lynx_screen_allreduce")
+        return self.out
