@@ -214,6 +214,14 @@ int lynx_parambeam_bwd(const lynx_program_t*, const float* d_params, int64_t B,
                        const float* d_g_bpm, float* d_g_params, float* d_g_mu_in,
                        float* d_g_cov_in, lynx_stream_t stream);
 
+/* K7 -- Screen.reading for a ParameterBeam (screen.py:157-194): bivariate-normal pdf of
+ * (x, y) from mu [B][7], cov [B][7][7] on the grid of pixel left edges
+ * xs = arange(left, right, hstep) [W], ys = arange(bottom, top, vstep) [H] (screen.py:181-191,
+ * taken from the host as data), indexed [b][ix][iy] and flipped along x as the reference
+ * does (:192-194, quirk B8): img[b][i][j] = pdf(xs[W-1-i], ys[j]).  img is [B][W][H].     */
+int lynx_screen_pdf(const float* d_mu, const float* d_cov, int64_t B, const float* d_xs,
+                    const float* d_ys, int32_t W, int32_t H, float* d_img, lynx_stream_t stream);
+
 /* Layout converters between the reference's AoS (..,N,7) ParticleBeam.particles
  * (particle_beam.py:24-45) and the SoA-6 device layout. */
 int lynx_aos7_to_soa6(const float* d_aos /*[R][N][7]*/, int64_t R, int64_t N,

@@ -67,6 +67,7 @@ SIGNATURES = {
     "lynx_parambeam_bwd": (
         C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
     ),
+    "lynx_screen_pdf": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i32, _i32, _vp, _vp]),
     "lynx_aos7_to_soa6": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _vp]),
     "lynx_soa6_to_aos7": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp]),
     "lynx_launch_count": (_i64, []),

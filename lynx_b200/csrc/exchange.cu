@@ -156,3 +156,69 @@ extern "C" int lynx_screen_allreduce(void* const* peer_bases, int32_t world, int
   LYNX_CUDA_OK(cudaGetLastError());
   return LYNX_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// K7: Screen.reading for a ParameterBeam (screen.py:157-194): bivariate normal pdf of
+// (x, y) evaluated on the grid of pixel LEFT edges (arange, :181-191), meshgrid "ij" so the
+// array is indexed [b][ix][iy], flipped along x (:194): img[b][i][j] = pdf(xs[W-1-i], ys[j]).
+// One float4 of consecutive iy per thread; HBM-write-bound (4 W H bytes per setting).
+namespace lynx {
+constexpr int kPdfTPB = 256;
+
+__global__ void __launch_bounds__(kPdfTPB) screen_pdf_kernel(const float* __restrict__ mu,
+                                                              const float* __restrict__ cov,
+                                                              const float* __restrict__ xs,
+                                                              const float* __restrict__ ys, int W,
+                                                              int H, float* __restrict__ img) {
+  const int64_t b = blockIdx.y;
+  const float mx = __ldg(mu + b * 7 + 0), my = __ldg(mu + b * 7 + 2);
+  const double sxx = __ldg(cov + b * 49 + 0), sxy = __ldg(cov + b * 49 + 2),
+               syy = __ldg(cov + b * 49 + 16);
+  const double det = sxx * syy - sxy * sxy;
+  const float qa = (float)(syy / det), qb = (float)(-sxy / det), qc = (float)(sxx / det);
+  const float lognorm = (float)(-1.8378770664093453 - 0.5 * log(det));  // -log(2 pi) - log|S|/2
+  float* out = img + b * (int64_t)W * H;
+  const int h4 = (H + 3) >> 2;
+  const int64_t n = (int64_t)W * h4;
+  for (int64_t t = (int64_t)blockIdx.x * kPdfTPB + threadIdx.x; t < n;
+       t += (int64_t)gridDim.x * kPdfTPB) {
+    const int i = (int)(t / h4), j0 = (int)(t - (int64_t)i * h4) << 2;
+    const float dx = __ldg(xs + (W - 1 - i)) - mx;
+    const float ax = qa * dx * dx, bx = 2.f * qb * dx;
+    float v[4];
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+      const int j = min(j0 + l, H - 1);
+      const float dy = __ldg(ys + j) - my;
+      const float q = fmaf(qc * dy, dy, fmaf(bx, dy, ax));
+      v[l] = expf(fmaf(-0.5f, q, lognorm));
+    }
+    float* p = out + (int64_t)i * H + j0;
+    if (j0 + 3 < H && !(((uintptr_t)p) & 15)) {
+      __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3]));
+    } else {
+#pragma unroll
+      for (int l = 0; l < 4; ++l)
+        if (j0 + l < H) p[l] = v[l];
+    }
+  }
+}
+}  // namespace lynx
+
+extern "C" int lynx_screen_pdf(const float* d_mu, const float* d_cov, int64_t B,
+                               const float* d_xs, const float* d_ys, int32_t W, int32_t H,
+                               float* d_img, lynx_stream_t stream) {
+  if (!d_mu || !d_cov || !d_xs || !d_ys || !d_img || B <= 0 || B > 65535 || W <= 0 || H <= 0)
+    return LYNX_E_BADARG;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int64_t n = (int64_t)W * ((H + 3) >> 2);
+  const int64_t per_b = std::max<int64_t>(1, (8LL * sms + B - 1) / B);
+  const unsigned gx = (unsigned)std::min<int64_t>((n + kPdfTPB - 1) / kPdfTPB, per_b);
+  screen_pdf_kernel<<<dim3(gx, (unsigned)B), kPdfTPB, 0, (cudaStream_t)stream>>>(d_mu, d_cov, d_xs,
+                                                                                 d_ys, W, H, d_img);
+  count_launch();
+  LYNX_CUDA_OK(cudaGetLastError());
+  return LYNX_OK;
+}

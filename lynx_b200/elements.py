@@ -421,7 +421,31 @@ class Screen(Element):
         shape = (*self.misalignment.shape[:-1], int(eff[1]), int(eff[0]))
         if self._read is None or self._read is Beam.empty:
             return torch.zeros(shape)
+        beam = self.get_read_beam()
+        if isinstance(beam, ParameterBeam):
+            self.cached_reading = self._parameter_beam_image(beam)
+            return self.cached_reading
         raise RuntimeError("screen reading is produced by Segment.track; none cached")
+
+    def _parameter_beam_image(self, beam: ParameterBeam) -> torch.Tensor:
+        """screen.py:157-194 on the device (K7): (..., W_eff, H_eff) as the reference
+        produces it (meshgrid "ij", flipped along x -- quirk B8)."""
+        mu, cov = beam._mu.contiguous(), beam._cov.contiguous()
+        device = mu.device
+        ext = self.extent
+        hstep = (self.pixel_size[0] * self.binning).cpu()
+        vstep = (self.pixel_size[1] * self.binning).cpu()
+        xs = torch.arange(ext[0], ext[1], hstep).to(device)  # :187-190 as data
+        ys = torch.arange(ext[2], ext[3], vstep).to(device)
+        bshape = tuple(mu.shape[:-1])
+        B = 1
+        for n in bshape:
+            B *= n
+        img = torch.empty((*bshape, xs.numel(), ys.numel()), dtype=torch.float32, device=device)
+        L.check(L.lib().lynx_screen_pdf(mu.data_ptr(), cov.data_ptr(), B, xs.data_ptr(),
+                                        ys.data_ptr(), xs.numel(), ys.numel(), img.data_ptr(),
+                                        L.current_stream()), "lynx_screen_pdf")
+        return img
 
     def broadcast(self, shape):
         new = super().broadcast(shape)

@@ -39,6 +39,7 @@ from .lattice import (  # noqa: F401
     element_map,
     is_skippable,
     screen_bin_edges,
+    screen_reading_parameter_beam,
     screen_reading_particles,
     segment_map,
     track,

@@ -327,6 +327,28 @@ def screen_reading_particles(xs, ys, edges_x, edges_y):
     return torch.stack(imgs)
 
 
+def screen_reading_parameter_beam(mu, cov, resolution, pixel_size, binning=1):
+    """screen.py:157-194: bivariate-normal pdf on the grid of pixel left edges, meshgrid
+    "ij", flipped along x (quirk B8) -> (B, W_eff, H_eff)."""
+    from torch.distributions import MultivariateNormal
+
+    dtype = mu.dtype
+    res = torch.tensor(resolution, dtype=torch.float32)
+    px = torch.tensor(pixel_size, dtype=torch.float32)
+    left, right = -res[0] * px[0] / 2, res[0] * px[0] / 2
+    bottom, top = -res[1] * px[1] / 2, res[1] * px[1] / 2
+    hstep, vstep = px[0] * binning, px[1] * binning
+    x, y = torch.meshgrid(torch.arange(left, right, hstep), torch.arange(bottom, top, vstep),
+                          indexing="ij")
+    pos = torch.dstack((x, y)).to(dtype)
+    imgs = []
+    for m, c in zip(mu, cov):
+        tm = torch.stack([m[0], m[2]])
+        tc = torch.stack([torch.stack([c[0, 0], c[0, 2]]), torch.stack([c[2, 0], c[2, 2]])])
+        imgs.append(MultivariateNormal(loc=tm, covariance_matrix=tc).log_prob(pos).exp())
+    return torch.flip(torch.stack(imgs), dims=[1])
+
+
 def track(elements, beam, per_entry=True, cavity_v0_as_drift=False, screen_quirk_b1=True):
     """segment.py:340-356: merge runs of skippable elements, step through the rest."""
     run = []

@@ -433,3 +433,34 @@ def test_forward_moment_collapse_matches_streaming():
     np.testing.assert_allclose(fast.mu_x[3].item(), out.mu(0).item(), rtol=1e-5, atol=1e-10)
     np.testing.assert_allclose(s1.BPM13SMATCH.reading[:, 3].cpu().numpy(),
                                els[-1].reading[:, 0].numpy(), rtol=1e-5, atol=1e-10)
+
+
+def test_parameter_beam_screen_reading():
+    """K7: Screen.reading for a ParameterBeam (screen.py:157-194) vs the oracle's
+    MultivariateNormal restatement: same (B, W, H) layout incl. the x flip (quirk B8);
+    values within 2e-5 of the peak (fp32 exp of an fp32 quadratic form)."""
+    B = 5
+    scr_spec = {"resolution": (120, 90), "pixel_size": (2e-5, 3e-5), "binning": 1}
+    k1, ang = F.random_settings(B, seed=17, k1_range=8.0, steer=2e-3)
+    seg = F.build_segment(F.ares_ea(screen_active=True, screen=scr_spec))
+    for i, nm in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")):
+        getattr(seg, nm).k1 = torch.from_numpy(k1[:, i])
+    seg.AREAMCVM1.angle = torch.from_numpy(ang[:, 0])
+    seg.AREAMCHM1.angle = torch.from_numpy(ang[:, 1])
+    t = lambda v: torch.tensor([v])  # noqa: E731
+    pb = lx.ParameterBeam.from_parameters(
+        mu_x=t(F.ASTRA_MU[0]), mu_y=t(F.ASTRA_MU[2]), sigma_x=t(F.ASTRA_SIGMA[0]),
+        sigma_xp=t(F.ASTRA_SIGMA[1]), sigma_y=t(F.ASTRA_SIGMA[2]), sigma_yp=t(F.ASTRA_SIGMA[3]),
+        energy=t(F.ASTRA_ENERGY))
+    assert seg.track(pb) is lx.Beam.empty
+    img = seg.AREABSCR1.reading
+    assert img.shape == (B, 120, 90)
+    rb = seg.AREABSCR1.get_read_beam()
+    want = O.screen_reading_parameter_beam(rb._mu.cpu().double(), rb._cov.cpu().double(),
+                                           scr_spec["resolution"], scr_spec["pixel_size"])
+    got = img.cpu().double()
+    peak = want.amax(dim=(1, 2), keepdim=True)
+    assert (peak > 0).all()
+    assert ((got - want).abs() / peak).max().item() < 2e-5
+    # x is flipped as in the reference: the brightest column sits where the oracle has it
+    assert torch.equal(got.sum(dim=2).argmax(dim=1), want.sum(dim=2).argmax(dim=1))
