@@ -170,14 +170,18 @@ int lynx_track_particles_fwd_bbox(const lynx_program_t*, const float* d_params, 
  *   - step k tracks into slot = k & 1: image = lynx_screen_symm_image(base, slot, ..),
  *     bbox = (int32_t*)image - 16, via lynx_track_particles_fwd_bbox
  *   - lynx_screen_allreduce(.., slot, epoch = k + 1, ..) then runs ONE kernel: cross-GPU
- *     barrier on epoch flags, union box, and d_out_img [B][H][W] = sum over ranks inside
- *     the box (coalesced peer loads), zeros outside.  Exact (integer counts < 2^24).
+ *     barrier on epoch flags (each rank pushes its box with its signal), union box, and
+ *     d_out_img [B][H][W] = sum over ranks inside the box (coalesced peer loads), zeros
+ *     outside.  Exact (integer counts < 2^24).  d_out_img is PERSISTENT: pass the same
+ *     buffer, zero-initialised once, with the same zero-initialised d_state [8] on every
+ *     call -- only the union of this and the previous call's rectangle is rewritten.
  *   epoch must increase by one per call on every rank; W % 4 == 0.                          */
 size_t lynx_screen_symm_bytes(int64_t B, int32_t W, int32_t H);
 float* lynx_screen_symm_image(void* d_symm_base, int32_t slot, int64_t B, int32_t W, int32_t H);
 int lynx_screen_allreduce(void* const* peer_bases /*host array [world]*/, int32_t world,
                           int32_t rank, int32_t slot, uint32_t epoch, int64_t B, int32_t W,
-                          int32_t H, float* d_out_img, lynx_stream_t stream);
+                          int32_t H, float* d_out_img, int32_t* d_state /*[8]*/,
+                          lynx_stream_t stream);
 
 /* K3 -- adjoint of lynx_track_particles_fwd w.r.t. every parameter column and
  * (optionally) the incoming particles.  The reference has no custom_vjp; this is the

@@ -56,7 +56,7 @@ SIGNATURES = {
     "lynx_screen_symm_bytes": (_sz, [_i64, _i32, _i32]),
     "lynx_screen_symm_image": (_vp, [_vp, _i32, _i64, _i32, _i32]),
     "lynx_screen_allreduce": (
-        C.c_int, [C.POINTER(_vp), _i32, _i32, _i32, C.c_uint32, _i64, _i32, _i32, _vp, _vp]
+        C.c_int, [C.POINTER(_vp), _i32, _i32, _i32, C.c_uint32, _i64, _i32, _i32, _vp, _vp, _vp]
     ),
     "lynx_track_particles_bwd": (
         C.c_int,

@@ -7,17 +7,20 @@
 // peer-mapped SYMMETRIC buffer (NVLink / NVSwitch P2P), K2 records the bounding box of the
 // bins it touched, and ONE kernel per rank
 //   1. signals / waits on per-rank epoch flags in the peers' buffers (cross-GPU barrier),
-//   2. forms the union bounding box from every peer's box,
-//   3. writes the caller's image: inside the box the sum of all peers' pixels read over
-//      NVLink (coalesced peer loads), outside it zeros (no remote traffic).
+//   2. forms the union bounding box from the boxes the peers pushed with their signal,
+//   3. updates the caller's persistent image: inside the box the sum of all peers' pixels
+//      read over NVLink (coalesced peer loads); the part of the PREVIOUS call's rectangle
+//      outside it is cleared; everything else is already zero (no 20 MB rewrite).
 // Counts are integers < 2^24 in fp32, so the sum is exact and order-independent.
 // Buffers are double-buffered by the caller (slot = step & 1), which makes a trailing
 // barrier unnecessary: a rank can only start zeroing slot s again after every peer has
 // passed the barrier of the step in between, i.e. finished reading slot s.
 //
 // Layout of one rank's symmetric buffer (lynx_screen_symm_bytes):
-//   [0, 256)                      uint32 flags[64]: flags[p] = last epoch signalled by rank p
-//   slot s at 256 + s * slot_bytes: int32 bbox[16] (v0 = max(W - ix), v1 = max(ix + 1),
+//   [0, 64)                       uint32 flags[16]: flags[p] = last epoch signalled by rank p
+//   [64, 576)                     int4 inbox[2][16]: rank p's bounding box of the step with
+//                                 epoch parity 0 / 1, PUSHED by rank p before its signal
+//   slot s at 1024 + s * slot_bytes: int32 bbox[16] (v0 = max(W - ix), v1 = max(ix + 1),
 //                                   v2 = max(H - iy), v3 = max(iy + 1); 0 = empty), then
 //                                   float image[B][H][W] (reference layout, row 0 = max y)
 #include <algorithm>
@@ -27,7 +30,8 @@
 namespace lynx {
 
 constexpr int kMaxWorld = 16;
-constexpr size_t kSymmHeader = 256;
+constexpr size_t kSymmHeader = 1024;  // flags[16] u32 @0, inbox int4[2][16] @64
+constexpr size_t kInboxOff = 64;
 constexpr size_t kBboxBytes = 64;
 
 struct ExchangeArgs {
@@ -37,7 +41,8 @@ struct ExchangeArgs {
   int64_t B;
   int W, H;
   size_t slot_bytes;
-  float* out;  // [B][H][W] local
+  float* out;    // [B][H][W] local, persistent: zero outside the last written rectangle
+  int* state;    // [2][4] local: rectangle (r0, r1, c0, c1) written at even / odd epochs
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -54,8 +59,16 @@ constexpr int kExTPB = 256;
 __global__ void __launch_bounds__(kExTPB) screen_allreduce_kernel(ExchangeArgs a) {
   __shared__ int s_box[4];
   const int tid = threadIdx.x;
-  // ---- 1. cross-GPU barrier on epoch flags (this launch is stream-ordered after K2)
+  const int par = a.epoch & 1;
+  // launched with programmatic stream serialization: resident early, waits for K2 here
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  // ---- 1. push my bounding box into every peer's inbox, then signal my epoch (cross-GPU
+  //         barrier; the release store orders the box before the flag)
   if (blockIdx.x == 0 && tid < a.world) {
+    const int4 box = __ldcg(reinterpret_cast<const int4*>(a.peers[a.rank] + kSymmHeader +
+                                                          a.slot * a.slot_bytes));
+    int4* inbox = reinterpret_cast<int4*>(a.peers[tid] + kInboxOff) + par * kMaxWorld + a.rank;
+    *inbox = box;
     __threadfence_system();
     st_release_sys(reinterpret_cast<uint32_t*>(a.peers[tid]) + a.rank, a.epoch);
   }
@@ -66,30 +79,44 @@ __global__ void __launch_bounds__(kExTPB) screen_allreduce_kernel(ExchangeArgs a
   }
   if (tid < 4) s_box[tid] = 0;
   __syncthreads();
-  // ---- 2. union bounding box
+  // ---- 2. union bounding box from the (local) inbox
   if (tid < a.world * 4) {
-    const int p = tid >> 2, k = tid & 3;
-    const int* bb = reinterpret_cast<const int*>(a.peers[p] + kSymmHeader + a.slot * a.slot_bytes);
-    atomicMax(&s_box[k], __ldcv(bb + k));
+    const int* in = reinterpret_cast<const int*>(a.peers[a.rank] + kInboxOff) +
+                    (par * kMaxWorld + (tid >> 2)) * 4 + (tid & 3);
+    atomicMax(&s_box[tid & 3], __ldcv(in));
   }
   __syncthreads();
   const bool empty = s_box[1] == 0 || s_box[3] == 0;
-  const int x0 = a.W - s_box[0], x1 = s_box[1];  // [x0, x1)
-  const int y0 = a.H - s_box[2], y1 = s_box[3];  // bins [y0, y1) -> image rows H-1-y
-  const int r0 = a.H - y1, r1 = a.H - y0;        // image rows [r0, r1)
-  const int c0 = x0 & ~3, c1 = min((x1 + 3) & ~3, a.W);
+  // bins [x0, x1) x [y0, y1) -> image rows [H - y1, H - y0), columns rounded to float4
+  const int r0 = empty ? 0 : a.H - s_box[3], r1 = empty ? 0 : s_box[2];
+  const int c0 = empty ? 0 : (a.W - s_box[0]) & ~3, c1 = empty ? 0 : min((s_box[1] + 3) & ~3, a.W);
+  // rectangle written by the previous call (it must be cleared where the new one is smaller)
+  const int* prev = a.state + (par ^ 1) * 4;
+  const int p_r0 = prev[0], p_r1 = prev[1], p_c0 = prev[2], p_c1 = prev[3];
+  const bool p_empty = p_r1 <= p_r0 || p_c1 <= p_c0;
+  const int ra = (empty ? p_r0 : (p_empty ? r0 : min(r0, p_r0)));
+  const int rb = (empty ? p_r1 : (p_empty ? r1 : max(r1, p_r1)));
+  const int ca = (empty ? p_c0 : (p_empty ? c0 : min(c0, p_c0)));
+  const int cb = (empty ? p_c1 : (p_empty ? c1 : max(c1, p_c1)));
+  if (blockIdx.x == 0 && tid == 0) {
+    int* cur = a.state + par * 4;
+    cur[0] = r0; cur[1] = r1; cur[2] = c0; cur[3] = c1;
+  }
+  if (rb <= ra || cb <= ca) return;
 
-  // ---- 3. write the caller's image: sums inside the box, zeros outside
-  const int64_t n4 = a.B * (int64_t)a.H * a.W / 4;  // W % 4 == 0 checked by the launcher
+  // ---- 3. inside the new box: sum of all peers' pixels (coalesced peer loads over NVLink);
+  //         rest of the union rectangle: zeros.  Everything else is already zero.
   const size_t img_off = kSymmHeader + a.slot * a.slot_bytes + kBboxBytes;
-  float4* out4 = reinterpret_cast<float4*>(a.out);
-  const int w4 = a.W >> 2;
-  for (int64_t i = (int64_t)blockIdx.x * kExTPB + tid; i < n4; i += (int64_t)gridDim.x * kExTPB) {
-    const int64_t row_all = i / w4;
-    const int c = (int)(i - row_all * w4) << 2;
-    const int r = (int)(row_all % a.H);
+  const int w4 = (cb - ca) >> 2, nr = rb - ra;
+  const int64_t n = a.B * (int64_t)nr * w4;
+  for (int64_t t = (int64_t)blockIdx.x * kExTPB + tid; t < n; t += (int64_t)gridDim.x * kExTPB) {
+    const int64_t rr = t / w4;
+    const int c = ca + ((int)(t - rr * w4) << 2);
+    const int64_t bq = rr / nr;
+    const int r = ra + (int)(rr - bq * nr);
+    const int64_t i = ((bq * a.H + r) * (int64_t)a.W + c) >> 2;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (!empty && r >= r0 && r < r1 && c >= c0 && c < c1) {
+    if (r >= r0 && r < r1 && c >= c0 && c < c1) {
       for (int p = 0; p < a.world; ++p) {
         const float4 v = __ldcv(reinterpret_cast<const float4*>(a.peers[p] + img_off) + i);
         s.x += v.x;
@@ -98,7 +125,7 @@ __global__ void __launch_bounds__(kExTPB) screen_allreduce_kernel(ExchangeArgs a
         s.w += v.w;
       }
     }
-    __stcs(out4 + i, s);
+    reinterpret_cast<float4*>(a.out)[i] = s;
   }
 }
 
@@ -127,10 +154,10 @@ extern "C" float* lynx_screen_symm_image(void* d_symm_base, int32_t slot, int64_
 
 extern "C" int lynx_screen_allreduce(void* const* peer_bases, int32_t world, int32_t rank,
                                      int32_t slot, uint32_t epoch, int64_t B, int32_t W, int32_t H,
-                                     float* d_out_img, lynx_stream_t stream) {
+                                     float* d_out_img, int32_t* d_state, lynx_stream_t stream) {
   if (!peer_bases || world < 1 || world > kMaxWorld || rank < 0 || rank >= world || slot < 0 ||
       slot > 1 || epoch == 0 || B <= 0 || W <= 0 || H <= 0 || (W & 3) || !d_out_img ||
-      ((uintptr_t)d_out_img & 15))
+      !d_state || ((uintptr_t)d_out_img & 15))
     return LYNX_E_BADARG;
   ExchangeArgs a{};
   for (int p = 0; p < world; ++p) {
@@ -146,15 +173,24 @@ extern "C" int lynx_screen_allreduce(void* const* peer_bases, int32_t world, int
   a.H = H;
   a.slot_bytes = slot_bytes_of(B, W, H);
   a.out = d_out_img;
+  a.state = d_state;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int64_t n4 = B * (int64_t)H * W / 4;
-  const unsigned blocks = (unsigned)std::min<int64_t>((n4 + kExTPB - 1) / kExTPB, 8LL * sms);
-  screen_allreduce_kernel<<<blocks, kExTPB, 0, (cudaStream_t)stream>>>(a);
+  // the rectangle is only known on the device: a fixed grid strides over it
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)(2 * sms));
+  cfg.blockDim = dim3(kExTPB);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const cudaError_t err = cudaLaunchKernelEx(&cfg, screen_allreduce_kernel, a);
   count_launch();
-  LYNX_CUDA_OK(cudaGetLastError());
-  return LYNX_OK;
+  return err == cudaSuccess ? LYNX_OK : LYNX_E_LAUNCH;
 }
 
 // ---------------------------------------------------------------------------------------

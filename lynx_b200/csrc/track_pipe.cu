@@ -189,6 +189,9 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
       issue_tile(it, t);
   }
 
+  // let a programmatically-serialized follower (the multi-GPU exchange kernel) become
+  // resident now; it waits (griddepcontrol.wait) for this grid to finish
+  asm volatile("griddepcontrol.launch_dependents;");
   // ---- everyone: plan, cleared window (independent of K1) ...
   for (int i = tid; i < a.n_plan; i += kPipeThreads) plan[i] = a.plan[i];
   for (int i = tid; i < a.n_snap * 2; i += kPipeThreads) s_bpm[i] = 0.0;

@@ -124,6 +124,7 @@ class ScreenExchange:
         self._L = L
         self.fused = False
         self.out = torch.zeros((B, H, W), dtype=torch.float32, device=device)
+        self.state = torch.zeros(8, dtype=torch.int32, device=device)
         try:
             import torch.distributed._symmetric_memory as symm_mem
 
@@ -159,5 +160,6 @@ class ScreenExchange:
             return self.out
         self._L.check(self.lib.lynx_screen_allreduce(
             self._peers, self.world, self.rank, slot, self.step, self.B, self.W, self.H,
-            self.out.data_ptr(), self._L.current_stream()), "lynx_screen_allreduce")
+            self.out.data_ptr(), self.state.data_ptr(), self._L.current_stream()),
+            "lynx_screen_allreduce")
         return self.out
