@@ -253,6 +253,14 @@ typedef struct lynx_host_ctx lynx_host_ctx_t;
 int lynx_host_ctx_create(int device, lynx_host_ctx_t** out);
 void lynx_host_ctx_destroy(lynx_host_ctx_t*);
 
+/* Context options.  LYNX_HOST_OPT_PERSISTENT_IMAGE = 1: the caller passes the SAME host
+ * screen_img buffer on every lynx_host_track_particles call of this context; the library
+ * then moves only the bounding rectangle of the lit pixels over PCIe (clearing the
+ * previous call's rectangle on the host first) instead of the full 4 W H bytes -- the
+ * host image is bit-identical to the dense transfer.  A new buffer is zero-filled once. */
+enum { LYNX_HOST_OPT_PERSISTENT_IMAGE = 1 };
+int lynx_host_ctx_set_option(lynx_host_ctx_t*, int32_t option, int32_t value);
+
 int lynx_host_track_particles(lynx_host_ctx_t*, const lynx_program_t*, const float* params,
                               int64_t n_param_floats, int64_t B, const float* in_soa,
                               int64_t Bb, int64_t N, const float* energy_in,

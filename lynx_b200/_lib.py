@@ -76,6 +76,7 @@ SIGNATURES = {
     "lynx_profile_last_ms": (C.c_float, [C.c_int]),
     "lynx_host_ctx_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
     "lynx_host_ctx_destroy": (None, [_vp]),
+    "lynx_host_ctx_set_option": (C.c_int, [_vp, _i32, _i32]),
     "lynx_host_track_particles": (
         C.c_int,
         [_vp, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp,

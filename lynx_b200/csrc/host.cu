@@ -15,7 +15,14 @@ struct lynx_host_ctx {
     size_t cap = 0;
   };
   Buf params, in, out, energy_in, energy_out, bpm, img, ex, ey, mom, ws, mu_in, cov_in, mu_out,
-      cov_out, bpm_f;
+      cov_out, bpm_f, bbox;
+  // LYNX_HOST_OPT_PERSISTENT_IMAGE: the caller passes the SAME zero-initialised host image on
+  // every call; only the bounding rectangle of the lit pixels crosses PCIe (the previous
+  // call's rectangle is cleared on the host first)
+  int persistent_image = 0;
+  const float* last_img = nullptr;
+  int last_rect[4] = {0, 0, 0, 0};  // r0, r1, c0, c1
+  int32_t* h_bbox = nullptr;        // pinned
   bool grow(Buf& b, size_t bytes) {
     if (bytes <= b.cap) return true;
     if (b.p) cudaFree(b.p);
@@ -56,10 +63,21 @@ extern "C" void lynx_host_ctx_destroy(lynx_host_ctx_t* c) {
   lynx_host_ctx::Buf* all[] = {&c->params, &c->in,  &c->out,   &c->energy_in, &c->energy_out,
                                &c->bpm,    &c->img, &c->ex,    &c->ey,        &c->mom,
                                &c->ws,     &c->mu_in, &c->cov_in, &c->mu_out, &c->cov_out,
-                               &c->bpm_f};
+                               &c->bpm_f,  &c->bbox};
+  if (c->h_bbox) cudaFreeHost(c->h_bbox);
   for (auto* b : all) c->release(*b);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
+}
+
+extern "C" int lynx_host_ctx_set_option(lynx_host_ctx_t* c, int32_t option, int32_t value) {
+  if (!c) return LYNX_E_BADARG;
+  if (option == LYNX_HOST_OPT_PERSISTENT_IMAGE) {
+    c->persistent_image = value != 0;
+    c->last_img = nullptr;
+    return LYNX_OK;
+  }
+  return LYNX_E_BADARG;
 }
 
 #define H2D(buf, src, bytes)                                                          \
@@ -107,13 +125,20 @@ extern "C" int lynx_host_track_particles(
   if (moment_mode && !c->grow(c->mom, sizeof(double) * 28 * B)) return LYNX_E_NOMEM;
   if (!c->grow(c->ws, lynx_workspace_bytes(p, B))) return LYNX_E_NOMEM;
 
-  int rc = lynx_track_particles_fwd(
+  const bool sparse_img = has_screen && c->persistent_image;
+  if (sparse_img) {
+    if (!c->grow(c->bbox, 64)) return LYNX_E_NOMEM;
+    if (!c->h_bbox && cudaMallocHost((void**)&c->h_bbox, 64) != cudaSuccess) return LYNX_E_NOMEM;
+  }
+  int rc = lynx_track_particles_fwd_bbox(
       p, (const float*)c->params.p, B, (const float*)c->in.p, (Bb == B) ? 1 : 0,
       ld, N, out_soa ? (float*)c->out.p : nullptr, ld, (double*)c->bpm.p,
       has_screen ? (float*)c->img.p : nullptr, W, H, (const float*)c->ex.p,
       (const float*)c->ey.p, moment_mode ? (double*)c->mom.p : nullptr, moment_mode,
-      (const float*)c->energy_in.p, (float*)c->energy_out.p, c->ws.p, (lynx_stream_t)st);
+      (const float*)c->energy_in.p, (float*)c->energy_out.p, c->ws.p,
+      sparse_img ? (int32_t*)c->bbox.p : nullptr, (lynx_stream_t)st);
   if (rc != LYNX_OK) return rc;
+  if (sparse_img) LYNX_CUDA_OK(cudaMemcpyAsync(c->h_bbox, c->bbox.p, 16, cudaMemcpyDeviceToHost, st));
 
   if (out_soa) {
     if (ld == N) {
@@ -124,10 +149,39 @@ extern "C" int lynx_host_track_particles(
     }
   }
   if (n_bpm > 0 && bpm_sums) D2H(bpm_sums, c->bpm, sizeof(double) * 2 * n_bpm * B);
-  if (has_screen) D2H(screen_img, c->img, sizeof(float) * (size_t)W * H * B);
+  if (has_screen && !sparse_img) D2H(screen_img, c->img, sizeof(float) * (size_t)W * H * B);
   if (moment_mode && moment_sums) D2H(moment_sums, c->mom, sizeof(double) * 28 * B);
   if (energy_out) D2H(energy_out, c->energy_out, sizeof(float) * B);
   LYNX_CUDA_OK(cudaStreamSynchronize(st));
+  if (sparse_img) {
+    // clear what the previous call lit (same persistent buffer), then fetch only the
+    // rectangle of lit pixels: rows [H - v3, v2), columns [W - v0, v1)
+    if (c->last_img == screen_img) {
+      const int* q = c->last_rect;
+      for (int64_t b = 0; b < B; ++b)
+        for (int r = q[0]; r < q[1]; ++r)
+          memset(screen_img + ((size_t)b * H + r) * W + q[2], 0, sizeof(float) * (q[3] - q[2]));
+    } else {
+      memset(screen_img, 0, sizeof(float) * (size_t)W * H * B);  // first use of this buffer
+    }
+    const int32_t* v = c->h_bbox;
+    int rect[4] = {0, 0, 0, 0};
+    if (v[1] > 0 && v[3] > 0) {
+      rect[0] = H - v[3];
+      rect[1] = v[2];
+      rect[2] = W - v[0];
+      rect[3] = v[1];
+      const size_t off = (size_t)rect[0] * W + rect[2];
+      for (int64_t b = 0; b < B; ++b)
+        LYNX_CUDA_OK(cudaMemcpy2DAsync(screen_img + (size_t)b * W * H + off, sizeof(float) * W,
+                                       (const float*)c->img.p + (size_t)b * W * H + off,
+                                       sizeof(float) * W, sizeof(float) * (rect[3] - rect[2]),
+                                       rect[1] - rect[0], cudaMemcpyDeviceToHost, st));
+      LYNX_CUDA_OK(cudaStreamSynchronize(st));
+    }
+    for (int i = 0; i < 4; ++i) c->last_rect[i] = rect[i];
+    c->last_img = screen_img;
+  }
   return LYNX_OK;
 }
 

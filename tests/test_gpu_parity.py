@@ -389,9 +389,25 @@ def test_host_buffer_abi_matches_device_path():
     L.check(L.lib().lynx_host_track_particles(
         ctx, prog.handle, vp(params), params.size, 1, vp(soa_c), 1, n, vp(e_in), None, None,
         vp(img), W, H, vp(ex), vp(ey), vp(mom), 2, vp(e_out)))
-    L.lib().lynx_host_ctx_destroy(ctx)
     assert np.array_equal(img, want)
     assert mom[0, 0] == n
+
+    # persistent-image mode: only the lit rectangle crosses PCIe; the host image must stay
+    # bit-identical to the dense transfer across calls with different settings
+    L.check(L.lib().lynx_host_ctx_set_option(ctx, 1, 1))
+    pimg = np.full((1, H, W), 7.0, dtype=np.float32)  # garbage: a new buffer is zero-filled
+    for k1, vk, hk in (((5.0, -5.0, 5.0), 1e-3, -2e-3), ((2.0, -3.0, 1.0), -1e-3, 1e-3),
+                       ((9.0, -9.0, 9.0), 2e-3, 2e-3), ((5.0, -5.0, 5.0), 1e-3, -2e-3)):
+        spec_k = F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True, screen=F.TEST_SCREEN)
+        seg_k = F.build_segment(spec_k)
+        seg_k.track(_gpu_beam(soa, F.ASTRA_ENERGY))
+        want_k = seg_k.AREABSCR1.reading.cpu().numpy()
+        params_k = pack_params(encode(seg_k.elements, (1,)), "cpu").numpy()
+        L.check(L.lib().lynx_host_track_particles(
+            ctx, prog.handle, vp(params_k), params_k.size, 1, vp(soa_c), 1, n, vp(e_in), None,
+            None, vp(pimg), W, H, vp(ex), vp(ey), None, 0, None))
+        assert np.array_equal(pimg, want_k)
+    L.lib().lynx_host_ctx_destroy(ctx)
 
 
 def test_forward_moment_collapse_matches_streaming():
