@@ -31,6 +31,11 @@ elif a.mode == "pb4096":
     w = bench.ParamBeamWorkload(4096, dev)
 elif a.mode == "pb1m":
     w = bench.ParamBeamWorkload(1 << 20, dev)
+elif a.mode == "adj32m":
+    w = bench.GradWorkload(32_000_000, 1, dev, per_particle=True)
+    w.step = w.backward
+elif a.mode == "grad1m1024":
+    w = bench.GradWorkload(1_000_000, 1024, dev)
 else:
     raise SystemExit("unknown mode")
 ms = bench.timed_steps(w.step, a.steps, 2, flush)
