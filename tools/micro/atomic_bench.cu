@@ -26,6 +26,23 @@ __global__ void k_red_co(const int* __restrict__ idx, T* img, long n) {
   long stride = (long)gridDim.x * blockDim.x;
   for (; i < n; i += stride) atomicAdd(img + idx[i], (T)1);
 }
+// R replicas of the image (distinct L2 lines): replica chosen per CTA
+__global__ void k_red_rep(const int* __restrict__ idx, float* img, long n, int R, long rep_stride) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  long stride = (long)gridDim.x * blockDim.x;
+  float* mine = img + (blockIdx.x % R) * rep_stride;
+  for (; i < n; i += stride) atomicAdd(mine + idx[i], 1.0f);
+}
+// warp-aggregated: lanes with the same bin elect a leader that adds the count
+__global__ void k_red_match(const int* __restrict__ idx, float* img, long n) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  long stride = (long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {  // n is a multiple of the warp size here
+    int v = idx[i];
+    unsigned m = __match_any_sync(0xffffffffu, v);
+    if ((__ffs(m) - 1) == (threadIdx.x & 31)) atomicAdd(img + v, (float)__popc(m));
+  }
+}
 __global__ void k_read(const int* __restrict__ idx, int* out, long n) {
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   long stride = (long)gridDim.x * blockDim.x;
@@ -48,6 +65,8 @@ int main(int argc, char** argv) {
     x = x < 0 ? 0 : (x >= W ? W - 1 : x); y = y < 0 ? 0 : (y >= H ? H - 1 : y);
     h[i] = y * W + x;
   }
+  const int RMAX = 8; const long rep_stride = (long)W * H + 32 * 37;
+  float* d_rep; CK(cudaMalloc(&d_rep, RMAX * rep_stride * 4));
   int* d_idx; float* d_f; unsigned* d_u; int* d_o;
   CK(cudaMalloc(&d_idx, n * 4)); CK(cudaMalloc(&d_f, W * H * 4)); CK(cudaMalloc(&d_u, W * H * 4)); CK(cudaMalloc(&d_o, 4));
   CK(cudaMemcpy(d_idx, h.data(), n * 4, cudaMemcpyHostToDevice));
@@ -66,6 +85,12 @@ int main(int argc, char** argv) {
     time("read only", [&] { k_read<<<blocks, 256>>>(d_idx, d_o, n); });
     time("f32 RED coalesced idx", [&] { k_red_co<float><<<blocks, 256>>>(d_idx, d_f, n); });
     time("u32 RED coalesced idx", [&] { k_red_co<unsigned><<<blocks, 256>>>(d_idx, d_u, n); });
+    for (int R : {2, 4, 8}) {
+      char nm[64]; snprintf(nm, 64, "f32 RED %d replicas", R);
+      CK(cudaMemset(d_rep, 0, RMAX * rep_stride * 4));
+      time(nm, [&] { k_red_rep<<<blocks, 256>>>(d_idx, d_rep, n, R, rep_stride); });
+    }
+    time("f32 RED match.any", [&] { k_red_match<<<blocks, 256>>>(d_idx, d_f, n & ~31L); });
     time("f32 RED 4/thread", [&] { k_red<float, 4><<<blocks, 256>>>(d_idx, d_f, n); });
     time("u32 RED 4/thread", [&] { k_red<unsigned, 4><<<blocks, 256>>>(d_idx, d_u, n); });
   }
