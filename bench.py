@@ -378,6 +378,7 @@ def timed_steps(step, steps, warmup, flush, post=None):
     torch.cuda.synchronize()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
            for _ in range(steps)]
+    t0 = time.perf_counter()
     for a, b in evs:
         flush.zero_()
         a.record()
@@ -385,7 +386,13 @@ def timed_steps(step, steps, warmup, flush, post=None):
         if post:
             post()
         b.record()
+    t1 = time.perf_counter()
     torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    # host enqueue time per step, and how long the device still ran after the last enqueue:
+    # the host must stay ahead of the device or launch gaps end up inside the events
+    timed_steps.host_us = (t1 - t0) / steps * 1e6
+    timed_steps.drain_us = (t2 - t1) * 1e6
     return [a.elapsed_time(b) for a, b in evs]
 
 
@@ -441,7 +448,30 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.synchronize()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     lib.lynx_launch_count_reset()
+    trace = None
+    if world > 1 and os.environ.get("LYNX_EX_TRACE"):
+        trace = torch.zeros(8192, dtype=torch.int64, device=device)
+        lib.lynx_exchange_trace(trace.data_ptr())
     ms = timed_steps(step_fn, args.steps, args.warmup, flush, post)
+    if trace is not None:
+        lib.lynx_exchange_trace(None)
+        t = trace.view(1024, 8)[args.warmup + 2:args.warmup + args.steps].double()
+        t = t[t[:, 0] > 0]
+        rel = ((t - t[:, 4:5]).mean(0) / 1e3).tolist()  # us after K2 passed its wait on K1
+        sys.stderr.write(f"[rank {rank}] host enqueue {timed_steps.host_us:.1f} us/step, device drain "
+                         f"after last enqueue {timed_steps.drain_us:.0f} us; K1 start {rel[6]:.2f}; ")
+        sys.stderr.write(f"[rank {rank}] us after K1 done: K2 CTA0 done {rel[5]:.2f}, EX resident "
+                         f"{rel[0]:.2f}, K2 complete {rel[1]:.2f}, peers arrived {rel[2]:.2f}, "
+                         f"written {rel[3]:.2f}, last CTA {rel[7]:.2f}; step mean {sum(ms) / len(ms) * 1e3:.2f}\n")
+        ms_local = timed_steps(wl.step, 50, 5, flush)
+        if hasattr(exch, "reduce"):
+            real_reduce = exch.reduce
+            exch.reduce = lambda: None  # track into the symmetric slot, no exchange
+            ms_symm = timed_steps(step_fn, 50, 5, flush)
+            exch.reduce = real_reduce
+            sys.stderr.write(f"[rank {rank}] no exchange: local image {np.mean(ms_local) * 1e3:.2f} us, "
+                             f"symmetric slot {np.mean(ms_symm) * 1e3:.2f} us\n")
+        sys.stderr.write(f"[rank {rank}] sharded step kernels: K1 {k1 * 1e3:.2f} us, K2 {k2 * 1e3:.2f} us\n")
     launches = lib.lynx_launch_count() - 0
     launches_timed = launches * args.steps // (args.steps + args.warmup)
     torch.cuda.synchronize()

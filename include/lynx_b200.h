@@ -244,6 +244,11 @@ void lynx_launch_count_reset(void);
  * 3 = K3 adjoint), or a negative value if none was recorded. */
 void lynx_profile_enable(int on);
 float lynx_profile_last_ms(int which);
+/* Debug: block 0 of lynx_screen_allreduce stamps %globaltimer (ns) into
+ * d_stamps[(epoch & 1023) * 8 + {0: resident, 1: K2 complete, 2: all peers arrived,
+ * 3: rectangle written, 4: K2 past its wait on K1, 5: K2 CTA 0 done}]; NULL switches it
+ * off.  Device buffer of 8192 uint64. */
+void lynx_exchange_trace(unsigned long long* d_stamps);
 
 /* ---- host-buffer entry points (what a NumPy / host-array binding calls) ------------
  * Same semantics as the device launchers, but every pointer is HOST memory (pinned for

@@ -22,6 +22,11 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
   // init, TMA requests for its first tiles) now; it waits (griddepcontrol.wait) for this
   // grid to finish before it reads the records or touches the zeroed image.
   asm volatile("griddepcontrol.launch_dependents;");
+  if (a.hist_out && blockIdx.x == 0 && threadIdx.x == 0) {  // debug stamp (exchange trace)
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    reinterpret_cast<unsigned long long*>(a.hist_out)[8] = t;  // K1 block 0 starts
+  }
   // the last block validates the screen's edge tables and writes the bin-lookup geometry
   const int hist_blocks = a.hist_out ? 1 : 0;
   if (hist_blocks && blockIdx.x == gridDim.x - 1) {

@@ -6,8 +6,10 @@
 // (70 us at 2 GPUs against a 30 us tracking step).  Here every rank's image lives in a
 // peer-mapped SYMMETRIC buffer (NVLink / NVSwitch P2P), K2 records the bounding box of the
 // bins it touched, and ONE kernel per rank
-//   1. signals / waits on per-rank epoch flags in the peers' buffers (cross-GPU barrier),
-//   2. forms the union bounding box from the boxes the peers pushed with their signal,
+//   1. pushes its bounding box, tagged with the step's epoch, into every peer's buffer and
+//      waits for all peers' boxes of this epoch in its OWN buffer (cross-GPU barrier, no
+//      polling over NVLink),
+//   2. forms the union bounding box,
 //   3. updates the caller's persistent image: inside the box the sum of all peers' pixels
 //      read over NVLink (coalesced peer loads); the part of the PREVIOUS call's rectangle
 //      outside it is cleared; everything else is already zero (no 20 MB rewrite).
@@ -17,21 +19,24 @@
 // passed the barrier of the step in between, i.e. finished reading slot s.
 //
 // Layout of one rank's symmetric buffer (lynx_screen_symm_bytes):
-//   [0, 64)                       uint32 flags[16]: flags[p] = last epoch signalled by rank p
-//   [64, 576)                     int4 inbox[2][16]: rank p's bounding box of the step with
-//                                 epoch parity 0 / 1, PUSHED by rank p before its signal
+//   [0, 512)                      uint64 msg[2][16][2]: rank p's message of the step with epoch
+//                                 parity 0 / 1, PUSHED by rank p: two self-validating 8-byte
+//                                 words (epoch << 32 | v_lo << 16 | v_hi), word 0 = (v0, v1),
+//                                 word 1 = (v2, v3) of p's bounding box.  An aligned 8-byte
+//                                 store is single-copy atomic, so the words need no fence
+//                                 between them and double as the barrier signal.
 //   slot s at 1024 + s * slot_bytes: int32 bbox[16] (v0 = max(W - ix), v1 = max(ix + 1),
 //                                   v2 = max(H - iy), v3 = max(iy + 1); 0 = empty), then
 //                                   float image[B][H][W] (reference layout, row 0 = max y)
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
 namespace lynx {
 
 constexpr int kMaxWorld = 16;
-constexpr size_t kSymmHeader = 1024;  // flags[16] u32 @0, inbox int4[2][16] @64
-constexpr size_t kInboxOff = 64;
+constexpr size_t kSymmHeader = 1024;  // msg[2][16][2] u64 @0
 constexpr size_t kBboxBytes = 64;
 
 struct ExchangeArgs {
@@ -43,49 +48,84 @@ struct ExchangeArgs {
   size_t slot_bytes;
   float* out;    // [B][H][W] local, persistent: zero outside the last written rectangle
   int* state;    // [2][4] local: rectangle (r0, r1, c0, c1) written at even / odd epochs
+  unsigned long long* trace;  // optional [1024][8] globaltimer stamps of block 0 (debug)
 };
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+// The message store needs no fence of its own: everything it publishes (K2's image and box)
+// was written by the PREVIOUS grid, which griddepcontrol.wait / the kernel boundary has
+// completed and made visible at this GPU's L2 -- the only place peers read it from (peer
+// memory is not cached on the reading side).  A release store would put a MEMBAR.SYS
+// (~2 us) on the critical path of every step.
+__device__ __forceinline__ void st_relaxed_sys(uint64_t* p, uint64_t v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ uint64_t ld_acquire_sys(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// peer image read: relaxed system-scope load (ordered after the acquire above), not cached in L1
+__device__ __forceinline__ float4 ld_peer(const float4* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
   return v;
 }
 
 constexpr int kExTPB = 256;
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
 __global__ void __launch_bounds__(kExTPB) screen_allreduce_kernel(ExchangeArgs a) {
   __shared__ int s_box[4];
   const int tid = threadIdx.x;
   const int par = a.epoch & 1;
+  unsigned long long* tr =
+      (a.trace && blockIdx.x == 0 && tid == 0) ? a.trace + (a.epoch & 1023u) * 8 : nullptr;
+  if (tr) tr[0] = globaltimer_ns();  // resident (possibly long before K2 ends)
   // launched with programmatic stream serialization: resident early, waits for K2 here
   asm volatile("griddepcontrol.wait;" ::: "memory");
-  // ---- 1. push my bounding box into every peer's inbox, then signal my epoch (cross-GPU
-  //         barrier; the release store orders the box before the flag)
-  if (blockIdx.x == 0 && tid < a.world) {
-    const int4 box = __ldcg(reinterpret_cast<const int4*>(a.peers[a.rank] + kSymmHeader +
-                                                          a.slot * a.slot_bytes));
-    int4* inbox = reinterpret_cast<int4*>(a.peers[tid] + kInboxOff) + par * kMaxWorld + a.rank;
-    *inbox = box;
-    __threadfence_system();
-    st_release_sys(reinterpret_cast<uint32_t*>(a.peers[tid]) + a.rank, a.epoch);
+  if (tr) {
+    tr[1] = globaltimer_ns();  // K2 complete
+    const unsigned long long* k2 = reinterpret_cast<const unsigned long long*>(
+        a.peers[a.rank] + kSymmHeader + a.slot * a.slot_bytes + 32);
+    tr[4] = __ldcg(k2);      // K2 past its wait on K1
+    tr[5] = __ldcg(k2 + 1);  // K2 CTA 0 issued its last RED
+    tr[6] = __ldcg(k2 + 2);  // K1 block 0 started
   }
-  if (tid < a.world) {
-    const uint32_t* mine = reinterpret_cast<const uint32_t*>(a.peers[a.rank]) + tid;
-    while ((int32_t)(ld_acquire_sys(mine) - a.epoch) < 0) {
-    }
+  // ---- 1. push my bounding box, tagged with the epoch, into every peer's message area
+  //         (thread = (peer, word))
+  if (blockIdx.x == 0 && tid < 2 * a.world) {
+    const int peer = tid >> 1, w = tid & 1;
+    const int* box = reinterpret_cast<const int*>(a.peers[a.rank] + kSymmHeader +
+                                                  a.slot * a.slot_bytes);
+    const uint32_t lo = (uint32_t)__ldcg(box + 2 * w), hi = (uint32_t)__ldcg(box + 2 * w + 1);
+    uint64_t* msg = reinterpret_cast<uint64_t*>(a.peers[peer]) + (par * kMaxWorld + a.rank) * 2 + w;
+    st_relaxed_sys(msg, ((uint64_t)a.epoch << 32) | ((uint64_t)(lo & 0xffffu) << 16) | (hi & 0xffffu));
   }
   if (tid < 4) s_box[tid] = 0;
   __syncthreads();
-  // ---- 2. union bounding box from the (local) inbox
-  if (tid < a.world * 4) {
-    const int* in = reinterpret_cast<const int*>(a.peers[a.rank] + kInboxOff) +
-                    (par * kMaxWorld + (tid >> 2)) * 4 + (tid & 3);
-    atomicMax(&s_box[tid & 3], __ldcv(in));
+  // ---- 2. every CTA waits for all peers' words of this epoch in the LOCAL buffer and forms
+  //         the union box from them
+  if (tid < 2 * a.world) {
+    const uint64_t* mine =
+        reinterpret_cast<const uint64_t*>(a.peers[a.rank]) + (par * kMaxWorld + (tid >> 1)) * 2 + (tid & 1);
+    uint64_t m;
+    do {
+      m = ld_acquire_sys(mine);
+    } while ((int32_t)((uint32_t)(m >> 32) - a.epoch) < 0);
+    atomicMax(&s_box[2 * (tid & 1)], (int)((m >> 16) & 0xffffu));
+    atomicMax(&s_box[2 * (tid & 1) + 1], (int)(m & 0xffffu));
   }
   __syncthreads();
+  if (tr) tr[2] = globaltimer_ns();  // all peers arrived
   const bool empty = s_box[1] == 0 || s_box[3] == 0;
   // bins [x0, x1) x [y0, y1) -> image rows [H - y1, H - y0), columns rounded to float4
   const int r0 = empty ? 0 : a.H - s_box[3], r1 = empty ? 0 : s_box[2];
@@ -117,17 +157,31 @@ __global__ void __launch_bounds__(kExTPB) screen_allreduce_kernel(ExchangeArgs a
     const int64_t i = ((bq * a.H + r) * (int64_t)a.W + c) >> 2;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     if (r >= r0 && r < r1 && c >= c0 && c < c1) {
-      for (int p = 0; p < a.world; ++p) {
-        const float4 v = __ldcv(reinterpret_cast<const float4*>(a.peers[p] + img_off) + i);
-        s.x += v.x;
-        s.y += v.y;
-        s.z += v.z;
-        s.w += v.w;
+      // all peer loads of a batch are issued before the first add: one NVLink round trip
+      // per batch of 8 peers instead of one per peer
+      for (int p0 = 0; p0 < a.world; p0 += 8) {
+        float4 v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          v[q] = (p0 + q < a.world)
+                     ? ld_peer(reinterpret_cast<const float4*>(a.peers[p0 + q] + img_off) + i)
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          s.x += v[q].x;
+          s.y += v[q].y;
+          s.z += v[q].z;
+          s.w += v[q].w;
+        }
       }
     }
     reinterpret_cast<float4*>(a.out)[i] = s;
   }
+  if (tr) tr[3] = globaltimer_ns();  // block 0's share of the rectangle written
+  if (a.trace && tid == 0) atomicMax(a.trace + (a.epoch & 1023u) * 8 + 7, globaltimer_ns());  // last CTA
 }
+
+static unsigned long long* g_exchange_trace = nullptr;
 
 }  // namespace lynx
 
@@ -152,11 +206,13 @@ extern "C" float* lynx_screen_symm_image(void* d_symm_base, int32_t slot, int64_
                                   kBboxBytes);
 }
 
+extern "C" void lynx_exchange_trace(unsigned long long* d_stamps) { lynx::g_exchange_trace = d_stamps; }
+
 extern "C" int lynx_screen_allreduce(void* const* peer_bases, int32_t world, int32_t rank,
                                      int32_t slot, uint32_t epoch, int64_t B, int32_t W, int32_t H,
                                      float* d_out_img, int32_t* d_state, lynx_stream_t stream) {
   if (!peer_bases || world < 1 || world > kMaxWorld || rank < 0 || rank >= world || slot < 0 ||
-      slot > 1 || epoch == 0 || B <= 0 || W <= 0 || H <= 0 || (W & 3) || !d_out_img ||
+      slot > 1 || epoch == 0 || B <= 0 || W <= 0 || H <= 0 || W > 65535 || H > 65535 || (W & 3) || !d_out_img ||
       !d_state || ((uintptr_t)d_out_img & 15))
     return LYNX_E_BADARG;
   ExchangeArgs a{};
@@ -174,6 +230,7 @@ extern "C" int lynx_screen_allreduce(void* const* peer_bases, int32_t world, int
   a.slot_bytes = slot_bytes_of(B, W, H);
   a.out = d_out_img;
   a.state = d_state;
+  a.trace = g_exchange_trace;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -359,6 +359,7 @@ extern "C" int lynx_track_particles_fwd_bbox(
   a.ey = d_edges_y;
   a.hist = reinterpret_cast<const HistAxis*>(hist_ws);
   a.bbox = has_img ? d_screen_bbox : nullptr;
+  a.stamp = bbox_adjacent ? reinterpret_cast<unsigned long long*>(d_screen_bbox + 8) : nullptr;
   a.mom = d_moment_sums;
   a.B = B;
   static const int dbg = [] { const char* e = getenv("LYNX_DBG"); return e ? atoi(e) : 0; }();

@@ -157,7 +157,10 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
   const int64_t b = blockIdx.y;
-  const int64_t n_tiles = (a.N + kPipeTile - 1) / kPipeTile;
+  // a.tile <= kPipeTile particles per tile (chosen by the launcher so that every CTA gets
+  // the same number of tiles); the shared-memory plane stride stays kPipeTile
+  const int64_t tile = a.tile;
+  const int64_t n_tiles = (a.N + tile - 1) / tile;
   const float* in_b = a.in + b * a.in_row_stride;
 
   if (tid == 0) {
@@ -172,8 +175,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
 
   auto issue_tile = [&](int it, int64_t t) {
     const int s = it % STAGES;
-    const int64_t p0 = t * kPipeTile;
-    const uint32_t cnt = (uint32_t)min((int64_t)kPipeTile, a.N - p0);
+    const int64_t p0 = t * tile;
+    const uint32_t cnt = (uint32_t)min(tile, a.N - p0);
     const uint32_t bytes = ((cnt + 3u) & ~3u) * 4u;
     mbar_arrive_expect_tx(full + s, 6u * bytes);
     float* dst = stages + s * kStageFloats;
@@ -200,6 +203,12 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   // ... then wait for the K1 grid (records + histogram geometry written, image zeroed) --
   // a no-op unless this kernel was launched with programmatic stream serialization
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (a.stamp && tid == 0 && blockIdx.x == 0 && b == 0) {  // exchange trace (exchange.cu)
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    a.stamp[0] = t;
+    a.stamp[2] = reinterpret_cast<const unsigned long long*>(a.hist)[8];  // K1 block 0 started  // K1 complete, K2 starts
+  }
   {
     const float* src = a.records + b * a.rec_floats;
     for (int i = tid; i < a.rec_floats; i += kPipeThreads) rec[i] = src[i];
@@ -235,8 +244,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
         const uint32_t u = (uint32_t)(it / STAGES);
         mbar_wait(done + s, u & 1);
         fence_proxy_async();
-        const int64_t p0 = t * kPipeTile;
-        const uint32_t cnt = (uint32_t)min((int64_t)kPipeTile, a.N - p0);
+        const int64_t p0 = t * tile;
+        const uint32_t cnt = (uint32_t)min(tile, a.N - p0);
         const uint32_t bytes = ((cnt + 3u) & ~3u) * 4u;
         const float* src = stages + s * kStageFloats;
 #pragma unroll
@@ -273,8 +282,9 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
     for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
       const int s = it % STAGES;
       const uint32_t u = (uint32_t)(it / STAGES);
-      const int64_t p0 = t * kPipeTile;
-      n_mine += min((int64_t)kPipeTile, a.N - p0);
+      const int64_t p0 = t * tile;
+      const int cnt = (int)min(tile, a.N - p0);
+      n_mine += cnt;
       float* st = stages + s * kStageFloats + cid * 4;
       mbar_wait(full + s, u & 1);
       float v[6][4];
@@ -290,10 +300,9 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
         __syncwarp();
         if (lane == 0) mbar_arrive(empty + s);
       }
-      const int64_t base = p0 + (int64_t)cid * 4;
       bool live[4];
 #pragma unroll
-      for (int l = 0; l < 4; ++l) live[l] = base + l < a.N;
+      for (int l = 0; l < 4; ++l) live[l] = cid * 4 + l < cnt;
 
       for (int pi = 0; pi < a.n_plan; ++pi) {
         const PlanItem p = plan[pi];
@@ -466,6 +475,11 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
     }
   }
   // ---- CTA epilogue
+  if (a.stamp && tid == 64 && blockIdx.x == 0 && b == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    a.stamp[1] = t;  // CTA 0's last RED issued
+  }
   if (MOM != 0) {
     mom_epilogue<MOM, kConsumerWarps>(acc, s_red, warp >= 2 ? warp - 2 : -1, lane, tid == 64,
                                       n_mine, ctr, a.mom + b * 28);
@@ -475,7 +489,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
     // n_mine is only tracked by consumers; recompute for the flushing threads
     int64_t n_cta = 0;
     for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x)
-      n_cta += min((int64_t)kPipeTile, a.N - t * kPipeTile);
+      n_cta += min(tile, a.N - t * tile);
     for (int pi = tid; pi < a.n_plan; pi += kPipeThreads) {
       const PlanItem p = plan[pi];
       if (p.kind == P_BPM) {
@@ -538,24 +552,34 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
     if (win_words < 1024) win_words = 0;
     L = pipe_layout(stages, a.rec_floats, a.n_plan, a.n_snap, win_words);
   }
-  const int64_t n_tiles = (a.N + kPipeTile - 1) / kPipeTile;
   int64_t per_b = (sm_count + a.B - 1) / a.B;
   if (per_b < 1) per_b = 1;
-  dim3 grid((unsigned)std::min<int64_t>(n_tiles, per_b), (unsigned)a.B);
+  // Tile size: the largest multiple of 32 particles <= kPipeTile that gives every CTA of a
+  // row the same number of tiles (1 M particles on 148 CTAs: 4 x 1696 each instead of 3 or
+  // 4 x 2048 -- the longest CTA sets the kernel time).
+  const int64_t full_tiles = (a.N + kPipeTile - 1) / kPipeTile;
+  const int64_t gx = std::min<int64_t>(full_tiles, per_b);
+  const int64_t rounds = (a.N + gx * kPipeTile - 1) / (gx * kPipeTile);
+  int64_t tile = (a.N + gx * rounds - 1) / (gx * rounds);
+  tile = std::min<int64_t>(kPipeTile, (tile + 31) & ~(int64_t)31);
+  const int64_t n_tiles = (a.N + tile - 1) / tile;
+  TrackArgs at = a;
+  at.tile = (int)tile;
+  dim3 grid((unsigned)std::min<int64_t>(n_tiles, gx), (unsigned)a.B);
   if (stages == 2) {
     switch (moment_mode) {
-      case 0: return launch_pipe<0, false, 2>(a, grid, L.total, win_words, st);
-      case 1: return launch_pipe<1, false, 2>(a, grid, L.total, win_words, st);
-      default: return launch_pipe<2, false, 2>(a, grid, L.total, win_words, st);
+      case 0: return launch_pipe<0, false, 2>(at, grid, L.total, win_words, st);
+      case 1: return launch_pipe<1, false, 2>(at, grid, L.total, win_words, st);
+      default: return launch_pipe<2, false, 2>(at, grid, L.total, win_words, st);
     }
   }
   switch (moment_mode * 2 + (has_out ? 1 : 0)) {
-    case 0: return launch_pipe<0, false, 4>(a, grid, L.total, 0, st);
-    case 1: return launch_pipe<0, true, 4>(a, grid, L.total, 0, st);
-    case 2: return launch_pipe<1, false, 4>(a, grid, L.total, 0, st);
-    case 3: return launch_pipe<1, true, 4>(a, grid, L.total, 0, st);
-    case 4: return launch_pipe<2, false, 4>(a, grid, L.total, 0, st);
-    default: return launch_pipe<2, true, 4>(a, grid, L.total, 0, st);
+    case 0: return launch_pipe<0, false, 4>(at, grid, L.total, 0, st);
+    case 1: return launch_pipe<0, true, 4>(at, grid, L.total, 0, st);
+    case 2: return launch_pipe<1, false, 4>(at, grid, L.total, 0, st);
+    case 3: return launch_pipe<1, true, 4>(at, grid, L.total, 0, st);
+    case 4: return launch_pipe<2, false, 4>(at, grid, L.total, 0, st);
+    default: return launch_pipe<2, true, 4>(at, grid, L.total, 0, st);
   }
 }
 
