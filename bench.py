@@ -183,15 +183,21 @@ class ParticleWorkload:
     """Pre-encoded Segment.track(ParticleBeam) (+ Screen.reading) on device buffers: what
     a jit-compiled caller holds -- program handle, packed parameters, resident beam."""
 
-    def __init__(self, n, device, seed, screen=True, want_out=False, moments=0):
+    def __init__(self, n, device, seed, screen=True, want_out=False, moments=0, lattice="ares"):
         import lynx_b200 as lx
         from lynx_b200 import _lib as L
         from lynx_b200 import fixtures as F
         from lynx_b200.program import Program, encode, pack_params
 
         self.L, self.n, self.device = L, n, device
-        spec = F.ares_ea(k1=K1, vkick=VKICK, hkick=HKICK, screen_active=screen,
-                         screen=F.TEST_SCREEN)
+        if lattice == "cfg4":  # BASELINE.json configs[3]: Cavity + Dipole + quadrupoles, E = 10
+            spec = F.cavity_dipole_line(screen_active=screen)
+            energy, beam_soa, scr_name = F.CFG4_ENERGY, F.cfg4_beam_soa, "SCR"
+        else:
+            spec = F.ares_ea(k1=K1, vkick=VKICK, hkick=HKICK, screen_active=screen,
+                             screen=F.TEST_SCREEN)
+            energy, beam_soa, scr_name = F.ASTRA_ENERGY, F.gaussian_beam_soa, "AREABSCR1"
+        self.n_elements = len(spec)
         self.seg = F.build_segment(spec)
         self.enc = encode(self.seg.elements, (1,))
         self.prog = Program.get(self.enc)
@@ -199,9 +205,9 @@ class ParticleWorkload:
         self.params_host = self.params.cpu().pin_memory()
         self.ld = (n + 3) & ~3
         self.soa_host = torch.empty((6, self.ld), dtype=torch.float32).pin_memory()
-        self.soa_host[:, :n] = torch.from_numpy(F.gaussian_beam_soa(n, seed=seed))
+        self.soa_host[:, :n] = torch.from_numpy(beam_soa(n, seed=seed))
         self.soa = self.soa_host.to(device)
-        self.e_in = torch.tensor([F.ASTRA_ENERGY], device=device)
+        self.e_in = torch.tensor([energy], dtype=torch.float32, device=device)
         self.e_out = torch.empty(1, device=device)
         self.ws = torch.empty(self.prog.workspace_bytes(1), dtype=torch.uint8, device=device)
         self.out = torch.empty((6, self.ld), device=device) if want_out else None
@@ -210,7 +216,7 @@ class ParticleWorkload:
         self.img = self.ex = self.ey = None
         self.W = self.H = 0
         if screen:
-            scr = self.seg.AREABSCR1
+            scr = getattr(self.seg, scr_name)
             self.ex, self.ey = scr._device_edges(device)
             self.W, self.H = self.ex.numel() - 1, self.ey.numel() - 1
             self.img = torch.empty((1, self.H, self.W), device=device)
@@ -604,6 +610,30 @@ def run_ours(args, rank, world, local_rank):
                 "frac_of_8000": a2 / 8000.0,
                 "particle_element_updates_per_s": ns * E_ARES / (km * 1e-3)}
             del w2
+        # config 4 per-GPU shard: 12.5 M particles through Cavity + Dipole + quadrupoles
+        n4 = 12_500_000
+        for name, kw in (("screen_24B", dict(screen=True)),
+                         ("out_48B", dict(screen=False, want_out=True))):
+            w4 = ParticleWorkload(n4, device, seed=1004, lattice="cfg4", **kw)
+            km = kernel_ms(w4.step, 1, 10, flush, lib)
+            sm = float(np.mean(timed_steps(w4.step, 10, 3, flush)))
+            a4 = w4.algorithmic_bytes() / (km * 1e-3) / 1e9
+            extras[f"cfg4_cavity_dipole_12.5M_{name}"] = {
+                "particles": n4, "elements": w4.n_elements, "kernel_ms": km, "step_ms": sm,
+                "achieved_gbs": a4, "frac": a4 / peak,
+                "particle_element_updates_per_s": n4 * w4.n_elements / (sm * 1e-3)}
+            del w4
+        # K9: beam generation on the device (24 B written per particle)
+        import lynx_b200 as lx
+        gen = lambda: lx.ParticleBeam.from_parameters(  # noqa: E731
+            num_particles=ns, sigma_x=torch.tensor([2e-4]), sigma_y=torch.tensor([2e-4]), seed=1)
+        gen()
+        gms_ = float(np.mean(timed_steps(gen, 10, 3, flush)))
+        extras["generate_beam_24B"] = {
+            "particles": ns, "ms": gms_, "achieved_gbs": 24 * ns / (gms_ * 1e-3) / 1e9,
+            "frac": 24 * ns / (gms_ * 1e-3) / 1e9 / peak,
+            "note": "ParticleBeam.from_parameters end to end (host Cholesky + H2D of 42 floats "
+                    "+ kernel), Philox4x32-10 + Box-Muller straight into the SoA planes"}
         # config 5: gradients, one 1M-particle beam x 1024 settings (moment loss)
         gw = GradWorkload(args.particles, 1024, device)
         gms = timed_steps(gw.step, 20, 3, flush)

@@ -226,6 +226,20 @@ int lynx_parambeam_bwd(const lynx_program_t*, const float* d_params, int64_t B,
 int lynx_screen_pdf(const float* d_mu, const float* d_cov, int64_t B, const float* d_xs,
                     const float* d_ys, int32_t W, int32_t H, float* d_img, lynx_stream_t stream);
 
+/* K9 -- Gaussian beam generation on the device.  Replaces the sampling inside
+ * ParticleBeam.from_parameters / from_twiss (particle_beam.py:143-170: one
+ * MultivariateNormal(mean, cov).sample((N,)) per batch row on the host + device copy).
+ *   d_mean [B][6], d_sqrt_cov [B][6][6] row-major A with A A^T = cov  ->  d_soa [B][6][ld]:
+ *   x = mean + A z, z ~ N(0, I) from Philox4x32-10 keyed by `seed`, counter =
+ *   (particle / 4, b, coordinate); particle n of this buffer is global particle
+ *   first_particle + n (multiple of 4), so shards of one beam generated on different GPUs
+ *   are slices of the same stream.  Padding lanes [N, ld) are written as zeros.          */
+int lynx_beam_generate(const float* d_mean, const float* d_sqrt_cov, int64_t B, int64_t N,
+                       int64_t first_particle, uint64_t seed, float* d_soa, int64_t ld,
+                       lynx_stream_t stream);
+/* One Philox4x32-10 block on the HOST (known-answer hook for the CPU tests). */
+void lynx_philox4x32_10(const uint32_t counter[4], const uint32_t key[2], uint32_t out[4]);
+
 /* Layout converters between the reference's AoS (..,N,7) ParticleBeam.particles
  * (particle_beam.py:24-45) and the SoA-6 device layout. */
 int lynx_aos7_to_soa6(const float* d_aos /*[R][N][7]*/, int64_t R, int64_t N,

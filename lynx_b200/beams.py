@@ -130,6 +130,102 @@ class ParticleBeam(Beam):
         self._sums = moment_sums
         return self
 
+    @classmethod
+    def from_parameters(cls, num_particles=None, mu_x=None, mu_y=None, mu_xp=None, mu_yp=None,
+                        sigma_x=None, sigma_y=None, sigma_xp=None, sigma_yp=None, sigma_s=None,
+                        sigma_p=None, cor_x=None, cor_y=None, cor_s=None, energy=None,
+                        total_charge=None, device=None, dtype=torch.float32, seed=None,
+                        first_particle=0):
+        """particle_beam.py:47-170 (same arguments and defaults), sampled ON the device by
+        ``lynx_beam_generate`` (csrc/generate.cu): the beam never exists on the host.
+
+        ``seed`` (extra): 64-bit key of the counter-based generator; ``None`` draws one from
+        torch's CPU generator, so ``torch.manual_seed`` makes beams reproducible.
+        ``first_particle`` (extra): global index of this buffer's first particle, for
+        generating one rank's shard of a larger beam (multiple of 4)."""
+        assert dtype == torch.float32, "device path is fp32 (SURVEY.md section 5)"
+        given = [a for a in (mu_x, mu_xp, mu_y, mu_yp, sigma_x, sigma_xp, sigma_y, sigma_yp,
+                             sigma_s, sigma_p, cor_x, cor_y, cor_s, energy, total_charge)
+                 if a is not None]
+        shape = tuple(given[0].shape) if given else (1,)
+        assert all(tuple(a.shape) == shape for a in given), "Arguments must have the same shape."
+        num_particles = int(num_particles) if num_particles is not None else 100_000
+        d = lambda a, v: (torch.as_tensor(a, dtype=torch.float64).cpu() if a is not None  # noqa: E731
+                          else torch.full(shape, v, dtype=torch.float64))
+        zero = torch.zeros(shape, dtype=torch.float64)
+        mean = torch.stack([d(mu_x, 0.0), d(mu_xp, 0.0), d(mu_y, 0.0), d(mu_yp, 0.0), zero, zero],
+                           dim=-1)
+        sig = [d(sigma_x, 175e-9), d(sigma_xp, 2e-7), d(sigma_y, 175e-9), d(sigma_yp, 2e-7),
+               d(sigma_s, 1e-6), d(sigma_p, 1e-6)]
+        cor = [d(cor_x, 0.0), d(cor_y, 0.0), d(cor_s, 0.0)]
+        cov = torch.zeros(*shape, 6, 6, dtype=torch.float64)
+        for i in range(6):
+            cov[..., i, i] = sig[i] ** 2
+        for n_, (i, j) in enumerate(((0, 1), (2, 3), (4, 5))):
+            cov[..., i, j] = cov[..., j, i] = cor[n_]
+        energy = d(energy, 1e8).float()
+        total_charge = d(total_charge, 0.0).float()
+        return cls._generate(mean, cov, num_particles, energy, total_charge, device, seed,
+                             first_particle)
+
+    @classmethod
+    def _generate(cls, mean, cov, num_particles, energy, total_charge, device, seed,
+                  first_particle=0):
+        """mean (*shape, 6), cov (*shape, 6, 6) float64 on the host -> beam on ``device``."""
+        device = torch.device(device if device is not None else "cuda")
+        shape = tuple(mean.shape[:-1])
+        B = 1
+        for s_ in shape:
+            B *= s_
+        # a square root of cov in float64: Cholesky, or V sqrt(L) when only semi-definite
+        # (sigma = 0 is legal: MultivariateNormal would reject it, the scale-tril form does not)
+        root, info = torch.linalg.cholesky_ex(cov)
+        bad = info.reshape(-1) != 0
+        if bool(bad.any()):
+            lam, vec = torch.linalg.eigh(cov)
+            alt = vec * torch.sqrt(torch.clamp_min(lam, 0.0)).unsqueeze(-2)
+            root = torch.where(bad.reshape(*shape, 1, 1), alt, root)
+        if seed is None:
+            seed = int(torch.randint(0, 2**62, (1,), dtype=torch.int64).item())
+        N = num_particles
+        ld = (N + 3) & ~3
+        soa = torch.empty((*shape, 6, ld), device=device, dtype=torch.float32)
+        mean_d = mean.reshape(B, 6).to(device=device, dtype=torch.float32).contiguous()
+        root_d = root.reshape(B, 6, 6).to(device=device, dtype=torch.float32).contiguous()
+        L.check(L.lib().lynx_beam_generate(mean_d.data_ptr(), root_d.data_ptr(), B, N,
+                                           int(first_particle), seed, soa.data_ptr(), ld,
+                                           L.current_stream()), "lynx_beam_generate")
+        # particle_beam.py:137-142: equal charges; kept as a stride-0 view (0 bytes)
+        charges = (total_charge.to(device) / N).unsqueeze(-1).expand(*shape, N)
+        return cls.from_soa(soa, N, energy.to(device), charges)
+
+    @classmethod
+    def from_twiss(cls, num_particles=None, beta_x=None, alpha_x=None, emittance_x=None,
+                   beta_y=None, alpha_y=None, emittance_y=None, energy=None, sigma_s=None,
+                   sigma_p=None, cor_s=None, total_charge=None, device=None,
+                   dtype=torch.float32, seed=None, first_particle=0):
+        """particle_beam.py:172-264 (same defaults, incl. num_particles = 1 000 000)."""
+        given = [a for a in (beta_x, alpha_x, emittance_x, beta_y, alpha_y, emittance_y, energy,
+                             sigma_s, sigma_p, cor_s, total_charge) if a is not None]
+        shape = tuple(given[0].shape) if given else (1,)
+        assert all(tuple(a.shape) == shape for a in given), "Arguments must have the same shape."
+        d = lambda a, v: (torch.as_tensor(a, dtype=torch.float64).cpu() if a is not None  # noqa: E731
+                          else torch.full(shape, v, dtype=torch.float64))
+        beta_x, alpha_x, emittance_x = d(beta_x, 0.0), d(alpha_x, 0.0), d(emittance_x, 0.0)
+        beta_y, alpha_y, emittance_y = d(beta_y, 0.0), d(alpha_y, 0.0), d(emittance_y, 0.0)
+        sigma_x = torch.sqrt(beta_x * emittance_x)
+        sigma_xp = torch.sqrt(emittance_x * (1 + alpha_x**2) / beta_x)
+        sigma_y = torch.sqrt(beta_y * emittance_y)
+        sigma_yp = torch.sqrt(emittance_y * (1 + alpha_y**2) / beta_y)
+        zero = torch.zeros(shape, dtype=torch.float64)
+        return cls.from_parameters(
+            num_particles=num_particles if num_particles is not None else 1_000_000,
+            mu_x=zero, mu_xp=zero, mu_y=zero, mu_yp=zero, sigma_x=sigma_x, sigma_xp=sigma_xp,
+            sigma_y=sigma_y, sigma_yp=sigma_yp, sigma_s=d(sigma_s, 1e-6), sigma_p=d(sigma_p, 1e-6),
+            energy=d(energy, 1e8), cor_s=d(cor_s, 0.0), cor_x=-emittance_x * alpha_x,
+            cor_y=-emittance_y * alpha_y, total_charge=d(total_charge, 0.0), device=device,
+            dtype=dtype, seed=seed, first_particle=first_particle)
+
     # ---- storage views
     @property
     def soa(self) -> torch.Tensor:

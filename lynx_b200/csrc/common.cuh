@@ -42,7 +42,8 @@ constexpr int kMapFloats = 42;  // rows 0..5 of the 7x7
 constexpr int kMapStride = 44;  // record stride of one map (16-byte aligned for LDS.128)
 constexpr int kCavFloats = 12;  // per active cavity scalars, see CavScal
 // cavity scalar slots
-enum CavScal { CV_AP = 0, CV_BP, CV_KB, CV_PHI, CV_T566, CV_T556, CV_T555, CV_ON, CV_DE };
+enum CavScal { CV_AP = 0, CV_BP, CV_KB, CV_PHI, CV_T566, CV_T556, CV_T555, CV_ON, CV_DE,
+               CV_SINPHI, CV_COSPHI };
 
 }  // namespace lynx
 

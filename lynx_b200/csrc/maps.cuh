@@ -355,6 +355,8 @@ __device__ inline void cavity_setting(T Lf, T Vf, T phase_deg, T freq, T energy,
     out.sc[CV_BP] = to_float(V * beta0 / (E1 * beta1));
     out.sc[CV_KB] = to_float(beta0 * k);
     out.sc[CV_PHI] = to_float(phi);
+    out.sc[CV_SINPHI] = to_float(sphi);
+    out.sc[CV_COSPHI] = to_float(cphi);
     if (val(dE) > 0.0) {  // :164, per setting
       const D dgamma = V / me;
       const D b03 = beta0 * beta0 * beta0, b13 = beta1 * beta1 * beta1;
@@ -379,12 +381,32 @@ __device__ inline void cavity_setting(T Lf, T Vf, T phase_deg, T freq, T energy,
 // :220-226.  (s0, p0) incoming, lin4 = (R v0)[4].  cos(phi - d) - cos(phi) is taken as
 // 2 sin(phi - d/2) sin(d/2): the subtraction form loses every digit in fp32 for
 // d = s0 beta0 k ~ 1e-4.
+// sin / cos of the half phase slip h = s0 beta0 k / 2.  For a bunch (|h| ~ 1e-5) short series
+// are exact to fp32 and cost a tenth of the library sincosf; the branch is warp-uniform in
+// practice.  Generic scalar types (double, dual numbers) take the library route.
+template <typename T>
+__device__ __forceinline__ void sincos_half_slip(T h, T& s, T& c) {
+  sincos_(h, &s, &c);
+}
+__device__ __forceinline__ void sincos_half_slip(float h, float& s, float& c) {
+  if (fabsf(h) < 0.03125f) {  // truncation: h^8/9! and h^8/8! relative, < 1e-15
+    const float h2 = h * h;
+    s = h * fmaf(h2, fmaf(h2, fmaf(h2, -1.9841270e-4f, 8.3333333e-3f), -0.16666667f), 1.0f);
+    c = fmaf(h2, fmaf(h2, fmaf(h2, -1.3888889e-3f, 4.1666667e-2f), -0.5f), 1.0f);
+  } else {
+    sincosf(h, &s, &c);
+  }
+}
+
 template <typename T>
 __device__ __forceinline__ void cavity_nonlinear(const T* sc, T s0, T p0, T lin4, T lin5, T& s1,
                                                   T& p1) {
   if (val(sc[CV_ON]) != 0.f) {
-    T d = s0 * sc[CV_KB];
-    T dc = 2.f * sin_(sc[CV_PHI] - 0.5f * d) * sin_(0.5f * d);
+    // cos(phi - d) - cos(phi) = 2 sin(phi - h) sin(h), h = d / 2, and
+    // sin(phi - h) = sin(phi) cos(h) - cos(phi) sin(h) with sin / cos(phi) from K1 (fp64)
+    T sh, ch;
+    sincos_half_slip(T(0.5f) * s0 * sc[CV_KB], sh, ch);
+    T dc = 2.f * (sc[CV_SINPHI] * ch - sc[CV_COSPHI] * sh) * sh;
     p1 = fma_(p0, sc[CV_AP], sc[CV_BP] * dc);
     s1 = lin4 + fma_(sc[CV_T566] * p0, p0, fma_(sc[CV_T556] * s0, p0, sc[CV_T555] * s0 * s0));
   } else {
