@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
   const int hist_blocks = a.hist_out ? 1 : 0;
   if (hist_blocks && blockIdx.x == gridDim.x - 1) {
     HistAxis* h = reinterpret_cast<HistAxis*>(a.hist_out);
+    if (threadIdx.x < 4) reinterpret_cast<int*>(a.hist_out)[32 + threadIdx.x] = 0;  // internal bbox cell
     hist_axis_setup(a.hist_ex, a.hist_W, h, threadIdx.x, kComposeTPB);
     hist_axis_setup(a.hist_ey, a.hist_H, h + 1, threadIdx.x, kComposeTPB);
     return;

@@ -10,6 +10,7 @@
 // Algorithmic HBM bytes: 24 B/particle read (+24 B written when outgoing particles are
 // requested); the per-setting record (<1 KB) is read once per CTA into shared memory.
 #include <algorithm>
+#include <mutex>
 #include <cstdlib>
 
 #include "track_common.cuh"
@@ -285,6 +286,40 @@ extern "C" int lynx_track_particles_fwd(
                                        d_workspace, nullptr, stream);
 }
 
+// Library-owned scratch for the histogram replicas, one buffer per device,
+// grown on demand and zeroed once: hist_fold_kernel restores the all-zero invariant after
+// every use.  Returns nullptr when the request is over the cap or the allocation fails (the
+// caller then histograms without replicas).
+static float* replica_scratch(size_t bytes) {
+  static std::mutex mu;
+  static void* buf[64] = {nullptr};
+  static size_t cap[64] = {0};
+  constexpr size_t kMaxBytes = (size_t)2 << 30;
+  int dev = 0;
+  if (bytes > kMaxBytes || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lk(mu);
+  if (cap[dev] < bytes) {
+    if (buf[dev]) {
+      cudaDeviceSynchronize();
+      cudaFree(buf[dev]);
+      buf[dev] = nullptr;
+      cap[dev] = 0;
+    }
+    void* q = nullptr;
+    if (cudaMalloc(&q, bytes) != cudaSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    if (cudaMemset(q, 0, bytes) != cudaSuccess) {
+      cudaFree(q);
+      return nullptr;
+    }
+    buf[dev] = q;
+    cap[dev] = bytes;
+  }
+  return reinterpret_cast<float*>(buf[dev]);
+}
+
 extern "C" int lynx_track_particles_fwd_bbox(
     const lynx_program_t* p, const float* d_params, int64_t B, const float* d_in_soa,
     int64_t in_row_stride, int64_t ld_in, int64_t N, float* d_out_soa, int64_t ld_out,
@@ -359,6 +394,19 @@ extern "C" int lynx_track_particles_fwd_bbox(
   a.ey = d_edges_y;
   a.hist = reinterpret_cast<const HistAxis*>(hist_ws);
   a.bbox = has_img ? d_screen_bbox : nullptr;
+  // histogram replicas: LYNX_HIST_REPLICAS copies (default 8, 1 = off) once the launch has at
+  // least LYNX_HIST_REPLICAS_MIN particle rows x particles (the fold pass costs ~3 us)
+  static const int n_rep_env = [] { const char* e = getenv("LYNX_HIST_REPLICAS"); return e ? atoi(e) : 8; }();
+  static const long long rep_min = [] { const char* e = getenv("LYNX_HIST_REPLICAS_MIN"); return e ? atoll(e) : 4000000LL; }();
+  a.rep = nullptr;
+  a.n_rep = 1;
+  if (has_img && fuse_zero && !(W & 3) && n_rep_env > 1 && n_rep_env <= 64 && B * N >= rep_min) {
+    a.rep = replica_scratch(img_bytes * (size_t)(n_rep_env - 1));
+    if (a.rep) {
+      a.n_rep = n_rep_env;
+      if (!a.bbox) a.bbox = reinterpret_cast<int*>(hist_ws) + 32;  // zeroed by K1's last block
+    }
+  }
   a.stamp = bbox_adjacent ? reinterpret_cast<unsigned long long*>(d_screen_bbox + 8) : nullptr;
   a.mom = d_moment_sums;
   a.B = B;
@@ -374,7 +422,9 @@ extern "C" int lynx_track_particles_fwd_bbox(
     const int r = launch_track_pipe(a, moment_mode, d_out_soa != nullptr, p->sm_count, st);
     if (r <= 0) return r;
   }
-  if (a.bbox) return LYNX_E_BADPROGRAM;  // bounding box is a feature of the pipelined kernel
+  if (d_screen_bbox) return LYNX_E_BADPROGRAM;  // bounding box is a feature of the pipelined kernel
+  a.bbox = nullptr;
+  a.n_rep = 1;
   const int64_t n_tiles = (N + kTile - 1) / kTile;
   int64_t per_b = (2LL * p->sm_count + B - 1) / B;
   if (per_b < 1) per_b = 1;

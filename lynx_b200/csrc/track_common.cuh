@@ -28,9 +28,11 @@ struct TrackArgs {
   int W, H;
   const float* ex;
   const float* ey;
-  const HistAxis* hist;
-  unsigned long long* stamp;  // [2] debug %globaltimer cell in a symmetric slot's box, or null
-  int tile;  // particles per pipeline tile (K2 pipe variant; set by its launcher)  // [2] x, y geometry written by K1 (pipelined kernel)
+  const HistAxis* hist;  // [2] x, y geometry written by K1 (pipelined kernel)
+  unsigned long long* stamp;  // [4] debug %globaltimer cell in a symmetric slot's box, or null
+  int tile;     // particles per pipeline tile (K2 pipe variant; set by its launcher)
+  float* rep;   // histogram replicas 1..n_rep-1: [n_rep - 1][B][H][W], all zero on entry
+  int n_rep;    // CTA x histograms into replica x % n_rep (0 = img); folded by hist_fold_kernel
   int* bbox;             // nullable: [4] max(W - ix), max(ix + 1), max(H - iy), max(iy + 1)
   double* mom;
   int64_t B;

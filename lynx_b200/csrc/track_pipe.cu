@@ -192,9 +192,6 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
       issue_tile(it, t);
   }
 
-  // let a programmatically-serialized follower (the multi-GPU exchange kernel) become
-  // resident now; it waits (griddepcontrol.wait) for this grid to finish
-  asm volatile("griddepcontrol.launch_dependents;");
   // ---- everyone: plan, cleared window (independent of K1) ...
   for (int i = tid; i < a.n_plan; i += kPipeThreads) plan[i] = a.plan[i];
   for (int i = tid; i < a.n_snap * 2; i += kPipeThreads) s_bpm[i] = 0.0;
@@ -267,7 +264,12 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
     const float* ex = a.ex;
     const float* ey = a.ey;
     HistAxis hx{0.f, 0.f, 0.f, 1.f}, hy{0.f, 0.f, 0.f, 1.f};
-    float* img_b = a.img ? a.img + b * (int64_t)a.W * a.H : nullptr;
+    // replicated histogram: the hot bins of a focused beam sit in a few
+    // hundred L2 lines whose slices saturate; CTA x adds into copy x % n_rep
+    const int rep_i = a.n_rep > 1 ? (int)(blockIdx.x % (unsigned)a.n_rep) : 0;
+    float* img_b = !a.img ? nullptr
+                   : rep_i == 0 ? a.img + b * (int64_t)a.W * a.H
+                                : a.rep + ((int64_t)(rep_i - 1) * a.B + b) * (int64_t)a.W * a.H;
     if (img_b) {
       hx = a.hist[0];
       hy = a.hist[1];
@@ -474,6 +476,12 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
       }
     }
   }
+  // Let a programmatically-serialized follower (histogram fold, multi-GPU exchange kernel)
+  // start launching only now, when this CTA's streaming work is done: issued at the top of
+  // the kernel, the follower's CTAs became resident while K1 still ran and squatted on SMs
+  // whose K2 CTA had not been placed yet (they wait for this whole grid) -- K2 then ran in
+  // two waves (+20..40 us, measured).
+  asm volatile("griddepcontrol.launch_dependents;");
   // ---- CTA epilogue
   if (a.stamp && tid == 64 && blockIdx.x == 0 && b == 0) {
     unsigned long long t;
@@ -502,6 +510,53 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   }
 }
 
+// Folds the histogram replicas into the image over the bounding box of the touched bins and
+// leaves the replicas zero again (their invariant between calls).  Launched behind K2 with
+// programmatic stream serialization.
+constexpr int kFoldTPB = 256;
+__global__ void __launch_bounds__(kFoldTPB) hist_fold_kernel(float* __restrict__ img,
+                                                              float* __restrict__ rep, int n_rep,
+                                                              int64_t B, int W, int H,
+                                                              const int* __restrict__ bbox) {
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const int v0 = __ldcg(bbox), v1 = __ldcg(bbox + 1), v2 = __ldcg(bbox + 2), v3 = __ldcg(bbox + 3);
+  if (v1 == 0 || v3 == 0) return;
+  const int r0 = H - v3, r1 = v2, c0 = (W - v0) & ~3, c1 = min((v1 + 3) & ~3, W);
+  const int w4 = (c1 - c0) >> 2, nr = r1 - r0;
+  const int64_t n = B * (int64_t)nr * w4, plane = B * (int64_t)W * H;
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int64_t t = (int64_t)blockIdx.x * kFoldTPB + threadIdx.x; t < n;
+       t += (int64_t)gridDim.x * kFoldTPB) {
+    const int64_t rr = t / w4;
+    const int c = c0 + ((int)(t - rr * w4) << 2);
+    const int64_t bq = rr / nr;
+    const int r = r0 + (int)(rr - bq * nr);
+    const int64_t i = (bq * H + r) * (int64_t)W + c;
+    // every load of a batch is issued before the first store: with one 16-B load in flight
+    // per thread the pass was latency-bound at 0.3 TB/s (46 us for 14 MB, measured)
+    float4 s = *reinterpret_cast<const float4*>(img + i);
+    for (int q0 = 0; q0 < n_rep - 1; q0 += 8) {
+      float4 v[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        v[q] = (q0 + q < n_rep - 1) ? __ldcg(reinterpret_cast<const float4*>(rep + (q0 + q) * plane + i))
+                                    : zero;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        s.x += v[q].x;
+        s.y += v[q].y;
+        s.z += v[q].z;
+        s.w += v[q].w;
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        if (q0 + q < n_rep - 1) *reinterpret_cast<float4*>(rep + (q0 + q) * plane + i) = zero;
+    }
+    *reinterpret_cast<float4*>(img + i) = s;
+  }
+}
+
 template <int MOM, bool HAS_OUT, int STAGES>
 static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, uint32_t win_words,
                        cudaStream_t st) {
@@ -527,6 +582,18 @@ static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, uint32_t win_
   {
     ProfileScope ps(1, st);
     err = cudaLaunchKernelEx(&cfg, k, a, win_words);
+    static const bool no_fold = [] { const char* e = getenv("LYNX_NO_FOLD"); return e && e[0] == '1'; }();
+    if (err == cudaSuccess && a.n_rep > 1 && !no_fold) {  // the fold is part of the histogram's cost
+      int dev = 0, sms = 148;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      cfg.gridDim = dim3((unsigned)(2 * sms));
+      cfg.blockDim = dim3(kFoldTPB);
+      cfg.dynamicSmemBytes = 0;
+      err = cudaLaunchKernelEx(&cfg, hist_fold_kernel, a.img, a.rep, a.n_rep, a.B, a.W, a.H,
+                               (const int*)a.bbox);
+      count_launch();
+    }
   }
   count_launch();
   return err == cudaSuccess ? LYNX_OK : LYNX_E_LAUNCH;

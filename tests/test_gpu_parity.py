@@ -480,3 +480,25 @@ def test_parameter_beam_screen_reading():
     assert ((got - want).abs() / peak).max().item() < 2e-5
     # x is flipped as in the reference: the brightest column sits where the oracle has it
     assert torch.equal(got.sum(dim=2).argmax(dim=1), want.sum(dim=2).argmax(dim=1))
+
+
+def test_screen_tests_with_histogram_replicas():
+    """The replicated-histogram path (csrc/track_pipe.cu hist_fold_kernel) only switches on
+    for launches of >= 4 M particles; rerun every screen test of this suite (and the host /
+    golden ones) in a subprocess with the threshold lowered to 1 so the small parity
+    cases exercise it, twice in one process so the 'replicas are zero again' invariant
+    is checked too."""
+    import os
+    import subprocess
+    import sys
+
+    env = dict(os.environ, LYNX_HIST_REPLICAS_MIN="1")
+    if env.get("LYNX_REPLICA_SUBPROCESS"):
+        pytest.skip("already inside the replica subprocess")
+    env["LYNX_REPLICA_SUBPROCESS"] = "1"
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", "-k", "screen or host_buffer or golden",
+           os.path.join(here, "test_gpu_parity.py"), os.path.join(here, "test_golden_files.py"),
+           os.path.join(here, "test_gpu_parity.py")]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]

@@ -21,6 +21,8 @@ if a.mode == "screen1m":
     w = bench.ParticleWorkload(1_000_000, dev, seed=1002, screen=True)
 elif a.mode == "screen32m":
     w = bench.ParticleWorkload(32_000_000, dev, seed=7, screen=True)
+elif a.mode == "cfg4screen":
+    w = bench.ParticleWorkload(12_500_000, dev, seed=1004, screen=True, lattice="cfg4")
 elif a.mode == "out32m":
     w = bench.ParticleWorkload(32_000_000, dev, seed=7, screen=False, want_out=True)
 elif a.mode == "outmom32m":
