@@ -475,13 +475,13 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
         atomicMax(a.bbox + 3, bb3);
       }
     }
+    // Let a programmatically-serialized follower (histogram fold, multi-GPU exchange kernel)
+    // start launching once the consumers of every CTA are through their tiles.  The first
+    // thread of a CTA to execute this counts for the CTA, so it must not sit on a path the
+    // loader warp reaches early; issued at the top of the kernel the follower's CTAs (which
+    // only wait for this grid) became resident before some K2 CTAs were placed.
+    asm volatile("griddepcontrol.launch_dependents;");
   }
-  // Let a programmatically-serialized follower (histogram fold, multi-GPU exchange kernel)
-  // start launching only now, when this CTA's streaming work is done: issued at the top of
-  // the kernel, the follower's CTAs became resident while K1 still ran and squatted on SMs
-  // whose K2 CTA had not been placed yet (they wait for this whole grid) -- K2 then ran in
-  // two waves (+20..40 us, measured).
-  asm volatile("griddepcontrol.launch_dependents;");
   // ---- CTA epilogue
   if (a.stamp && tid == 64 && blockIdx.x == 0 && b == 0) {
     unsigned long long t;
