@@ -263,6 +263,8 @@ float lynx_profile_last_ms(int which);
  * 3: rectangle written, 4: K2 past its wait on K1, 5: K2 CTA 0 done}]; NULL switches it
  * off.  Device buffer of 8192 uint64. */
 void lynx_exchange_trace(unsigned long long* d_stamps);
+/* Debug: a one-thread kernel that writes %globaltimer (ns) to *d_cell. */
+void lynx_debug_stamp(unsigned long long* d_cell, lynx_stream_t stream);
 
 /* ---- host-buffer entry points (what a NumPy / host-array binding calls) ------------
  * Same semantics as the device launchers, but every pointer is HOST memory (pinned for

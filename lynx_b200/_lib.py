@@ -77,6 +77,7 @@ SIGNATURES = {
     "lynx_profile_enable": (None, [C.c_int]),
     "lynx_profile_last_ms": (C.c_float, [C.c_int]),
     "lynx_exchange_trace": (None, [_vp]),
+    "lynx_debug_stamp": (None, [_vp, _vp]),
     "lynx_host_ctx_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
     "lynx_host_ctx_destroy": (None, [_vp]),
     "lynx_host_ctx_set_option": (C.c_int, [_vp, _i32, _i32]),

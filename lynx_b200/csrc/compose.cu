@@ -203,6 +203,7 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
     const int r = compose_warp_launch(p, a, st);
     if (r <= 0) return r;
   }
+  static const int zero_blocks_per_sm = [] { const char* e = getenv("LYNX_ZERO_BLOCKS"); return e ? atoi(e) : 2; }();
   const int n_cols = (int)p->col_offset.size();
   const size_t budget = 40 * 1024;
   const size_t ops_bytes = a.n_ops * sizeof(DevOp);
@@ -216,7 +217,7 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   const size_t smem = staged ? ops_bytes + (size_t)n_cols * S * 4 : 0;
   unsigned blocks = (unsigned)((B + S - 1) / S);
   if (a.zero_vec4 > 0)
-    blocks += (unsigned)std::min<int64_t>(2 * p->sm_count, (a.zero_vec4 + kComposeTPB - 1) / kComposeTPB);
+    blocks += (unsigned)std::min<int64_t>(zero_blocks_per_sm * p->sm_count, (a.zero_vec4 + kComposeTPB - 1) / kComposeTPB);
   if (hist_out) blocks += 1;
   {
     ProfileScope ps(0, st);

@@ -206,6 +206,17 @@ extern "C" float* lynx_screen_symm_image(void* d_symm_base, int32_t slot, int64_
                                   kBboxBytes);
 }
 
+namespace lynx {
+__global__ void debug_stamp_kernel(unsigned long long* d) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  *d = t;
+}
+}  // namespace lynx
+extern "C" void lynx_debug_stamp(unsigned long long* d_cell, lynx_stream_t stream) {
+  lynx::debug_stamp_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(d_cell);
+}
+
 extern "C" void lynx_exchange_trace(unsigned long long* d_stamps) { lynx::g_exchange_trace = d_stamps; }
 
 extern "C" int lynx_screen_allreduce(void* const* peer_bases, int32_t world, int32_t rank,

@@ -11,8 +11,11 @@
 // requested); the per-setting record (<1 KB) is read once per CTA into shared memory.
 #include <algorithm>
 #include <mutex>
+#include <utility>
+#include <vector>
 #include <cstdlib>
 
+#include "walk.cuh"
 #include "track_common.cuh"
 
 namespace lynx {
@@ -320,6 +323,25 @@ static float* replica_scratch(size_t bytes) {
   return reinterpret_cast<float*>(buf[dev]);
 }
 
+// Persistent state of the fused kernel's grid barrier: 2 words per stream (launches on one
+// stream are serialised, so they can share it; the barrier leaves the state reusable).
+static unsigned int* grid_barrier_state(cudaStream_t st) {
+  static std::mutex mu;
+  static std::vector<std::pair<std::pair<int, cudaStream_t>, unsigned int*>> table;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+  std::lock_guard<std::mutex> lk(mu);
+  for (auto& e : table)
+    if (e.first.first == dev && e.first.second == st) return e.second;
+  void* q = nullptr;
+  if (cudaMalloc(&q, 256) != cudaSuccess || cudaMemset(q, 0, 256) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  table.push_back({{dev, st}, reinterpret_cast<unsigned int*>(q)});
+  return reinterpret_cast<unsigned int*>(q);
+}
+
 extern "C" int lynx_track_particles_fwd_bbox(
     const lynx_program_t* p, const float* d_params, int64_t B, const float* d_in_soa,
     int64_t in_row_stride, int64_t ld_in, int64_t N, float* d_out_soa, int64_t ld_out,
@@ -359,21 +381,9 @@ extern "C" int lynx_track_particles_fwd_bbox(
   // (exchange.cu): one fused zeroing range covers both
   const bool bbox_adjacent = d_screen_bbox && has_img && fuse_zero &&
                              (char*)d_screen_bbox + 64 == (char*)d_screen_img;
-  if (d_screen_bbox && !bbox_adjacent) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_bbox, 0, 16, st));
-  // accumulators are cleared BEFORE K1 so that K1 -> K2 stay adjacent in the stream
-  // (programmatic dependent launch overlaps K2's prologue with K1)
-  if (p->n_bpm_slots > 0)
-    LYNX_CUDA_OK(cudaMemsetAsync(d_bpm_sums, 0, sizeof(double) * 2 * p->n_bpm_slots * B, st));
-  if (has_img && !fuse_zero) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
-  if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
-  int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
-                          records, nullptr, d_energy_out,
-                          fuse_zero ? (bbox_adjacent ? (void*)d_screen_bbox : (void*)d_screen_img) : nullptr,
-                          fuse_zero ? img_bytes + (bbox_adjacent ? 64 : 0) : 0, st, has_img ? d_edges_x : nullptr,
-                          has_img ? d_edges_y : nullptr, W, H, has_img ? hist_ws : nullptr);
-  if (rc != LYNX_OK) return rc;
+  if (B > 65535) return LYNX_E_BADARG;
 
-  TrackArgs a;
+  TrackArgs a{};
   a.in = d_in_soa;
   a.in_row_stride = in_row_stride * 6 * ld_in;
   a.ld_in = ld_in;
@@ -394,30 +404,71 @@ extern "C" int lynx_track_particles_fwd_bbox(
   a.ey = d_edges_y;
   a.hist = reinterpret_cast<const HistAxis*>(hist_ws);
   a.bbox = has_img ? d_screen_bbox : nullptr;
+  a.stamp = bbox_adjacent ? reinterpret_cast<unsigned long long*>(d_screen_bbox + 8) : nullptr;
+  a.mom = d_moment_sums;
+  a.B = B;
+  static const int dbg = [] { const char* e = getenv("LYNX_DBG"); return e ? atoi(e) : 0; }();
+  a.dbg = dbg;
+  // fused composer fields (track_pipe_kernel<.., OPS>)
+  a.ops = p->d_ops;
+  a.n_ops = (int)p->dev_ops.size();
+  a.final_stage = p->final_stage;
+  a.n_cols = (int)p->col_offset.size();
+  a.col_offset = p->d_col_offset;
+  a.col_stride = p->d_col_stride;
+  a.params = d_params;
+  a.energy_in = d_energy_in;
+  a.energy_out = d_energy_out;
+  a.off_cav = p->off_cav;
+  a.off_centre = p->off_centre;
+  a.off_screen = p->off_screen;
   // histogram replicas: LYNX_HIST_REPLICAS copies (default 8, 1 = off) once the launch has at
-  // least LYNX_HIST_REPLICAS_MIN particle rows x particles (the fold pass costs ~3 us)
+  // least LYNX_HIST_REPLICAS_MIN particle rows x particles (the fold pass costs ~8 us)
   static const int n_rep_env = [] { const char* e = getenv("LYNX_HIST_REPLICAS"); return e ? atoi(e) : 8; }();
   static const long long rep_min = [] { const char* e = getenv("LYNX_HIST_REPLICAS_MIN"); return e ? atoll(e) : 4000000LL; }();
   a.rep = nullptr;
   a.n_rep = 1;
   if (has_img && fuse_zero && !(W & 3) && n_rep_env > 1 && n_rep_env <= 64 && B * N >= rep_min) {
     a.rep = replica_scratch(img_bytes * (size_t)(n_rep_env - 1));
-    if (a.rep) {
-      a.n_rep = n_rep_env;
-      if (!a.bbox) a.bbox = reinterpret_cast<int*>(hist_ws) + 32;  // zeroed by K1's last block
-    }
+    if (a.rep) a.n_rep = n_rep_env;
   }
-  a.stamp = bbox_adjacent ? reinterpret_cast<unsigned long long*>(d_screen_bbox + 8) : nullptr;
-  a.mom = d_moment_sums;
-  a.B = B;
-  static const int dbg = [] { const char* e = getenv("LYNX_DBG"); return e ? atoi(e) : 0; }();
-  a.dbg = dbg;
+  const bool internal_bbox = a.n_rep > 1 && !a.bbox;
+  if (internal_bbox) a.bbox = reinterpret_cast<int*>(hist_ws) + 32;
 
-  if (B > 65535) return LYNX_E_BADARG;
+  // accumulators are cleared first so that the kernels stay adjacent in the stream
+  if (p->n_bpm_slots > 0)
+    LYNX_CUDA_OK(cudaMemsetAsync(d_bpm_sums, 0, sizeof(double) * 2 * p->n_bpm_slots * B, st));
+  if (has_img && !fuse_zero) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
+  if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
+
   static const bool force_ldg = [] {
     const char* e = getenv("LYNX_K2");
     return e && e[0] == 'l';
   }();
+  // ---- fused path: no K1 launch; every CTA composes its own setting (B <= SM count)
+  static const bool no_fused = [] { const char* e = getenv("LYNX_FUSED"); return !(e && e[0] == '1'); }();
+  if (!force_ldg && !no_fused && B <= p->sm_count) {
+    a.zero_img = fuse_zero ? 1 : 0;
+    a.grid_bar = fuse_zero ? grid_barrier_state(st) : nullptr;
+    if (!fuse_zero || a.grid_bar) {
+      if (a.bbox && !a.zero_img) LYNX_CUDA_OK(cudaMemsetAsync(a.bbox, 0, 16, st));
+      const bool light = (p->op_mask & ~kOpsLight) == 0;
+      const int r = launch_track_pipe(a, moment_mode, d_out_soa != nullptr, p->sm_count, st,
+                                      light ? kOpsLight : kOpsAll);
+      if (r <= 0) return r;
+    }
+  }
+  a.zero_img = 0;
+  a.grid_bar = nullptr;
+
+  // ---- K1 (records, image zeroing, histogram geometry) then K2
+  if (d_screen_bbox && !bbox_adjacent) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_bbox, 0, 16, st));
+  int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
+                          records, nullptr, d_energy_out,
+                          fuse_zero ? (bbox_adjacent ? (void*)d_screen_bbox : (void*)d_screen_img) : nullptr,
+                          fuse_zero ? img_bytes + (bbox_adjacent ? 64 : 0) : 0, st, has_img ? d_edges_x : nullptr,
+                          has_img ? d_edges_y : nullptr, W, H, has_img ? hist_ws : nullptr);
+  if (rc != LYNX_OK) return rc;
   if (!force_ldg) {
     const int r = launch_track_pipe(a, moment_mode, d_out_soa != nullptr, p->sm_count, st);
     if (r <= 0) return r;

@@ -37,6 +37,18 @@ struct TrackArgs {
   double* mom;
   int64_t B;
   int dbg;  // experiments only (LYNX_DBG): bit0 = skip the screen atomics
+  // ---- fused composer (track_pipe_kernel<.., OPS != 0>): every CTA walks its own setting's
+  //      lattice into the shared-memory record; no K1 launch, no record round trip
+  const DevOp* ops;
+  int n_ops, final_stage, n_cols;
+  const int64_t* col_offset;
+  const int32_t* col_stride;
+  const float* params;
+  const float* energy_in;
+  float* energy_out;
+  int off_cav, off_centre, off_screen;
+  unsigned int* grid_bar;  // [2] arrival count, generation (library-owned, self-resetting)
+  int zero_img;            // the kernel zeroes the image (+ bbox) itself, behind a grid barrier
 };
 
 __device__ __forceinline__ float4 ld_stream(const float* p) {
@@ -143,7 +155,7 @@ __host__ __device__ constexpr int tri(int i, int j) { return i * 6 - i * (i - 1)
 
 // TMA-bulk pipelined variant (track_pipe.cu); returns 1 if it cannot take the problem.
 int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_count,
-                      cudaStream_t st);
+                      cudaStream_t st, int fused_ops = 0);
 
 // Accumulate shifted first / second moments of one particle (d = v - centre).
 template <int MOM>

@@ -24,6 +24,7 @@
 #include <cstdio>
 #include <cstdlib>
 
+#include "compose_common.cuh"
 #include "track_common.cuh"
 
 namespace lynx {
@@ -88,11 +89,12 @@ __device__ __forceinline__ void fence_mbar_init() {
 
 struct PipeSmemLayout {
   // byte offsets from the (128-B aligned) dynamic shared memory base
-  uint32_t rec, plan, bpm, bars, win, total;
+  uint32_t rec, plan, bpm, bars, win, ops, vals, total;
 };
 
 __host__ __device__ inline PipeSmemLayout pipe_layout(int stages, int rec_floats, int n_plan,
-                                                      int n_snap, uint32_t win_words) {
+                                                      int n_snap, uint32_t win_words,
+                                                      int fused_ops = 0, int fused_cols = 0) {
   PipeSmemLayout L;
   uint32_t o = (uint32_t)(sizeof(float) * kStageFloats * stages);
   L.rec = o;
@@ -108,6 +110,11 @@ __host__ __device__ inline PipeSmemLayout pipe_layout(int stages, int rec_floats
   o = (o + 15u) & ~15u;
   L.win = o;
   o += 4u * win_words;
+  o = (o + 15u) & ~15u;
+  L.ops = o;  // fused composer: the program and this setting's parameter columns
+  o += (uint32_t)sizeof(DevOp) * fused_ops;
+  L.vals = o;
+  o += 4u * fused_cols;
   L.total = o;
   return L;
 }
@@ -119,6 +126,53 @@ struct HistWindow {
 };
 
 __device__ __forceinline__ void consumers_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory"); }
+
+// Histogram update as an explicit reduction: in a kernel that also contains acquire / release
+// synchronisation (the fused variant's grid barrier) nvcc lowers a result-less atomicAdd to
+// ATOMG instead of REDG, which cost 35 % of the 32 M-particle screen kernel (measured).
+__device__ __forceinline__ void red_add_f32(float* p, float v) {
+  asm volatile("red.relaxed.gpu.global.add.f32 [%0], %1;" ::"l"(p), "f"(v));
+}
+
+__device__ __forceinline__ void dbg_stamp(const TrackArgs& a, int slot, bool who) {
+  if ((a.dbg & 2) && who && blockIdx.x == 0 && blockIdx.y == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    reinterpret_cast<unsigned long long*>(const_cast<HistAxis*>(a.hist))[16 + slot] = t;
+  }
+}
+
+// OR-reduction over the consumer threads (named barrier 1).
+__device__ __forceinline__ bool consumers_or(bool pred) {
+  int r;
+  asm volatile(
+      "{ .reg .pred p, q; setp.ne.b32 q, %1, 0; barrier.red.or.pred p, 1, %2, q; selp.b32 %0, 1, 0, p; }"
+      : "=r"(r)
+      : "r"((int)pred), "n"(kConsumers)
+      : "memory");
+  return r != 0;
+}
+
+// Grid-wide barrier for the fused variant, executed by ONE thread per CTA (the caller brackets
+// it with CTA-level barriers).  All CTAs of the launch are co-resident (grid <= SM count, one
+// CTA per SM, cooperative launch).  bar[0] counts arrivals and is reset by the last arriver,
+// bar[1] is the generation the waiters spin on: the state is valid again when the launch ends.
+__device__ __forceinline__ void grid_barrier_one_thread(unsigned int* bar, unsigned int n_ctas) {
+  unsigned int gen;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(gen) : "l"(bar + 1) : "memory");
+  __threadfence();  // this CTA's stores (ordered before by the CTA barrier) before the arrival
+  const unsigned int old = atomicAdd(bar, 1u);
+  if (old == n_ctas - 1) {
+    bar[0] = 0u;
+    __threadfence();
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(bar + 1), "r"(gen + 1u) : "memory");
+  } else {
+    unsigned int g;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(bar + 1) : "memory");
+    } while (g == gen);
+  }
+}
 
 // Flush the window into the image with coalesced REDs and clear it (consumer threads).
 __device__ __forceinline__ void window_flush(uint32_t* __restrict__ win, const HistWindow& hw,
@@ -138,10 +192,51 @@ __device__ __forceinline__ void window_flush(uint32_t* __restrict__ win, const H
   }
 }
 
-template <int MOM, bool HAS_OUT, int STAGES>
+// The composer of the fused variant: K1's walk (compose_common.cuh) for one setting, straight
+// into the shared-memory record.  Not inlined: one thread per CTA runs it once, and its
+// register needs (127 in K1) must not leak into the allocation of the streaming loop.
+struct FusedWalkArgs {
+  const DevOp* ops;
+  const float* vals;
+  float* rec;
+  const float* seed;  // particle 0 of the row: plane i at seed[i * ld]
+  int64_t ld;
+  const float* energy_in;
+  float* energy_out;  // nullable
+  int n_ops, final_stage, final_centre, off_cav, off_centre, off_screen;
+};
+
+template <int OPS>
+__device__ __noinline__ void fused_walk(FusedWalkArgs w) {
+  RecordSink sink;
+  sink.rec = w.rec;
+  sink.maps_out = nullptr;
+  sink.off_cav = w.off_cav;
+  sink.off_centre = w.off_centre;
+  sink.off_screen = w.off_screen;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) sink.ctr[i] = __ldg(w.seed + i * w.ld);
+  float energy = __ldg(w.energy_in);
+  SmemParamView P{w.vals, 1, 0};
+  walk_program<OPS>(w.ops, w.n_ops, w.final_stage, P, energy, sink);
+#pragma unroll
+  for (int i = 0; i < 6; ++i) w.rec[w.final_centre + i] = sink.ctr[i];
+  if (w.energy_out) *w.energy_out = energy;
+}
+
+// OPS == 0: the per-setting record comes from K1 (compose.cu) through global memory.
+// OPS != 0 (opcode set, walk.cuh): FUSED composer -- one thread of every CTA walks the CTA's
+// setting into the shared-memory record while the first tiles are in flight and the consumer
+// warps zero the CTA's slice of the image and check the edge tables; one grid barrier orders
+// the zeroing before the first RED.  At 1 M particles the K1 launch, its completion and the
+// record round trip were a third of the step.
+template <int MOM, bool HAS_OUT, int STAGES, int OPS = 0>
 __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a, uint32_t win_words) {
   extern __shared__ __align__(128) unsigned char psm[];
-  const PipeSmemLayout L = pipe_layout(STAGES, a.rec_floats, a.n_plan, a.n_snap, win_words);
+  constexpr bool kFused = OPS != 0;
+  if (kFused) dbg_stamp(a, 10, threadIdx.x == 0);  // first instruction of CTA 0
+  const PipeSmemLayout L = pipe_layout(STAGES, a.rec_floats, a.n_plan, a.n_snap, win_words,
+                                       kFused ? a.n_ops : 0, kFused ? a.n_cols : 0);
   float* stages = reinterpret_cast<float*>(psm);
   float* rec = reinterpret_cast<float*>(psm + L.rec);
   PlanItem* plan = reinterpret_cast<PlanItem*>(psm + L.plan);
@@ -163,16 +258,6 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   const int64_t n_tiles = (a.N + tile - 1) / tile;
   const float* in_b = a.in + b * a.in_row_stride;
 
-  if (tid == 0) {
-    for (int s = 0; s < STAGES; ++s) {
-      mbar_init(full + s, 1);
-      mbar_init(empty + s, HAS_OUT ? 1 : kConsumerWarps);
-      mbar_init(done + s, kConsumerWarps);
-    }
-    fence_mbar_init();
-  }
-  __syncthreads();
-
   auto issue_tile = [&](int it, int64_t t) {
     const int s = it % STAGES;
     const int64_t p0 = t * tile;
@@ -185,32 +270,131 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
       bulk_g2s(dst + k * kPipeTile, in_b + k * a.ld_in + p0, bytes, full + s);
   };
 
-  // ---- prologue: request this CTA's first tiles before anything else touches memory
+  // ---- prologue: barriers, then this CTA's first tiles are requested before anything else
+  //      touches memory.  Thread 0 initialises the barriers it then arms itself; every other
+  //      thread first touches them after a CTA-wide barrier below.
   if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, HAS_OUT ? 1 : kConsumerWarps);
+      mbar_init(done + s, kConsumerWarps);
+    }
+    fence_mbar_init();
     int it = 0;
     for (int64_t t = blockIdx.x; t < n_tiles && it < STAGES; t += gridDim.x, ++it)
       issue_tile(it, t);
+    s_win = HistWindow{0, 0, 0, 0};
   }
-
-  // ---- everyone: plan, cleared window (independent of K1) ...
-  for (int i = tid; i < a.n_plan; i += kPipeThreads) plan[i] = a.plan[i];
-  for (int i = tid; i < a.n_snap * 2; i += kPipeThreads) s_bpm[i] = 0.0;
-  for (uint32_t i = tid; i < win_words; i += kPipeThreads) win[i] = 0u;
-  if (tid == 0) s_win = HistWindow{0, 0, 0, 0};
-  // ... then wait for the K1 grid (records + histogram geometry written, image zeroed) --
-  // a no-op unless this kernel was launched with programmatic stream serialization
-  asm volatile("griddepcontrol.wait;" ::: "memory");
-  if (a.stamp && tid == 0 && blockIdx.x == 0 && b == 0) {  // exchange trace (exchange.cu)
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    a.stamp[0] = t;
-    a.stamp[2] = reinterpret_cast<const unsigned long long*>(a.hist)[8];  // K1 block 0 started  // K1 complete, K2 starts
+  if constexpr (!kFused) {
+    // ---- everyone: plan, cleared window (independent of K1) ...
+    for (int i = tid; i < a.n_plan; i += kPipeThreads) plan[i] = a.plan[i];
+    for (int i = tid; i < a.n_snap * 2; i += kPipeThreads) s_bpm[i] = 0.0;
+    for (uint32_t i = tid; i < win_words; i += kPipeThreads) win[i] = 0u;
   }
-  {
+  __shared__ HistAxis s_hist[2];
+  if constexpr (!kFused) {
+    // ... then wait for the K1 grid (records + histogram geometry written, image zeroed) --
+    // a no-op unless this kernel was launched with programmatic stream serialization
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (a.stamp && tid == 0 && blockIdx.x == 0 && b == 0) {  // exchange trace (exchange.cu)
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      a.stamp[0] = t;  // K1 complete, K2 starts
+      a.stamp[2] = reinterpret_cast<const unsigned long long*>(a.hist)[8];  // K1 block 0 started
+    }
     const float* src = a.records + b * a.rec_floats;
     for (int i = tid; i < a.rec_floats; i += kPipeThreads) rec[i] = src[i];
+    if (a.img && tid < 2) s_hist[tid] = a.hist[tid];
+    __syncthreads();
+  } else {
+    if (a.stamp && tid == 0 && blockIdx.x == 0 && b == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      a.stamp[0] = t;
+      a.stamp[2] = t;
+    }
+    dbg_stamp(a, 0, tid == 0);
+    if ((a.dbg & 2) && tid == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      unsigned long long* d = reinterpret_cast<unsigned long long*>(const_cast<HistAxis*>(a.hist));
+      atomicMin(d + 16 + 8, t);
+      atomicMax(d + 16 + 9, t);
+    }
+    // Three independent strands run concurrently from the first instruction on; one CTA
+    // barrier joins them:
+    //   thread 0   barriers + first tiles (above)
+    //   warp 1     program + this setting's parameter columns -> shared memory, then the walk
+    //   consumers  plan, BPM accumulators, image slice zeroed, edge tables checked, grid barrier
+    DevOp* s_ops = reinterpret_cast<DevOp*>(psm + L.ops);
+    float* s_vals = reinterpret_cast<float*>(psm + L.vals);
+    if (warp == 1) {
+      for (int i = lane; i < a.n_ops * (int)(sizeof(DevOp) / 4); i += 32)
+        reinterpret_cast<float*>(s_ops)[i] = reinterpret_cast<const float*>(a.ops)[i];
+      for (int c = lane; c < a.n_cols; c += 32)
+        s_vals[c] = __ldg(a.params + __ldg(a.col_offset + c) + b * (int64_t)__ldg(a.col_stride + c));
+      __syncwarp();
+      dbg_stamp(a, 1, lane == 0);
+      // the walk (K1's arithmetic, compose_common.cuh), straight into shared memory
+      if (lane == 0) {
+        FusedWalkArgs w;
+        w.ops = s_ops;
+        w.vals = s_vals;
+        w.rec = rec;
+        w.seed = in_b;
+        w.ld = a.ld_in;
+        w.energy_in = a.energy_in + b;
+        w.energy_out = (blockIdx.x == 0 && a.energy_out) ? a.energy_out + b : nullptr;
+        w.n_ops = a.n_ops;
+        w.final_stage = a.final_stage;
+        w.final_centre = a.final_centre;
+        w.off_cav = a.off_cav;
+        w.off_centre = a.off_centre;
+        w.off_screen = a.off_screen;
+        fused_walk<OPS>(w);
+        dbg_stamp(a, 2, true);
+      }
+    } else if (warp >= 2) {
+      const int cid = tid - 64;
+      for (int i = cid; i < a.n_plan; i += kConsumers) plan[i] = a.plan[i];
+      for (int i = cid; i < a.n_snap * 2; i += kConsumers) s_bpm[i] = 0.0;
+      if (a.img) {
+        if (a.zero_img) {
+          float4* z = reinterpret_cast<float4*>(a.img + b * (int64_t)a.W * a.H);
+          const int64_t n4 = ((int64_t)a.W * a.H) >> 2;
+          const int64_t per = (n4 + gridDim.x - 1) / gridDim.x;
+          const int64_t lo = blockIdx.x * per, hi = min(n4, lo + per);
+          const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int64_t i = lo + cid; i < hi; i += kConsumers) z[i] = zero;
+          if (a.bbox && blockIdx.x == 0 && b == 0 && cid < 4) a.bbox[cid] = 0;
+        }
+#pragma unroll
+        for (int ax = 0; ax < 2; ++ax) {
+          const float* e = ax ? a.ey : a.ex;
+          const int n = ax ? a.H : a.W;
+          const double e0 = (double)__ldg(e), en = (double)__ldg(e + n);
+          const double step = (en - e0) / n;
+          int bad = 0;
+          for (int i = cid; i <= n; i += kConsumers)
+            bad |= fabs((double)__ldg(e + i) - (e0 + step * i)) > step * (1.0 / 1024.0);
+          const bool any_bad = consumers_or(bad != 0);
+          if (cid == 0) {  // same arithmetic as hist_axis_setup (track_common.cuh)
+            s_hist[ax].e0 = (float)e0;
+            s_hist[ax].en = (float)en;
+            s_hist[ax].inv = (float)n / ((float)en - (float)e0);
+            s_hist[ax].margin = any_bad ? 1.f : fmaxf(1.f / 256.f, (float)n * (1.f / 1048576.f));
+          }
+        }
+        dbg_stamp(a, 3, cid == 0);
+        if (a.zero_img) {  // every CTA's slice is zero before anyone's first RED
+          consumers_sync();
+          if (cid == 0) grid_barrier_one_thread(a.grid_bar, gridDim.x * gridDim.y);
+        }
+        dbg_stamp(a, 4, cid == 0);
+      }
+    }
+    __syncthreads();
   }
-  __syncthreads();
 
   MomAcc<MOM> acc;
 #pragma unroll
@@ -271,8 +455,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
                    : rep_i == 0 ? a.img + b * (int64_t)a.W * a.H
                                 : a.rep + ((int64_t)(rep_i - 1) * a.B + b) * (int64_t)a.W * a.H;
     if (img_b) {
-      hx = a.hist[0];
-      hy = a.hist[1];
+      hx = s_hist[0];
+      hy = s_hist[1];
     }
     constexpr bool kWin = (STAGES == 2);  // window code only in the screen variants
     const bool use_win = kWin && img_b && win_words > 0;
@@ -289,6 +473,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
       n_mine += cnt;
       float* st = stages + s * kStageFloats + cid * 4;
       mbar_wait(full + s, u & 1);
+      if (it == 0) dbg_stamp(a, 5, cid == 0);  // first tile landed
       float v[6][4];
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
@@ -429,7 +614,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
               } else if (kWin && dx < (unsigned)hw.w && dy < (unsigned)hw.h) {
                 atomicAdd(win + dy * wpr + (dx >> 1), 1u << ((dx & 1u) * 16u));
               } else {
-                atomicAdd(img_b + (int64_t)(a.H - 1 - iy) * a.W + ix, 1.0f);
+                red_add_f32(img_b + (int64_t)(a.H - 1 - iy) * a.W + ix, 1.0f);
               }
             }
         }
@@ -480,6 +665,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
     // thread of a CTA to execute this counts for the CTA, so it must not sit on a path the
     // loader warp reaches early; issued at the top of the kernel the follower's CTAs (which
     // only wait for this grid) became resident before some K2 CTAs were placed.
+    dbg_stamp(a, 6, cid == 0);
     asm volatile("griddepcontrol.launch_dependents;");
   }
   // ---- CTA epilogue
@@ -507,6 +693,11 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
         atomicAdd(g + 1, s_bpm[2 * p.c + 1] + n * (double)rec[p.b + 2]);
       }
     }
+  }
+  if ((a.dbg & 2) && tid == 64) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    atomicMax(reinterpret_cast<unsigned long long*>(const_cast<HistAxis*>(a.hist)) + 16 + 7, t);
   }
 }
 
@@ -557,10 +748,10 @@ __global__ void __launch_bounds__(kFoldTPB) hist_fold_kernel(float* __restrict__
   }
 }
 
-template <int MOM, bool HAS_OUT, int STAGES>
+template <int MOM, bool HAS_OUT, int STAGES, int OPS = 0>
 static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, uint32_t win_words,
                        cudaStream_t st) {
-  auto k = track_pipe_kernel<MOM, HAS_OUT, STAGES>;
+  auto k = track_pipe_kernel<MOM, HAS_OUT, STAGES, OPS>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096) !=
@@ -574,10 +765,17 @@ static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, uint32_t win_
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  if (OPS != 0) {
+    // fused composer: nothing to overlap with; the grid barrier needs every CTA resident
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+  } else {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  static const bool no_coop = [] { const char* e = getenv("LYNX_FUSED_NOCOOP"); return e && e[0] == '1'; }();
+  cfg.numAttrs = (OPS != 0 && no_coop) ? 0 : 1;
   cudaError_t err;
   {
     ProfileScope ps(1, st);
@@ -590,6 +788,9 @@ static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, uint32_t win_
       cfg.gridDim = dim3((unsigned)(2 * sms));
       cfg.blockDim = dim3(kFoldTPB);
       cfg.dynamicSmemBytes = 0;
+      attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.numAttrs = 1;
       err = cudaLaunchKernelEx(&cfg, hist_fold_kernel, a.img, a.rep, a.n_rep, a.B, a.W, a.H,
                                (const int*)a.bbox);
       count_launch();
@@ -602,7 +803,7 @@ static int launch_pipe(const TrackArgs& a, dim3 grid, size_t smem, uint32_t win_
 // Returns LYNX_OK after enqueueing, or 1 if this variant cannot take the problem (the
 // caller then uses the LDG kernel).
 int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_count,
-                      cudaStream_t st) {
+                      cudaStream_t st, int fused_ops) {
   const uint32_t cap = 227 * 1024 - 4096 - 1024;  // static shared memory takes the rest
   const bool hist = a.img != nullptr && !has_out;
   // The shared-memory window is OPT-IN (LYNX_WINDOW=1): measured on B200 it loses to plain
@@ -610,17 +811,22 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
   // memory costs ~7 cycles/lane/SM (bank conflicts) against 1.29 for REDG, so it only pays
   // where L2 line contention pushes global REDs below ~40 G updates/s.
   static const bool no_win = [] { const char* e = getenv("LYNX_WINDOW"); return !(e && e[0] == '1'); }();
-  const int stages = (hist && !no_win) ? 2 : 4;
-  PipeSmemLayout L = pipe_layout(stages, a.rec_floats, a.n_plan, a.n_snap, 0);
+  const int stages = (hist && !no_win && !fused_ops) ? 2 : 4;
+  PipeSmemLayout L = pipe_layout(stages, a.rec_floats, a.n_plan, a.n_snap, 0,
+                                 fused_ops ? a.n_ops : 0, fused_ops ? a.n_cols : 0);
   if (L.total > cap) return 1;
   uint32_t win_words = 0;
-  if (hist && !no_win) {
+  if (stages == 2) {
     win_words = ((cap - L.total) / 4u) & ~3u;
     if (win_words < 1024) win_words = 0;
     L = pipe_layout(stages, a.rec_floats, a.n_plan, a.n_snap, win_words);
   }
-  int64_t per_b = (sm_count + a.B - 1) / a.B;
-  if (per_b < 1) per_b = 1;
+  // the fused variant synchronises the grid: every CTA must be resident (one per SM)
+  int64_t per_b = fused_ops ? sm_count / a.B : (sm_count + a.B - 1) / a.B;
+  if (per_b < 1) {
+    if (fused_ops) return 1;
+    per_b = 1;
+  }
   // Tile size: the largest multiple of 32 particles <= kPipeTile that gives every CTA of a
   // row the same number of tiles (1 M particles on 148 CTAs: 4 x 1696 each instead of 3 or
   // 4 x 2048 -- the longest CTA sets the kernel time).
@@ -640,7 +846,28 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
       default: return launch_pipe<2, false, 2>(at, grid, L.total, win_words, st);
     }
   }
-  switch (moment_mode * 2 + (has_out ? 1 : 0)) {
+  const int v = moment_mode * 2 + (has_out ? 1 : 0);
+  if (fused_ops == kOpsLight) {
+    switch (v) {
+      case 0: return launch_pipe<0, false, 4, kOpsLight>(at, grid, L.total, 0, st);
+      case 1: return launch_pipe<0, true, 4, kOpsLight>(at, grid, L.total, 0, st);
+      case 2: return launch_pipe<1, false, 4, kOpsLight>(at, grid, L.total, 0, st);
+      case 3: return launch_pipe<1, true, 4, kOpsLight>(at, grid, L.total, 0, st);
+      case 4: return launch_pipe<2, false, 4, kOpsLight>(at, grid, L.total, 0, st);
+      default: return launch_pipe<2, true, 4, kOpsLight>(at, grid, L.total, 0, st);
+    }
+  }
+  if (fused_ops) {
+    switch (v) {
+      case 0: return launch_pipe<0, false, 4, kOpsAll>(at, grid, L.total, 0, st);
+      case 1: return launch_pipe<0, true, 4, kOpsAll>(at, grid, L.total, 0, st);
+      case 2: return launch_pipe<1, false, 4, kOpsAll>(at, grid, L.total, 0, st);
+      case 3: return launch_pipe<1, true, 4, kOpsAll>(at, grid, L.total, 0, st);
+      case 4: return launch_pipe<2, false, 4, kOpsAll>(at, grid, L.total, 0, st);
+      default: return launch_pipe<2, true, 4, kOpsAll>(at, grid, L.total, 0, st);
+    }
+  }
+  switch (v) {
     case 0: return launch_pipe<0, false, 4>(at, grid, L.total, 0, st);
     case 1: return launch_pipe<0, true, 4>(at, grid, L.total, 0, st);
     case 2: return launch_pipe<1, false, 4>(at, grid, L.total, 0, st);

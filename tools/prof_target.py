@@ -16,7 +16,7 @@ ap.add_argument("--steps", type=int, default=3)
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(0)
-flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+flush = torch.empty((1 << 10) if os.environ.get('LYNX_NOFLUSH') else (256 << 20), dtype=torch.uint8, device=dev)
 if a.mode == "screen1m":
     w = bench.ParticleWorkload(1_000_000, dev, seed=1002, screen=True)
 elif a.mode == "screen32m":
