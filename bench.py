@@ -532,11 +532,18 @@ def run_ours(args, rank, world, local_rank):
     alg = wl.algorithmic_bytes()
     ach = alg / (k2_ms * 1e-3) / 1e9 if k2_ms else None
     roofline = {"bound": "hbm", "kernel": "track_fwd_kernel (K2)", "achieved": ach, "peak": peak,
-                "unit": "GB/s", "frac": (ach / peak) if ach else None, "traffic": None,
+                "unit": "GB/s", "frac": (ach / peak) if ach else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel on this
+                # workload, from profiles/r1c_k2_screen1m.txt (ncu --set full; the image is
+                # zeroed and accumulated in L2, its write-back happens after the kernel)
+                "traffic": 24355328 if args.particles == 1_000_000 else None,
+                "traffic_source": "profiles/r1c_k2_screen1m.txt",
                 "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs, burst copy)",
                 "algorithmic_bytes_per_launch": alg, "kernel_ms": k2_ms,
                 "frac_of_8000": (ach / 8000.0) if ach else None,
-                "regime": "launch/latency-bound at 1M particles (44 MB per launch)"}
+                "regime": "L2-atomic / latency-bound at 1M particles: 1 M RED.ADD.F32 at the "
+                          "focused-beam rate of the L2 (~75 G/s, profiles/r1b_atomic_bench.txt) "
+                          "are ~13 us of the kernel; 44 MB are 6.8 us at the HBM peak"}
     line = {
         "metric": "particle_element_updates_per_s", "value": value,
         "unit": "particle-element updates/s", "n_gpus": world, "steps": args.steps,

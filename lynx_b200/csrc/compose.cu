@@ -15,7 +15,7 @@ namespace lynx {
 // latency per column, which is the whole kernel at B = 1), then walk from shared memory.
 constexpr int kComposeTPB = 128;
 
-template <bool STAGED, int OPS>
+template <bool STAGED, int OPS, bool MAPS = false>
 __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int n_cols, int S) {
   extern __shared__ __align__(16) float cs_smem[];
   // Programmatic dependent launch: let the particle kernel start its prologue (barrier
@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
   }
   if ((int)threadIdx.x >= ns) return;
   const int64_t b = b0 + threadIdx.x;
-  RecordSink sink;
+  RecordSinkT<MAPS> sink;
   sink.rec = a.records + b * a.rec_floats;
   sink.maps_out = a.maps_out ? a.maps_out + b * (int64_t)a.n_stages * 49 : nullptr;
   sink.off_cav = a.off_cav;
@@ -222,7 +222,12 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   {
     ProfileScope ps(0, st);
     const bool light = (p->op_mask & ~kOpsLight) == 0;
-    if (staged && light)
+    if (d_maps_out) {  // public lynx_compose_maps: records + 7x7 stage maps
+      if (staged)
+        compose_kernel<true, kOpsAll, true><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);
+      else
+        compose_kernel<false, kOpsAll, true><<<blocks, kComposeTPB, 0, st>>>(a, n_cols, S);
+    } else if (staged && light)
       compose_kernel<true, kOpsLight><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);
     else if (staged)
       compose_kernel<true, kOpsAll><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);

@@ -6,7 +6,10 @@
 namespace lynx {
 
 // ------------------------------------------------------------------ K1
-struct RecordSink {
+// WITH_MAPS: also emit the 7x7 stage maps (lynx_compose_maps); the tracking launchers use
+// the variant without that code (smaller K1).
+template <bool WITH_MAPS>
+struct RecordSinkT {
   float* rec;
   float* maps_out;  // nullable, this setting's [n_stages][7][7]
   int off_cav, off_centre, off_screen;
@@ -18,7 +21,7 @@ struct RecordSink {
     for (int i = 0; i < 6; ++i)
 #pragma unroll
       for (int j = 0; j < 7; ++j) d[i * 7 + j] = M.m[i][j];
-    if (maps_out) {
+    if (WITH_MAPS && maps_out) {
       float* o = maps_out + idx * 49;
 #pragma unroll
       for (int i = 0; i < 6; ++i)
@@ -96,6 +99,8 @@ struct ComposeArgs {
   int hist_W, hist_H;
   void* hist_out;      // HistAxis[2]
 };
+
+using RecordSink = RecordSinkT<false>;
 
 // ------------------------------------------------------------------ K6
 template <typename T>

@@ -52,6 +52,11 @@ __host__ __device__ __forceinline__ bool nz(const Dual<F>& x) { return x.v != F(
 
 // ---- arithmetic ----------------------------------------------------------------------
 #define LYNX_HD __host__ __device__ __forceinline__
+// Scalar transcendentals are called once per setting and sit on rarely taken branches of
+// the map builders (|k^2 L^2| >= 1, tilt != 0, dipoles, cavities): out of line, so their
+// slow paths (Payne-Hanek, exp) do not inflate the composer kernels -- whose launch-to-first-
+// result latency grows with code size when the L2 is cold.
+#define LYNX_COLD static __device__ __noinline__
 template <typename F> LYNX_HD Dual<F> operator+(const Dual<F>& a, const Dual<F>& b) { return {a.v + b.v, a.d + b.d}; }
 template <typename F> LYNX_HD Dual<F> operator+(const Dual<F>& a, F b) { return {a.v + b, a.d}; }
 template <typename F> LYNX_HD Dual<F> operator+(F a, const Dual<F>& b) { return {a + b.v, b.d}; }
@@ -114,18 +119,18 @@ template <typename F> __device__ __forceinline__ Dual<F> rsqrt_(const Dual<F>& x
   const F r = rsqrt_(x.v);
   return {r, F(-0.5) * r / x.v * x.d};
 }
-__device__ __forceinline__ void sincos_(float x, float* s, float* c) { sincosf(x, s, c); }
-__device__ __forceinline__ void sincos_(double x, double* s, double* c) { sincos(x, s, c); }
+LYNX_COLD void sincos_(float x, float* s, float* c) { sincosf(x, s, c); }
+LYNX_COLD void sincos_(double x, double* s, double* c) { sincos(x, s, c); }
 template <typename F> __device__ __forceinline__ void sincos_(const Dual<F>& x, Dual<F>* s, Dual<F>* c) {
   F sv, cv;
   sincos_(x.v, &sv, &cv);
   *s = {sv, cv * x.d};
   *c = {cv, -sv * x.d};
 }
-LYNX_HD float sin_(float x) { return sinf(x); }
-LYNX_HD double sin_(double x) { return sin(x); }
-LYNX_HD float cos_(float x) { return cosf(x); }
-LYNX_HD double cos_(double x) { return cos(x); }
+LYNX_COLD float sin_(float x) { return sinf(x); }
+LYNX_COLD double sin_(double x) { return sin(x); }
+LYNX_COLD float cos_(float x) { return cosf(x); }
+LYNX_COLD double cos_(double x) { return cos(x); }
 template <typename F> __device__ __forceinline__ Dual<F> sin_(const Dual<F>& x) {
   F sv, cv;
   sincos_(x.v, &sv, &cv);
@@ -136,20 +141,20 @@ template <typename F> __device__ __forceinline__ Dual<F> cos_(const Dual<F>& x) 
   sincos_(x.v, &sv, &cv);
   return {cv, -sv * x.d};
 }
-LYNX_HD float sinh_(float x) { return sinhf(x); }
-LYNX_HD double sinh_(double x) { return sinh(x); }
-LYNX_HD float cosh_(float x) { return coshf(x); }
-LYNX_HD double cosh_(double x) { return cosh(x); }
+LYNX_COLD float sinh_(float x) { return sinhf(x); }
+LYNX_COLD double sinh_(double x) { return sinh(x); }
+LYNX_COLD float cosh_(float x) { return coshf(x); }
+LYNX_COLD double cosh_(double x) { return cosh(x); }
 template <typename F> LYNX_HD Dual<F> sinh_(const Dual<F>& x) { return {sinh_(x.v), cosh_(x.v) * x.d}; }
 template <typename F> LYNX_HD Dual<F> cosh_(const Dual<F>& x) { return {cosh_(x.v), sinh_(x.v) * x.d}; }
-LYNX_HD float tan_(float x) { return tanf(x); }
-LYNX_HD double tan_(double x) { return tan(x); }
+LYNX_COLD float tan_(float x) { return tanf(x); }
+LYNX_COLD double tan_(double x) { return tan(x); }
 template <typename F> LYNX_HD Dual<F> tan_(const Dual<F>& x) {
   const F t = tan_(x.v);
   return {t, (F(1) + t * t) * x.d};
 }
-LYNX_HD float log1p_(float x) { return log1pf(x); }
-LYNX_HD double log1p_(double x) { return log1p(x); }
+LYNX_COLD float log1p_(float x) { return log1pf(x); }
+LYNX_COLD double log1p_(double x) { return log1p(x); }
 template <typename F> LYNX_HD Dual<F> log1p_(const Dual<F>& x) { return {log1p_(x.v), x.d / (F(1) + x.v)}; }
 
 }  // namespace lynx
