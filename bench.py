@@ -665,6 +665,12 @@ def run_ours(args, rank, world, local_rank):
         line["extras"] = extras
 
     lib.lynx_host_ctx_destroy(ctx)
+    # NCCL writes its version banner through C stdio, which is block-buffered on a pipe and
+    # would otherwise come out after this line at exit: the JSON must be the LAST line
+    try:
+        C.CDLL(None).fflush(None)
+    except Exception:
+        pass
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

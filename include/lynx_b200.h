@@ -182,6 +182,12 @@ int lynx_screen_allreduce(void* const* peer_bases /*host array [world]*/, int32_
                           int32_t rank, int32_t slot, uint32_t epoch, int64_t B, int32_t W,
                           int32_t H, float* d_out_img, int32_t* d_state /*[8]*/,
                           lynx_stream_t stream);
+/* Same, with the multicast (NVLS) mapping of the symmetric buffer: the peers' pixels are
+ * summed inside the NVSwitch by multimem.ld_reduce instead of world separate peer loads.
+ * multicast_base = NULL selects the peer-load path. */
+int lynx_screen_allreduce_mc(void* const* peer_bases, void* multicast_base, int32_t world,
+                             int32_t rank, int32_t slot, uint32_t epoch, int64_t B, int32_t W,
+                             int32_t H, float* d_out_img, int32_t* d_state, lynx_stream_t stream);
 
 /* K3 -- adjoint of lynx_track_particles_fwd w.r.t. every parameter column and
  * (optionally) the incoming particles.  The reference has no custom_vjp; this is the

@@ -58,6 +58,9 @@ SIGNATURES = {
     "lynx_screen_allreduce": (
         C.c_int, [C.POINTER(_vp), _i32, _i32, _i32, C.c_uint32, _i64, _i32, _i32, _vp, _vp, _vp]
     ),
+    "lynx_screen_allreduce_mc": (
+        C.c_int, [C.POINTER(_vp), _vp, _i32, _i32, _i32, C.c_uint32, _i64, _i32, _i32, _vp, _vp, _vp]
+    ),
     "lynx_track_particles_bwd": (
         C.c_int,
         [_vp, _vp, _i64, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp],

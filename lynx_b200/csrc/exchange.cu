@@ -49,6 +49,7 @@ struct ExchangeArgs {
   float* out;    // [B][H][W] local, persistent: zero outside the last written rectangle
   int* state;    // [2][4] local: rectangle (r0, r1, c0, c1) written at even / odd epochs
   unsigned long long* trace;  // optional [1024][8] globaltimer stamps of block 0 (debug)
+  char* mc;      // multicast (NVLS) mapping of the symmetric buffer, or null
 };
 
 // The message store needs no fence of its own: everything it publishes (K2's image and box)
@@ -69,6 +70,19 @@ __device__ __forceinline__ uint64_t ld_acquire_sys(const uint64_t* p) {
 __device__ __forceinline__ float4 ld_peer(const float4* p) {
   float4 v;
   asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+
+// In-switch reduction (NVLS): one load on the multicast mapping of the symmetric buffer returns
+// the sum of the word over all peers, so a rank issues W*H/4 loads instead of world * W*H/4
+// (3 MB of outstanding peer reads per rank at 8 GPUs made the sum phase 12.6 us, measured).
+// Integer-valued fp32 counts: the switch's summation order does not matter.
+__device__ __forceinline__ float4 ld_reduce_mc(const float4* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
                : "l"(p)
                : "memory");
@@ -156,7 +170,9 @@ __global__ void __launch_bounds__(kExTPB) screen_allreduce_kernel(ExchangeArgs a
     const int r = ra + (int)(rr - bq * nr);
     const int64_t i = ((bq * a.H + r) * (int64_t)a.W + c) >> 2;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (r >= r0 && r < r1 && c >= c0 && c < c1) {
+    if (r >= r0 && r < r1 && c >= c0 && c < c1 && a.mc) {
+      s = ld_reduce_mc(reinterpret_cast<const float4*>(a.mc + img_off) + i);
+    } else if (r >= r0 && r < r1 && c >= c0 && c < c1) {
       // all peer loads of a batch are issued before the first add: one NVLink round trip
       // per batch of 8 peers instead of one per peer
       for (int p0 = 0; p0 < a.world; p0 += 8) {
@@ -222,6 +238,14 @@ extern "C" void lynx_exchange_trace(unsigned long long* d_stamps) { lynx::g_exch
 extern "C" int lynx_screen_allreduce(void* const* peer_bases, int32_t world, int32_t rank,
                                      int32_t slot, uint32_t epoch, int64_t B, int32_t W, int32_t H,
                                      float* d_out_img, int32_t* d_state, lynx_stream_t stream) {
+  return lynx_screen_allreduce_mc(peer_bases, nullptr, world, rank, slot, epoch, B, W, H, d_out_img,
+                                  d_state, stream);
+}
+
+extern "C" int lynx_screen_allreduce_mc(void* const* peer_bases, void* multicast_base, int32_t world,
+                                        int32_t rank, int32_t slot, uint32_t epoch, int64_t B,
+                                        int32_t W, int32_t H, float* d_out_img, int32_t* d_state,
+                                        lynx_stream_t stream) {
   if (!peer_bases || world < 1 || world > kMaxWorld || rank < 0 || rank >= world || slot < 0 ||
       slot > 1 || epoch == 0 || B <= 0 || W <= 0 || H <= 0 || W > 65535 || H > 65535 || (W & 3) || !d_out_img ||
       !d_state || ((uintptr_t)d_out_img & 15))
@@ -242,6 +266,7 @@ extern "C" int lynx_screen_allreduce(void* const* peer_bases, int32_t world, int
   a.out = d_out_img;
   a.state = d_state;
   a.trace = g_exchange_trace;
+  a.mc = reinterpret_cast<char*>(multicast_base);
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -123,6 +123,7 @@ class ScreenExchange:
         self.lib = L.lib()
         self._L = L
         self.fused = False
+        self._mc = 0
         self.out = torch.zeros((B, H, W), dtype=torch.float32, device=device)
         self.state = torch.zeros(8, dtype=torch.int32, device=device)
         try:
@@ -135,6 +136,11 @@ class ScreenExchange:
             self.hdl = symm_mem.rendezvous(self.buf, self.group)
             ptrs = list(self.hdl.buffer_ptrs)
             self._peers = (C.c_void_p * self.world)(*ptrs)
+            # NVLS: the multicast mapping lets the switch sum the peers' pixels (0 = unsupported)
+            import os
+            self._mc = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
+            if os.environ.get("LYNX_EX_NO_MULTICAST") == "1":
+                self._mc = 0
             self.hdl.barrier()
             torch.cuda.synchronize(device)
             self.fused = W % 4 == 0 and self.world <= 16
@@ -158,8 +164,8 @@ class ScreenExchange:
             self.out.copy_(self.buf[slot])
             dist.all_reduce(self.out, group=self.group)
             return self.out
-        self._L.check(self.lib.lynx_screen_allreduce(
-            self._peers, self.world, self.rank, slot, self.step, self.B, self.W, self.H,
-            self.out.data_ptr(), self.state.data_ptr(), self._L.current_stream()),
+        self._L.check(self.lib.lynx_screen_allreduce_mc(
+            self._peers, self._mc or None, self.world, self.rank, slot, self.step, self.B, self.W,
+            self.H, self.out.data_ptr(), self.state.data_ptr(), self._L.current_stream()),
             "lynx_screen_allreduce")
         return self.out

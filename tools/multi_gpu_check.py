@@ -41,7 +41,7 @@ for step, (k1, vk, hk) in enumerate([((5.0, -5.0, 5.0), 1e-3, -2e-3), ((3.0, -6.
     if ex is None:
         ex = S.ScreenExchange(1, W, H, dev)
         if rank == 0:
-            print("fused exchange:", ex.fused, getattr(ex, "why", ""), flush=True)
+            print("fused exchange:", ex.fused, getattr(ex, "why", ""), "multicast:", hex(ex._mc), flush=True)
     e_in = torch.tensor([F.ASTRA_ENERGY], device=dev)
     e_out = torch.empty(1, device=dev)
     ws = torch.empty(prog.workspace_bytes(1), dtype=torch.uint8, device=dev)
