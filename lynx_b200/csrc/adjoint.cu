@@ -23,6 +23,7 @@
 #include <algorithm>
 #include <cstdlib>
 
+#include "pipe.cuh"
 #include "compose_common.cuh"
 #include "track_common.cuh"
 
@@ -225,7 +226,9 @@ template <bool NOCAV>
 __device__ __forceinline__ void adj_particle(const AdjStreamArgs& a, const float* __restrict__ rec,
                                              const float (&x)[6], const float (&go)[6],
                                              bool has_go, float (&acc)[kAdjSums],
-                                             float (&gin)[6]) {
+                                             float (&gin)[6], const float* __restrict__ seg0 = nullptr) {
+  // seg0 (NOCAV only): the single segment block held by the caller, e.g. in registers
+  if (!NOCAV || !seg0) seg0 = rec;
   const int n_seg = NOCAV ? 1 : a.L.n_seg;
   float u[NOCAV ? 1 : kMaxSeg][6];
   float v[6];
@@ -236,7 +239,7 @@ __device__ __forceinline__ void adj_particle(const AdjStreamArgs& a, const float
 #pragma unroll
     for (int i = 0; i < 6; ++i) u[k][i] = v[i];
     float w[6];
-    affine6(rec + k * kAdjBlock, v, w);
+    affine6(NOCAV ? seg0 : rec + k * kAdjBlock, v, w);
     if (!NOCAV && k < n_seg - 1) {
       const float* cb = rec + (n_seg + k) * kAdjBlock;
       float vl[6];
@@ -271,7 +274,7 @@ __device__ __forceinline__ void adj_particle(const AdjStreamArgs& a, const float
   }
   // ---- backward
   for (int k = n_seg - 1; k >= 0; --k) {
-    const float* sb = rec + k * kAdjBlock;
+    const float* sb = NOCAV ? seg0 : rec + k * kAdjBlock;
     if (a.target == k) {
       float d[6];
 #pragma unroll
@@ -428,6 +431,206 @@ __global__ void __launch_bounds__(kAdjTPB) adj_stream_kernel(AdjStreamArgs a) {
     for (int ww = 0; ww < kAdjTPB / 32; ++ww) s += s_red[ww][tid];
     const int n_t = a.L.n_seg + a.L.n_cav;
     if (s != 0.0) atomicAdd(a.sums + ((int64_t)b * n_t + a.target) * kAdjSums + tid, s);
+  }
+}
+
+// ------------------------------------------------------------------ K3a, pipelined
+// Same arithmetic (adj_particle), data path of K2 (track_pipe.cu): one persistent CTA per SM,
+// warp 0 streams the x (and g_out) planes of a tile into shared memory with cp.async.bulk +
+// mbarrier, 8 consumer warps run the adjoint per particle out of shared memory and write
+// g_in over the x planes in place, warp 1 drains finished tiles with bulk stores.  The
+// grid-stride kernel above keeps 18 float4 of particle data in registers (182 registers, one
+// 256-thread CTA per SM, no prefetch): 0.60 of the HBM peak at 32 M particles.  Here the bytes
+// in flight are set by shared memory (4 stages x 48 KB) and the consumers hold the accumulators
+// and -- for a cavity-free lattice -- the segment's map in registers (the first version read
+// the 6x7 map from shared memory twice per particle: LSU pipe 58 % busy, 35 % short-scoreboard
+// stalls, 0.69 of the HBM peak).  Particle q of a tile belongs to consumer q mod 256:
+// LDS.32 / STS.32 are conflict-free without transposing.
+constexpr int kAPConsumers = 256;
+constexpr int kAPWarps = kAPConsumers / 32;
+constexpr int kAPThreads = kAPConsumers + 64;
+constexpr int kAPTile = 4 * kAPConsumers;  // particles per stage
+constexpr int kAPStages = 4;
+
+template <bool NOCAV, bool HAS_GO, bool HAS_GIN>
+__global__ void __launch_bounds__(kAPThreads, 1) adj_pipe_kernel(AdjStreamArgs a, int tile_i) {
+  extern __shared__ __align__(128) unsigned char apsm[];
+  constexpr int kPlanes = HAS_GO ? 12 : 6;
+  constexpr int kStage = kPlanes * kAPTile;  // floats
+  float* stages = reinterpret_cast<float*>(apsm);
+  float* arec_s = stages + kAPStages * kStage;
+  uint64_t* full = reinterpret_cast<uint64_t*>(arec_s + ((a.L.rec_floats + 3) & ~3));
+  uint64_t* empty = full + kAPStages;
+  uint64_t* done = empty + kAPStages;
+  __shared__ double s_red[kAPWarps][kAdjSums];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t b = blockIdx.y;
+  const int64_t tile = tile_i;
+  const int64_t n_tiles = (a.N + tile - 1) / tile;
+  const float* in_b = a.in + b * a.in_row_stride;
+  const float* go_b = HAS_GO ? a.g_out + b * 6 * a.ld_g : nullptr;
+  float* gi_b = HAS_GIN ? a.g_in + b * a.gin_row_stride : nullptr;
+
+  auto issue_tile = [&](int it, int64_t t) {
+    const int s = it % kAPStages;
+    const int64_t p0 = t * tile;
+    const uint32_t cnt = (uint32_t)min(tile, a.N - p0);
+    const uint32_t bytes = ((cnt + 3u) & ~3u) * 4u;
+    mbar_arrive_expect_tx(full + s, (uint32_t)kPlanes * bytes);
+    float* dst = stages + s * kStage;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) bulk_g2s(dst + k * kAPTile, in_b + k * a.ld_in + p0, bytes, full + s);
+    if (HAS_GO) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k)
+        bulk_g2s(dst + (6 + k) * kAPTile, go_b + k * a.ld_g + p0, bytes, full + s);
+    }
+  };
+  if (tid == 0) {
+    for (int s = 0; s < kAPStages; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, HAS_GIN ? 1 : kAPWarps);
+      mbar_init(done + s, kAPWarps);
+    }
+    fence_mbar_init();
+    int it = 0;
+    for (int64_t t = blockIdx.x; t < n_tiles && it < kAPStages; t += gridDim.x, ++it) issue_tile(it, t);
+  }
+  {
+    const float* src = a.arec + b * a.L.rec_floats;
+    for (int i = tid; i < a.L.rec_floats; i += kAPThreads) arec_s[i] = src[i];
+  }
+  __syncthreads();
+
+  float acc[kAdjSums];
+#pragma unroll
+  for (int i = 0; i < kAdjSums; ++i) acc[i] = 0.f;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int it = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+        if (it < kAPStages) continue;
+        mbar_wait(empty + (it % kAPStages), ((uint32_t)(it / kAPStages) - 1) & 1);
+        issue_tile(it, t);
+      }
+    }
+  } else if (warp == 1) {
+    if (HAS_GIN && lane == 0) {
+      int it = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+        const int s = it % kAPStages;
+        mbar_wait(done + s, (uint32_t)(it / kAPStages) & 1);
+        fence_proxy_async();
+        const int64_t p0 = t * tile;
+        const uint32_t cnt = (uint32_t)min(tile, a.N - p0);
+        const uint32_t bytes = ((cnt + 3u) & ~3u) * 4u;
+        const float* src = stages + s * kStage;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) bulk_s2g(gi_b + k * a.ld_gin + p0, src + k * kAPTile, bytes);
+        bulk_commit();
+        bulk_wait_read<0>();  // the stage has been read: hand it back to the loader
+        mbar_arrive(empty + s);
+      }
+    }
+  } else {
+    const int cid = tid - 64;
+    float seg[kAdjBlock];  // NOCAV: map, injection and centre of the one segment, in registers
+    if (NOCAV) {
+#pragma unroll
+      for (int i = 0; i < kAdjBlock; ++i) seg[i] = arec_s[i];
+    }
+    int it = 0;
+    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+      const int s = it % kAPStages;
+      const int64_t p0 = t * tile;
+      const int cnt = (int)min(tile, a.N - p0);
+      float* st = stages + s * kStage;
+      mbar_wait(full + s, (uint32_t)(it / kAPStages) & 1);
+#pragma unroll 1
+      for (int q = cid; q < ((cnt + 3) & ~3); q += kAPConsumers) {
+        float x[6], go[6], gin[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+          x[k] = st[k * kAPTile + q];
+          go[k] = HAS_GO ? st[(6 + k) * kAPTile + q] : 0.f;
+        }
+        if (q < cnt) {
+          adj_particle<NOCAV>(a, arec_s, x, go, HAS_GO, acc, gin, NOCAV ? seg : nullptr);
+        } else {  // padding lanes [N, ld) of the last tile
+#pragma unroll
+          for (int k = 0; k < 6; ++k) gin[k] = 0.f;
+        }
+        if (HAS_GIN) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k) st[k * kAPTile + q] = gin[k];
+        }
+      }
+      if (HAS_GIN) fence_proxy_async();  // generic-proxy writes before the bulk store reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(HAS_GIN ? done + s : empty + s);
+    }
+  }
+
+  // ---- CTA reduction -> double atomics (consumer warps hold the sums)
+  if (warp >= 2) {
+#pragma unroll
+    for (int i = 0; i < kAdjSums; ++i) {
+      const double sdbl = warp_sum((double)acc[i]);
+      if (lane == 0) s_red[warp - 2][i] = sdbl;
+    }
+  }
+  __syncthreads();
+  if (tid < kAdjSums) {
+    double sdbl = 0.0;
+#pragma unroll
+    for (int ww = 0; ww < kAPWarps; ++ww) sdbl += s_red[ww][tid];
+    const int n_t = a.L.n_seg + a.L.n_cav;
+    if (sdbl != 0.0) atomicAdd(a.sums + ((int64_t)b * n_t + a.target) * kAdjSums + tid, sdbl);
+  }
+}
+
+template <bool NOCAV, bool HAS_GO, bool HAS_GIN>
+static cudaError_t launch_adj_pipe(const AdjStreamArgs& sa, dim3 grid, size_t smem, int tile,
+                                   cudaStream_t st) {
+  auto k = adj_pipe_kernel<NOCAV, HAS_GO, HAS_GIN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 8192);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  k<<<grid, kAPThreads, smem, st>>>(sa, tile);
+  return cudaGetLastError();
+}
+
+// Returns cudaSuccess after enqueueing, cudaErrorNotSupported if the variant cannot take it.
+static cudaError_t adj_pipe_dispatch(const AdjStreamArgs& sa, bool nocav, int sm_count, cudaStream_t st) {
+  const bool has_go = sa.g_out != nullptr, has_gin = sa.g_in != nullptr;
+  if (has_gin && sa.atomic_gin) return cudaErrorNotSupported;  // reduced over settings: atomics
+  if ((sa.ld_in & 3) || (has_go && (sa.ld_g & 3)) || (has_gin && (sa.ld_gin & 3))) return cudaErrorNotSupported;
+  const size_t planes = has_go ? 12 : 6;
+  const size_t smem = sizeof(float) * (kAPStages * planes * kAPTile + ((sa.L.rec_floats + 3) & ~3)) +
+                      8 * 3 * kAPStages;
+  if (smem > 227 * 1024 - 8192) return cudaErrorNotSupported;
+  int64_t per_b = std::max<int64_t>(1, sm_count / sa.B);
+  const int64_t full_tiles = (sa.N + kAPTile - 1) / kAPTile;
+  const int64_t gx = std::min<int64_t>(full_tiles, per_b);
+  const int64_t rounds = (sa.N + gx * kAPTile - 1) / (gx * kAPTile);
+  int64_t tile = (sa.N + gx * rounds - 1) / (gx * rounds);
+  tile = std::min<int64_t>(kAPTile, (tile + 31) & ~(int64_t)31);
+  const int64_t n_tiles = (sa.N + tile - 1) / tile;
+  dim3 grid((unsigned)std::min<int64_t>(n_tiles, gx), (unsigned)sa.B);
+  const int v = (nocav ? 4 : 0) + (has_go ? 2 : 0) + (has_gin ? 1 : 0);
+  switch (v) {
+    case 0: return launch_adj_pipe<false, false, false>(sa, grid, smem, (int)tile, st);
+    case 1: return launch_adj_pipe<false, false, true>(sa, grid, smem, (int)tile, st);
+    case 2: return launch_adj_pipe<false, true, false>(sa, grid, smem, (int)tile, st);
+    case 3: return launch_adj_pipe<false, true, true>(sa, grid, smem, (int)tile, st);
+    case 4: return launch_adj_pipe<true, false, false>(sa, grid, smem, (int)tile, st);
+    case 5: return launch_adj_pipe<true, false, true>(sa, grid, smem, (int)tile, st);
+    case 6: return launch_adj_pipe<true, true, false>(sa, grid, smem, (int)tile, st);
+    default: return launch_adj_pipe<true, true, true>(sa, grid, smem, (int)tile, st);
   }
 }
 
@@ -993,10 +1196,17 @@ extern "C" int lynx_track_particles_bwd(
       sa.target = t;
       if (t > 0) sa.g_in = nullptr;  // written by the first pass only
       ProfileScope ps(3, st);
-      if (p->n_cav == 0)
-        adj_stream_kernel<true><<<dim3((unsigned)gx, (unsigned)B), kAdjTPB, smem, st>>>(sa);
-      else
-        adj_stream_kernel<false><<<dim3((unsigned)gx, (unsigned)B), kAdjTPB, smem, st>>>(sa);
+      static const bool no_pipe = [] { const char* e = getenv("LYNX_K3"); return e && e[0] == 'l'; }();
+      cudaError_t pe = (no_pipe || B > 65535) ? cudaErrorNotSupported
+                                              : adj_pipe_dispatch(sa, p->n_cav == 0, p->sm_count, st);
+      if (pe == cudaErrorNotSupported) {  // grid-stride LDG variant
+        if (p->n_cav == 0)
+          adj_stream_kernel<true><<<dim3((unsigned)gx, (unsigned)B), kAdjTPB, smem, st>>>(sa);
+        else
+          adj_stream_kernel<false><<<dim3((unsigned)gx, (unsigned)B), kAdjTPB, smem, st>>>(sa);
+      } else if (pe != cudaSuccess) {
+        return LYNX_E_LAUNCH;
+      }
       count_launch();
     }
     LYNX_CUDA_OK(cudaGetLastError());
