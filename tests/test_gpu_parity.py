@@ -502,3 +502,59 @@ def test_screen_tests_with_histogram_replicas():
            os.path.join(here, "test_gpu_parity.py")]
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_screen_exchange_kernel_single_rank():
+    """csrc/exchange.cu on one GPU (world = 1: the rank is its own only peer): the fused
+    bounding-box all-reduce must reproduce the dense image of lynx_track_particles_fwd, clear
+    what the previous step lit and nothing else, and alternate its two slots -- the same
+    kernel, epoch messages and persistent-rectangle logic the multi-GPU path runs
+    (tools/multi_gpu_check.py covers world > 1)."""
+    import ctypes as C
+
+    from lynx_b200 import _lib as L
+    from lynx_b200.program import Program, encode, pack_params
+
+    lib = L.lib()
+    dev = torch.device("cuda")
+    n = 200_003
+    soa = torch.from_numpy(F.gaussian_beam_soa(n, seed=77))
+    ld = (n + 3) & ~3
+    soa_d = torch.zeros((6, ld), device=dev)
+    soa_d[:, :n] = soa.to(dev)
+    out = state = buf = None
+    for step, (k1, vk, hk) in enumerate([((5.0, -5.0, 5.0), 1e-3, -2e-3), ((3.0, -6.0, 4.0), -5e-4, 1e-3),
+                                         ((0.0, 0.0, 0.0), 0.0, 0.0), ((8.0, -9.0, 7.0), 2e-3, 2e-3)]):
+        seg = F.build_segment(F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True,
+                                        screen=F.TEST_SCREEN))
+        enc = encode(seg.elements, (1,))
+        prog = Program.get(enc)
+        params = pack_params(enc, dev)
+        ex_d, ey_d = seg.AREABSCR1._device_edges(dev)
+        W, H = ex_d.numel() - 1, ey_d.numel() - 1
+        if buf is None:
+            nbytes = lib.lynx_screen_symm_bytes(1, W, H)
+            buf = torch.zeros(nbytes // 4, dtype=torch.float32, device=dev)
+            out = torch.zeros((1, H, W), device=dev)
+            state = torch.zeros(8, dtype=torch.int32, device=dev)
+            peers = (C.c_void_p * 1)(buf.data_ptr())
+        e_in = torch.tensor([F.ASTRA_ENERGY], device=dev)
+        e_out = torch.empty(1, device=dev)
+        ws = torch.empty(prog.workspace_bytes(1), dtype=torch.uint8, device=dev)
+        ref = torch.empty((1, H, W), device=dev)
+
+        def track(img_ptr, bbox_ptr):
+            L.check(lib.lynx_track_particles_fwd_bbox(
+                prog.handle, params.data_ptr(), 1, soa_d.data_ptr(), 1, ld, n, None, ld, None,
+                img_ptr, W, H, ex_d.data_ptr(), ey_d.data_ptr(), None, 0, e_in.data_ptr(),
+                e_out.data_ptr(), ws.data_ptr(), bbox_ptr, L.current_stream()))
+
+        track(ref.data_ptr(), None)
+        slot = step & 1
+        img = lib.lynx_screen_symm_image(buf.data_ptr(), slot, 1, W, H)
+        track(img, img - 64)
+        L.check(lib.lynx_screen_allreduce(peers, 1, 0, slot, step + 1, 1, W, H, out.data_ptr(),
+                                          state.data_ptr(), L.current_stream()))
+        torch.cuda.synchronize()
+        assert torch.equal(out, ref), f"step {step}"
+        assert float(out.sum()) > 0.5 * n  # some settings steer part of the beam off the screen
