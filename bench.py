@@ -662,6 +662,39 @@ def run_ours(args, rank, world, local_rank):
             "particles": ns, "kernel_ms": k3, "achieved_gbs": k3_bytes / (k3 * 1e-3) / 1e9,
             "frac": k3_bytes / (k3 * 1e-3) / 1e9 / peak}
         del gw
+        # beam-level kernels at scale: K10 transformed_to (48 B),
+        # K11 Aperture compaction (56 B over three launches), K9b ellipsoid generation (24 B)
+        try:
+            beam = lx.ParticleBeam.from_parameters(
+                num_particles=ns, sigma_x=torch.tensor([2e-4]), sigma_y=torch.tensor([2e-4]), seed=2)
+            beam.moment_sums()
+            tf = lambda: beam.transformed_to(sigma_x=torch.tensor([1e-4]))  # noqa: E731
+            k10 = kernel_ms(tf, 4, 10, flush, lib)
+            extras["at_scale_transformed_to_48B"] = {
+                "particles": ns, "kernel_ms": k10, "achieved_gbs": 48 * ns / (k10 * 1e-3) / 1e9,
+                "frac": 48 * ns / (k10 * 1e-3) / 1e9 / peak}
+            ap = lx.Aperture(x_max=torch.tensor(2e-4), y_max=torch.tensor(2e-4), shape="elliptical")
+            apf = lambda: ap.track(beam)  # noqa: E731
+            apf()
+            ams = float(np.mean(timed_steps(apf, 10, 3, flush)))
+            k11 = kernel_ms(apf, 5, 10, flush, lib)
+            extras["at_scale_aperture_56B"] = {
+                "particles": ns, "ms_three_launches_and_count_readback": ams,
+                "scatter_kernel_ms": k11,
+                "achieved_gbs": 56 * ns / (ams * 1e-3) / 1e9,
+                "frac": 56 * ns / (ams * 1e-3) / 1e9 / peak,
+                "scatter_achieved_gbs": 48 * ns / (k11 * 1e-3) / 1e9 if k11 else None}
+            del beam
+            ell = lambda: lx.ParticleBeam.uniform_3d_ellipsoid(  # noqa: E731
+                num_particles=ns, radius_x=torch.tensor([1e-3]), seed=3)
+            ell()
+            ems = float(np.mean(timed_steps(ell, 10, 3, flush)))
+            extras["generate_ellipsoid_24B"] = {
+                "particles": ns, "ms": ems, "achieved_gbs": 24 * ns / (ems * 1e-3) / 1e9,
+                "frac": 24 * ns / (ems * 1e-3) / 1e9 / peak,
+                "note": "per-particle Philox rejection (1.91 draws per particle) + 3 normals"}
+        except Exception as e:  # noqa: BLE001 -- extras never take the headline line down
+            extras["beamops_error"] = repr(e)
         line["extras"] = extras
 
     lib.lynx_host_ctx_destroy(ctx)

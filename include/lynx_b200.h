@@ -246,6 +246,57 @@ int lynx_beam_generate(const float* d_mean, const float* d_sqrt_cov, int64_t B, 
 /* One Philox4x32-10 block on the HOST (known-answer hook for the CPU tests). */
 void lynx_philox4x32_10(const uint32_t counter[4], const uint32_t key[2], uint32_t out[4]);
 
+/* K9b -- ParticleBeam.uniform_3d_ellipsoid on the device (particle_beam.py:266-385): (x, y, s)
+ * uniform inside the ellipsoid with semi-axes d_radii [B][3] = (r_x, r_y, r_s) by per-particle
+ * rejection from the bounding box (the reference's test, particle_beam.py:346, in exact fp32
+ * round-to-nearest operations); xp, yp, p = d_sigma [B][3] * z with the same normals z that
+ * lynx_beam_generate draws for these coordinates under the same seed (the reference builds
+ * the beam as from_parameters(...) with the spatial coordinates replaced, :363-383).
+ * Counter layout: attempt a of global particle n uses Philox counter (n_lo, n_hi, b, 16 + a). */
+int lynx_beam_generate_ellipsoid(const float* d_radii, const float* d_sigma, int64_t B, int64_t N,
+                                 int64_t first_particle, uint64_t seed, float* d_soa, int64_t ld,
+                                 lynx_stream_t stream);
+
+/* K10 -- ParticleBeam.transformed_to (particle_beam.py:580-715), the particle pass :696-702:
+ *     out = (in - old_mu) / old_sigma * new_sigma + new_mu          per coordinate, per row
+ * in exactly that order of fp32 operations (bit-identical to the reference's array ops).
+ *   d_table [B][24] = old_mu[6], old_sigma[6], new_sigma[6], new_mu[6] per beam row
+ *   in_row_stride    floats between beam rows of d_in_soa (6*ld_in, or 0: one beam, B targets)
+ * Padding lanes [N, ld_out) are written as zeros.  48 B per particle.                      */
+int lynx_beam_transform(const float* d_in_soa, int64_t in_row_stride, int64_t ld_in, int64_t B,
+                        int64_t N, const float* d_table, float* d_out_soa, int64_t ld_out,
+                        lynx_stream_t stream);
+
+/* K11 -- Aperture.track (aperture.py:69-109): order-preserving compaction of the particles
+ * that pass the aperture; the complement goes to d_lost_soa (the reference's lost_particles).
+ *   shape 0 = "rectangular": -x_max < x < x_max and -y_max < y < y_max        (:80-84)
+ *         1 = "elliptical":  x^2/x_max^2 + y^2/y_max^2 <= 1, fp32 op by op    (:85-88)
+ *   d_x_max, d_y_max [R] (lim_stride 1) or one value for all rows (lim_stride 0)
+ *   d_charges_in [R][ld_q] nullable -> d_charges_out / d_charges_lost [R][ld_out] (nullable)
+ *   d_out_soa, d_lost_soa (nullable) [R][6][ld_out]: row r holds counts[r] survivors resp.
+ *   N - counts[r] lost particles in their incoming order; lanes beyond are NOT written
+ *   d_counts [R] int64 survivors per beam row
+ *   d_workspace  lynx_aperture_workspace_bytes(R, N) bytes
+ * Three launches (tile counts, scan, scatter); 56 B per particle.                          */
+size_t lynx_aperture_workspace_bytes(int64_t R, int64_t N);
+int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N, int64_t ld_in,
+                          const float* d_charges_in, int64_t ld_q, const float* d_x_max,
+                          const float* d_y_max, int64_t lim_stride, int32_t shape,
+                          float* d_out_soa, float* d_lost_soa, int64_t ld_out,
+                          float* d_charges_out, float* d_charges_lost, int64_t* d_counts,
+                          void* d_workspace, lynx_stream_t stream);
+
+/* K6-along -- ParameterBeam tracked element by element, one snapshot per program op
+ * (the loop of Segment.plot_twiss, segment.py:490-518: element.track(beam) per element,
+ * every intermediate beam kept).  Nothing is merged: op i's own map is applied to the beam
+ * after op i-1 (element.py:71-82; active cavities as in lynx_parambeam_fwd).  BPMs and
+ * screens pass the beam through.
+ *   d_snap_mu [n_ops][B][7], d_snap_cov [n_ops][B][7][7], d_snap_energy [n_ops][B]          */
+int lynx_parambeam_along(const lynx_program_t*, const float* d_params, int64_t B,
+                         const float* d_mu_in, const float* d_cov_in, int64_t beam_stride,
+                         const float* d_energy_in, float* d_snap_mu, float* d_snap_cov,
+                         float* d_snap_energy, lynx_stream_t stream);
+
 /* Layout converters between the reference's AoS (..,N,7) ParticleBeam.particles
  * (particle_beam.py:24-45) and the SoA-6 device layout. */
 int lynx_aos7_to_soa6(const float* d_aos /*[R][N][7]*/, int64_t R, int64_t N,
@@ -261,7 +312,8 @@ void lynx_launch_count_reset(void);
  * dominant kernel with CUDA events on the launch stream.  lynx_profile_last_ms
  * synchronises on the stop event and returns the device time of the last launch of
  * kernel class `which` (0 = K1 composer, 1 = K2 tracker, 2 = K6 ParameterBeam,
- * 3 = K3 adjoint), or a negative value if none was recorded. */
+ * 3 = K3 adjoint, 4 = K10 transform, 5 = K11 aperture scatter), or a negative value if none
+ * was recorded. */
 void lynx_profile_enable(int on);
 float lynx_profile_last_ms(int which);
 /* Debug: block 0 of lynx_screen_allreduce stamps %globaltimer (ns) into

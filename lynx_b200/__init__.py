@@ -8,6 +8,7 @@ CUDA kernels behind the C ABI of ``include/lynx_b200.h``.  No CPU fallback.
 from .beams import Beam, ParameterBeam, ParticleBeam  # noqa: F401
 from .elements import (  # noqa: F401
     BPM,
+    Aperture,
     Cavity,
     CustomTransferMap,
     Dipole,

@@ -73,6 +73,15 @@ SIGNATURES = {
     "lynx_screen_pdf": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i32, _i32, _vp, _vp]),
     "lynx_beam_generate": (C.c_int, [_vp, _vp, _i64, _i64, _i64, C.c_uint64, _vp, _i64, _vp]),
     "lynx_philox4x32_10": (None, [_vp, _vp, _vp]),
+    "lynx_beam_generate_ellipsoid": (C.c_int, [_vp, _vp, _i64, _i64, _i64, C.c_uint64, _vp, _i64, _vp]),
+    "lynx_beam_transform": (C.c_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _i64, _vp]),
+    "lynx_aperture_workspace_bytes": (_sz, [_i64, _i64]),
+    "lynx_aperture_compact": (
+        C.c_int,
+        [_vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _i64, _i32, _vp, _vp, _i64, _vp, _vp, _vp,
+         _vp, _vp],
+    ),
+    "lynx_parambeam_along": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "lynx_aos7_to_soa6": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _vp]),
     "lynx_soa6_to_aos7": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp]),
     "lynx_launch_count": (_i64, []),

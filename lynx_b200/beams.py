@@ -226,6 +226,107 @@ class ParticleBeam(Beam):
             cor_y=-emittance_y * alpha_y, total_charge=d(total_charge, 0.0), device=device,
             dtype=dtype, seed=seed, first_particle=first_particle)
 
+    @classmethod
+    def uniform_3d_ellipsoid(cls, num_particles=None, radius_x=None, radius_y=None,
+                             radius_s=None, sigma_xp=None, sigma_yp=None, sigma_p=None,
+                             energy=None, total_charge=None, device=None, dtype=torch.float32,
+                             seed=None, first_particle=0):
+        """particle_beam.py:266-385 (same arguments and defaults: as written, a ``None``
+        sigma falls through to ``from_parameters``' defaults 2e-7 / 2e-7 / 1e-6, :363-374),
+        generated ON the device by ``lynx_beam_generate_ellipsoid``: per-particle rejection
+        from the bounding box instead of the reference's host loop over whole candidate
+        batches; the momentum planes are those of ``from_parameters(seed=seed)``."""
+        assert dtype == torch.float32, "device path is fp32 (SURVEY.md section 5)"
+        given = [a for a in (radius_x, radius_y, radius_s, sigma_xp, sigma_yp, sigma_p, energy,
+                             total_charge) if a is not None]
+        shape = tuple(given[0].shape) if given else (1,)
+        assert all(tuple(a.shape) == shape for a in given), "Arguments must have the same shape."
+        num_particles = int(num_particles) if num_particles is not None else 1_000_000
+        device = torch.device(device if device is not None else "cuda")
+        d = lambda a, v: (torch.as_tensor(a, dtype=torch.float32).cpu() if a is not None  # noqa: E731
+                          else torch.full(shape, v, dtype=torch.float32))
+        radii = torch.stack([d(radius_x, 1e-3), d(radius_y, 1e-3), d(radius_s, 1e-3)], dim=-1)
+        sigma = torch.stack([d(sigma_xp, 2e-7), d(sigma_yp, 2e-7), d(sigma_p, 1e-6)], dim=-1)
+        B = 1
+        for s_ in shape:
+            B *= s_
+        if seed is None:
+            seed = int(torch.randint(0, 2**62, (1,), dtype=torch.int64).item())
+        N = num_particles
+        ld = (N + 3) & ~3
+        soa = torch.empty((*shape, 6, ld), device=device, dtype=torch.float32)
+        radii_d = radii.reshape(B, 3).to(device).contiguous()
+        sigma_d = sigma.reshape(B, 3).to(device).contiguous()
+        L.check(L.lib().lynx_beam_generate_ellipsoid(
+            radii_d.data_ptr(), sigma_d.data_ptr(), B, N, int(first_particle), seed,
+            soa.data_ptr(), ld, L.current_stream()), "lynx_beam_generate_ellipsoid")
+        charges = (d(total_charge, 0.0).to(device) / N).unsqueeze(-1).expand(*shape, N)
+        return cls.from_soa(soa, N, d(energy, 1e8).to(device), charges)
+
+    @classmethod
+    def make_linspaced(cls, num_particles=None, mu_x=None, mu_y=None, mu_xp=None, mu_yp=None,
+                       sigma_x=None, sigma_y=None, sigma_xp=None, sigma_yp=None, sigma_s=None,
+                       sigma_p=None, energy=None, total_charge=None, device=None,
+                       dtype=torch.float32):
+        """particle_beam.py:387-503: every coordinate ``linspace(mu - sigma, mu + sigma, n)``
+        (a handful of reference particles for trace plots; built with torch on the device,
+        no kernel of its own)."""
+        given = [a for a in (mu_x, mu_xp, mu_y, mu_yp, sigma_x, sigma_xp, sigma_y, sigma_yp,
+                             sigma_s, sigma_p, energy, total_charge) if a is not None]
+        shape = tuple(given[0].shape) if given else (1,)
+        assert all(tuple(a.shape) == shape for a in given), "Arguments must have the same shape."
+        n = int(num_particles) if num_particles is not None else 10
+        device = torch.device(device if device is not None else "cuda")
+        d = lambda a, v: (torch.as_tensor(a, dtype=torch.float32).to(device) if a is not None  # noqa: E731
+                          else torch.full(shape, v, dtype=torch.float32, device=device))
+        mus = [d(mu_x, 0.0), d(mu_xp, 0.0), d(mu_y, 0.0), d(mu_yp, 0.0), d(None, 0.0), d(None, 0.0)]
+        sgs = [d(sigma_x, 175e-9), d(sigma_xp, 2e-7), d(sigma_y, 175e-9), d(sigma_yp, 2e-7),
+               d(sigma_s, 0.0), d(sigma_p, 0.0)]
+        w = torch.linspace(-1.0, 1.0, n, device=device)
+        ld = (n + 3) & ~3
+        soa = torch.zeros((*shape, 6, ld), device=device)
+        for k in range(6):
+            soa[..., k, :n] = mus[k].unsqueeze(-1) + sgs[k].unsqueeze(-1) * w
+        charges = (d(total_charge, 0.0) / n).unsqueeze(-1).expand(*shape, n)
+        return cls.from_soa(soa, n, d(energy, 1e8), charges)
+
+    def transformed_to(self, mu_x=None, mu_y=None, mu_xp=None, mu_yp=None, sigma_x=None,
+                       sigma_y=None, sigma_xp=None, sigma_yp=None, sigma_s=None, sigma_p=None,
+                       energy=None, total_charge=None, device=None, dtype=torch.float32):
+        """particle_beam.py:580-715: the particle pass ``(x - old_mu) / old_sigma * new_sigma
+        + new_mu`` (:696-702) is ONE kernel (``lynx_beam_transform``, 48 B/particle); the old
+        moments come from the fused sums (one 24 B/particle pass if the beam has none yet)."""
+        shape = self.batch_shape
+        given = [a for a in (mu_x, mu_xp, mu_y, mu_yp, sigma_x, sigma_xp, sigma_y, sigma_yp,
+                             sigma_s, sigma_p, energy, total_charge) if a is not None]
+        assert all(tuple(a.shape) == tuple(shape) for a in given), (
+            "Arguments must have the same shape.")
+        dev = self._soa.device
+        g = lambda a, cur: (torch.as_tensor(a, dtype=torch.float32).to(dev) if a is not None  # noqa: E731
+                            else cur)
+        zero = torch.zeros(shape, device=dev)
+        old_mu = [self.mu_x, self.mu_xp, self.mu_y, self.mu_yp, zero, zero]
+        old_sg = [self.sigma_x, self.sigma_xp, self.sigma_y, self.sigma_yp, self.sigma_s,
+                  self.sigma_p]
+        new_mu = [g(mu_x, old_mu[0]), g(mu_xp, old_mu[1]), g(mu_y, old_mu[2]),
+                  g(mu_yp, old_mu[3]), zero, zero]
+        new_sg = [g(sigma_x, old_sg[0]), g(sigma_xp, old_sg[1]), g(sigma_y, old_sg[2]),
+                  g(sigma_yp, old_sg[3]), g(sigma_s, old_sg[4]), g(sigma_p, old_sg[5])]
+        table = torch.stack(old_mu + old_sg + new_sg + new_mu, dim=-1).contiguous()  # (*shape, 24)
+        B = 1
+        for s_ in shape:
+            B *= s_
+        soa = self._soa if self._soa.is_contiguous() else self._soa.contiguous()
+        out = torch.empty_like(soa)
+        L.check(L.lib().lynx_beam_transform(soa.data_ptr(), 6 * self.ld, self.ld, max(B, 1),
+                                            self._n, table.data_ptr(), out.data_ptr(), self.ld,
+                                            L.current_stream()), "lynx_beam_transform")
+        pc = self.particle_charges
+        if total_charge is not None and pc is not None:  # particle_beam.py:655-664
+            tq = torch.as_tensor(total_charge, dtype=torch.float32).to(dev)
+            pc = torch.ones_like(pc) * tq.reshape(*shape, 1) / pc.shape[-1]
+        return ParticleBeam.from_soa(out, self._n, g(energy, self.energy), pc)
+
     # ---- storage views
     @property
     def soa(self) -> torch.Tensor:

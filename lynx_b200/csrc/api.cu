@@ -9,9 +9,10 @@ namespace lynx {
 std::atomic<int64_t> g_launches{0};
 
 static std::atomic<int> g_profile{0};
-static cudaEvent_t g_ev[4][2];
-static bool g_ev_made[4] = {false, false, false, false};
-static bool g_ev_used[4] = {false, false, false, false};
+constexpr int kProfSlots = 8;
+static cudaEvent_t g_ev[kProfSlots][2];
+static bool g_ev_made[kProfSlots] = {};
+static bool g_ev_used[kProfSlots] = {};
 
 ProfileScope::ProfileScope(int w, cudaStream_t s) : which(w), st(s), on(g_profile.load() != 0) {
   if (!on) return;
@@ -108,7 +109,7 @@ extern "C" const char* lynx_status_str(int s) {
 
 extern "C" void lynx_profile_enable(int on) { g_profile.store(on); }
 extern "C" float lynx_profile_last_ms(int which) {
-  if (which < 0 || which > 3 || !g_ev_used[which]) return -1.f;
+  if (which < 0 || which >= kProfSlots || !g_ev_used[which]) return -1.f;
   float ms = -1.f;
   if (cudaEventSynchronize(g_ev[which][1]) != cudaSuccess) return -1.f;
   if (cudaEventElapsedTime(&ms, g_ev[which][0], g_ev[which][1]) != cudaSuccess) return -1.f;

@@ -112,6 +112,82 @@ __global__ void __launch_bounds__(kGenTPB) beam_generate_kernel(
   }
 }
 
+// K9b: ParticleBeam.uniform_3d_ellipsoid (particle_beam.py:266-385): (x, y, s) uniform inside
+// the ellipsoid with semi-axes (r_x, r_y, r_s) by rejection from the bounding box, xp / yp / p
+// from the uncorrelated Gaussian beam of from_parameters (particle_beam.py:363-374).
+//
+// The reference redraws whole batches of N candidates from the global generator until N were
+// accepted; here every particle rejects on its own private counter stream, so a particle
+// depends only on (seed, setting, global particle index):
+//   attempt a of particle n: Philox counter (n_lo, n_hi, b, 16 + a), words 0..2 ->
+//   t = ((w >> 9) - 2^22 + 0.5) 2^-22 in (-1, 1), exact in fp32 (= (rand - 0.5) * 2 of
+//   particle_beam.py:342-344 for rand = ((w >> 9) + 0.5) 2^-23);  candidate = t * r;
+//   accepted iff x^2/r_x^2 + y^2/r_y^2 + s^2/r_s^2 < 1 (particle_beam.py:346), evaluated
+//   with explicit round-to-nearest fp32 operations (no FMA contraction), so the CPU
+//   restatement (oracle/generate.py) makes bit-identical decisions.  After kEllMaxTries
+//   rejections (probability 0.4764^64 ~ 2e-21) the particle is placed at the centre.
+// The momentum planes use K9's stream (coordinates j = 1, 3, 5 of the particle's group): the
+// beam equals from_parameters(seed) with the three spatial planes replaced, which is exactly
+// how the reference builds it.
+constexpr int kEllMaxTries = 64;
+
+__host__ __device__ __forceinline__ float ell_unit(uint32_t w) {
+  return ((float)((int32_t)(w >> 9) - 4194304) + 0.5f) * 2.384185791015625e-7f;  // 2^-22
+}
+
+__global__ void __launch_bounds__(kGenTPB) beam_ellipsoid_kernel(
+    const float* __restrict__ radii, const float* __restrict__ sigma, int64_t N, int64_t first,
+    uint32_t seed_lo, uint32_t seed_hi, float* __restrict__ soa, int64_t ld) {
+  const int64_t b = blockIdx.y;
+  const float rx = __ldg(radii + b * 3 + 0), ry = __ldg(radii + b * 3 + 1),
+              rs = __ldg(radii + b * 3 + 2);
+  const float sg[3] = {__ldg(sigma + b * 3 + 0), __ldg(sigma + b * 3 + 1), __ldg(sigma + b * 3 + 2)};
+  const float rx2 = __fmul_rn(rx, rx), ry2 = __fmul_rn(ry, ry), rs2 = __fmul_rn(rs, rs);
+  float* out = soa + b * 6 * ld;
+  const int64_t groups = (N + 3) >> 2;
+  for (int64_t g = (int64_t)blockIdx.x * kGenTPB + threadIdx.x; g < groups;
+       g += (int64_t)gridDim.x * kGenTPB) {
+    float pos[3][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint64_t n = (uint64_t)(first + g * 4 + q);
+      float x = 0.f, y = 0.f, s = 0.f;
+      for (int a = 0; a < kEllMaxTries; ++a) {
+        uint32_t c[4] = {(uint32_t)n, (uint32_t)(n >> 32), (uint32_t)b, (uint32_t)(16 + a)};
+        philox4x32_10(c, seed_lo, seed_hi);
+        const float cx = __fmul_rn(ell_unit(c[0]), rx), cy = __fmul_rn(ell_unit(c[1]), ry),
+                    cs = __fmul_rn(ell_unit(c[2]), rs);
+        const float t = __fadd_rn(__fadd_rn(__fdiv_rn(__fmul_rn(cx, cx), rx2),
+                                            __fdiv_rn(__fmul_rn(cy, cy), ry2)),
+                                  __fdiv_rn(__fmul_rn(cs, cs), rs2));
+        if (t < 1.0f) {
+          x = cx, y = cy, s = cs;
+          break;
+        }
+      }
+      const bool live = g * 4 + q < N;
+      pos[0][q] = live ? x : 0.f;
+      pos[1][q] = live ? y : 0.f;
+      pos[2][q] = live ? s : 0.f;
+    }
+    const uint64_t gg = (uint64_t)(g + (first >> 2));
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      uint32_t c[4] = {(uint32_t)gg, (uint32_t)(gg >> 32), (uint32_t)b, (uint32_t)(2 * j + 1)};
+      philox4x32_10(c, seed_lo, seed_hi);
+      float z[4];
+      box_muller(c[0], c[1], z[0], z[1]);
+      box_muller(c[2], c[3], z[2], z[3]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) z[q] = (g * 4 + q < N) ? __fmul_rn(sg[j], z[q]) : 0.f;
+      __stcs(reinterpret_cast<float4*>(out + (2 * j) * ld + g * 4),
+             make_float4(pos[j][0], pos[j][1], pos[j][2], pos[j][3]));
+      __stcs(reinterpret_cast<float4*>(out + (2 * j + 1) * ld + g * 4),
+             make_float4(z[0], z[1], z[2], z[3]));
+    }
+  }
+}
+
 }  // namespace lynx
 
 using namespace lynx;
@@ -130,6 +206,25 @@ extern "C" int lynx_beam_generate(const float* d_mean, const float* d_sqrt_cov, 
   const unsigned gx = (unsigned)std::min<int64_t>((groups + kGenTPB - 1) / kGenTPB, per_b);
   beam_generate_kernel<<<dim3(gx, (unsigned)B), kGenTPB, 0, (cudaStream_t)stream>>>(
       d_mean, d_sqrt_cov, N, first_particle, (uint32_t)seed, (uint32_t)(seed >> 32), d_soa, ld);
+  count_launch();
+  LYNX_CUDA_OK(cudaGetLastError());
+  return LYNX_OK;
+}
+
+extern "C" int lynx_beam_generate_ellipsoid(const float* d_radii, const float* d_sigma, int64_t B,
+                                            int64_t N, int64_t first_particle, uint64_t seed,
+                                            float* d_soa, int64_t ld, lynx_stream_t stream) {
+  if (!d_radii || !d_sigma || !d_soa || B <= 0 || B > 65535 || N <= 0 || ld < N || (ld & 3) ||
+      first_particle < 0 || (first_particle & 3) || ((uintptr_t)d_soa & 15))
+    return LYNX_E_BADARG;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int64_t groups = (N + 3) >> 2;
+  const int64_t per_b = std::max<int64_t>(1, (8LL * sms + B - 1) / B);
+  const unsigned gx = (unsigned)std::min<int64_t>((groups + kGenTPB - 1) / kGenTPB, per_b);
+  beam_ellipsoid_kernel<<<dim3(gx, (unsigned)B), kGenTPB, 0, (cudaStream_t)stream>>>(
+      d_radii, d_sigma, N, first_particle, (uint32_t)seed, (uint32_t)(seed >> 32), d_soa, ld);
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());
   return LYNX_OK;

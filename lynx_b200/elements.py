@@ -103,6 +103,18 @@ class Element:
         return f"{self.__class__.__name__}({ps}, name={self.name!r})"
 
 
+def _split_lengths(length, resolution):
+    """Slice lengths of the ``split`` loops (drift.py:71-78 et al.): ``min(resolution,
+    remaining)`` while ``remaining > 0``."""
+    remaining = torch.as_tensor(length, dtype=torch.float32).clone()
+    resolution = torch.as_tensor(resolution, dtype=torch.float32)
+    out = []
+    while bool((remaining > 0).all()) and remaining.numel() > 0:
+        out.append(torch.minimum(resolution, remaining))
+        remaining = remaining - resolution
+    return out
+
+
 class Marker(Element):
     """marker.py:22-64."""
 
@@ -121,6 +133,9 @@ class Drift(Element):
 
     def _encode(self):
         return (L.OP_DRIFT, [self.length], 0)
+
+    def split(self, resolution):  # drift.py:71-78
+        return [Drift(l_) for l_ in _split_lengths(self.length, resolution)]
 
 
 class Quadrupole(Element):
@@ -147,6 +162,10 @@ class Quadrupole(Element):
         m = self.misalignment
         return (L.OP_QUAD, [self.length, self.k1, m[..., 0], m[..., 1], self.tilt], 0)
 
+    def split(self, resolution):  # quadrupole.py:99-110 (the tilt is dropped there, as written)
+        return [Quadrupole(l_, self.k1, misalignment=self.misalignment)
+                for l_ in _split_lengths(self.length, resolution)]
+
 
 class HorizontalCorrector(Element):
     """horizontal_corrector.py:25-110."""
@@ -165,6 +184,10 @@ class HorizontalCorrector(Element):
 
     def _encode(self):
         return (self._opcode, [self.length, self.angle], 0)
+
+    def split(self, resolution):  # horizontal_corrector.py:82-90, vertical_corrector.py:81-89
+        return [self.__class__(l_, self.angle * l_ / self.length)
+                for l_ in _split_lengths(self.length, resolution)]
 
 
 class VerticalCorrector(HorizontalCorrector):
@@ -323,6 +346,105 @@ class CustomTransferMap(Element):
     def _encode(self):
         tm = self._transfer_map
         return (L.OP_CUSTOM, [tm[..., r, c] for r in range(6) for c in range(7)], 0)
+
+
+class Aperture(Element):
+    """aperture.py:24-153.  ``track`` for a ParticleBeam is an order-preserving stream
+    compaction on the device (``lynx_aperture_compact``): the survivors form the outgoing
+    beam, the rest is kept as ``lost_particles`` / ``lost_particle_charges`` exactly as the
+    reference's boolean-mask indexing produces them (aperture.py:89-97)."""
+
+    _params = ("x_max", "y_max")
+
+    def __init__(self, x_max=None, y_max=None, shape="rectangular", is_active=True, name=None,
+                 device=None, dtype=torch.float32):
+        self.x_max = _t(x_max, default=float("inf"))
+        self.y_max = _t(y_max, default=float("inf"))
+        self.shape = shape
+        self.is_active = is_active
+        self.lost_particles = None
+        self.lost_particle_charges = None
+        super().__init__(name)
+
+    @property
+    def is_skippable(self) -> bool:
+        return not self.is_active
+
+    def _encode(self):
+        return None  # identity map (aperture.py:63-67); the cut itself is not a map
+
+    def track(self, incoming):
+        if incoming is Beam.empty:
+            return incoming
+        if not (isinstance(incoming, ParticleBeam) and self.is_active):
+            return incoming  # aperture.py:71-72
+        assert bool((self.x_max >= 0).all()) and bool((self.y_max >= 0).all())
+        assert self.shape in ("rectangular", "elliptical"), f"Unknown aperture shape {self.shape}"
+        soa = incoming.soa
+        dev = soa.device
+        if dev.type != "cuda":
+            raise L.LynxError("lynx_b200 tracks on a CUDA device only (no CPU fallback)")
+        R = 1
+        for s_ in incoming.batch_shape:
+            R *= s_
+        if R != 1 or self.x_max.numel() != 1 or self.y_max.numel() != 1:
+            # every beam row keeps a different number of particles: not one ParticleBeam
+            # (the reference's mask indexing flattens the batch in that case)
+            raise NotImplementedError("Aperture.track: one beam row (batch size 1) only")
+        soa = soa if soa.is_contiguous() else soa.contiguous()
+        N, ld = incoming.num_particles, incoming.ld
+        xm = self.x_max.reshape(1).to(device=dev, dtype=torch.float32)
+        ym = self.y_max.reshape(1).to(device=dev, dtype=torch.float32)
+        pc = incoming.particle_charges
+        uniform_pc = pc is not None and pc.stride(-1) == 0
+        q_in = pc.reshape(1, N).contiguous() if (pc is not None and not uniform_pc) else None
+        kept = torch.empty_like(soa)
+        lost = torch.empty_like(soa)
+        q_kept = torch.empty((1, ld), device=dev) if q_in is not None else None
+        q_lost = torch.empty((1, ld), device=dev) if q_in is not None else None
+        counts = torch.empty(1, dtype=torch.int64, device=dev)
+        ws = torch.empty(max(L.lib().lynx_aperture_workspace_bytes(1, N), 16), dtype=torch.uint8,
+                         device=dev)
+        L.check(L.lib().lynx_aperture_compact(
+            soa.data_ptr(), 1, N, ld, L.ptr(q_in), N if q_in is not None else 0, xm.data_ptr(),
+            ym.data_ptr(), 0, 0 if self.shape == "rectangular" else 1, kept.data_ptr(),
+            lost.data_ptr(), ld, L.ptr(q_kept), L.ptr(q_lost), counts.data_ptr(), ws.data_ptr(),
+            L.current_stream()), "lynx_aperture_compact")
+        n = int(counts.item())  # the boolean-mask indexing of the reference syncs here too
+        bshape = incoming.batch_shape
+
+        def charges(buf, m):
+            if pc is None:
+                return None
+            if uniform_pc:
+                return pc[..., :1].expand(*bshape, m)
+            return buf[0, :m].reshape(*bshape, m)
+
+        # aperture.py:91-96: lost particles in the reference's (n_lost, 7) AoS layout
+        n_lost = N - n
+        if n_lost > 0:
+            lost[..., n_lost:(n_lost + 3) & ~3] = 0
+            lb = ParticleBeam.from_soa(lost, n_lost, incoming.energy, None)
+            self.lost_particles = lb.particles.reshape(n_lost, 7)
+            self.lost_particle_charges = (
+                charges(q_lost, n_lost).reshape(n_lost) if pc is not None else None)
+        else:
+            self.lost_particles = torch.empty((0, 7), device=dev)
+            self.lost_particle_charges = torch.empty(0, device=dev) if pc is not None else None
+        if n == 0:
+            return ParticleBeam.empty  # aperture.py:98-108
+        kept[..., n:(n + 3) & ~3] = 0  # padding lanes [N, round4(N)) of the SoA contract
+        return ParticleBeam.from_soa(kept, n, incoming.energy, charges(q_kept, n))
+
+    def broadcast(self, shape):
+        new = self.__class__(x_max=self.x_max.repeat(shape), y_max=self.y_max.repeat(shape),
+                             shape=self.shape, is_active=self.is_active, name=self.name)
+        new.length = self.length.repeat(shape)
+        return new
+
+    @property
+    def defining_features(self):
+        return ["x_max", "y_max", "shape", "is_active"]
 
 
 class BPM(Element):

@@ -12,7 +12,7 @@ import torch
 from . import _lib as L
 from . import autograd as AG
 from .beams import Beam, ParameterBeam, ParticleBeam
-from .elements import BPM, CustomTransferMap, Drift, Element, Marker, Screen
+from .elements import BPM, Aperture, CustomTransferMap, Drift, Element, Marker, Screen
 from .program import Program, encode, pack_params
 
 
@@ -107,6 +107,13 @@ def track_elements(elements, incoming, *, particles: bool = True, moments: int =
         return _track_parameter_beam(flat, incoming)
     if not isinstance(incoming, ParticleBeam):
         raise TypeError(f"Parameter incoming is of invalid type {type(incoming)}")
+    # an active Aperture changes the number of particles: the lattice is cut there
+    # (aperture.py:61-62 is_skippable = not is_active; segment.py:344-351 steps through it)
+    cut = next((i for i, e in enumerate(flat) if isinstance(e, Aperture) and e.is_active), None)
+    if cut is not None:
+        beam = track_elements(flat[:cut], incoming, moments=moments) if cut else incoming
+        beam = flat[cut].track(beam)
+        return track_elements(flat[cut + 1:], beam, particles=particles, moments=moments)
     device = incoming.soa.device
     _require_cuda(device)
     enc = encode(flat, incoming.energy.shape)
@@ -210,6 +217,38 @@ def _track_parameter_beam(flat, incoming: ParameterBeam):
         enc.screen_element.set_read_beam(out)
         return Beam.empty
     return out
+
+
+def track_parameter_beam_along(flat, incoming: ParameterBeam):
+    """``lynx_parambeam_along``: the beam after EVERY element of ``flat`` (each of which must
+    encode to one op).  Returns ``(mu (E, *batch, 7), cov (E, *batch, 7, 7), energy (E, *batch))``."""
+    device = incoming._mu.device
+    _require_cuda(device)
+    enc = encode(flat, incoming.energy.shape)
+    assert len(enc.ops) == len(flat), "every element must encode to exactly one op"
+    bshape = tuple(torch.broadcast_shapes(enc.batch_shape, tuple(incoming._mu.shape[:-1])))
+    enc.batch_shape = bshape
+    B = enc.B
+    prog = Program.get(enc)
+    params = pack_params(enc, device)
+    e_in = incoming.energy.to(device).expand(bshape).reshape(B).contiguous()
+    mu, cov = incoming._mu, incoming._cov
+    nb = mu.dim() - 1
+    shared = _is_shared(mu, nb) and _is_shared(cov, nb)
+    if shared:
+        mu_in, cov_in = mu[(0,) * nb].contiguous(), cov[(0,) * nb].contiguous()
+    else:
+        mu_in = mu.expand(*bshape, 7).contiguous()
+        cov_in = cov.expand(*bshape, 7, 7).contiguous()
+    E = len(flat)
+    s_mu = torch.empty((E, *bshape, 7), device=device)
+    s_cov = torch.empty((E, *bshape, 7, 7), device=device)
+    s_en = torch.empty((E, *bshape), device=device)
+    L.check(L.lib().lynx_parambeam_along(
+        prog.handle, params.data_ptr(), B, mu_in.data_ptr(), cov_in.data_ptr(),
+        0 if shared else 1, e_in.data_ptr(), s_mu.data_ptr(), s_cov.data_ptr(), s_en.data_ptr(),
+        L.current_stream()), "lynx_parambeam_along")
+    return s_mu, s_cov, s_en
 
 
 # --------------------------------------------------------------------------- Segment
@@ -317,6 +356,42 @@ class Segment(Element):
             e if getattr(e, "is_active", False) or bool((e.length == 0.0).all())
             or e.name in except_for else Drift(e.length)
             for e in self.elements], name=self.name)
+
+    def twiss_along(self, beam):
+        """The data of ``plot_twiss`` (segment.py:490-518): the beam after every element of
+        non-zero length, tracked element by element.  Returns ``(s_positions, beams)`` with
+        ``beams[0]`` the incoming beam.  A ParameterBeam takes ONE launch for the whole
+        lattice (``lynx_parambeam_along``, a snapshot per element); a ParticleBeam is stepped
+        element by element like the reference."""
+        flat = [e for e in _flatten(self.elements) if bool((e.length != 0).any())]
+        s_positions, beams = [0.0], [beam]
+        for e in flat:
+            s_positions.append(s_positions[-1] + float(e.length.reshape(-1)[0]))
+        if isinstance(beam, ParameterBeam) and flat:
+            mu, cov, en = track_parameter_beam_along(flat, beam)
+            for i in range(len(flat)):
+                b = ParameterBeam.__new__(ParameterBeam)
+                b._mu, b._cov, b.energy, b.total_charge = mu[i], cov[i], en[i], beam.total_charge
+                beams.append(b)
+        else:
+            for e in flat:
+                beams.append(e.track(beams[-1]))
+        return s_positions, beams
+
+    def plot_twiss(self, beam, ax=None):
+        """segment.py:490-518.  Returns ``(s_positions, beta_x, beta_y)``; draws them when an
+        axis is passed (matplotlib itself is outside this package's scope)."""
+        s_positions, beams = self.twiss_along(beam)
+        beta_x = [float(b.beta_x.reshape(-1)[0]) for b in beams]
+        beta_y = [float(b.beta_y.reshape(-1)[0]) for b in beams]
+        if ax is not None:
+            ax.set_title("Twiss Parameters")
+            ax.set_xlabel("s (m)")
+            ax.set_ylabel(r"$\beta$ (m)")
+            ax.plot(s_positions, beta_x, label=r"$\beta_x$", c="tab:red")
+            ax.plot(s_positions, beta_y, label=r"$\beta_y$", c="tab:green")
+            ax.legend()
+        return s_positions, beta_x, beta_y
 
     def __repr__(self) -> str:
         return f"Segment(elements={self.elements!r}, name={self.name!r})"
