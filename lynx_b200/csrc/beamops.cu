@@ -70,8 +70,9 @@ __global__ void __launch_bounds__(kXfTPB) beam_transform_kernel(
 //   1. aperture_count_kernel   survivors per tile of kApTile particles (reads x, y: 8 B)
 //   2. aperture_scan_kernel    exclusive scan of the tile counts, one CTA per beam row
 //   3. aperture_scatter_kernel re-evaluates the mask, ranks the particles of the tile with
-//                              warp ballots + a CTA scan and copies all planes (24 B read,
-//                              24 B written: survivors and lost particles together are N)
+//                              a packed CTA scan, compacts the tile in shared memory and
+//                              streams all planes out (24 B read, 24 B written: survivors
+//                              and lost particles together are N)
 // 56 B per particle.  (A single-pass decoupled look-back scan would be 48 B; it needs
 // inter-CTA spinning, which this library otherwise avoids.)
 constexpr int kApTPB = 256;
@@ -193,8 +194,36 @@ struct ApertureArgs {
   float* q_lost;  // nullable [R][ld_out]
 };
 
+// Copies n floats from shared memory to dst[d0 .. d0 + n): scalar stores up to the first
+// 16-byte boundary of the destination, 16-byte stores for the aligned body, scalar tail.
+// `dst` itself is 16-byte aligned (plane base; ld multiple of 4), so the alignment of
+// element d0 + i is that of (d0 + i) & 3.
+__device__ __forceinline__ void copy_out(const float* __restrict__ s, float* __restrict__ dst,
+                                         int64_t d0, int n, bool vec_ok) {
+  if (n <= 0) return;
+  if (!vec_ok) {
+    for (int i = threadIdx.x; i < n; i += kApTPB) dst[d0 + i] = s[i];
+    return;
+  }
+  const int head = min(n, (int)((4 - (d0 & 3)) & 3));
+  if ((int)threadIdx.x < head) dst[d0 + threadIdx.x] = s[threadIdx.x];
+  const int body = (n - head) >> 2;
+  for (int v = threadIdx.x; v < body; v += kApTPB) {
+    const float* q = s + head + v * 4;
+    __stcs(reinterpret_cast<float4*>(dst + d0 + head + (int64_t)v * 4),
+           make_float4(q[0], q[1], q[2], q[3]));
+  }
+  const int done = head + body * 4;
+  if ((int)threadIdx.x < n - done) dst[d0 + done + threadIdx.x] = s[done + threadIdx.x];
+}
+
+// The tile's particles are first compacted inside shared memory (survivors at [0, cnt), lost
+// particles at [cnt, n) of each plane), then leave as contiguous, 16-byte-vectorised streams.
+// (First version: every thread stored its up to four survivors straight to global memory --
+// eight partial-sector store instructions per thread and plane, 2.7 TB/s)
 template <int SHAPE>
-__global__ void __launch_bounds__(kApTPB) aperture_scatter_kernel(ApertureArgs a) {
+__global__ void __launch_bounds__(kApTPB, 2) aperture_scatter_kernel(ApertureArgs a) {
+  extern __shared__ __align__(16) float ap_smem[];  // [7][kApTile]
   const int64_t r = blockIdx.y;
   const float xm = __ldg(a.x_max + r * a.lim_stride), ym = __ldg(a.y_max + r * a.lim_stride);
   const float* src = a.in + r * 6 * a.ld_in;
@@ -202,15 +231,54 @@ __global__ void __launch_bounds__(kApTPB) aperture_scatter_kernel(ApertureArgs a
   const float* ys = src + 2 * a.ld_in;
   float* kept = a.out + r * 6 * a.ld_out;
   float* lost = a.lost ? a.lost + r * 6 * a.ld_out : nullptr;
+  const bool has_q = a.q_in != nullptr;
+  const bool q_vec = has_q && (a.ld_q & 3) == 0 && ((uintptr_t)a.q_in & 15) == 0;
+  const bool out_vec = (a.ld_out & 3) == 0 && ((uintptr_t)a.out & 15) == 0 &&
+                       (!a.lost || ((uintptr_t)a.lost & 15) == 0);
+  const bool qo_vec = (a.ld_out & 3) == 0 && (!a.q_out || ((uintptr_t)a.q_out & 15) == 0) &&
+                      (!a.q_lost || ((uintptr_t)a.q_lost & 15) == 0);
   __shared__ unsigned s_w[kApTPB / 32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
     const int64_t tile0 = t * kApTile;
+    const int n_tile = (int)min((int64_t)kApTile, a.N - tile0);
+    // all loads of the tile are issued before anything depends on them
+    float4 v[kApVec][7];
+#pragma unroll
+    for (int it = 0; it < kApVec; ++it) {
+      const int64_t p = tile0 + ((int64_t)it * kApTPB + threadIdx.x) * 4;
+      if (p < a.N) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          v[it][k] = __ldcs(reinterpret_cast<const float4*>(src + k * a.ld_in + p));
+        if (has_q) {
+          const float* qp = a.q_in + r * a.ld_q + p;
+          if (q_vec) {
+            v[it][6] = __ldcs(reinterpret_cast<const float4*>(qp));
+          } else {
+            const int nv = (int)min((int64_t)4, a.N - p);
+            v[it][6].x = __ldcs(qp);
+            v[it][6].y = nv > 1 ? __ldcs(qp + 1) : 0.f;
+            v[it][6].z = nv > 2 ? __ldcs(qp + 2) : 0.f;
+            v[it][6].w = nv > 3 ? __ldcs(qp + 3) : 0.f;
+          }
+        }
+      }
+    }
     unsigned flags[kApVec], packed = 0;  // packed: survivors of vector `it` in bits 12*it..
 #pragma unroll
     for (int it = 0; it < kApVec; ++it) {
-      flags[it] = tile_flags<SHAPE>(xs, ys, tile0, a.N, xm, ym, it);
-      packed += (unsigned)__popc(flags[it]) << (12 * it);
+      const int64_t p = tile0 + ((int64_t)it * kApTPB + threadIdx.x) * 4;
+      unsigned f = 0;
+      if (p < a.N) {
+        const float4 x = v[it][0], y = v[it][2];
+        f |= survives<SHAPE>(x.x, y.x, xm, ym) ? 1u : 0u;
+        f |= (p + 1 < a.N && survives<SHAPE>(x.y, y.y, xm, ym)) ? 2u : 0u;
+        f |= (p + 2 < a.N && survives<SHAPE>(x.z, y.z, xm, ym)) ? 4u : 0u;
+        f |= (p + 3 < a.N && survives<SHAPE>(x.w, y.w, xm, ym)) ? 8u : 0u;
+      }
+      flags[it] = f;
+      packed += (unsigned)__popc(f) << (12 * it);
     }
     // exclusive scan of `packed` over the CTA (each 12-bit field holds at most 1024)
     unsigned inc = packed;
@@ -220,7 +288,7 @@ __global__ void __launch_bounds__(kApTPB) aperture_scatter_kernel(ApertureArgs a
       if (lane >= d) inc += o;
     }
     if (lane == 31) s_w[warp] = inc;
-    __syncthreads();
+    __syncthreads();  // also: the previous tile's copy-out has finished reading ap_smem
     unsigned before = inc - packed, total = 0;
 #pragma unroll
     for (int w = 0; w < kApTPB / 32; ++w) {
@@ -228,57 +296,49 @@ __global__ void __launch_bounds__(kApTPB) aperture_scatter_kernel(ApertureArgs a
       if (w < warp) before += sw;
       total += sw;
     }
-    __syncthreads();  // s_w is rewritten by the next tile
-    const int64_t kept0 = a.tile_offsets[r * a.n_tiles + t];
-    const int64_t lost0 = tile0 - kept0;
+    int cnt = 0;
+#pragma unroll
+    for (int it = 0; it < kApVec; ++it) cnt += (int)((total >> (12 * it)) & 0xFFFu);
     unsigned field_base = 0;  // survivors of the vectors it' < it of the whole CTA
 #pragma unroll
     for (int it = 0; it < kApVec; ++it) {
-      const int64_t p = tile0 + ((int64_t)it * kApTPB + threadIdx.x) * 4;
-      const unsigned k_rank = field_base + ((before >> (12 * it)) & 0xFFFu);
+      const int local = (it * kApTPB + threadIdx.x) * 4;
+      const int k_rank = (int)(field_base + ((before >> (12 * it)) & 0xFFFu));
       field_base += (total >> (12 * it)) & 0xFFFu;
-      if (p >= a.N) continue;
-      // rank of this float4's first particle among the tile's survivors / lost particles
-      const int64_t kdst = kept0 + k_rank;
-      const int64_t ldst = lost0 + ((int64_t)(it * kApTPB + threadIdx.x) * 4 - k_rank);
+      if (local >= n_tile) continue;
+      const int l_rank = cnt + (local - k_rank);  // lost particles live behind the survivors
       const unsigned f = flags[it];
-      const int nvalid = (int)min((int64_t)4, a.N - p);
+      const int nvalid = min(4, n_tile - local);
 #pragma unroll
       for (int k = 0; k < 7; ++k) {
-        const float* sp;
-        float *dk, *dl;
-        if (k < 6) {
-          sp = src + k * a.ld_in;
-          dk = kept + k * a.ld_out;
-          dl = lost ? lost + k * a.ld_out : nullptr;
-        } else {
-          if (!a.q_in) break;
-          sp = a.q_in + r * a.ld_q;
-          dk = a.q_out ? a.q_out + r * a.ld_out : nullptr;
-          dl = a.q_lost ? a.q_lost + r * a.ld_out : nullptr;
-        }
-        float v[4];
-        if (k < 6 || ((a.ld_q & 3) == 0 && ((uintptr_t)a.q_in & 15) == 0)) {
-          const float4 t4 = __ldcs(reinterpret_cast<const float4*>(sp + p));
-          v[0] = t4.x, v[1] = t4.y, v[2] = t4.z, v[3] = t4.w;
-        } else {
-#pragma unroll
-          for (int q = 0; q < 4; ++q) v[q] = q < nvalid ? __ldcs(sp + p + q) : 0.f;
-        }
+        if (k == 6 && !has_q) break;
+        float* sp = ap_smem + k * kApTile;
+        const float e[4] = {v[it][k].x, v[it][k].y, v[it][k].z, v[it][k].w};
         int kk = 0, ll = 0;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          if (q >= nvalid) break;
-          if (f & (1u << q)) {
-            if (dk) dk[kdst + kk] = v[q];
-            ++kk;
-          } else {
-            if (dl) dl[ldst + ll] = v[q];
-            ++ll;
+          if (q < nvalid) {
+            if (f & (1u << q)) sp[k_rank + kk++] = e[q];
+            else sp[l_rank + ll++] = e[q];
           }
         }
       }
     }
+    __syncthreads();
+    const int64_t kept0 = a.tile_offsets[r * a.n_tiles + t];
+    const int64_t lost0 = tile0 - kept0;
+#pragma unroll 1
+    for (int k = 0; k < 6; ++k) {
+      const float* sp = ap_smem + k * kApTile;
+      copy_out(sp, kept + k * a.ld_out, kept0, cnt, out_vec);
+      if (lost) copy_out(sp + cnt, lost + k * a.ld_out, lost0, n_tile - cnt, out_vec);
+    }
+    if (has_q) {
+      const float* sp = ap_smem + 6 * kApTile;
+      if (a.q_out) copy_out(sp, a.q_out + r * a.ld_out, kept0, cnt, qo_vec);
+      if (a.q_lost) copy_out(sp + cnt, a.q_lost + r * a.ld_out, lost0, n_tile - cnt, qo_vec);
+    }
+    // the next iteration's first __syncthreads() orders these reads before its writes
   }
 }
 
@@ -360,11 +420,16 @@ extern "C" int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N
   a.q_out = d_charges_out;
   a.q_lost = d_charges_lost;
   {
+    const size_t smem = (size_t)(d_charges_in ? 7 : 6) * kApTile * sizeof(float);
+    auto kern = shape == 0 ? aperture_scatter_kernel<0> : aperture_scatter_kernel<1>;
+    static bool attr_set[2] = {false, false};
+    if (!attr_set[shape]) {
+      LYNX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        7 * kApTile * (int)sizeof(float)));
+      attr_set[shape] = true;
+    }
     ProfileScope ps(5, st);
-    if (shape == 0)
-      aperture_scatter_kernel<0><<<grid, kApTPB, 0, st>>>(a);
-    else
-      aperture_scatter_kernel<1><<<grid, kApTPB, 0, st>>>(a);
+    kern<<<grid, kApTPB, smem, st>>>(a);
   }
   count_launch(3);
   LYNX_CUDA_OK(cudaGetLastError());

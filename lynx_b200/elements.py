@@ -362,9 +362,17 @@ class Aperture(Element):
         self.y_max = _t(y_max, default=float("inf"))
         self.shape = shape
         self.is_active = is_active
-        self.lost_particles = None
+        self._lost_beam = None  # SoA planes of the lost particles (device)
+        self._lost_aos = None
         self.lost_particle_charges = None
         super().__init__(name)
+
+    @property
+    def lost_particles(self):
+        """aperture.py:91: ``incoming.particles[~survived_mask]``, shape (n_lost, 7)."""
+        if self._lost_aos is None and self._lost_beam is not None:
+            self._lost_aos = self._lost_beam.particles.reshape(-1, 7)
+        return self._lost_aos
 
     @property
     def is_skippable(self) -> bool:
@@ -420,16 +428,18 @@ class Aperture(Element):
                 return pc[..., :1].expand(*bshape, m)
             return buf[0, :m].reshape(*bshape, m)
 
-        # aperture.py:91-96: lost particles in the reference's (n_lost, 7) AoS layout
+        # aperture.py:91-96: lost particles; the reference's (n_lost, 7) AoS view is built
+        # on first access of ``lost_particles`` (it is a diagnostic, not part of the track)
         n_lost = N - n
         if n_lost > 0:
             lost[..., n_lost:(n_lost + 3) & ~3] = 0
-            lb = ParticleBeam.from_soa(lost, n_lost, incoming.energy, None)
-            self.lost_particles = lb.particles.reshape(n_lost, 7)
+            self._lost_beam = ParticleBeam.from_soa(lost, n_lost, incoming.energy, None)
+            self._lost_aos = None
             self.lost_particle_charges = (
                 charges(q_lost, n_lost).reshape(n_lost) if pc is not None else None)
         else:
-            self.lost_particles = torch.empty((0, 7), device=dev)
+            self._lost_beam = None
+            self._lost_aos = torch.empty((0, 7), device=dev)
             self.lost_particle_charges = torch.empty(0, device=dev) if pc is not None else None
         if n == 0:
             return ParticleBeam.empty  # aperture.py:98-108

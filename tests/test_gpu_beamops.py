@@ -272,8 +272,11 @@ def test_twiss_along_matches_element_by_element_oracle():
                                    atol=2e-5 * sd.max())
         gc, wc = got._cov[0].cpu().numpy(), w.cov_[0].numpy()
         assert (np.abs(gc - wc) <= 3e-5 * (np.outer(sd, sd) + np.abs(wc))).all()
-        np.testing.assert_allclose(got.beta_x.cpu().numpy(), w.beta("x").numpy(), rtol=2e-4)
-        np.testing.assert_allclose(got.beta_y.cpu().numpy(), w.beta("y").numpy(), rtol=2e-4)
+        # beta = sigma^2 / sqrt(sigma_x^2 sigma_xp^2 - sigma_xxp^2): the emittance is a
+        # difference of nearly equal products once the beam is focused, so fp32 covariances
+        # that are right to 3e-5 give a beta that is right to ~1e-3 (beam.py:262-279)
+        np.testing.assert_allclose(got.beta_x.cpu().numpy(), w.beta("x").numpy(), rtol=3e-3)
+        np.testing.assert_allclose(got.beta_y.cpu().numpy(), w.beta("y").numpy(), rtol=3e-3)
     # the last snapshot is the merged track's outgoing beam (to fp32 rounding)
     end = seg.track(pb)
     ec = end._cov[0].cpu().numpy()

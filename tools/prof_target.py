@@ -38,6 +38,27 @@ elif a.mode == "adj32m":
     w.step = w.backward
 elif a.mode == "grad1m1024":
     w = bench.GradWorkload(1_000_000, 1024, dev)
+elif a.mode in ("transform32m", "aperture32m", "ellipsoid32m"):
+    import lynx_b200 as lx
+
+    class _W:
+        pass
+
+    w = _W()
+    if a.mode == "ellipsoid32m":
+        w.step = lambda: lx.ParticleBeam.uniform_3d_ellipsoid(
+            num_particles=32_000_000, radius_x=torch.tensor([1e-3]), seed=3)
+    else:
+        beam = lx.ParticleBeam.from_parameters(
+            num_particles=32_000_000, sigma_x=torch.tensor([2e-4]), sigma_y=torch.tensor([2e-4]),
+            seed=2)
+        beam.moment_sums()
+        if a.mode == "transform32m":
+            w.step = lambda: beam.transformed_to(sigma_x=torch.tensor([1e-4]))
+        else:
+            apert = lx.Aperture(x_max=torch.tensor(2e-4), y_max=torch.tensor(2e-4),
+                                shape="elliptical")
+            w.step = lambda: apert.track(beam)
 else:
     raise SystemExit("unknown mode")
 ms = bench.timed_steps(w.step, a.steps, 2, flush)
