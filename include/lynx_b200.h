@@ -273,7 +273,8 @@ int lynx_beam_transform(const float* d_in_soa, int64_t in_row_stride, int64_t ld
  *         1 = "elliptical":  x^2/x_max^2 + y^2/y_max^2 <= 1, fp32 op by op    (:85-88)
  *   d_x_max, d_y_max [R] (lim_stride 1) or one value for all rows (lim_stride 0)
  *   d_charges_in [R][ld_q] nullable -> d_charges_out / d_charges_lost [R][ld_out] (nullable)
- *   d_out_soa, d_lost_soa (nullable) [R][6][ld_out]: row r holds counts[r] survivors resp.
+ *   d_out_soa, d_lost_soa (nullable) [R][6][ld_out], 16-byte aligned, ld_out % 4 == 0 (as the
+ *   charge outputs): row r holds counts[r] survivors resp.
  *   N - counts[r] lost particles in their incoming order; lanes beyond are NOT written
  *   d_counts [R] int64 survivors per beam row
  *   d_workspace  lynx_aperture_workspace_bytes(R, N) bytes

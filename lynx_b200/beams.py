@@ -304,15 +304,24 @@ class ParticleBeam(Beam):
         dev = self._soa.device
         g = lambda a, cur: (torch.as_tensor(a, dtype=torch.float32).to(dev) if a is not None  # noqa: E731
                             else cur)
-        zero = torch.zeros(shape, device=dev)
-        old_mu = [self.mu_x, self.mu_xp, self.mu_y, self.mu_yp, zero, zero]
-        old_sg = [self.sigma_x, self.sigma_xp, self.sigma_y, self.sigma_yp, self.sigma_s,
-                  self.sigma_p]
-        new_mu = [g(mu_x, old_mu[0]), g(mu_xp, old_mu[1]), g(mu_y, old_mu[2]),
-                  g(mu_yp, old_mu[3]), zero, zero]
-        new_sg = [g(sigma_x, old_sg[0]), g(sigma_xp, old_sg[1]), g(sigma_y, old_sg[2]),
-                  g(sigma_yp, old_sg[3]), g(sigma_s, old_sg[4]), g(sigma_p, old_sg[5])]
-        table = torch.stack(old_mu + old_sg + new_sg + new_mu, dim=-1).contiguous()  # (*shape, 24)
+        # all twelve old moments from the 28 raw sums in a handful of vector ops (the same
+        # arithmetic as the mu_* / sigma_* properties: double sums, N-1, rounded to fp32)
+        sums = self.moment_sums()
+        cnt = sums[..., 0:1]
+        first = sums[..., 1:7]
+        diag = sums[..., [7 + _tri(i, i) for i in range(6)]]
+        old_mu = (first / cnt).to(torch.float32)
+        old_mu[..., 4:] = 0.0  # particle_beam.py:675-676, 687-688: s and p are not re-centred
+        old_sg = torch.sqrt(torch.clamp_min((diag - first**2 / cnt) / (cnt - 1), 0.0)).to(
+            torch.float32)
+        new_mu, new_sg = old_mu.clone(), old_sg.clone()
+        for i, a in enumerate((mu_x, mu_xp, mu_y, mu_yp)):
+            if a is not None:
+                new_mu[..., i] = g(a, None)
+        for i, a in enumerate((sigma_x, sigma_xp, sigma_y, sigma_yp, sigma_s, sigma_p)):
+            if a is not None:
+                new_sg[..., i] = g(a, None)
+        table = torch.cat([old_mu, old_sg, new_sg, new_mu], dim=-1).contiguous()  # (*shape, 24)
         B = 1
         for s_ in shape:
             B *= s_

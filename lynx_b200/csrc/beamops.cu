@@ -7,6 +7,7 @@
 // FMA: the results are bit-identical to the reference's op-by-op fp32 array arithmetic
 // (and to the numpy / torch-CPU restatement in oracle/beamops.py).
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -18,8 +19,8 @@ namespace lynx {
 // per coordinate, per beam row.  Table layout per row: old_mu[6], old_sigma[6],
 // new_sigma[6], new_mu[6] (24 floats).  48 B per particle (24 read + 24 written).
 constexpr int kXfTPB = 256;
-constexpr int kXfUnroll = 2;
 
+template <int kXfUnroll>
 __global__ void __launch_bounds__(kXfTPB) beam_transform_kernel(
     const float* __restrict__ in, int64_t in_row_stride, int64_t ld_in, int64_t N,
     const float* __restrict__ table, float* __restrict__ out, int64_t ld_out) {
@@ -76,8 +77,9 @@ __global__ void __launch_bounds__(kXfTPB) beam_transform_kernel(
 // 56 B per particle.  (A single-pass decoupled look-back scan would be 48 B; it needs
 // inter-CTA spinning, which this library otherwise avoids.)
 constexpr int kApTPB = 256;
-constexpr int kApVec = 2;                       // float4 per thread per plane
-constexpr int kApTile = kApTPB * kApVec * 4;    // 2048 particles per CTA
+constexpr int kApVec = 1;                       // float4 per thread per plane
+constexpr int kApTile = kApTPB * kApVec * 4;    // 1024 particles per CTA
+constexpr int kApPlane = kApTile + 12;          // shared floats per plane (phase pads: 3 + 3 + 3, rounded)
 
 // aperture.py:80-88.  NaN coordinates fail every comparison: lost.
 template <int SHAPE>
@@ -194,94 +196,104 @@ struct ApertureArgs {
   float* q_lost;  // nullable [R][ld_out]
 };
 
-// Copies n floats from shared memory to dst[d0 .. d0 + n): scalar stores up to the first
-// 16-byte boundary of the destination, 16-byte stores for the aligned body, scalar tail.
-// `dst` itself is 16-byte aligned (plane base; ld multiple of 4), so the alignment of
-// element d0 + i is that of (d0 + i) & 3.
-__device__ __forceinline__ void copy_out(const float* __restrict__ s, float* __restrict__ dst,
-                                         int64_t d0, int n, bool vec_ok) {
-  if (n <= 0) return;
-  if (!vec_ok) {
-    for (int i = threadIdx.x; i < n; i += kApTPB) dst[d0 + i] = s[i];
-    return;
+// One region (survivors or lost particles) of the compacted tile leaves shared memory.  The
+// region sits in shared memory with the SAME 16-byte phase as its destination: shared float
+// index i (vector-aligned base `sv0`, first valid element sv0 + phase) maps to global element
+// g0 + (i - sv0) with g0 a multiple of 4, so the body moves as LDS.128 -> STG.128 and only the
+// first and the last vector of a region fall back to predicated scalar stores.  All planes of
+// one vector are handled together (independent loads and stores in flight).
+template <int PLANES>
+__device__ __forceinline__ void copy_region(const float* __restrict__ sm, int sv0, int phase,
+                                            int count, float* __restrict__ dst, int64_t plane_ld,
+                                            int64_t g0, float* __restrict__ qdst, bool has_q) {
+  if (count <= 0) return;
+  const int lo = phase, hi = phase + count;  // valid shared elements, relative to sv0
+  const int nvec = (hi + 3) >> 2;
+  for (int v = threadIdx.x; v < nvec; v += kApTPB) {
+    const int e0 = v * 4;
+    const bool full = e0 >= lo && e0 + 4 <= hi;
+    float4 x[PLANES + 1];
+#pragma unroll
+    for (int k = 0; k < PLANES; ++k)
+      x[k] = *reinterpret_cast<const float4*>(sm + k * kApPlane + sv0 + e0);
+    if (has_q) x[PLANES] = *reinterpret_cast<const float4*>(sm + PLANES * kApPlane + sv0 + e0);
+    if (full) {
+#pragma unroll
+      for (int k = 0; k < PLANES; ++k)
+        __stcs(reinterpret_cast<float4*>(dst + k * plane_ld + g0 + e0), x[k]);
+      if (has_q && qdst) __stcs(reinterpret_cast<float4*>(qdst + g0 + e0), x[PLANES]);
+    } else {
+#pragma unroll
+      for (int k = 0; k <= PLANES; ++k) {
+        if (k == PLANES && !(has_q && qdst)) break;
+        float* d = (k < PLANES ? dst + k * plane_ld : qdst) + g0 + e0;
+        const float e[4] = {x[k].x, x[k].y, x[k].z, x[k].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (e0 + q >= lo && e0 + q < hi) d[q] = e[q];
+      }
+    }
   }
-  const int head = min(n, (int)((4 - (d0 & 3)) & 3));
-  if ((int)threadIdx.x < head) dst[d0 + threadIdx.x] = s[threadIdx.x];
-  const int body = (n - head) >> 2;
-  for (int v = threadIdx.x; v < body; v += kApTPB) {
-    const float* q = s + head + v * 4;
-    __stcs(reinterpret_cast<float4*>(dst + d0 + head + (int64_t)v * 4),
-           make_float4(q[0], q[1], q[2], q[3]));
-  }
-  const int done = head + body * 4;
-  if ((int)threadIdx.x < n - done) dst[d0 + done + threadIdx.x] = s[done + threadIdx.x];
 }
 
-// The tile's particles are first compacted inside shared memory (survivors at [0, cnt), lost
-// particles at [cnt, n) of each plane), then leave as contiguous, 16-byte-vectorised streams.
-// (First version: every thread stored its up to four survivors straight to global memory --
-// eight partial-sector store instructions per thread and plane, 2.7 TB/s)
+// The tile's particles are first compacted inside shared memory, then leave as contiguous
+// 16-byte streams (copy_region).  History (32 M particles): every thread
+// storing its up to four survivors straight to global memory -- eight partial-sector store
+// instructions per thread and plane -- ran at 2.7 TB/s; compaction in shared memory with a
+// scalar-head / vector-body / scalar-tail copy per plane at 3.5 TB/s (instruction-bound:
+// twelve branchy copy loops per tile); this version phase-aligns the shared-memory regions
+// to their destinations.
 template <int SHAPE>
-__global__ void __launch_bounds__(kApTPB, 2) aperture_scatter_kernel(ApertureArgs a) {
-  extern __shared__ __align__(16) float ap_smem[];  // [7][kApTile]
+__global__ void __launch_bounds__(kApTPB, 3) aperture_scatter_kernel(ApertureArgs a) {
+  extern __shared__ __align__(16) float ap_smem[];  // [6 or 7][kApPlane]
   const int64_t r = blockIdx.y;
   const float xm = __ldg(a.x_max + r * a.lim_stride), ym = __ldg(a.y_max + r * a.lim_stride);
   const float* src = a.in + r * 6 * a.ld_in;
-  const float* xs = src;
-  const float* ys = src + 2 * a.ld_in;
   float* kept = a.out + r * 6 * a.ld_out;
   float* lost = a.lost ? a.lost + r * 6 * a.ld_out : nullptr;
   const bool has_q = a.q_in != nullptr;
   const bool q_vec = has_q && (a.ld_q & 3) == 0 && ((uintptr_t)a.q_in & 15) == 0;
-  const bool out_vec = (a.ld_out & 3) == 0 && ((uintptr_t)a.out & 15) == 0 &&
-                       (!a.lost || ((uintptr_t)a.lost & 15) == 0);
-  const bool qo_vec = (a.ld_out & 3) == 0 && (!a.q_out || ((uintptr_t)a.q_out & 15) == 0) &&
-                      (!a.q_lost || ((uintptr_t)a.q_lost & 15) == 0);
+  float* q_kept = a.q_out ? a.q_out + r * a.ld_out : nullptr;
+  float* q_lost = a.q_lost ? a.q_lost + r * a.ld_out : nullptr;
   __shared__ unsigned s_w[kApTPB / 32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
     const int64_t tile0 = t * kApTile;
     const int n_tile = (int)min((int64_t)kApTile, a.N - tile0);
+    const int64_t kept0 = __ldg(a.tile_offsets + r * a.n_tiles + t);
+    const int64_t lost0 = tile0 - kept0;
     // all loads of the tile are issued before anything depends on them
-    float4 v[kApVec][7];
+    const int local = threadIdx.x * 4;
+    const int64_t p = tile0 + local;
+    float4 v[7];
+    if (p < a.N) {
 #pragma unroll
-    for (int it = 0; it < kApVec; ++it) {
-      const int64_t p = tile0 + ((int64_t)it * kApTPB + threadIdx.x) * 4;
-      if (p < a.N) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k)
-          v[it][k] = __ldcs(reinterpret_cast<const float4*>(src + k * a.ld_in + p));
-        if (has_q) {
-          const float* qp = a.q_in + r * a.ld_q + p;
-          if (q_vec) {
-            v[it][6] = __ldcs(reinterpret_cast<const float4*>(qp));
-          } else {
-            const int nv = (int)min((int64_t)4, a.N - p);
-            v[it][6].x = __ldcs(qp);
-            v[it][6].y = nv > 1 ? __ldcs(qp + 1) : 0.f;
-            v[it][6].z = nv > 2 ? __ldcs(qp + 2) : 0.f;
-            v[it][6].w = nv > 3 ? __ldcs(qp + 3) : 0.f;
-          }
+      for (int k = 0; k < 6; ++k)
+        v[k] = __ldcs(reinterpret_cast<const float4*>(src + k * a.ld_in + p));
+      if (has_q) {
+        const float* qp = a.q_in + r * a.ld_q + p;
+        if (q_vec) {
+          v[6] = __ldcs(reinterpret_cast<const float4*>(qp));
+        } else {
+          const int nv = (int)min((int64_t)4, a.N - p);
+          v[6].x = __ldcs(qp);
+          v[6].y = nv > 1 ? __ldcs(qp + 1) : 0.f;
+          v[6].z = nv > 2 ? __ldcs(qp + 2) : 0.f;
+          v[6].w = nv > 3 ? __ldcs(qp + 3) : 0.f;
         }
       }
     }
-    unsigned flags[kApVec], packed = 0;  // packed: survivors of vector `it` in bits 12*it..
-#pragma unroll
-    for (int it = 0; it < kApVec; ++it) {
-      const int64_t p = tile0 + ((int64_t)it * kApTPB + threadIdx.x) * 4;
-      unsigned f = 0;
-      if (p < a.N) {
-        const float4 x = v[it][0], y = v[it][2];
-        f |= survives<SHAPE>(x.x, y.x, xm, ym) ? 1u : 0u;
-        f |= (p + 1 < a.N && survives<SHAPE>(x.y, y.y, xm, ym)) ? 2u : 0u;
-        f |= (p + 2 < a.N && survives<SHAPE>(x.z, y.z, xm, ym)) ? 4u : 0u;
-        f |= (p + 3 < a.N && survives<SHAPE>(x.w, y.w, xm, ym)) ? 8u : 0u;
-      }
-      flags[it] = f;
-      packed += (unsigned)__popc(f) << (12 * it);
+    unsigned f = 0;
+    if (p < a.N) {
+      const float4 x = v[0], y = v[2];
+      f |= survives<SHAPE>(x.x, y.x, xm, ym) ? 1u : 0u;
+      f |= (p + 1 < a.N && survives<SHAPE>(x.y, y.y, xm, ym)) ? 2u : 0u;
+      f |= (p + 2 < a.N && survives<SHAPE>(x.z, y.z, xm, ym)) ? 4u : 0u;
+      f |= (p + 3 < a.N && survives<SHAPE>(x.w, y.w, xm, ym)) ? 8u : 0u;
     }
-    // exclusive scan of `packed` over the CTA (each 12-bit field holds at most 1024)
-    unsigned inc = packed;
+    // exclusive scan of the survivor counts over the CTA
+    const unsigned mine = (unsigned)__popc(f);
+    unsigned inc = mine;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const unsigned o = __shfl_up_sync(0xffffffffu, inc, d);
@@ -289,55 +301,40 @@ __global__ void __launch_bounds__(kApTPB, 2) aperture_scatter_kernel(ApertureArg
     }
     if (lane == 31) s_w[warp] = inc;
     __syncthreads();  // also: the previous tile's copy-out has finished reading ap_smem
-    unsigned before = inc - packed, total = 0;
+    int k_rank = (int)(inc - mine), cnt = 0;
 #pragma unroll
     for (int w = 0; w < kApTPB / 32; ++w) {
-      const unsigned sw = s_w[w];
-      if (w < warp) before += sw;
-      total += sw;
+      const int sw = (int)s_w[w];
+      if (w < warp) k_rank += sw;
+      cnt += sw;
     }
-    int cnt = 0;
-#pragma unroll
-    for (int it = 0; it < kApVec; ++it) cnt += (int)((total >> (12 * it)) & 0xFFFu);
-    unsigned field_base = 0;  // survivors of the vectors it' < it of the whole CTA
-#pragma unroll
-    for (int it = 0; it < kApVec; ++it) {
-      const int local = (it * kApTPB + threadIdx.x) * 4;
-      const int k_rank = (int)(field_base + ((before >> (12 * it)) & 0xFFFu));
-      field_base += (total >> (12 * it)) & 0xFFFu;
-      if (local >= n_tile) continue;
-      const int l_rank = cnt + (local - k_rank);  // lost particles live behind the survivors
-      const unsigned f = flags[it];
+    // shared-memory layout of a plane: survivors from float index ka (phase of kept0), lost
+    // particles from the next vector boundary + the phase of lost0
+    const int ka = (int)(kept0 & 3);
+    const int lv0 = (ka + cnt + 3) & ~3;
+    const int la = (int)(lost0 & 3);
+    if (local < n_tile) {
+      const int l_rank = local - k_rank;
       const int nvalid = min(4, n_tile - local);
 #pragma unroll
       for (int k = 0; k < 7; ++k) {
         if (k == 6 && !has_q) break;
-        float* sp = ap_smem + k * kApTile;
-        const float e[4] = {v[it][k].x, v[it][k].y, v[it][k].z, v[it][k].w};
-        int kk = 0, ll = 0;
+        float* sp = ap_smem + k * kApPlane;
+        const float e[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+        int kk = ka + k_rank, ll = lv0 + la + l_rank;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           if (q < nvalid) {
-            if (f & (1u << q)) sp[k_rank + kk++] = e[q];
-            else sp[l_rank + ll++] = e[q];
+            if (f & (1u << q)) sp[kk++] = e[q];
+            else sp[ll++] = e[q];
           }
         }
       }
     }
     __syncthreads();
-    const int64_t kept0 = a.tile_offsets[r * a.n_tiles + t];
-    const int64_t lost0 = tile0 - kept0;
-#pragma unroll 1
-    for (int k = 0; k < 6; ++k) {
-      const float* sp = ap_smem + k * kApTile;
-      copy_out(sp, kept + k * a.ld_out, kept0, cnt, out_vec);
-      if (lost) copy_out(sp + cnt, lost + k * a.ld_out, lost0, n_tile - cnt, out_vec);
-    }
-    if (has_q) {
-      const float* sp = ap_smem + 6 * kApTile;
-      if (a.q_out) copy_out(sp, a.q_out + r * a.ld_out, kept0, cnt, qo_vec);
-      if (a.q_lost) copy_out(sp + cnt, a.q_lost + r * a.ld_out, lost0, n_tile - cnt, qo_vec);
-    }
+    copy_region<6>(ap_smem, 0, ka, cnt, kept, a.ld_out, kept0 - ka, q_kept, has_q);
+    if (lost)
+      copy_region<6>(ap_smem, lv0, la, n_tile - cnt, lost, a.ld_out, lost0 - la, q_lost, has_q);
     // the next iteration's first __syncthreads() orders these reads before its writes
   }
 }
@@ -357,13 +354,17 @@ extern "C" int lynx_beam_transform(const float* d_in_soa, int64_t in_row_stride,
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int64_t groups = (N + 3) >> 2;
-  const int64_t want = (groups + kXfTPB * kXfUnroll - 1) / (kXfTPB * kXfUnroll);
-  const int64_t per_b = std::max<int64_t>(1, (8LL * sms + B - 1) / B);
-  const unsigned gx = (unsigned)std::max<int64_t>(1, std::min<int64_t>(want, per_b));
+  static const int unroll = [] { const char* e = getenv("LYNX_XF_UNROLL"); return e ? atoi(e) : 2; }();
+  static const int ctas = [] { const char* e = getenv("LYNX_XF_CTAS"); return e ? atoi(e) : 8; }();
+  const int64_t want = (groups + kXfTPB * unroll - 1) / (kXfTPB * unroll);
+  const int64_t per_b = std::max<int64_t>(1, ((int64_t)ctas * sms + B - 1) / B);
+  const dim3 grid((unsigned)std::max<int64_t>(1, std::min<int64_t>(want, per_b)), (unsigned)B);
   {
     ProfileScope ps(4, (cudaStream_t)stream);
-    beam_transform_kernel<<<dim3(gx, (unsigned)B), kXfTPB, 0, (cudaStream_t)stream>>>(
-        d_in_soa, in_row_stride, ld_in, N, d_table, d_out_soa, ld_out);
+    auto kern = unroll == 1 ? beam_transform_kernel<1>
+                : unroll == 4 ? beam_transform_kernel<4> : beam_transform_kernel<2>;
+    kern<<<grid, kXfTPB, 0, (cudaStream_t)stream>>>(d_in_soa, in_row_stride, ld_in, N, d_table,
+                                                    d_out_soa, ld_out);
   }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());
@@ -385,7 +386,9 @@ extern "C" int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N
                                      void* d_workspace, lynx_stream_t stream) {
   if (!d_in_soa || !d_x_max || !d_y_max || !d_out_soa || !d_counts || !d_workspace || R <= 0 ||
       R > 65535 || N <= 0 || N >= (1LL << 32) || ld_in < N || ld_out < N || (ld_in & 3) ||
-      ((uintptr_t)d_in_soa & 15) || (shape != 0 && shape != 1) ||
+      (ld_out & 3) || ((uintptr_t)d_in_soa & 15) || ((uintptr_t)d_out_soa & 15) ||
+      ((uintptr_t)d_lost_soa & 15) || ((uintptr_t)d_charges_out & 15) ||
+      ((uintptr_t)d_charges_lost & 15) || (shape != 0 && shape != 1) ||
       (lim_stride != 0 && lim_stride != 1) || (d_charges_in && ld_q < N))
     return LYNX_E_BADARG;
   int dev = 0, sms = 148;
@@ -420,12 +423,12 @@ extern "C" int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N
   a.q_out = d_charges_out;
   a.q_lost = d_charges_lost;
   {
-    const size_t smem = (size_t)(d_charges_in ? 7 : 6) * kApTile * sizeof(float);
+    const size_t smem = (size_t)(d_charges_in ? 7 : 6) * kApPlane * sizeof(float);
     auto kern = shape == 0 ? aperture_scatter_kernel<0> : aperture_scatter_kernel<1>;
     static bool attr_set[2] = {false, false};
     if (!attr_set[shape]) {
       LYNX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        7 * kApTile * (int)sizeof(float)));
+                                        7 * kApPlane * (int)sizeof(float)));
       attr_set[shape] = true;
     }
     ProfileScope ps(5, st);
