@@ -257,15 +257,14 @@ __global__ void __launch_bounds__(kApTPB, 3) aperture_scatter_kernel(ApertureArg
   float* q_lost = a.q_lost ? a.q_lost + r * a.ld_out : nullptr;
   __shared__ unsigned s_w[kApTPB / 32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
-    const int64_t tile0 = t * kApTile;
-    const int n_tile = (int)min((int64_t)kApTile, a.N - tile0);
-    const int64_t kept0 = __ldg(a.tile_offsets + r * a.n_tiles + t);
-    const int64_t lost0 = tile0 - kept0;
-    // all loads of the tile are issued before anything depends on them
-    const int local = threadIdx.x * 4;
-    const int64_t p = tile0 + local;
-    float4 v[7];
+  // Software pipeline: the loads of the CTA's NEXT tile are issued as soon as the current
+  // tile's values have been scattered into shared memory, so they are in flight during the
+  // copy-out phase (and across the two barriers) without costing extra registers.
+  float4 v[7];
+  int64_t kept0_next = 0;
+  auto load_tile = [&](int64_t t) {
+    const int64_t p = t * kApTile + threadIdx.x * 4;
+    kept0_next = __ldg(a.tile_offsets + r * a.n_tiles + t);
     if (p < a.N) {
 #pragma unroll
       for (int k = 0; k < 6; ++k)
@@ -283,6 +282,15 @@ __global__ void __launch_bounds__(kApTPB, 3) aperture_scatter_kernel(ApertureArg
         }
       }
     }
+  };
+  if ((int64_t)blockIdx.x < a.n_tiles) load_tile(blockIdx.x);
+  for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+    const int64_t tile0 = t * kApTile;
+    const int n_tile = (int)min((int64_t)kApTile, a.N - tile0);
+    const int64_t kept0 = kept0_next;
+    const int64_t lost0 = tile0 - kept0;
+    const int local = threadIdx.x * 4;
+    const int64_t p = tile0 + local;
     unsigned f = 0;
     if (p < a.N) {
       const float4 x = v[0], y = v[2];
@@ -331,6 +339,7 @@ __global__ void __launch_bounds__(kApTPB, 3) aperture_scatter_kernel(ApertureArg
         }
       }
     }
+    if (t + gridDim.x < a.n_tiles) load_tile(t + gridDim.x);
     __syncthreads();
     copy_region<6>(ap_smem, 0, ka, cnt, kept, a.ld_out, kept0 - ka, q_kept, has_q);
     if (lost)
@@ -431,8 +440,11 @@ extern "C" int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N
                                         7 * kApPlane * (int)sizeof(float)));
       attr_set[shape] = true;
     }
+    // persistent: as many CTAs as are resident (3 per SM), each loops over its tiles
+    const dim3 sgrid((unsigned)std::max<int64_t>(1, std::min<int64_t>(n_tiles, (3LL * sms + R - 1) / R)),
+                     (unsigned)R);
     ProfileScope ps(5, st);
-    kern<<<grid, kApTPB, smem, st>>>(a);
+    kern<<<sgrid, kApTPB, smem, st>>>(a);
   }
   count_launch(3);
   LYNX_CUDA_OK(cudaGetLastError());
