@@ -111,3 +111,71 @@ def test_track_requires_cuda():
     with pytest.raises(Exception):
         lx.ParticleBeam(torch.ones(1, 8, 7), torch.tensor([1e8]))
     assert seg.track(lx.Beam.empty) is lx.Beam.empty
+
+
+def test_split_slices_follow_the_reference_loops():
+    """drift.py:71-78, quadrupole.py:99-110, horizontal_corrector.py:82-90."""
+    parts = lx.Drift(torch.tensor([0.43])).split(torch.tensor(0.05))
+    assert len(parts) == 9 and all(isinstance(p, lx.Drift) for p in parts)
+    assert float(sum(p.length for p in parts)) == pytest.approx(0.43, rel=1e-6)
+    assert float(parts[-1].length) == pytest.approx(0.03, rel=1e-4)
+    q = lx.Quadrupole(torch.tensor([0.122]), k1=torch.tensor([7.5]),
+                      misalignment=torch.tensor([[1e-4, -2e-4]]))
+    qs = q.split(torch.tensor(0.05))
+    assert [round(float(p.length), 3) for p in qs] == [0.05, 0.05, 0.022]
+    assert all(float(p.k1) == 7.5 and torch.equal(p.misalignment, q.misalignment) for p in qs)
+    hc = lx.VerticalCorrector(torch.tensor([0.1]), angle=torch.tensor([2e-3]))
+    hs = hc.split(torch.tensor(0.04))
+    assert all(isinstance(p, lx.VerticalCorrector) for p in hs) and len(hs) == 3
+    assert float(sum(p.angle for p in hs)) == pytest.approx(2e-3, rel=1e-5)  # kick is shared out
+    # elements the reference does not split return themselves (dipole.py:196-199 et al.)
+    d = lx.Dipole(torch.tensor([0.5]), angle=torch.tensor([0.1]))
+    assert d.split(torch.tensor(0.1)) == [d]
+    seg = lx.Segment([lx.Drift(torch.tensor([0.1])), d, lx.Marker(name="m")])
+    assert len(seg.split(torch.tensor(0.05))) == 2 + 1 + 1
+
+
+def test_aperture_surface():
+    """aperture.py:24-68, 111-145."""
+    ap = lx.Aperture(name="a")
+    assert ap.is_active and not ap.is_skippable and ap.shape == "rectangular"
+    assert torch.isinf(ap.x_max).all() and torch.isinf(ap.y_max).all()
+    assert ap.lost_particles is None and ap._encode() is None
+    ap.is_active = False
+    assert ap.is_skippable
+    pb = object.__new__(lx.ParameterBeam)
+    assert ap.track(pb) is pb  # only ParticleBeams are cut (aperture.py:71-72)
+    assert lx.Aperture().track(lx.Beam.empty) is lx.Beam.empty
+    b = lx.Aperture(x_max=torch.tensor([1e-3]), y_max=torch.tensor([2e-3]), shape="elliptical")
+    bb = b.broadcast((3,))
+    assert bb.x_max.shape == (3,) and bb.shape == "elliptical" and bb.name == b.name
+    assert b.defining_features == ["x_max", "y_max", "shape", "is_active"]
+    # an inactive aperture vanishes from the encoded program; an active one is not an op either
+    seg = lx.Segment([lx.Drift(torch.tensor([0.1])), ap, lx.Drift(torch.tensor([0.2]))])
+    assert [o[0] for o in encode(seg.elements, (1,)).ops] == [L.OP_DRIFT, L.OP_DRIFT]
+
+
+def test_new_entry_points_validate_arguments():
+    """LYNX_E_BADARG before anything touches the device (no GPU needed)."""
+    lib = L.lib()
+    assert lib.lynx_beam_transform(None, 0, 4, 1, 4, None, None, 4, None) == L.E_BADARG
+    assert lib.lynx_beam_transform(16, 0, 6, 1, 4, 16, 16, 8, None) == L.E_BADARG  # ld % 4
+    assert lib.lynx_beam_transform(16, 0, 8, 1, 9, 16, 16, 8, None) == L.E_BADARG  # ld < N
+    assert lib.lynx_beam_transform(20, 0, 8, 1, 8, 16, 16, 8, None) == L.E_BADARG  # alignment
+    assert lib.lynx_beam_generate_ellipsoid(None, None, 1, 4, 0, 1, None, 4, None) == L.E_BADARG
+    assert lib.lynx_beam_generate_ellipsoid(16, 16, 1, 8, 2, 1, 16, 8, None) == L.E_BADARG  # first % 4
+    assert lib.lynx_aperture_workspace_bytes(1, 1) == 4
+    assert lib.lynx_aperture_workspace_bytes(2, 1025) == 16
+    assert lib.lynx_aperture_workspace_bytes(0, 10) == 0
+    args = [16, 1, 8, 8, None, 0, 16, 16, 0, 0, 16, None, 8, None, None, 16, 16, None]
+    bad_shape = list(args)
+    bad_shape[9] = 2
+    assert lib.lynx_aperture_compact(*bad_shape) == L.E_BADARG
+    bad_ld = list(args)
+    bad_ld[12] = 6
+    assert lib.lynx_aperture_compact(*bad_ld) == L.E_BADARG
+    no_counts = list(args)
+    no_counts[15] = None
+    assert lib.lynx_aperture_compact(*no_counts) == L.E_BADARG
+    assert lib.lynx_parambeam_along(None, None, 1, None, None, 0, None, None, None, None,
+                                    None) == L.E_BADARG
