@@ -4,6 +4,7 @@
 // context and only grows.
 #include <cstring>
 #include <new>
+#include <vector>
 
 #include "common.cuh"
 
@@ -21,8 +22,11 @@ struct lynx_host_ctx {
   // call's rectangle is cleared on the host first)
   int persistent_image = 0;
   const float* last_img = nullptr;
-  int last_rect[4] = {0, 0, 0, 0};  // r0, r1, c0, c1
+  int last_rect[4] = {0, 0, 0, 0};  // r0, r1, c0, c1: the only part of last_img that may be non-zero
   int32_t* h_bbox = nullptr;        // pinned
+  // host copies of the last edge tables sent to the device: an unchanged screen geometry is
+  // not sent again (two DMA operations less per call)
+  std::vector<float> ex_sent, ey_sent;
   bool grow(Buf& b, size_t bytes) {
     if (bytes <= b.cap) return true;
     if (b.p) cudaFree(b.p);
@@ -119,8 +123,16 @@ extern "C" int lynx_host_track_particles(
   if (n_bpm > 0 && !c->grow(c->bpm, sizeof(double) * 2 * n_bpm * B)) return LYNX_E_NOMEM;
   if (has_screen) {
     if (!c->grow(c->img, sizeof(float) * (size_t)W * H * B)) return LYNX_E_NOMEM;
-    H2D(c->ex, edges_x, sizeof(float) * (W + 1));
-    H2D(c->ey, edges_y, sizeof(float) * (H + 1));
+    if (c->ex_sent.size() != (size_t)W + 1 ||
+        memcmp(c->ex_sent.data(), edges_x, sizeof(float) * (W + 1)) != 0) {
+      H2D(c->ex, edges_x, sizeof(float) * (W + 1));
+      c->ex_sent.assign(edges_x, edges_x + W + 1);
+    }
+    if (c->ey_sent.size() != (size_t)H + 1 ||
+        memcmp(c->ey_sent.data(), edges_y, sizeof(float) * (H + 1)) != 0) {
+      H2D(c->ey, edges_y, sizeof(float) * (H + 1));
+      c->ey_sent.assign(edges_y, edges_y + H + 1);
+    }
   }
   if (moment_mode && !c->grow(c->mom, sizeof(double) * 28 * B)) return LYNX_E_NOMEM;
   if (!c->grow(c->ws, lynx_workspace_bytes(p, B))) return LYNX_E_NOMEM;
@@ -138,7 +150,42 @@ extern "C" int lynx_host_track_particles(
       (const float*)c->energy_in.p, (float*)c->energy_out.p, c->ws.p,
       sparse_img ? (int32_t*)c->bbox.p : nullptr, (lynx_stream_t)st);
   if (rc != LYNX_OK) return rc;
-  if (sparse_img) LYNX_CUDA_OK(cudaMemcpyAsync(c->h_bbox, c->bbox.p, 16, cudaMemcpyDeviceToHost, st));
+  // Sparse read-back of the persistent host image.  Invariant: the host image is zero
+  // outside last_rect.  The device image is exact everywhere (zero outside this call's
+  // bounding box), so copying ANY rectangle S that contains last_rect both clears what the
+  // previous call lit and brings in what this call lit inside S.  S = last_rect grown by a
+  // margin is requested speculatively right behind the kernels -- no wait for the bounding
+  // box, no host-side clearing; only if this call's box is not inside S does a second copy
+  // (and a second synchronisation) follow.
+  constexpr int kRectMargin = 16;
+  int spec[4] = {0, 0, 0, 0};
+  auto copy_rect = [&](const int* q) -> cudaError_t {
+    const size_t off = (size_t)q[0] * W + q[2];
+    for (int64_t b = 0; b < B; ++b) {
+      cudaError_t e = cudaMemcpy2DAsync(
+          screen_img + (size_t)b * W * H + off, sizeof(float) * W,
+          (const float*)c->img.p + (size_t)b * W * H + off, sizeof(float) * W,
+          sizeof(float) * (q[3] - q[2]), q[1] - q[0], cudaMemcpyDeviceToHost, st);
+      if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+  };
+  if (sparse_img) {
+    LYNX_CUDA_OK(cudaMemcpyAsync(c->h_bbox, c->bbox.p, 16, cudaMemcpyDeviceToHost, st));
+    if (c->last_img != screen_img) {
+      memset(screen_img, 0, sizeof(float) * (size_t)W * H * B);  // first use of this buffer
+      c->last_rect[0] = c->last_rect[1] = c->last_rect[2] = c->last_rect[3] = 0;
+      c->last_img = screen_img;
+    }
+    const int* q = c->last_rect;
+    if (q[1] > q[0] && q[3] > q[2]) {
+      spec[0] = q[0] > kRectMargin ? q[0] - kRectMargin : 0;
+      spec[1] = q[1] + kRectMargin < H ? q[1] + kRectMargin : H;
+      spec[2] = q[2] > kRectMargin ? q[2] - kRectMargin : 0;
+      spec[3] = q[3] + kRectMargin < W ? q[3] + kRectMargin : W;
+      LYNX_CUDA_OK(copy_rect(spec));
+    }
+  }
 
   if (out_soa) {
     if (ld == N) {
@@ -154,16 +201,7 @@ extern "C" int lynx_host_track_particles(
   if (energy_out) D2H(energy_out, c->energy_out, sizeof(float) * B);
   LYNX_CUDA_OK(cudaStreamSynchronize(st));
   if (sparse_img) {
-    // clear what the previous call lit (same persistent buffer), then fetch only the
-    // rectangle of lit pixels: rows [H - v3, v2), columns [W - v0, v1)
-    if (c->last_img == screen_img) {
-      const int* q = c->last_rect;
-      for (int64_t b = 0; b < B; ++b)
-        for (int r = q[0]; r < q[1]; ++r)
-          memset(screen_img + ((size_t)b * H + r) * W + q[2], 0, sizeof(float) * (q[3] - q[2]));
-    } else {
-      memset(screen_img, 0, sizeof(float) * (size_t)W * H * B);  // first use of this buffer
-    }
+    // this call's lit rectangle: rows [H - v3, v2), columns [W - v0, v1)
     const int32_t* v = c->h_bbox;
     int rect[4] = {0, 0, 0, 0};
     if (v[1] > 0 && v[3] > 0) {
@@ -171,16 +209,14 @@ extern "C" int lynx_host_track_particles(
       rect[1] = v[2];
       rect[2] = W - v[0];
       rect[3] = v[1];
-      const size_t off = (size_t)rect[0] * W + rect[2];
-      for (int64_t b = 0; b < B; ++b)
-        LYNX_CUDA_OK(cudaMemcpy2DAsync(screen_img + (size_t)b * W * H + off, sizeof(float) * W,
-                                       (const float*)c->img.p + (size_t)b * W * H + off,
-                                       sizeof(float) * W, sizeof(float) * (rect[3] - rect[2]),
-                                       rect[1] - rect[0], cudaMemcpyDeviceToHost, st));
-      LYNX_CUDA_OK(cudaStreamSynchronize(st));
+      const bool inside = rect[0] >= spec[0] && rect[1] <= spec[1] && rect[2] >= spec[2] &&
+                          rect[3] <= spec[3];
+      if (!inside) {
+        LYNX_CUDA_OK(copy_rect(rect));
+        LYNX_CUDA_OK(cudaStreamSynchronize(st));
+      }
     }
     for (int i = 0; i < 4; ++i) c->last_rect[i] = rect[i];
-    c->last_img = screen_img;
   }
   return LYNX_OK;
 }

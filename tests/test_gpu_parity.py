@@ -396,17 +396,29 @@ def test_host_buffer_abi_matches_device_path():
     # bit-identical to the dense transfer across calls with different settings
     L.check(L.lib().lynx_host_ctx_set_option(ctx, 1, 1))
     pimg = np.full((1, H, W), 7.0, dtype=np.float32)  # garbage: a new buffer is zero-filled
-    for k1, vk, hk in (((5.0, -5.0, 5.0), 1e-3, -2e-3), ((2.0, -3.0, 1.0), -1e-3, 1e-3),
-                       ((9.0, -9.0, 9.0), 2e-3, 2e-3), ((5.0, -5.0, 5.0), 1e-3, -2e-3)):
-        spec_k = F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True, screen=F.TEST_SCREEN)
+    # (k1, vkick, hkick, pixel-size scale): moving / growing / shrinking spots (the speculative
+    # rectangle of csrc/host.cu misses and a second copy follows), the same spot twice (it
+    # hits), a beam kicked off the screen (nothing lit), and a changed screen geometry (the
+    # cached edge tables must be re-sent)
+    cases = (((5.0, -5.0, 5.0), 1e-3, -2e-3, 1.0), ((2.0, -3.0, 1.0), -1e-3, 1e-3, 1.0),
+             ((9.0, -9.0, 9.0), 2e-3, 2e-3, 1.0), ((9.0, -9.0, 9.0), 2e-3, 2e-3, 1.0),
+             ((5.0, -5.0, 5.0), 1e-3, 0.3, 1.0), ((5.0, -5.0, 5.0), 1e-3, -2e-3, 1.0),
+             ((5.0, -5.0, 5.0), 1e-3, -2e-3, 0.5), ((5.0, -5.0, 5.0), 1e-3, -2e-3, 1.0))
+    for k1, vk, hk, px in cases:
+        scr_k = dict(F.TEST_SCREEN)
+        scr_k["pixel_size"] = tuple(v * px for v in F.TEST_SCREEN["pixel_size"])
+        spec_k = F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True, screen=scr_k)
         seg_k = F.build_segment(spec_k)
         seg_k.track(_gpu_beam(soa, F.ASTRA_ENERGY))
         want_k = seg_k.AREABSCR1.reading.cpu().numpy()
+        if hk > 0.1:
+            assert want_k.sum() == 0  # off the screen
         params_k = pack_params(encode(seg_k.elements, (1,)), "cpu").numpy()
+        ex_k, ey_k = (e.numpy() for e in seg_k.AREABSCR1.pixel_bin_edges)
         L.check(L.lib().lynx_host_track_particles(
             ctx, prog.handle, vp(params_k), params_k.size, 1, vp(soa_c), 1, n, vp(e_in), None,
-            None, vp(pimg), W, H, vp(ex), vp(ey), None, 0, None))
-        assert np.array_equal(pimg, want_k)
+            None, vp(pimg), W, H, vp(ex_k), vp(ey_k), None, 0, None))
+        assert np.array_equal(pimg, want_k), (k1, vk, hk, px)
     L.lib().lynx_host_ctx_destroy(ctx)
 
 
