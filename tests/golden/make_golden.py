@@ -93,7 +93,34 @@ def gradients():
              loss=loss.item(), g_k1=k1o.grad.numpy(), g_angles=ango.grad.numpy())
 
 
+def beam_ops():
+    """Byte-level vectors of the beam-level operations (oracle/beamops.py, numpy fp32):
+    transformed_to, Aperture.track (both shapes) and the ellipsoid sampler."""
+    from oracle import beamops as BO
+
+    n = 1500
+    x = F.gaussian_beam_soa(n, seed=2006).astype(np.float32)
+    mu, sd = BO.beam_stats(x)
+    mu[4:] = 0.0
+    new_mu = np.array([1e-5, 1e-7, 2e-5, 2e-7, 0.0, 0.0], dtype=np.float32)
+    new_sd = np.array([1.75e-7, 2e-7, 1.75e-7, 2e-7, 1e-6, 1e-6], dtype=np.float32)
+    y = BO.transformed_to(x, mu, sd, new_mu, new_sd)
+    q = np.linspace(1e-15, 2e-15, n).astype(np.float32)
+    xm, ym = np.float32(2e-4), np.float32(1.5e-4)
+    mr = BO.aperture_mask(x[0], x[2], xm, ym, "rectangular")
+    me = BO.aperture_mask(x[0], x[2], xm, ym, "elliptical")
+    radii = np.array([[1e-3, 1e-4, 1e-5], [2e-3, 2e-4, 2e-5]], dtype=np.float32)
+    sigma = np.array([[2e-7, 3e-7, 1e-6], [1e-7, 2e-7, 2e-6]], dtype=np.float32)
+    seed = 0x2006_0000_BEA7
+    ell = BO.uniform_3d_ellipsoid(1000, radii, sigma, seed)
+    np.savez(os.path.join(HERE, "beam_ops.npz"), in_soa=x, old_mu=mu, old_sigma=sd, new_mu=new_mu,
+             new_sigma=new_sd, transformed=y, charges=q, x_max=xm, y_max=ym, mask_rect=mr,
+             mask_ellipse=me, radii=radii, sigma3=sigma, seed=np.uint64(seed),
+             ellipsoid_pos=ell[:, 0::2].astype(np.float32), ellipsoid_mom=ell[:, 1::2])
+
+
 if __name__ == "__main__":
+    beam_ops()
     ares_particles()
     cavity_line_particles()
     parameter_beam_settings()

@@ -39,10 +39,30 @@ def test_oracle_reproduces_golden_particles():
                                atol=1e-20)
 
 
+def test_oracle_reproduces_golden_beam_ops():
+    from oracle import beamops as BO
+
+    g = _load("beam_ops.npz")
+    x = g["in_soa"]
+    mu, sd = BO.beam_stats(x)
+    mu[4:] = 0.0
+    np.testing.assert_array_equal(mu, g["old_mu"])
+    np.testing.assert_array_equal(sd, g["old_sigma"])
+    y = BO.transformed_to(x, g["old_mu"], g["old_sigma"], g["new_mu"], g["new_sigma"])
+    np.testing.assert_array_equal(y, g["transformed"])
+    for shape, key in (("rectangular", "mask_rect"), ("elliptical", "mask_ellipse")):
+        m = BO.aperture_mask(x[0], x[2], g["x_max"], g["y_max"], shape)
+        np.testing.assert_array_equal(m, g[key])
+    assert 0 < g["mask_ellipse"].sum() < g["mask_rect"].sum() < x.shape[1]
+    ell = BO.uniform_3d_ellipsoid(1000, g["radii"], g["sigma3"], int(g["seed"]))
+    np.testing.assert_array_equal(ell[:, 0::2].astype(np.float32), g["ellipsoid_pos"])
+    np.testing.assert_allclose(ell[:, 1::2], g["ellipsoid_mom"], rtol=1e-12, atol=0)
+
+
 def test_golden_files_are_small_and_complete():
     names = sorted(f for f in os.listdir(G) if f.endswith(".npz"))
     assert names == ["ares_ea_gradients.npz", "ares_ea_parameter_beam.npz",
-                     "ares_ea_particles.npz", "cavity_dipole_line_particles.npz"]
+                     "ares_ea_particles.npz", "beam_ops.npz", "cavity_dipole_line_particles.npz"]
     assert all(os.path.getsize(os.path.join(G, n)) < 200_000 for n in names)
 
 
@@ -127,3 +147,51 @@ def test_gpu_parameter_beam_and_gradients_vs_golden():
     for got, want, nm in ((k1.grad, gg["g_k1"], "g_k1"), (ang.grad, gg["g_angles"], "g_angles")):
         err = np.abs(got.numpy() - want).max() / np.abs(want).max()
         assert err < 3e-5, f"{nm}: {err:.3e}"
+
+
+@pytest.mark.gpu
+def test_gpu_beam_ops_vs_golden():
+    """transformed_to, Aperture.track and uniform_3d_ellipsoid through the public API
+    against the committed byte-level vectors (no oracle involved)."""
+    import lynx_b200 as lx
+    from lynx_b200 import _lib as L
+
+    g = _load("beam_ops.npz")
+    x = g["in_soa"]
+    n = x.shape[1]
+    charges = torch.from_numpy(g["charges"]).unsqueeze(0)
+    beam = lx.ParticleBeam(torch.from_numpy(F.soa_to_aos7(x)).unsqueeze(0),
+                           torch.tensor([F.ASTRA_ENERGY]), particle_charges=charges)
+    assert torch.equal(beam.soa[0, :, :n].cpu(), torch.from_numpy(x))
+    # the beam's own moments are the fixture's (double sums, rounded to fp32)
+    got_mu = np.array([float(getattr(beam, f"mu_{c}")[0]) for c in ("x", "xp", "y", "yp")])
+    np.testing.assert_allclose(got_mu, g["old_mu"][:4], rtol=1e-6, atol=1e-12)
+    t = lambda v: torch.tensor([float(v)])  # noqa: E731
+    nm, ns = g["new_mu"], g["new_sigma"]
+    tb = beam.transformed_to(mu_x=t(nm[0]), mu_xp=t(nm[1]), mu_y=t(nm[2]), mu_yp=t(nm[3]),
+                             sigma_x=t(ns[0]), sigma_xp=t(ns[1]), sigma_y=t(ns[2]),
+                             sigma_yp=t(ns[3]), sigma_s=t(ns[4]), sigma_p=t(ns[5]))
+    got = tb.soa[0, :, :n].cpu().numpy()
+    # the kernel itself is byte-exact for given moments (tests/test_gpu_beamops.py); here the
+    # old moments come from the device's fused sums (fp32 partial sums shifted by the centre,
+    # DESIGN.md K5), which agree with the fixture's float64 statistics to ~1e-7: allow
+    # 1e-6 sigma_new + 2 ulp of the value, per plane
+    tol = 1e-6 * ns[:, None] + 2.4e-7 * np.abs(g["transformed"])
+    assert np.all(np.abs(got - g["transformed"]) <= tol)
+    for shape, key in (("rectangular", "mask_rect"), ("elliptical", "mask_ellipse")):
+        ap = lx.Aperture(x_max=torch.tensor(float(g["x_max"])), y_max=torch.tensor(float(g["y_max"])),
+                         shape=shape)
+        out = ap.track(beam)
+        m = g[key]
+        assert out.num_particles == int(m.sum())
+        np.testing.assert_array_equal(out.soa[0, :, : out.num_particles].cpu().numpy(), x[:, m])
+        np.testing.assert_array_equal(out.particle_charges[0].cpu().numpy(), g["charges"][m])
+        np.testing.assert_array_equal(ap.lost_particles[:, :6].T.cpu().numpy(), x[:, ~m])
+    r, s3 = torch.from_numpy(g["radii"]), torch.from_numpy(g["sigma3"])
+    eb = lx.ParticleBeam.uniform_3d_ellipsoid(
+        num_particles=1000, radius_x=r[:, 0], radius_y=r[:, 1], radius_s=r[:, 2],
+        sigma_xp=s3[:, 0], sigma_yp=s3[:, 1], sigma_p=s3[:, 2], seed=int(g["seed"]))
+    np.testing.assert_array_equal(eb.soa[:, 0::2, :1000].cpu().numpy(), g["ellipsoid_pos"])
+    err = np.abs(eb.soa[:, 1::2, :1000].cpu().numpy() - g["ellipsoid_mom"])
+    assert np.all(err <= 3e-5 * g["sigma3"][:, :, None])
+    assert L.lib().lynx_launch_count() > 0
