@@ -161,6 +161,24 @@ int lynx_track_particles_fwd_bbox(const lynx_program_t*, const float* d_params, 
                                   void* d_workspace, int32_t* d_screen_bbox,
                                   lynx_stream_t stream);
 
+/* Same, for a PERSISTENT screen image (an RL loop or a scan reading the same screen every
+ * step): d_screen_img and d_img_state [8] (int32) are zero-initialised ONCE by the caller and
+ * passed unchanged on every call, with `epoch` increasing by one per call.  Instead of zeroing
+ * the whole B*H*W image (20 MB for the ARES screen) the call clears only the rectangle the
+ * previous call lit -- its bounding box, kept in the state -- and records its own.  After the
+ * call the image is exactly what lynx_track_particles_fwd writes.  W % 4 == 0, image 16-byte
+ * aligned; returns LYNX_E_BADPROGRAM for lattices the pipelined kernel cannot take (then use
+ * lynx_track_particles_fwd and re-zero image and state before coming back).                */
+int lynx_track_particles_fwd_persistent(const lynx_program_t*, const float* d_params, int64_t B,
+                                        const float* d_in_soa, int64_t in_row_stride,
+                                        int64_t ld_in, int64_t N, float* d_out_soa, int64_t ld_out,
+                                        double* d_bpm_sums, float* d_screen_img, int32_t W,
+                                        int32_t H, const float* d_edges_x, const float* d_edges_y,
+                                        double* d_moment_sums, int32_t moment_mode,
+                                        const float* d_energy_in, float* d_energy_out,
+                                        void* d_workspace, int32_t* d_img_state, uint32_t epoch,
+                                        lynx_stream_t stream);
+
 /* Multi-GPU exchange step of the particle-sharded path (one process per GPU; the reference
  * has no distributed code): all-reduce (SUM) of the screen image over
  * NVLink peer memory, restricted to the union bounding box of the bins any rank touched.

@@ -53,6 +53,11 @@ SIGNATURES = {
         [_vp, _vp, _i64, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _i32, _i32, _vp, _vp, _vp,
          _i32, _vp, _vp, _vp, _vp, _vp],
     ),
+    "lynx_track_particles_fwd_persistent": (
+        C.c_int,
+        [_vp, _vp, _i64, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _i32, _i32, _vp, _vp, _vp,
+         _i32, _vp, _vp, _vp, _vp, C.c_uint32, _vp],
+    ),
     "lynx_screen_symm_bytes": (_sz, [_i64, _i32, _i32]),
     "lynx_screen_symm_image": (_vp, [_vp, _i32, _i64, _i32, _i32]),
     "lynx_screen_allreduce": (

@@ -81,7 +81,8 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
                    int64_t seed_ld, float* d_records, float* d_maps_out, float* d_energy_out,
                    void* zero_ptr, size_t zero_bytes, cudaStream_t st,
                    const float* hist_ex = nullptr, const float* hist_ey = nullptr, int hist_W = 0,
-                   int hist_H = 0, void* hist_out = nullptr);
+                   int hist_H = 0, void* hist_out = nullptr, const int* zero_rect = nullptr,
+                   int* bbox_clear = nullptr);
 
 // forward moment collapse (adjoint.cu): one beam shared by B settings, moments / BPM sums
 // only, no active cavity -> the beam is streamed once instead of once per setting

@@ -32,6 +32,7 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
   if (hist_blocks && blockIdx.x == gridDim.x - 1) {
     HistAxis* h = reinterpret_cast<HistAxis*>(a.hist_out);
     if (threadIdx.x < 4) reinterpret_cast<int*>(a.hist_out)[32 + threadIdx.x] = 0;  // internal bbox cell
+    if (a.bbox_clear && threadIdx.x < 4) a.bbox_clear[threadIdx.x] = 0;  // this call's cell
     hist_axis_setup(a.hist_ex, a.hist_W, h, threadIdx.x, kComposeTPB);
     hist_axis_setup(a.hist_ey, a.hist_H, h + 1, threadIdx.x, kComposeTPB);
     return;
@@ -42,6 +43,24 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
     const int zb = blockIdx.x - compose_blocks, nzb = gridDim.x - compose_blocks - hist_blocks;
     float4* z = reinterpret_cast<float4*>(a.zero_ptr);
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.zero_rect) {
+      // persistent image: rows [H - v3, v2) x columns [W - v0, v1) of every setting's image
+      // (the cell holds max(W - ix), max(ix + 1), max(H - iy), max(iy + 1); all 0 = nothing lit)
+      const int v0 = __ldg(a.zero_rect), v1 = __ldg(a.zero_rect + 1), v2 = __ldg(a.zero_rect + 2),
+                v3 = __ldg(a.zero_rect + 3);
+      if (v1 <= 0 || v3 <= 0) return;
+      const int r0 = a.hist_H - v3, nr = v2 - r0;
+      const int c0 = (a.hist_W - v0) & ~3, nv = (min((v1 + 3) & ~3, a.hist_W) - c0) >> 2;
+      const int64_t per_img = (int64_t)nr * nv, total = a.B * per_img;
+      for (int64_t i = (int64_t)zb * kComposeTPB + threadIdx.x; i < total;
+           i += (int64_t)nzb * kComposeTPB) {
+        const int64_t b = i / per_img, rem = i - b * per_img;
+        const int r = (int)(rem / nv), cv = (int)(rem - (int64_t)r * nv);
+        *reinterpret_cast<float4*>(a.zero_ptr + ((b * a.hist_H + r0 + r) * (int64_t)a.hist_W + c0 +
+                                                 4 * cv)) = zero;
+      }
+      return;
+    }
     for (int64_t i = (int64_t)zb * kComposeTPB + threadIdx.x; i < a.zero_vec4;
          i += (int64_t)nzb * kComposeTPB)
       z[i] = zero;
@@ -161,7 +180,8 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
                    const float* d_energy_in, const float* d_seed_soa, int64_t seed_row_stride,
                    int64_t seed_ld, float* d_records, float* d_maps_out, float* d_energy_out,
                    void* zero_ptr, size_t zero_bytes, cudaStream_t st, const float* hist_ex,
-                   const float* hist_ey, int hist_W, int hist_H, void* hist_out) {
+                   const float* hist_ey, int hist_W, int hist_H, void* hist_out,
+                   const int* zero_rect, int* bbox_clear) {
   if (!p || !d_params || !d_energy_in || !d_records || B <= 0) return LYNX_E_BADARG;
   if (zero_bytes && (((uintptr_t)zero_ptr & 15) || (zero_bytes & 15))) return LYNX_E_BADARG;
   ComposeArgs a;
@@ -192,6 +212,9 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   a.hist_W = hist_W;
   a.hist_H = hist_H;
   a.hist_out = hist_out;
+  a.zero_rect = zero_rect;
+  a.bbox_clear = bbox_clear;
+  if (zero_rect && (!hist_out || !zero_ptr || (hist_W & 3))) return LYNX_E_BADARG;
   // The warp-per-setting variant (compose_warp.cu) is opt-in: on B200 it did not beat
   // the thread-per-setting walk at any measured B (both are bound by single-warp
   // instruction latency / fetch, not by instruction count) -- see DESIGN.md.
@@ -216,7 +239,9 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   }
   const size_t smem = staged ? ops_bytes + (size_t)n_cols * S * 4 : 0;
   unsigned blocks = (unsigned)((B + S - 1) / S);
-  if (a.zero_vec4 > 0)
+  if (zero_rect)
+    blocks += (unsigned)p->sm_count;  // the rectangle's size is only known on the device
+  else if (a.zero_vec4 > 0)
     blocks += (unsigned)std::min<int64_t>(zero_blocks_per_sm * p->sm_count, (a.zero_vec4 + kComposeTPB - 1) / kComposeTPB);
   if (hist_out) blocks += 1;
   {
@@ -247,7 +272,7 @@ extern "C" int lynx_compose_maps(const lynx_program_t* p, const float* d_params,
                                  lynx_stream_t stream) {
   return compose_launch(p, d_params, B, d_energy_in, d_seed_soa, seed_row_stride, seed_ld,
                         d_records, d_maps_out, d_energy_out, nullptr, 0, (cudaStream_t)stream, nullptr,
-                        nullptr, 0, 0, nullptr);
+                        nullptr, 0, 0, nullptr, nullptr, nullptr);
 }
 
 extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params, int64_t B,

@@ -98,6 +98,11 @@ struct ComposeArgs {
   const float* hist_ey;
   int hist_W, hist_H;
   void* hist_out;      // HistAxis[2]
+  // persistent screen image (lynx_track_particles_fwd_persistent): instead of the whole
+  // buffer the extra blocks clear only the rectangle the PREVIOUS call lit (its bounding-box
+  // cell, zero_rect[4]); the last block clears this call's cell
+  const int* zero_rect;
+  int* bbox_clear;
 };
 
 using RecordSink = RecordSinkT<false>;

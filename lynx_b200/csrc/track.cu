@@ -289,6 +289,38 @@ extern "C" int lynx_track_particles_fwd(
                                        d_workspace, nullptr, stream);
 }
 
+static int track_fwd_impl(const lynx_program_t*, const float*, int64_t, const float*, int64_t,
+                          int64_t, int64_t, float*, int64_t, double*, float*, int32_t, int32_t,
+                          const float*, const float*, double*, int32_t, const float*, float*,
+                          void*, int32_t*, int32_t*, uint32_t, lynx_stream_t);
+
+extern "C" int lynx_track_particles_fwd_bbox(
+    const lynx_program_t* p, const float* d_params, int64_t B, const float* d_in_soa,
+    int64_t in_row_stride, int64_t ld_in, int64_t N, float* d_out_soa, int64_t ld_out,
+    double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H, const float* d_edges_x,
+    const float* d_edges_y, double* d_moment_sums, int32_t moment_mode,
+    const float* d_energy_in, float* d_energy_out, void* d_workspace, int32_t* d_screen_bbox,
+    lynx_stream_t stream) {
+  return track_fwd_impl(p, d_params, B, d_in_soa, in_row_stride, ld_in, N, d_out_soa, ld_out,
+                        d_bpm_sums, d_screen_img, W, H, d_edges_x, d_edges_y, d_moment_sums,
+                        moment_mode, d_energy_in, d_energy_out, d_workspace, d_screen_bbox, nullptr,
+                        0u, stream);
+}
+
+extern "C" int lynx_track_particles_fwd_persistent(
+    const lynx_program_t* p, const float* d_params, int64_t B, const float* d_in_soa,
+    int64_t in_row_stride, int64_t ld_in, int64_t N, float* d_out_soa, int64_t ld_out,
+    double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H, const float* d_edges_x,
+    const float* d_edges_y, double* d_moment_sums, int32_t moment_mode,
+    const float* d_energy_in, float* d_energy_out, void* d_workspace, int32_t* d_img_state,
+    uint32_t epoch, lynx_stream_t stream) {
+  if (!d_img_state || !d_screen_img || !p || p->n_screen == 0) return LYNX_E_BADARG;
+  return track_fwd_impl(p, d_params, B, d_in_soa, in_row_stride, ld_in, N, d_out_soa, ld_out,
+                        d_bpm_sums, d_screen_img, W, H, d_edges_x, d_edges_y, d_moment_sums,
+                        moment_mode, d_energy_in, d_energy_out, d_workspace, nullptr, d_img_state,
+                        epoch, stream);
+}
+
 // Library-owned scratch for the histogram replicas, one buffer per device,
 // grown on demand and zeroed once: hist_fold_kernel restores the all-zero invariant after
 // every use.  Returns nullptr when the request is over the cap or the allocation fails (the
@@ -342,13 +374,16 @@ static unsigned int* grid_barrier_state(cudaStream_t st) {
   return reinterpret_cast<unsigned int*>(q);
 }
 
-extern "C" int lynx_track_particles_fwd_bbox(
+// d_img_state != nullptr: persistent screen image (lynx_track_particles_fwd_persistent) -- the
+// image is NOT zeroed as a whole; K1's extra blocks clear the rectangle the previous call lit
+// (bounding-box cell (epoch + 1) & 1 of the state), K2 records this call's box in cell epoch & 1.
+static int track_fwd_impl(
     const lynx_program_t* p, const float* d_params, int64_t B, const float* d_in_soa,
     int64_t in_row_stride, int64_t ld_in, int64_t N, float* d_out_soa, int64_t ld_out,
     double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H, const float* d_edges_x,
     const float* d_edges_y, double* d_moment_sums, int32_t moment_mode,
     const float* d_energy_in, float* d_energy_out, void* d_workspace, int32_t* d_screen_bbox,
-    lynx_stream_t stream) {
+    int32_t* d_img_state, uint32_t epoch, lynx_stream_t stream) {
   if (!p || !d_params || !d_in_soa || !d_energy_in || !d_workspace || B <= 0 || N <= 0)
     return LYNX_E_BADARG;
   if ((ld_in & 3) || ld_in < N || ((uintptr_t)d_in_soa & 15)) return LYNX_E_BADARG;
@@ -376,7 +411,12 @@ extern "C" int lynx_track_particles_fwd_bbox(
   // the screen image is zeroed by spare blocks of the K1 launch when its size allows
   const bool has_img = d_screen_img && p->n_screen > 0;
   const size_t img_bytes = has_img ? sizeof(float) * (size_t)W * H * B : 0;
-  const bool fuse_zero = has_img && !(img_bytes & 15) && !((uintptr_t)d_screen_img & 15);
+  const bool img_aligned = has_img && !(img_bytes & 15) && !((uintptr_t)d_screen_img & 15);
+  const bool persistent = d_img_state != nullptr && has_img;
+  if (persistent && (!img_aligned || (W & 3) || d_screen_bbox)) return LYNX_E_BADARG;
+  int32_t* cell_cur = persistent ? d_img_state + 4 * (epoch & 1u) : nullptr;
+  const int32_t* cell_prev = persistent ? d_img_state + 4 * ((epoch + 1u) & 1u) : nullptr;
+  const bool fuse_zero = img_aligned && !persistent;
   // the bounding box sits right in front of the image in the symmetric exchange buffer
   // (exchange.cu): one fused zeroing range covers both
   const bool bbox_adjacent = d_screen_bbox && has_img && fuse_zero &&
@@ -403,7 +443,7 @@ extern "C" int lynx_track_particles_fwd_bbox(
   a.ex = d_edges_x;
   a.ey = d_edges_y;
   a.hist = reinterpret_cast<const HistAxis*>(hist_ws);
-  a.bbox = has_img ? d_screen_bbox : nullptr;
+  a.bbox = has_img ? (persistent ? cell_cur : d_screen_bbox) : nullptr;
   a.stamp = bbox_adjacent ? reinterpret_cast<unsigned long long*>(d_screen_bbox + 8) : nullptr;
   a.mom = d_moment_sums;
   a.B = B;
@@ -428,7 +468,7 @@ extern "C" int lynx_track_particles_fwd_bbox(
   static const long long rep_min = [] { const char* e = getenv("LYNX_HIST_REPLICAS_MIN"); return e ? atoll(e) : 4000000LL; }();
   a.rep = nullptr;
   a.n_rep = 1;
-  if (has_img && fuse_zero && !(W & 3) && n_rep_env > 1 && n_rep_env <= 64 && B * N >= rep_min) {
+  if (has_img && img_aligned && !(W & 3) && n_rep_env > 1 && n_rep_env <= 64 && B * N >= rep_min) {
     a.rep = replica_scratch(img_bytes * (size_t)(n_rep_env - 1));
     if (a.rep) a.n_rep = n_rep_env;
   }
@@ -438,7 +478,8 @@ extern "C" int lynx_track_particles_fwd_bbox(
   // accumulators are cleared first so that the kernels stay adjacent in the stream
   if (p->n_bpm_slots > 0)
     LYNX_CUDA_OK(cudaMemsetAsync(d_bpm_sums, 0, sizeof(double) * 2 * p->n_bpm_slots * B, st));
-  if (has_img && !fuse_zero) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
+  if (has_img && !fuse_zero && !persistent)
+    LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
   if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
 
   static const bool force_ldg = [] {
@@ -447,7 +488,7 @@ extern "C" int lynx_track_particles_fwd_bbox(
   }();
   // ---- fused path: no K1 launch; every CTA composes its own setting (B <= SM count)
   static const bool no_fused = [] { const char* e = getenv("LYNX_FUSED"); return !(e && e[0] == '1'); }();
-  if (!force_ldg && !no_fused && B <= p->sm_count) {
+  if (!force_ldg && !no_fused && !persistent && B <= p->sm_count) {
     a.zero_img = fuse_zero ? 1 : 0;
     a.grid_bar = fuse_zero ? grid_barrier_state(st) : nullptr;
     if (!fuse_zero || a.grid_bar) {
@@ -465,15 +506,18 @@ extern "C" int lynx_track_particles_fwd_bbox(
   if (d_screen_bbox && !bbox_adjacent) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_bbox, 0, 16, st));
   int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
                           records, nullptr, d_energy_out,
-                          fuse_zero ? (bbox_adjacent ? (void*)d_screen_bbox : (void*)d_screen_img) : nullptr,
+                          fuse_zero ? (bbox_adjacent ? (void*)d_screen_bbox : (void*)d_screen_img)
+                                    : (persistent ? (void*)d_screen_img : nullptr),
                           fuse_zero ? img_bytes + (bbox_adjacent ? 64 : 0) : 0, st, has_img ? d_edges_x : nullptr,
-                          has_img ? d_edges_y : nullptr, W, H, has_img ? hist_ws : nullptr);
+                          has_img ? d_edges_y : nullptr, W, H, has_img ? hist_ws : nullptr,
+                          cell_prev, cell_cur);
   if (rc != LYNX_OK) return rc;
   if (!force_ldg) {
     const int r = launch_track_pipe(a, moment_mode, d_out_soa != nullptr, p->sm_count, st);
     if (r <= 0) return r;
   }
-  if (d_screen_bbox) return LYNX_E_BADPROGRAM;  // bounding box is a feature of the pipelined kernel
+  // the bounding box (and with it the persistent image) is a feature of the pipelined kernel
+  if (d_screen_bbox || persistent) return LYNX_E_BADPROGRAM;
   a.bbox = nullptr;
   a.n_rep = 1;
   const int64_t n_tiles = (N + kTile - 1) / kTile;

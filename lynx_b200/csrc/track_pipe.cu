@@ -196,6 +196,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   uint32_t* win = reinterpret_cast<uint32_t*>(psm + L.win);
   __shared__ double s_red[kConsumerWarps][28];
   __shared__ float s_wstat[kConsumerWarps][5];
+  __shared__ float s_chk[kConsumerWarps];  // sink of the load-completion dependency (see below)
   __shared__ HistWindow s_win;
 
   const int tid = threadIdx.x;
@@ -432,9 +433,21 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
         v[k][2] = q.z;
         v[k][3] = q.w;
       }
-      if (!HAS_OUT) {  // values live in registers now: the stage can be refilled already
+      if (!HAS_OUT) {
+        // The stage can be refilled as soon as the values are in registers -- but ISSUING the
+        // shared-memory loads is not enough: the arrive below is not ordered behind their
+        // completion, and the loader's next bulk copy then overwrote a stage some warps had not
+        // read yet (those threads tracked particles of tile it + STAGES twice and dropped their
+        // own: images differed from run to run once a CTA had more than STAGES tiles, i.e.
+        // above ~1.3 M particles; sums were unaffected).  A store that depends on one word of
+        // every 16-byte load forces the scoreboard wait: it cannot issue before all six loads
+        // have returned, and the arrive is issued behind it.
+        const float chk = ((v[0][0] + v[1][0]) + (v[2][0] + v[3][0])) + (v[4][0] + v[5][0]);
         __syncwarp();
-        if (lane == 0) mbar_arrive(empty + s);
+        if (lane == 0) {
+          *reinterpret_cast<volatile float*>(&s_chk[warp - 2]) = chk;
+          mbar_arrive(empty + s);
+        }
       }
       bool live[4];
 #pragma unroll

@@ -570,3 +570,109 @@ def test_screen_exchange_kernel_single_rank():
         torch.cuda.synchronize()
         assert torch.equal(out, ref), f"step {step}"
         assert float(out.sum()) > 0.5 * n  # some settings steer part of the beam off the screen
+
+
+@pytest.mark.parametrize("n", [20_001, 4_200_000])
+def test_persistent_screen_image_matches_fresh_image(n):
+    """lynx_track_particles_fwd_persistent: the image and its 8-int state are zeroed ONCE; every
+    call clears only the rectangle the previous call lit.  After each call the image must be
+    bit-identical to what lynx_track_particles_fwd writes into a fresh buffer -- for a moving /
+    growing / shrinking spot, a beam kicked off the screen, the same spot twice, and (4.2 M
+    particles) with the histogram replicas + fold pass in play."""
+    from lynx_b200 import _lib as L
+    from lynx_b200.program import Program, encode, pack_params
+
+    lib = L.lib()
+    soa_np = F.gaussian_beam_soa(n, seed=21)
+    ld = (n + 3) & ~3
+    soa = torch.zeros((6, ld), device="cuda")
+    soa[:, :n] = torch.from_numpy(soa_np).cuda()
+    e_in = torch.tensor([F.ASTRA_ENERGY], device="cuda")
+    e_out = torch.empty(1, device="cuda")
+    img_p = state = None
+    cases = (((5.0, -5.0, 5.0), 1e-3, -2e-3), ((2.0, -3.0, 1.0), -1e-3, 1e-3),
+             ((9.0, -9.0, 9.0), 2e-3, 2e-3), ((9.0, -9.0, 9.0), 2e-3, 2e-3),
+             ((5.0, -5.0, 5.0), 1e-3, 0.3), ((5.0, -5.0, 5.0), 1e-3, -2e-3),
+             ((0.0, 0.0, 0.0), 0.0, 0.0))
+    for epoch, (k1, vk, hk) in enumerate(cases, start=7):
+        seg = F.build_segment(F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True,
+                                        screen=F.TEST_SCREEN))
+        enc = encode(seg.elements, (1,))
+        prog = Program.get(enc)
+        params = pack_params(enc, "cuda")
+        ex, ey = seg.AREABSCR1._device_edges(torch.device("cuda"))
+        W, H = ex.numel() - 1, ey.numel() - 1
+        ws = torch.empty(prog.workspace_bytes(1), dtype=torch.uint8, device="cuda")
+        fresh = torch.full((1, H, W), 3.0, device="cuda")
+        L.check(lib.lynx_track_particles_fwd(
+            prog.handle, params.data_ptr(), 1, soa.data_ptr(), 1, ld, n, None, ld, None,
+            fresh.data_ptr(), W, H, ex.data_ptr(), ey.data_ptr(), None, 0, e_in.data_ptr(),
+            e_out.data_ptr(), ws.data_ptr(), L.current_stream()))
+        if img_p is None:
+            img_p = torch.zeros((1, H, W), device="cuda")
+            state = torch.zeros(8, dtype=torch.int32, device="cuda")
+        L.check(lib.lynx_track_particles_fwd_persistent(
+            prog.handle, params.data_ptr(), 1, soa.data_ptr(), 1, ld, n, None, ld, None,
+            img_p.data_ptr(), W, H, ex.data_ptr(), ey.data_ptr(), None, 0, e_in.data_ptr(),
+            e_out.data_ptr(), ws.data_ptr(), state.data_ptr(), epoch, L.current_stream()))
+        assert torch.equal(img_p, fresh), (epoch, k1, vk, hk)
+        lit = float(fresh.sum())
+        assert lit == (0.0 if hk > 0.1 else lit) and lit <= n
+    # two settings at once (the rectangle is the union over the settings' images)
+    seg = F.build_segment(F.ares_ea(k1=(5.0, -5.0, 5.0), screen_active=True, screen=F.TEST_SCREEN))
+    seg.AREAMCHM1.angle = torch.tensor([-2e-3, 1.5e-3])
+    enc = encode(seg.elements, (1,))
+    prog = Program.get(enc)
+    params = pack_params(enc, "cuda")
+    ws = torch.empty(prog.workspace_bytes(2), dtype=torch.uint8, device="cuda")
+    e2, e2o = e_in.expand(2).contiguous(), torch.empty(2, device="cuda")
+    img2 = torch.zeros((2, H, W), device="cuda")
+    st2 = torch.zeros(8, dtype=torch.int32, device="cuda")
+    for epoch, ang in enumerate(((-2e-3, 1.5e-3), (1e-3, -1e-3), (1e-3, -1e-3))):
+        seg.AREAMCHM1.angle = torch.tensor(ang)
+        params = pack_params(encode(seg.elements, (1,)), "cuda")
+        fresh = torch.empty((2, H, W), device="cuda")
+        L.check(lib.lynx_track_particles_fwd(
+            prog.handle, params.data_ptr(), 2, soa.data_ptr(), 0, ld, n, None, ld, None,
+            fresh.data_ptr(), W, H, ex.data_ptr(), ey.data_ptr(), None, 0, e2.data_ptr(),
+            e2o.data_ptr(), ws.data_ptr(), L.current_stream()))
+        L.check(lib.lynx_track_particles_fwd_persistent(
+            prog.handle, params.data_ptr(), 2, soa.data_ptr(), 0, ld, n, None, ld, None,
+            img2.data_ptr(), W, H, ex.data_ptr(), ey.data_ptr(), None, 0, e2.data_ptr(),
+            e2o.data_ptr(), ws.data_ptr(), st2.data_ptr(), epoch, L.current_stream()))
+        assert torch.equal(img2, fresh), ang
+        assert float(fresh[0].sum()) > 0 and not torch.equal(fresh[0], fresh[1])
+
+
+def test_large_beam_refilled_pipeline_stages():
+    """4.2 M particles: every CTA of the pipelined K2 runs ~14 tiles through its 4-stage ring,
+    so stages are refilled while other warps may still be reading them.  (Regression: the
+    screen variant released a stage right after ISSUING its shared-memory loads; above ~1.3 M
+    particles some threads then saw a later tile's particles, and the image -- not its sum --
+    changed from run to run.)  The image must be bit-identical between runs, equal to an
+    independent histogram (torch.histogramdd semantics, the oracle's) of the coordinates the
+    particle-output variant produces, and those coordinates must equal M x + kick in fp64."""
+    n = 4_200_000
+    soa_np = F.gaussian_beam_soa(n, seed=33)
+    beam = lx.ParticleBeam.from_soa(torch.from_numpy(soa_np).cuda().unsqueeze(0).contiguous(), n,
+                                    torch.tensor([F.ASTRA_ENERGY], device="cuda"))
+    kw = dict(k1=(5.0, -5.0, 5.0), vkick=1e-3, hkick=-2e-3)
+    seg_s = F.build_segment(F.ares_ea(screen_active=True, screen=F.TEST_SCREEN, **kw))
+    imgs = []
+    for _ in range(3):
+        assert seg_s.track(beam) is lx.Beam.empty
+        imgs.append(seg_s.AREABSCR1.reading.clone())
+    assert torch.equal(imgs[0], imgs[1]) and torch.equal(imgs[0], imgs[2])
+    seg_o = F.build_segment(F.ares_ea(**kw))
+    out = seg_o.track(beam)
+    out2 = seg_o.track(beam)
+    assert torch.equal(out.soa, out2.soa)
+    ex, ey = seg_s.AREABSCR1.pixel_bin_edges
+    want = screen_reading_particles(out.xs.cpu(), out.ys.cpu(), ex, ey)
+    assert torch.equal(imgs[0].cpu(), want)
+    tm = seg_o.transfer_map(torch.tensor([F.ASTRA_ENERGY]).cuda())[0].cpu().double().numpy()
+    x7 = np.concatenate([soa_np.astype(np.float64), np.ones((1, n))])
+    ref = (tm @ x7)[:6]
+    got = out.soa[0, :, :n].cpu().numpy()
+    scale = np.sqrt(np.mean(ref**2, axis=1, keepdims=True))
+    assert np.max(np.abs(got - ref) / scale) < 2e-5
