@@ -27,6 +27,12 @@ struct lynx_host_ctx {
   // host copies of the last edge tables sent to the device: an unchanged screen geometry is
   // not sent again (two DMA operations less per call)
   std::vector<float> ex_sent, ey_sent;
+  // the device image is persistent (lynx_track_particles_fwd_persistent): zeroed when it is
+  // (re)allocated, afterwards only the rectangle the previous call lit is cleared
+  Buf img_state;
+  uint32_t img_epoch = 0;
+  int64_t img_geom[3] = {0, 0, 0};  // W, H, B the image had when it was last zeroed as a whole
+  bool img_persistent_ok = true;  // false once a lattice needed the non-pipelined kernel
   bool grow(Buf& b, size_t bytes) {
     if (bytes <= b.cap) return true;
     if (b.p) cudaFree(b.p);
@@ -67,7 +73,7 @@ extern "C" void lynx_host_ctx_destroy(lynx_host_ctx_t* c) {
   lynx_host_ctx::Buf* all[] = {&c->params, &c->in,  &c->out,   &c->energy_in, &c->energy_out,
                                &c->bpm,    &c->img, &c->ex,    &c->ey,        &c->mom,
                                &c->ws,     &c->mu_in, &c->cov_in, &c->mu_out, &c->cov_out,
-                               &c->bpm_f,  &c->bbox};
+                               &c->bpm_f,  &c->bbox,  &c->img_state};
   if (c->h_bbox) cudaFreeHost(c->h_bbox);
   for (auto* b : all) c->release(*b);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -142,13 +148,44 @@ extern "C" int lynx_host_track_particles(
     if (!c->grow(c->bbox, 64)) return LYNX_E_NOMEM;
     if (!c->h_bbox && cudaMallocHost((void**)&c->h_bbox, 64) != cudaSuccess) return LYNX_E_NOMEM;
   }
-  int rc = lynx_track_particles_fwd_bbox(
-      p, (const float*)c->params.p, B, (const float*)c->in.p, (Bb == B) ? 1 : 0,
-      ld, N, out_soa ? (float*)c->out.p : nullptr, ld, (double*)c->bpm.p,
-      has_screen ? (float*)c->img.p : nullptr, W, H, (const float*)c->ex.p,
-      (const float*)c->ey.p, moment_mode ? (double*)c->mom.p : nullptr, moment_mode,
-      (const float*)c->energy_in.p, (float*)c->energy_out.p, c->ws.p,
-      sparse_img ? (int32_t*)c->bbox.p : nullptr, (lynx_stream_t)st);
+  const size_t img_bytes = has_screen ? sizeof(float) * (size_t)W * H * B : 0;
+  bool dev_persistent = has_screen && c->img_persistent_ok && !(W & 3);
+  const int32_t* d_box = sparse_img ? (const int32_t*)c->bbox.p : nullptr;
+  int rc = LYNX_OK;
+  if (dev_persistent) {
+    if (!c->grow(c->img_state, 32)) return LYNX_E_NOMEM;
+    if (c->img_geom[0] != W || c->img_geom[1] != H || c->img_geom[2] != B) {
+      // new geometry / batch size (or a reallocated buffer): start from zeros
+      LYNX_CUDA_OK(cudaMemsetAsync(c->img.p, 0, img_bytes, st));
+      LYNX_CUDA_OK(cudaMemsetAsync(c->img_state.p, 0, 32, st));
+      c->img_geom[0] = W;
+      c->img_geom[1] = H;
+      c->img_geom[2] = B;
+      c->img_epoch = 0;
+    }
+    const uint32_t epoch = c->img_epoch++;
+    rc = lynx_track_particles_fwd_persistent(
+        p, (const float*)c->params.p, B, (const float*)c->in.p, (Bb == B) ? 1 : 0, ld, N,
+        out_soa ? (float*)c->out.p : nullptr, ld, (double*)c->bpm.p, (float*)c->img.p, W, H,
+        (const float*)c->ex.p, (const float*)c->ey.p, moment_mode ? (double*)c->mom.p : nullptr,
+        moment_mode, (const float*)c->energy_in.p, (float*)c->energy_out.p, c->ws.p,
+        (int32_t*)c->img_state.p, epoch, (lynx_stream_t)st);
+    d_box = (const int32_t*)c->img_state.p + 4 * (epoch & 1u);
+    if (rc == LYNX_E_BADPROGRAM) {  // lattice outside the pipelined kernel: plain path from now on
+      c->img_persistent_ok = false;
+      c->img_geom[0] = c->img_geom[1] = c->img_geom[2] = 0;
+      dev_persistent = false;
+      d_box = sparse_img ? (const int32_t*)c->bbox.p : nullptr;
+    }
+  }
+  if (!dev_persistent)
+    rc = lynx_track_particles_fwd_bbox(
+        p, (const float*)c->params.p, B, (const float*)c->in.p, (Bb == B) ? 1 : 0,
+        ld, N, out_soa ? (float*)c->out.p : nullptr, ld, (double*)c->bpm.p,
+        has_screen ? (float*)c->img.p : nullptr, W, H, (const float*)c->ex.p,
+        (const float*)c->ey.p, moment_mode ? (double*)c->mom.p : nullptr, moment_mode,
+        (const float*)c->energy_in.p, (float*)c->energy_out.p, c->ws.p,
+        sparse_img ? (int32_t*)c->bbox.p : nullptr, (lynx_stream_t)st);
   if (rc != LYNX_OK) return rc;
   // Sparse read-back of the persistent host image.  Invariant: the host image is zero
   // outside last_rect.  The device image is exact everywhere (zero outside this call's
@@ -171,7 +208,7 @@ extern "C" int lynx_host_track_particles(
     return cudaSuccess;
   };
   if (sparse_img) {
-    LYNX_CUDA_OK(cudaMemcpyAsync(c->h_bbox, c->bbox.p, 16, cudaMemcpyDeviceToHost, st));
+    LYNX_CUDA_OK(cudaMemcpyAsync(c->h_bbox, d_box, 16, cudaMemcpyDeviceToHost, st));
     if (c->last_img != screen_img) {
       memset(screen_img, 0, sizeof(float) * (size_t)W * H * B);  // first use of this buffer
       c->last_rect[0] = c->last_rect[1] = c->last_rect[2] = c->last_rect[3] = 0;

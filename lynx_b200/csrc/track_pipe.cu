@@ -197,6 +197,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
   __shared__ double s_red[kConsumerWarps][28];
   __shared__ float s_wstat[kConsumerWarps][5];
   __shared__ float s_chk[kConsumerWarps];  // sink of the load-completion dependency (see below)
+  __shared__ int s_bb[4];                  // CTA bounding box of the touched bins
+  if (threadIdx.x < 4) s_bb[threadIdx.x] = 0;  // ordered before its use by the CTA barriers below
   __shared__ HistWindow s_win;
 
   const int tid = threadIdx.x;
@@ -615,12 +617,16 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
         bb2 = max(bb2, __shfl_xor_sync(0xffffffffu, bb2, o));
         bb3 = max(bb3, __shfl_xor_sync(0xffffffffu, bb3, o));
       }
+      // one set of global atomics per CTA, not per warp: 16 x 148 x 4 atomicMax on the same
+      // four words were ~3 us of the 1 M-particle step (serialised in one L2 slice)
       if (lane == 0 && bb1 > 0) {
-        atomicMax(a.bbox + 0, bb0);
-        atomicMax(a.bbox + 1, bb1);
-        atomicMax(a.bbox + 2, bb2);
-        atomicMax(a.bbox + 3, bb3);
+        atomicMax(&s_bb[0], bb0);
+        atomicMax(&s_bb[1], bb1);
+        atomicMax(&s_bb[2], bb2);
+        atomicMax(&s_bb[3], bb3);
       }
+      consumers_sync();
+      if (cid < 4 && s_bb[1] > 0) atomicMax(a.bbox + cid, s_bb[cid]);
     }
     // Let a programmatically-serialized follower (histogram fold, multi-GPU exchange kernel)
     // start launching once the consumers of every CTA are through their tiles.  The first
