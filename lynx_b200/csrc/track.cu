@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(kTPB, 2) track_fwd_kernel(TrackArgs a) {
           s0[j] = v[4][j];
           p0[j] = v[5][j];
         }
-        apply_affine(rec + p.a, v);
+        apply_block2(rec + p.a, v);  // the cavity's own map is block-diagonal
         const float* sc = rec + p.b;
 #pragma unroll
         for (int j = 0; j < kNP; ++j) {

@@ -466,7 +466,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1) track_pipe_kernel(TrackArgs a
             s0[j] = v[4][j];
             q0[j] = v[5][j];
           }
-          apply_affine(rec + p.a, v);
+          apply_block2(rec + p.a, v);  // the cavity's own map is block-diagonal
           const float* sc = rec + p.b;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {

@@ -676,3 +676,15 @@ def test_large_beam_refilled_pipeline_stages():
     got = out.soa[0, :, :n].cpu().numpy()
     scale = np.sqrt(np.mean(ref**2, axis=1, keepdims=True))
     assert np.max(np.abs(got - ref) / scale) < 2e-5
+    # the moments-only variant shares the early stage hand-back: its sums against float64
+    # statistics of the particle-output variant's coordinates
+    mo = seg_o.track(beam, particles=False, moments=2)
+    g64 = got.astype(np.float64)
+    np.testing.assert_allclose(mo.mu_x.cpu().numpy(), [g64[0].mean()], rtol=1e-5, atol=1e-9)
+    np.testing.assert_allclose(mo.mu_y.cpu().numpy(), [g64[2].mean()], rtol=1e-5, atol=1e-9)
+    for i, c in enumerate(("x", "xp", "y", "yp", "s", "p")):
+        np.testing.assert_allclose(getattr(mo, f"sigma_{c}").cpu().numpy(), [g64[i].std(ddof=1)],
+                                   rtol=1e-5)
+    mo2 = seg_o.track(beam, particles=False, moments=2)
+    assert torch.equal(mo.moment_sums(), mo2.moment_sums()) or torch.allclose(
+        mo.moment_sums(), mo2.moment_sums(), rtol=1e-12)
