@@ -194,6 +194,10 @@ struct ApertureArgs {
   int64_t ld_out;
   float* q_out;   // nullable [R][ld_out]
   float* q_lost;  // nullable [R][ld_out]
+  // one-pass variant
+  unsigned int* ticket;        // [R] next tile to hand out (zeroed per call)
+  unsigned long long* status;  // [R][n_tiles] look-back words (zeroed per call)
+  int64_t* counts;             // [R]
 };
 
 // One region (survivors or lost particles) of the compacted tile leaves shared memory.  The
@@ -243,7 +247,21 @@ __device__ __forceinline__ void copy_region(const float* __restrict__ sm, int sv
 // scalar-head / vector-body / scalar-tail copy per plane at 3.5 TB/s (instruction-bound:
 // twelve branchy copy loops per tile); this version phase-aligns the shared-memory regions
 // to their destinations.
-template <int SHAPE>
+// ONEPASS: no count / scan launches.  Tiles are handed out by a ticket counter (so every
+// predecessor of a tile is held by a running CTA) and a tile learns the number of survivors in
+// front of it by decoupled look-back over 64-bit status words (flag << 62 | value; flag 1 =
+// this tile's own count, 2 = inclusive prefix), read by one warp, 32 predecessors at a time.
+// The words carry their whole message, so no fences are involved.  48 B per particle.
+__device__ __forceinline__ unsigned long long ld_status(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_status(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+template <int SHAPE, bool ONEPASS>
 __global__ void __launch_bounds__(kApTPB, 3) aperture_scatter_kernel(ApertureArgs a) {
   extern __shared__ __align__(16) float ap_smem[];  // [6 or 7][kApPlane]
   const int64_t r = blockIdx.y;
@@ -255,16 +273,18 @@ __global__ void __launch_bounds__(kApTPB, 3) aperture_scatter_kernel(ApertureArg
   const bool q_vec = has_q && (a.ld_q & 3) == 0 && ((uintptr_t)a.q_in & 15) == 0;
   float* q_kept = a.q_out ? a.q_out + r * a.ld_out : nullptr;
   float* q_lost = a.q_lost ? a.q_lost + r * a.ld_out : nullptr;
+  unsigned long long* status = ONEPASS ? a.status + r * a.n_tiles : nullptr;
   __shared__ unsigned s_w[kApTPB / 32];
+  __shared__ long long s_tile[2];  // ONEPASS: [0] this CTA's next tile, [1] survivors in front
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // Software pipeline: the loads of the CTA's NEXT tile are issued as soon as the current
   // tile's values have been scattered into shared memory, so they are in flight during the
-  // copy-out phase (and across the two barriers) without costing extra registers.
+  // copy-out phase (and across the barriers) without costing extra registers.
   float4 v[7];
   int64_t kept0_next = 0;
   auto load_tile = [&](int64_t t) {
     const int64_t p = t * kApTile + threadIdx.x * 4;
-    kept0_next = __ldg(a.tile_offsets + r * a.n_tiles + t);
+    if (!ONEPASS) kept0_next = __ldg(a.tile_offsets + r * a.n_tiles + t);
     if (p < a.N) {
 #pragma unroll
       for (int k = 0; k < 6; ++k)
@@ -283,12 +303,20 @@ __global__ void __launch_bounds__(kApTPB, 3) aperture_scatter_kernel(ApertureArg
       }
     }
   };
-  if ((int64_t)blockIdx.x < a.n_tiles) load_tile(blockIdx.x);
-  for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+  int64_t t;
+  if (ONEPASS) {
+    if (threadIdx.x == 0) s_tile[0] = (long long)atomicAdd(a.ticket + r, 1u);
+    __syncthreads();
+    t = s_tile[0];
+    __syncthreads();  // s_tile[0] is rewritten at the top of the loop
+  } else {
+    t = blockIdx.x;
+  }
+  if (t < a.n_tiles) load_tile(t);
+  while (t < a.n_tiles) {
+    if (ONEPASS && threadIdx.x == 0) s_tile[0] = (long long)atomicAdd(a.ticket + r, 1u);
     const int64_t tile0 = t * kApTile;
     const int n_tile = (int)min((int64_t)kApTile, a.N - tile0);
-    const int64_t kept0 = kept0_next;
-    const int64_t lost0 = tile0 - kept0;
     const int local = threadIdx.x * 4;
     const int64_t p = tile0 + local;
     unsigned f = 0;
@@ -316,6 +344,44 @@ __global__ void __launch_bounds__(kApTPB, 3) aperture_scatter_kernel(ApertureArg
       if (w < warp) k_rank += sw;
       cnt += sw;
     }
+    int64_t kept0;
+    const int64_t t_next = ONEPASS ? (int64_t)s_tile[0] : t + gridDim.x;
+    if (ONEPASS) {
+      if (warp == 0) {
+        constexpr unsigned long long kAgg = 1ull << 62, kPre = 2ull << 62, kVal = (1ull << 62) - 1;
+        unsigned long long excl = 0;
+        if (t > 0) {
+          if (lane == 0) st_status(status + t, kAgg | (unsigned long long)cnt);
+          int64_t j = t - 1;  // nearest predecessor of the current window
+          while (true) {
+            const int64_t idx = j - lane;
+            const unsigned long long wd = idx >= 0 ? ld_status(status + idx) : kPre;
+            const unsigned flag = (unsigned)(wd >> 62);
+            const unsigned pre = __ballot_sync(0xffffffffu, flag == 2u);
+            const unsigned inv = __ballot_sync(0xffffffffu, flag == 0u);
+            const int first = pre ? __ffs(pre) - 1 : 31;  // nearest lane holding a prefix
+            const unsigned rel = first == 31 ? 0xffffffffu : ((2u << first) - 1u);
+            if (inv & rel) continue;  // a predecessor in range has not published yet
+            unsigned long long part = (rel >> lane) & 1u ? (wd & kVal) : 0ull;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+            excl += part;
+            if (pre) break;
+            j -= 32;
+          }
+        }
+        if (lane == 0) {
+          st_status(status + t, kPre | (excl + (unsigned long long)cnt));
+          s_tile[1] = (long long)excl;
+          if (t == a.n_tiles - 1) a.counts[r] = (int64_t)(excl + (unsigned long long)cnt);
+        }
+      }
+      __syncthreads();
+      kept0 = s_tile[1];
+    } else {
+      kept0 = kept0_next;
+    }
+    const int64_t lost0 = tile0 - kept0;
     // shared-memory layout of a plane: survivors from float index ka (phase of kept0), lost
     // particles from the next vector boundary + the phase of lost0
     const int ka = (int)(kept0 & 3);
@@ -339,12 +405,13 @@ __global__ void __launch_bounds__(kApTPB, 3) aperture_scatter_kernel(ApertureArg
         }
       }
     }
-    if (t + gridDim.x < a.n_tiles) load_tile(t + gridDim.x);
+    if (t_next < a.n_tiles) load_tile(t_next);
     __syncthreads();
     copy_region<6>(ap_smem, 0, ka, cnt, kept, a.ld_out, kept0 - ka, q_kept, has_q);
     if (lost)
       copy_region<6>(ap_smem, lv0, la, n_tile - cnt, lost, a.ld_out, lost0 - la, q_lost, has_q);
     // the next iteration's first __syncthreads() orders these reads before its writes
+    t = t_next;
   }
 }
 
@@ -383,7 +450,8 @@ extern "C" int lynx_beam_transform(const float* d_in_soa, int64_t in_row_stride,
 extern "C" size_t lynx_aperture_workspace_bytes(int64_t R, int64_t N) {
   if (R <= 0 || N <= 0) return 0;
   const int64_t n_tiles = (N + kApTile - 1) / kApTile;
-  return (size_t)(R * n_tiles) * sizeof(uint32_t);
+  // three-pass: R * n_tiles counts; one-pass: R * n_tiles 64-bit status words + R tickets
+  return (size_t)(R * n_tiles) * sizeof(unsigned long long) + (size_t)((R + 3) & ~3LL) * 4;
 }
 
 extern "C" int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N, int64_t ld_in,
@@ -405,6 +473,53 @@ extern "C" int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t n_tiles = (N + kApTile - 1) / kApTile;
+  ApertureArgs a;
+  a.in = d_in_soa;
+  a.ld_in = ld_in;
+  a.N = N;
+  a.q_in = d_charges_in;
+  a.ld_q = ld_q;
+  a.x_max = d_x_max;
+  a.y_max = d_y_max;
+  a.lim_stride = lim_stride;
+  a.n_tiles = n_tiles;
+  a.out = d_out_soa;
+  a.lost = d_lost_soa;
+  a.ld_out = ld_out;
+  a.q_out = d_charges_out;
+  a.q_lost = d_charges_lost;
+  a.counts = d_counts;
+  const size_t smem = (size_t)(d_charges_in ? 7 : 6) * kApPlane * sizeof(float);
+  // persistent: as many CTAs as are resident (3 per SM), each loops over its tiles
+  const dim3 sgrid((unsigned)std::max<int64_t>(1, std::min<int64_t>(n_tiles, (3LL * sms + R - 1) / R)),
+                   (unsigned)R);
+  // Opt-in (LYNX_APERTURE_ONEPASS=1), a measured negative result: one launch and 48 B per
+  // particle, but 1.08 ms against 0.29 + 0.08 ms at 32 M particles.  With 1024-particle tiles
+  // and 444 resident CTAs running in lock-step a tile's nearest published prefix is ~14
+  // look-back windows (dependent L2 round trips) away, and the scatter cannot start before it.
+  static const bool onepass = [] { const char* e = getenv("LYNX_APERTURE_ONEPASS"); return e && e[0] == '1'; }();
+  if (onepass) {
+    // one launch: ticketed tiles + decoupled look-back (48 B per particle)
+    a.status = reinterpret_cast<unsigned long long*>(d_workspace);
+    a.ticket = reinterpret_cast<unsigned int*>(a.status + R * n_tiles);
+    a.tile_offsets = nullptr;
+    LYNX_CUDA_OK(cudaMemsetAsync(d_workspace, 0, lynx_aperture_workspace_bytes(R, N), st));
+    auto kern = shape == 0 ? aperture_scatter_kernel<0, true> : aperture_scatter_kernel<1, true>;
+    static bool attr_set[2] = {false, false};
+    if (!attr_set[shape]) {
+      LYNX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        7 * kApPlane * (int)sizeof(float)));
+      attr_set[shape] = true;
+    }
+    {
+      ProfileScope ps(5, st);
+      kern<<<sgrid, kApTPB, smem, st>>>(a);
+    }
+    count_launch(1);
+    LYNX_CUDA_OK(cudaGetLastError());
+    return LYNX_OK;
+  }
+  // three launches: tile counts, scan, scatter (56 B per particle)
   uint32_t* tiles = reinterpret_cast<uint32_t*>(d_workspace);
   const int64_t per_r = std::max<int64_t>(1, (8LL * sms + R - 1) / R);
   const dim3 grid((unsigned)std::min<int64_t>(n_tiles, per_r), (unsigned)R);
@@ -415,34 +530,17 @@ extern "C" int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N
     aperture_count_kernel<1><<<grid, kApTPB, 0, st>>>(d_in_soa, ld_in, N, d_x_max, d_y_max,
                                                       lim_stride, tiles, n_tiles);
   aperture_scan_kernel<<<(unsigned)R, kScanTPB, 0, st>>>(tiles, n_tiles, d_counts);
-  ApertureArgs a;
-  a.in = d_in_soa;
-  a.ld_in = ld_in;
-  a.N = N;
-  a.q_in = d_charges_in;
-  a.ld_q = ld_q;
-  a.x_max = d_x_max;
-  a.y_max = d_y_max;
-  a.lim_stride = lim_stride;
   a.tile_offsets = tiles;
-  a.n_tiles = n_tiles;
-  a.out = d_out_soa;
-  a.lost = d_lost_soa;
-  a.ld_out = ld_out;
-  a.q_out = d_charges_out;
-  a.q_lost = d_charges_lost;
+  a.status = nullptr;
+  a.ticket = nullptr;
   {
-    const size_t smem = (size_t)(d_charges_in ? 7 : 6) * kApPlane * sizeof(float);
-    auto kern = shape == 0 ? aperture_scatter_kernel<0> : aperture_scatter_kernel<1>;
+    auto kern = shape == 0 ? aperture_scatter_kernel<0, false> : aperture_scatter_kernel<1, false>;
     static bool attr_set[2] = {false, false};
     if (!attr_set[shape]) {
       LYNX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         7 * kApPlane * (int)sizeof(float)));
       attr_set[shape] = true;
     }
-    // persistent: as many CTAs as are resident (3 per SM), each loops over its tiles
-    const dim3 sgrid((unsigned)std::max<int64_t>(1, std::min<int64_t>(n_tiles, (3LL * sms + R - 1) / R)),
-                     (unsigned)R);
     ProfileScope ps(5, st);
     kern<<<sgrid, kApTPB, smem, st>>>(a);
   }

@@ -164,8 +164,8 @@ def test_new_entry_points_validate_arguments():
     assert lib.lynx_beam_transform(20, 0, 8, 1, 8, 16, 16, 8, None) == L.E_BADARG  # alignment
     assert lib.lynx_beam_generate_ellipsoid(None, None, 1, 4, 0, 1, None, 4, None) == L.E_BADARG
     assert lib.lynx_beam_generate_ellipsoid(16, 16, 1, 8, 2, 1, 16, 8, None) == L.E_BADARG  # first % 4
-    assert lib.lynx_aperture_workspace_bytes(1, 1) == 4
-    assert lib.lynx_aperture_workspace_bytes(2, 1025) == 16
+    assert lib.lynx_aperture_workspace_bytes(1, 1) == 8 + 16  # one status word + the ticket block
+    assert lib.lynx_aperture_workspace_bytes(2, 1025) == 2 * 2 * 8 + 16
     assert lib.lynx_aperture_workspace_bytes(0, 10) == 0
     args = [16, 1, 8, 8, None, 0, 16, 16, 0, 0, 16, None, 8, None, None, 16, 16, None]
     bad_shape = list(args)
