@@ -688,3 +688,31 @@ def test_large_beam_refilled_pipeline_stages():
     mo2 = seg_o.track(beam, particles=False, moments=2)
     assert torch.equal(mo.moment_sums(), mo2.moment_sums()) or torch.allclose(
         mo.moment_sums(), mo2.moment_sums(), rtol=1e-12)
+
+
+def test_non_finite_particles_propagate_like_a_dense_product():
+    """A dense 7x7 product (element.py:83-92) turns every coordinate of a particle into NaN as
+    soon as one of them is inf / NaN (0 * inf).  The block-sparse application of the cavity's
+    own map must keep that behaviour, and must not touch the other particles."""
+    n = 4099
+    soa = F.cfg4_beam_soa(n, seed=5).copy()
+    soa[4, 17] = np.inf   # s of particle 17
+    soa[0, 123] = np.nan  # x of particle 123
+    # C1 alone, and C1 + D2: the particles meet the cavity's block-diagonal map first
+    spec = F.cavity_dipole_line(screen_active=False)[3:4]
+    out = F.build_segment(spec).track(_gpu_beam(soa, F.CFG4_ENERGY))
+    got = out.soa[0, :, :n].cpu().numpy()
+    # s = inf also poisons the cavity's own p update (cos(inf)); x = NaN does not: as in the
+    # reference, p is overwritten from the INCOMING s and p (cavity.py:142-161), so it stays finite
+    assert np.isnan(got[:, 17]).all()
+    assert np.isnan(got[:5, 123]).all() and np.isfinite(got[5, 123])
+    ok = np.ones(n, dtype=bool)
+    ok[[17, 123]] = False
+    assert np.isfinite(got[:, ok]).all()
+    clean = F.cfg4_beam_soa(n, seed=5)
+    ref = F.build_segment(spec).track(_gpu_beam(clean, F.CFG4_ENERGY)).soa[0, :, :n].cpu().numpy()
+    np.testing.assert_array_equal(got[:, ok], ref[:, ok])
+    assert got[5, 123] == ref[5, 123]
+    spec2 = F.cavity_dipole_line(screen_active=False)[3:5]
+    got2 = F.build_segment(spec2).track(_gpu_beam(soa, F.CFG4_ENERGY)).soa[0, :, :n].cpu().numpy()
+    assert np.isnan(got2[:, [17, 123]]).all() and np.isfinite(got2[:, ok]).all()
