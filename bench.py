@@ -558,10 +558,10 @@ def run_ours(args, rank, world, local_rank):
     roofline = {"bound": "hbm", "kernel": "track_fwd_kernel (K2)", "achieved": ach, "peak": peak,
                 "unit": "GB/s", "frac": (ach / peak) if ach else None,
                 # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel on this
-                # workload, from profiles/r1c_k2_screen1m.txt (ncu --set full; the image is
+                # workload, from profiles/r1e_k2_screen1m.txt (ncu --set full; the image is
                 # zeroed and accumulated in L2, its write-back happens after the kernel)
-                "traffic": 24355328 if args.particles == 1_000_000 else None,
-                "traffic_source": "profiles/r1c_k2_screen1m.txt",
+                "traffic": 24355840 if args.particles == 1_000_000 else None,
+                "traffic_source": "profiles/r1e_k2_screen1m.txt",
                 "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs, burst copy)",
                 "algorithmic_bytes_per_launch": alg, "kernel_ms": k2_ms,
                 "frac_of_8000": (ach / 8000.0) if ach else None,
