@@ -475,6 +475,49 @@ class ParameterBeam(Beam):
             cov[..., i, j] = cov[..., j, i] = cor[n].float()
         return cls(mu, cov, d(energy, 1e8).float(), d(total_charge, 0.0).float(), device=device)
 
+    @classmethod
+    def from_twiss(cls, beta_x=None, alpha_x=None, emittance_x=None, beta_y=None, alpha_y=None,
+                   emittance_y=None, sigma_s=None, sigma_p=None, cor_s=None, energy=None,
+                   total_charge=None, device=None, dtype=torch.float32):
+        """parameter_beam.py:147-233 (same defaults: beta 1, alpha 0, emittance 7.1971891e-13)."""
+        given = [a for a in (beta_x, alpha_x, emittance_x, beta_y, alpha_y, emittance_y, sigma_s,
+                             sigma_p, cor_s, energy, total_charge) if a is not None]
+        shape = tuple(given[0].shape) if given else (1,)
+        assert all(tuple(a.shape) == shape for a in given), "Arguments must have the same shape."
+        d = lambda a, v: (torch.as_tensor(a, dtype=torch.float64).cpu() if a is not None  # noqa: E731
+                          else torch.full(shape, v, dtype=torch.float64))
+        beta_x, alpha_x, emittance_x = d(beta_x, 1.0), d(alpha_x, 0.0), d(emittance_x, 7.1971891e-13)
+        beta_y, alpha_y, emittance_y = d(beta_y, 1.0), d(alpha_y, 0.0), d(emittance_y, 7.1971891e-13)
+        assert bool((beta_x > 0).all()), "Beta function in x direction must be larger than 0 everywhere."
+        assert bool((beta_y > 0).all()), "Beta function in y direction must be larger than 0 everywhere."
+        return cls.from_parameters(
+            sigma_x=torch.sqrt(emittance_x * beta_x),
+            sigma_xp=torch.sqrt(emittance_x * (1 + alpha_x**2) / beta_x),
+            sigma_y=torch.sqrt(emittance_y * beta_y),
+            sigma_yp=torch.sqrt(emittance_y * (1 + alpha_y**2) / beta_y),
+            sigma_s=d(sigma_s, 1e-6), sigma_p=d(sigma_p, 1e-6), energy=d(energy, 1e8),
+            cor_s=d(cor_s, 0.0), cor_x=-emittance_x * alpha_x, cor_y=-emittance_y * alpha_y,
+            total_charge=d(total_charge, 0.0), device=device, dtype=dtype)
+
+    def transformed_to(self, mu_x=None, mu_xp=None, mu_y=None, mu_yp=None, sigma_x=None,
+                       sigma_xp=None, sigma_y=None, sigma_yp=None, sigma_s=None, sigma_p=None,
+                       energy=None, total_charge=None, device=None, dtype=torch.float32):
+        """parameter_beam.py:278-369: a new beam from the requested moments, the rest taken
+        from this beam (as written there, the correlations are NOT carried over)."""
+        shape = tuple(self.mu_x.shape)
+        given = [a for a in (mu_x, mu_xp, mu_y, mu_yp, sigma_x, sigma_xp, sigma_y, sigma_yp,
+                             sigma_s, sigma_p, energy, total_charge) if a is not None]
+        assert all(tuple(a.shape) == shape for a in given), "Arguments must have the same shape."
+        device = device if device is not None else self._mu.device
+        g = lambda a, cur: a if a is not None else cur  # noqa: E731
+        return self.__class__.from_parameters(
+            mu_x=g(mu_x, self.mu_x), mu_xp=g(mu_xp, self.mu_xp), mu_y=g(mu_y, self.mu_y),
+            mu_yp=g(mu_yp, self.mu_yp), sigma_x=g(sigma_x, self.sigma_x),
+            sigma_xp=g(sigma_xp, self.sigma_xp), sigma_y=g(sigma_y, self.sigma_y),
+            sigma_yp=g(sigma_yp, self.sigma_yp), sigma_s=g(sigma_s, self.sigma_s),
+            sigma_p=g(sigma_p, self.sigma_p), energy=g(energy, self.energy),
+            total_charge=g(total_charge, self.total_charge), device=device, dtype=dtype)
+
     def _sigma(self, i):  # parameter_beam.py:375-417
         return torch.sqrt(torch.clamp_min(self._cov[..., i, i], 1e-20))
 

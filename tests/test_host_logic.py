@@ -179,3 +179,42 @@ def test_new_entry_points_validate_arguments():
     assert lib.lynx_aperture_compact(*no_counts) == L.E_BADARG
     assert lib.lynx_parambeam_along(None, None, 1, None, None, 0, None, None, None, None,
                                     None) == L.E_BADARG
+
+
+def test_parameter_beam_from_twiss_and_transformed_to():
+    """parameter_beam.py:147-233, 278-369 (host logic; constructed on the CPU here) with the
+    reference's own checks: tests/test_parameter_beam.py from_twiss -> twiss, transformed_to."""
+    t = lambda v: torch.tensor([v])  # noqa: E731
+    beam = lx.ParameterBeam.from_twiss(
+        beta_x=t(5.91253676811640894), alpha_x=t(3.55631307633660354),
+        emittance_x=t(3.494768647122823e-09), beta_y=t(5.91253676811640982),
+        alpha_y=t(1.0), emittance_y=t(3.497810737006068e-09), energy=t(6e6), device="cpu")
+    assert beam._mu.shape == (1, 7) and beam._cov.shape == (1, 7, 7)
+    assert beam.beta_x.item() == pytest.approx(5.91253676811640894, rel=1e-4)
+    assert beam.alpha_x.item() == pytest.approx(3.55631307633660354, rel=1e-4)
+    assert beam.emittance_x.item() == pytest.approx(3.494768647122823e-09, rel=1e-4)
+    assert beam.beta_y.item() == pytest.approx(5.91253676811640982, rel=1e-4)
+    assert beam.alpha_y.item() == pytest.approx(1.0, rel=1e-4)
+    assert beam.energy.item() == pytest.approx(6e6)
+    default = lx.ParameterBeam.from_twiss(device="cpu")
+    assert default.beta_x.item() == pytest.approx(1.0, rel=1e-5)
+    assert default.emittance_x.item() == pytest.approx(7.1971891e-13, rel=1e-4)
+    with pytest.raises(AssertionError):
+        lx.ParameterBeam.from_twiss(beta_x=t(-1.0), device="cpu")
+
+    original = lx.ParameterBeam.from_parameters(device="cpu")
+    tb = original.transformed_to(
+        mu_x=t(1e-5), mu_xp=t(1e-7), mu_y=t(2e-5), mu_yp=t(2e-7), sigma_x=t(1.75e-7),
+        sigma_xp=t(2e-7), sigma_y=t(1.75e-7), sigma_yp=t(2e-7), sigma_s=t(0.000001),
+        sigma_p=t(0.000001), energy=t(1e7), total_charge=t(1e-9))
+    assert isinstance(tb, lx.ParameterBeam)
+    for name, want in (("mu_x", 1e-5), ("mu_xp", 1e-7), ("mu_y", 2e-5), ("mu_yp", 2e-7),
+                       ("sigma_x", 1.75e-7), ("sigma_xp", 2e-7), ("sigma_y", 1.75e-7),
+                       ("sigma_yp", 2e-7), ("sigma_s", 1e-6), ("sigma_p", 1e-6),
+                       ("energy", 1e7), ("total_charge", 1e-9)):
+        assert getattr(tb, name).item() == pytest.approx(want, rel=1e-5), name
+    # only what is asked for changes
+    tb2 = original.transformed_to(sigma_x=t(3e-6))
+    assert tb2.sigma_x.item() == pytest.approx(3e-6, rel=1e-5)
+    assert tb2.sigma_y.item() == pytest.approx(original.sigma_y.item(), rel=1e-6)
+    assert tb2._mu.device.type == "cpu"
