@@ -378,12 +378,22 @@ class ParticleBeam(Beam):
     def _plane(self, k):
         return self._soa[..., k, : self._n]
 
-    xs = property(lambda self: self._plane(0))
-    xps = property(lambda self: self._plane(1))
-    ys = property(lambda self: self._plane(2))
-    yps = property(lambda self: self._plane(3))
-    ss = property(lambda self: self._plane(4))
-    ps = property(lambda self: self._plane(5))
+    def _set_plane(self, k, value):
+        """particle_beam.py:732-734 et al. (``particles[..., k] = value``): written into the
+        SoA plane in place; cached moment sums are dropped."""
+        if self._soa.stride(-1) == 0 or any(
+                st == 0 and sz > 1 for st, sz in zip(self._soa.stride(), self._soa.shape)):
+            self._soa = self._soa.contiguous()  # a broadcast (stride-0) beam gets its own storage
+        self._soa[..., k, : self._n] = torch.as_tensor(value, dtype=torch.float32).to(
+            self._soa.device)
+        self._sums = None
+
+    xs = property(lambda self: self._plane(0), lambda self, v: self._set_plane(0, v))
+    xps = property(lambda self: self._plane(1), lambda self, v: self._set_plane(1, v))
+    ys = property(lambda self: self._plane(2), lambda self, v: self._set_plane(2, v))
+    yps = property(lambda self: self._plane(3), lambda self, v: self._set_plane(3, v))
+    ss = property(lambda self: self._plane(4), lambda self, v: self._set_plane(4, v))
+    ps = property(lambda self: self._plane(5), lambda self, v: self._set_plane(5, v))
 
     # ---- moments (particle_beam.py:736-836)
     def moment_sums(self) -> torch.Tensor:

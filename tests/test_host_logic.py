@@ -218,3 +218,20 @@ def test_parameter_beam_from_twiss_and_transformed_to():
     assert tb2.sigma_x.item() == pytest.approx(3e-6, rel=1e-5)
     assert tb2.sigma_y.item() == pytest.approx(original.sigma_y.item(), rel=1e-6)
     assert tb2._mu.device.type == "cpu"
+
+
+def test_particle_beam_coordinate_setters():
+    """particle_beam.py:728-812: xs / xps / ... are settable (uniform_3d_ellipsoid itself
+    assigns them, :381-383); the SoA plane is updated in place and cached moments dropped."""
+    soa = torch.zeros((1, 6, 8))
+    beam = lx.ParticleBeam.from_soa(soa, 6, torch.tensor([1e8]), moment_sums=torch.ones(1, 28))
+    beam.xs = torch.arange(6.0).reshape(1, 6)
+    beam.ps = torch.full((1, 6), 2.0)
+    assert beam._sums is None
+    assert torch.equal(beam.xs, torch.arange(6.0).reshape(1, 6))
+    assert torch.equal(beam.soa[0, 0], torch.tensor([0.0, 1, 2, 3, 4, 5, 0, 0]))  # padding stays 0
+    assert torch.equal(beam.soa[0, 5, :6], torch.full((6,), 2.0)) and float(beam.soa[0, 1].sum()) == 0
+    # a broadcast beam does not write through to the beam it was broadcast from
+    b2 = beam.broadcast((3,))
+    b2.ys = torch.ones(3, 6)
+    assert float(beam.ys.sum()) == 0.0 and float(b2.ys.sum()) == 18.0
