@@ -35,8 +35,8 @@ class Encoded:
 
 
 def _batch_shape(shapes) -> Tuple[int, ...]:
-    """Broadcast of all column shapes; a lattice has a handful of distinct ones, so broadcast
-    the distinct shapes once instead of once per column (this was 90 % of ``encode``)."""
+    """Broadcast of the DISTINCT column shapes (one ``torch.broadcast_shapes`` per column was
+    90 % of ``encode``)."""
     distinct = {tuple(s) for s in shapes}
     if len(distinct) == 1:
         return distinct.pop()
@@ -47,7 +47,6 @@ def encode(elements, energy_shape=()) -> Encoded:
     """elements: flat list of lynx_b200 elements (no nested Segments)."""
     ops, cols = [], []
     bpms, screen = [], None
-    shapes = [tuple(energy_shape)]
     for el in elements:
         op = el._encode()  # (opcode, [tensors], flags) or None for identity elements
         if op is None:
@@ -60,14 +59,14 @@ def encode(elements, energy_shape=()) -> Encoded:
         elif opcode == L.OP_SCREEN:
             screen = el
         col = len(cols) if tensors else -1
-        for t in tensors:
-            cols.append(t)
-            shapes.append(t.shape)
+        cols.extend(tensors)
         ops.append((opcode, col, flags, aux))
         if opcode == L.OP_SCREEN:
             break  # terminal: the reference returns Beam.empty from here on (screen.py:139)
     if not ops:
         ops.append((L.OP_MARKER, -1, 0, 0))
+    shapes = {t.shape for t in cols}  # distinct shapes only: a lattice has a handful
+    shapes.add(tuple(energy_shape))
     return Encoded(ops, cols, _batch_shape(shapes), bpms, screen)
 
 
@@ -78,8 +77,9 @@ def layout(enc: Encoded):
     memo = enc.__dict__.get("_layout")  # callers may widen batch_shape after encode(): key on B
     if memo is not None and memo[0] == B:
         return memo[1]
-    shared = [i for i, t in enumerate(enc.columns) if t.numel() == 1]
-    varying = [i for i, t in enumerate(enc.columns) if t.numel() != 1]
+    shared, varying = [], []
+    for i, t in enumerate(enc.columns):
+        (shared if t.numel() == 1 else varying).append(i)
     n_shared = len(shared)
     # keep the per-setting block 16-byte aligned
     base = (n_shared + 3) & ~3
@@ -115,6 +115,10 @@ def pack_params(enc: Encoded, device) -> torch.Tensor:
     pad = base - n_shared
     for i in varying:
         parts.append(enc.columns[i].to(torch.float32).expand(enc.batch_shape).reshape(B))
+    if len({t.device for t in parts}) == 1:  # the normal case: everything lives in one place
+        if pad:
+            parts.insert(n_shared, torch.zeros(pad, dtype=f32, device=parts[0].device))
+        return torch.cat(parts).to(device)
     # split into runs of equal source device; the padding joins the run in front of it
     out, run, run_dev = [], [], None
 

@@ -117,7 +117,9 @@ def track_elements(elements, incoming, *, particles: bool = True, moments: int =
     device = incoming.soa.device
     _require_cuda(device)
     enc = encode(flat, incoming.energy.shape)
-    bshape = tuple(torch.broadcast_shapes(enc.batch_shape, incoming.batch_shape))
+    bshape = enc.batch_shape
+    if bshape != incoming.batch_shape:
+        bshape = tuple(torch.broadcast_shapes(bshape, incoming.batch_shape))
     enc.batch_shape = bshape
     B = enc.B
     prog = Program.get(enc)
