@@ -13,7 +13,7 @@ from . import _lib as L
 from . import autograd as AG
 from .beams import Beam, ParameterBeam, ParticleBeam
 from .elements import BPM, Aperture, CustomTransferMap, Drift, Element, Marker, Screen
-from .program import Program, encode, pack_params
+from .program import Program, broadcast_shapes, encode, pack_params
 
 
 def _flatten(elements):
@@ -119,7 +119,7 @@ def track_elements(elements, incoming, *, particles: bool = True, moments: int =
     enc = encode(flat, incoming.energy.shape)
     bshape = enc.batch_shape
     if bshape != incoming.batch_shape:
-        bshape = tuple(torch.broadcast_shapes(bshape, incoming.batch_shape))
+        bshape = broadcast_shapes(bshape, incoming.batch_shape)
     enc.batch_shape = bshape
     B = enc.B
     prog = Program.get(enc)
@@ -191,7 +191,7 @@ def _track_parameter_beam(flat, incoming: ParameterBeam):
     device = incoming._mu.device
     _require_cuda(device)
     enc = encode(flat, incoming.energy.shape)
-    bshape = tuple(torch.broadcast_shapes(enc.batch_shape, tuple(incoming._mu.shape[:-1])))
+    bshape = broadcast_shapes(enc.batch_shape, tuple(incoming._mu.shape[:-1]))
     enc.batch_shape = bshape
     B = enc.B
     prog = Program.get(enc)
@@ -228,7 +228,7 @@ def track_parameter_beam_along(flat, incoming: ParameterBeam):
     _require_cuda(device)
     enc = encode(flat, incoming.energy.shape)
     assert len(enc.ops) == len(flat), "every element must encode to exactly one op"
-    bshape = tuple(torch.broadcast_shapes(enc.batch_shape, tuple(incoming._mu.shape[:-1])))
+    bshape = broadcast_shapes(enc.batch_shape, tuple(incoming._mu.shape[:-1]))
     enc.batch_shape = bshape
     B = enc.B
     prog = Program.get(enc)

@@ -235,3 +235,24 @@ def test_particle_beam_coordinate_setters():
     b2 = beam.broadcast((3,))
     b2.ys = torch.ones(3, 6)
     assert float(beam.ys.sum()) == 0.0 and float(b2.ys.sum()) == 18.0
+
+
+def test_broadcast_shapes_matches_torch():
+    """program.broadcast_shapes replaces torch.broadcast_shapes on the call path of
+    Segment.track: same result (or the same RuntimeError) for every combination."""
+    import itertools
+
+    from lynx_b200.program import _batch_shape, broadcast_shapes
+
+    cands = [(), (1,), (3,), (3, 1), (1, 4), (2, 3, 4), (1, 1), torch.Size([5, 1, 1]), (0,), (4,)]
+    for r in range(0, 4):
+        for combo in itertools.product(cands, repeat=r):
+            try:
+                want = tuple(torch.broadcast_shapes(*combo))
+            except RuntimeError:
+                with pytest.raises(RuntimeError):
+                    broadcast_shapes(*combo)
+                continue
+            assert broadcast_shapes(*combo) == want
+            if r:
+                assert _batch_shape(list(combo)) == want
