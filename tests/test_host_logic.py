@@ -256,3 +256,62 @@ def test_broadcast_shapes_matches_torch():
             assert broadcast_shapes(*combo) == want
             if r:
                 assert _batch_shape(list(combo)) == want
+
+
+class _RecordingLib:
+    """Stands in for the shared library so that the Python call path around the C ABI can be
+    exercised without a GPU: records the arguments of every entry point, computes nothing."""
+
+    def __init__(self, param_floats=0):
+        self.calls = []
+        self.param_floats = param_floats  # snapshot taken DURING the call: the buffer is freed after
+        self.params = None
+
+    def __getattr__(self, name):
+        def fn(*args):
+            import ctypes
+
+            self.calls.append((name, args))
+            if name.startswith("lynx_track_particles_fwd") and self.param_floats:
+                self.params = list((ctypes.c_float * self.param_floats).from_address(args[1]))
+            if name == "lynx_program_num_stages":
+                return 1
+            if name.endswith("workspace_bytes"):
+                return 256
+            return 0
+
+        return fn
+
+
+def test_track_call_path_arguments_without_gpu(monkeypatch):
+    """Segment.track up to the C-ABI call, with the library replaced by a recorder: the
+    packed parameter buffer, the batch size, the leading dimension and the particle count
+    that reach ``lynx_track_particles_fwd`` are the ones the lattice and the beam define."""
+    from lynx_b200 import program, segment
+
+    fake = _RecordingLib()
+    monkeypatch.setattr(L, "lib", lambda: fake)
+    monkeypatch.setattr(L, "current_stream", lambda: 0)
+    monkeypatch.setattr(segment, "_require_cuda", lambda d: None)
+    monkeypatch.setattr(torch.cuda, "current_device", lambda: 0)
+    monkeypatch.setattr(program.Program, "_cache", {})
+
+    seg = F.build_segment(F.ares_ea(k1=(5.0, -5.0, 5.0), vkick=1e-3, hkick=-2e-3))
+    seg.AREAMQZM2.k1 = torch.linspace(-3.0, 3.0, 6).reshape(2, 3)
+    n, ld = 1001, 1004
+    beam = lx.ParticleBeam.from_soa(torch.zeros(1, 6, ld), n, torch.tensor([1e8]), torch.ones(n))
+    enc = encode(seg.elements, (1,))
+    enc.batch_shape = (2, 3)
+    off, stride, shared, varying, total = layout(enc)
+    fake.param_floats = total
+    out = seg.track(beam)
+    assert out.num_particles == n and tuple(out.soa.shape) == (2, 3, 6, ld)
+
+    name, a = [c for c in fake.calls if c[0].startswith("lynx_track_particles_fwd")][-1]
+    B, beam_stride, a_ld, a_n = a[2], a[4], a[5], a[6]
+    assert (B, beam_stride, a_ld, a_n) == (6, 0, ld, n)  # one shared beam, six settings
+    want = pack_params(enc, "cpu")
+    assert fake.params == want.tolist()
+    assert len(varying) == 1 and stride[varying[0]] == 1
+    k = off[varying[0]]
+    assert want[k:k + 6].tolist() == seg.AREAMQZM2.k1.reshape(-1).tolist()
