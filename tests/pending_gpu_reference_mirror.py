@@ -1,0 +1,232 @@
+"""The reference's own tracking tests, restated one to one against ``lynx_b200``.
+
+NOT collected by default (the file name does not match ``test_*.py``): it was written after
+this round's GPU budget was spent and has not run on a GPU yet.  First GPU call of the next
+round:  python -m pytest tests/pending_gpu_reference_mirror.py -q -m gpu  -- then rename it
+to ``test_gpu_reference_mirror.py``.  Where the reference reads an ASTRA file
+(``from_astra``, file parsers are out of scope) a ``from_parameters`` beam stands in.
+"""
+
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import lynx_b200 as lx  # noqa: E402
+
+
+def T(*v):
+    return torch.tensor(list(v), dtype=torch.float32)
+
+
+# ------------------------------------------------------------------ tests/test_dipole.py
+def test_dipole_off():
+    """tests/test_dipole.py:6-22."""
+    dipole = lx.Dipole(length=T(1.0), angle=T(0.0))
+    drift = lx.Drift(length=T(1.0))
+    incoming = lx.ParticleBeam.from_parameters(sigma_xp=T(2e-7), sigma_yp=T(2e-7))
+    off = dipole(incoming)
+    ref = drift(incoming)
+    dipole.angle = T(1.0)
+    on = dipole(incoming)
+    assert torch.allclose(off.sigma_x, ref.sigma_x)
+    assert not torch.allclose(on.sigma_x, ref.sigma_x)
+
+
+def test_dipole_batched_execution():
+    """tests/test_dipole.py:25-44."""
+    batch_shape = (3,)
+    incoming = lx.ParticleBeam.from_parameters(num_particles=1_000_000, energy=T(1e9),
+                                               mu_x=T(1e-5)).broadcast(batch_shape)
+    segment = lx.Segment([
+        lx.Dipole(length=T(0.5, 0.5, 0.5), angle=T(0.1, 0.2, 0.1)),
+        lx.Drift(length=T(0.5)).broadcast(batch_shape),
+    ])
+    outgoing = segment(incoming)
+    assert torch.allclose(outgoing.particles[0], outgoing.particles[2])
+    assert not torch.allclose(outgoing.particles[0], outgoing.particles[1])
+
+
+# ------------------------------------------------------------------ tests/test_quadrupole.py
+def test_quadrupole_off():
+    """tests/test_quadrupole.py:6-22."""
+    quadrupole = lx.Quadrupole(length=T(1.0), k1=T(0.0))
+    drift = lx.Drift(length=T(1.0))
+    incoming = lx.ParameterBeam.from_parameters(sigma_xp=T(2e-7), sigma_yp=T(2e-7))
+    off = quadrupole(incoming)
+    ref = drift(incoming)
+    quadrupole.k1 = T(1.0)
+    on = quadrupole(incoming)
+    assert torch.allclose(off.sigma_x, ref.sigma_x)
+    assert not torch.allclose(on.sigma_x, ref.sigma_x)
+
+
+def test_quadrupole_with_misalignments_batched():
+    """tests/test_quadrupole.py:25-45."""
+    with_mis = lx.Quadrupole(length=T(1.0), k1=T(1.0), misalignment=torch.tensor([[0.1, 0.1]]))
+    without = lx.Quadrupole(length=T(1.0), k1=T(1.0))
+    incoming = lx.ParameterBeam.from_parameters(sigma_xp=T(2e-7), sigma_yp=T(2e-7))
+    assert not torch.allclose(with_mis(incoming).mu_x, without(incoming).mu_x)
+
+
+def test_quadrupole_with_misalignments_multiple_batch_dimension():
+    """tests/test_quadrupole.py:48-75."""
+    batch_shape = (4, 3)
+    with_mis = lx.Quadrupole(length=T(1.0), k1=T(1.0),
+                             misalignment=torch.tensor([[0.1, 0.1]])).broadcast(batch_shape)
+    without = lx.Quadrupole(length=T(1.0), k1=T(1.0)).broadcast(batch_shape)
+    incoming = lx.ParameterBeam.from_parameters(sigma_xp=T(2e-7),
+                                                sigma_yp=T(2e-7)).broadcast(batch_shape)
+    a, b = with_mis(incoming), without(incoming)
+    assert not torch.allclose(a.mu_x, b.mu_x)
+    assert tuple(a.mu_x.shape) == batch_shape
+
+
+def test_tilted_quadrupole_batch():
+    """tests/test_quadrupole.py:78-99: a quadrupole turned by pi/4 and by 5pi/4 is the same
+    magnet, one turned by pi/2 is not."""
+    batch_shape = (3,)
+    incoming = lx.ParticleBeam.from_parameters(num_particles=1_000_000, energy=T(1e9),
+                                               mu_x=T(1e-5)).broadcast(batch_shape)
+    segment = lx.Segment([
+        lx.Quadrupole(length=T(0.5, 0.5, 0.5), k1=T(1.0, 1.0, 1.0),
+                      tilt=T(math.pi / 4, math.pi / 2, math.pi * 5 / 4)),
+        lx.Drift(length=T(0.5)).broadcast(batch_shape),
+    ])
+    outgoing = segment(incoming)
+    assert torch.allclose(outgoing.particles[0], outgoing.particles[2], atol=1e-10, rtol=1e-4)
+    assert not torch.allclose(outgoing.particles[0], outgoing.particles[1])
+
+
+def test_tilted_quadrupole_multiple_batch_dimension():
+    """tests/test_quadrupole.py:102-120."""
+    batch_shape = (3, 2)
+    incoming = lx.ParticleBeam.from_parameters(num_particles=10_000, energy=T(1e9),
+                                               mu_x=T(1e-5)).broadcast(batch_shape)
+    segment = lx.Segment([
+        lx.Quadrupole(length=T(0.5), k1=T(1.0), tilt=T(math.pi / 4)),
+        lx.Drift(length=T(0.5)),
+    ]).broadcast(batch_shape)
+    outgoing = segment(incoming)
+    assert torch.allclose(outgoing.particles[0, 0], outgoing.particles[0, 1])
+
+
+# ------------------------------------------------------------------ tests/test_drift.py
+def test_diverging_parameter_beam():
+    """tests/test_drift.py:7-20."""
+    drift = lx.Drift(length=T(1.0))
+    incoming = lx.ParameterBeam.from_parameters(sigma_xp=T(2e-7), sigma_yp=T(2e-7))
+    outgoing = drift.track(incoming)
+    assert bool((outgoing.sigma_x > incoming.sigma_x).all())
+    assert bool((outgoing.sigma_y > incoming.sigma_y).all())
+    assert torch.allclose(torch.as_tensor(outgoing.total_charge).cpu(),
+                          torch.as_tensor(incoming.total_charge).cpu())
+
+
+def test_diverging_particle_beam():
+    """tests/test_drift.py:23-36."""
+    drift = lx.Drift(length=T(1.0))
+    incoming = lx.ParticleBeam.from_parameters(num_particles=1_000, sigma_xp=T(2e-7),
+                                               sigma_yp=T(2e-7))
+    outgoing = drift.track(incoming)
+    assert bool((outgoing.sigma_x > incoming.sigma_x).all())
+    assert bool((outgoing.sigma_y > incoming.sigma_y).all())
+    assert torch.allclose(outgoing.particle_charges.cpu(), incoming.particle_charges.cpu())
+
+
+# ------------------------------------------------------------------ tests/test_bpm.py
+@pytest.mark.parametrize("is_bpm_active", [True, False])
+@pytest.mark.parametrize("beam_class", [lx.ParticleBeam, lx.ParameterBeam])
+def test_no_tracking_error(is_bpm_active, beam_class):
+    """tests/test_bpm.py:7-22."""
+    segment = lx.Segment(elements=[lx.Drift(length=T(1.0)), lx.BPM(name="my_bpm"),
+                                   lx.Drift(length=T(1.0))])
+    beam = beam_class.from_parameters(mu_x=T(1e-4), mu_y=T(-2e-4))
+    segment.my_bpm.is_active = is_bpm_active
+    _ = segment.track(beam)
+    if is_bpm_active:
+        reading = segment.my_bpm.reading.reshape(-1).cpu()
+        assert torch.allclose(reading, T(1e-4, -2e-4), atol=2e-6 if beam_class is lx.ParticleBeam else 1e-9)
+
+
+# ------------------------------------------------ tests/test_tracking_lengthless_elements.py
+def test_tracking_marker_only():
+    """tests/test_tracking_lengthless_elements.py:9-14."""
+    beam_in = lx.ParticleBeam.from_parameters(num_particles=100)
+    beam_out = lx.Segment([lx.Marker(name="start")]).track(beam_in)
+    assert torch.allclose(beam_out.particles, beam_in.particles)
+
+
+def test_tracking_lengthless_elements():
+    """tests/test_tracking_lengthless_elements.py:18-28."""
+    beam_in = lx.ParticleBeam.from_parameters(num_particles=100)
+    segment = lx.Segment([
+        lx.Cavity(length=T(0.1), voltage=T(1e6), name="C2"),
+        lx.Marker(name="start"),
+        lx.Cavity(length=T(0.1), voltage=T(1e6), name="C1"),
+    ])
+    out = segment.track(beam_in)
+    assert bool(torch.isfinite(out.particles).all())
+
+
+# ------------------------------------------------------------------ cavities in a batch
+def _k26(voltage):
+    return lx.Cavity(length=T(3.0441, 3.0441, 3.0441), voltage=T(*voltage),
+                     phase=T(48198468.0, 48198468.0, 48198468.0),
+                     frequency=T(2.8560e09, 2.8560e09, 2.8560e09), name="k26_2a")
+
+
+def test_assert_ei_greater_zero():
+    """tests/test_cavity.py:6-33: a batched cavity must not trip over a tensor-valued assert."""
+    beam = lx.ParticleBeam.from_parameters(num_particles=100_000, sigma_x=T(1e-5)).broadcast((3,))
+    out = _k26((48198468.0, 48198468.0, 48198468.0)).track(beam)
+    assert tuple(out.particles.shape) == (3, 100_000, 7)
+
+
+def test_cavity_with_zero_and_non_zero_voltage():
+    """tests/test_vectorized.py:423-439; the V = 0 settings take the drift map (DESIGN.md 1.4,
+    quirk B6) and therefore agree with each other and stay finite."""
+    beam = lx.ParticleBeam.from_parameters(num_particles=100_000, sigma_x=T(1e-5)).broadcast((3,))
+    out = _k26((0.0, 48198468.0, 0.0)).track(beam)
+    p = out.particles
+    assert bool(torch.isfinite(p[0]).all()) and torch.equal(p[0], p[2])
+    assert not torch.allclose(p[0], p[1])
+
+
+# ------------------------------------------------------------------ tests/test_screen.py
+@pytest.mark.parametrize("beam_class", [lx.ParticleBeam, lx.ParameterBeam])
+def test_reading_shows_beam(beam_class):
+    """tests/test_screen.py:10-68."""
+    segment = lx.Segment(elements=[
+        lx.Drift(length=T(1.0)),
+        lx.Screen(resolution=torch.tensor((100, 100)), pixel_size=torch.tensor((1e-5, 1e-5)),
+                  is_active=True, name="my_screen"),
+    ])
+    beam = beam_class.from_parameters(sigma_x=T(1e-4), sigma_y=T(5e-5))
+    # before tracking the reading has the screen's own batch shape: () for the default
+    # misalignment of shape (2,) (screen.py:71-76,164-170; the reference test's (1, 100, 100)
+    # does not follow from the reference code)
+    reading = segment.my_screen.reading
+    assert isinstance(reading, torch.Tensor) and tuple(reading.shape[-2:]) == (100, 100)
+    assert bool((reading == 0).all())
+    _ = segment.track(beam)
+    reading = segment.my_screen.reading
+    assert tuple(reading.shape) == (1, 100, 100)
+    assert bool((reading >= 0).all()) and bool((reading > 0).any())
+
+
+def test_reading_shows_beam_ares():
+    """tests/test_screen.py:71-101 (ARES EA from the built-in fixture instead of Ocelot)."""
+    from lynx_b200 import fixtures as F
+
+    segment = F.build_segment(F.ares_ea(screen_active=True))
+    scr = segment.AREABSCR1
+    assert tuple(scr.reading.shape) == (1, 2040, 2448) and bool((scr.reading == 0).all())
+    beam = lx.ParticleBeam.from_parameters(num_particles=100_000, sigma_x=T(1.75e-4),
+                                           sigma_y=T(1.75e-4), energy=T(1.0732e8))
+    _ = segment.track(beam)
+    reading = scr.reading
+    assert tuple(reading.shape) == (1, 2040, 2448)
+    assert bool((reading >= 0).all()) and bool((reading > 0).any())
