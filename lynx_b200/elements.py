@@ -332,6 +332,12 @@ class CustomTransferMap(Element):
     def transfer_map(self, energy):
         return self._transfer_map
 
+    @property
+    def defining_features(self):
+        # custom_transfer_map.py:108-109 lists "transfer_map" only, which loses the length in a
+        # saved lattice; "length" is a constructor argument there too, so files stay loadable
+        return ["length", "transfer_map"]
+
     def broadcast(self, shape):
         tm = self._transfer_map
         one = tm.shape[:-2] in ((), (1,))
@@ -496,6 +502,10 @@ class Screen(Element):
     @property
     def is_skippable(self) -> bool:
         return not self.is_active
+
+    @property
+    def defining_features(self):  # screen.py:253-261
+        return ["resolution", "pixel_size", "binning", "misalignment", "is_active"]
 
     @property
     def effective_resolution(self):

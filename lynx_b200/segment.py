@@ -281,6 +281,20 @@ class Segment(Element):
                 break
         return self.__class__(sub)
 
+    @classmethod
+    def from_lattice_json(cls, filepath: str) -> "Segment":
+        """segment.py:220-228: load a LatticeJSON file (``lynx_b200/latticejson.py``)."""
+        from . import latticejson
+
+        return latticejson.load(filepath)
+
+    def to_lattice_json(self, filepath: str, title: Optional[str] = None,
+                        info: str = "This is a placeholder lattice description") -> None:
+        """segment.py:230-247."""
+        from . import latticejson
+
+        latticejson.save(self, filepath, title, info)
+
     def flattened(self) -> "Segment":
         return Segment(_flatten(self.elements), name=self.name)
 
