@@ -200,6 +200,17 @@ class ParticleBeam(Beam):
         return cls.from_soa(soa, N, energy.to(device), charges)
 
     @classmethod
+    def from_astra(cls, path: str, device=None, dtype=torch.float32) -> "ParticleBeam":
+        """particle_beam.py:563-578: ASTRA distribution file (``lynx_b200/astra.py``)."""
+        from .astra import read_astra_beam
+
+        coords, energy, charges = read_astra_beam(path)
+        aos = torch.ones((1, coords.shape[0], 7), dtype=torch.float32)
+        aos[0, :, :6] = torch.from_numpy(coords).to(torch.float32)
+        return cls(aos, torch.tensor([energy], dtype=torch.float32),
+                   torch.from_numpy(charges).to(torch.float32).unsqueeze(0), device=device)
+
+    @classmethod
     def from_twiss(cls, num_particles=None, beta_x=None, alpha_x=None, emittance_x=None,
                    beta_y=None, alpha_y=None, emittance_y=None, energy=None, sigma_s=None,
                    sigma_p=None, cor_s=None, total_charge=None, device=None,
@@ -484,6 +495,22 @@ class ParameterBeam(Beam):
         for n, (i, j) in enumerate(((0, 1), (2, 3), (4, 5))):
             cov[..., i, j] = cov[..., j, i] = cor[n].float()
         return cls(mu, cov, d(energy, 1e8).float(), d(total_charge, 0.0).float(), device=device)
+
+    @classmethod
+    def from_astra(cls, path: str, device=None, dtype=torch.float32) -> "ParameterBeam":
+        """parameter_beam.py:255-276: mean and (unbiased, ``np.cov``) covariance of the
+        ASTRA distribution, total charge = sum of the macro-particle charges."""
+        import numpy as np
+
+        from .astra import read_astra_beam
+
+        coords, energy, charges = read_astra_beam(path)
+        mu = torch.ones(1, 7, dtype=torch.float32)
+        mu[0, :6] = torch.from_numpy(coords.mean(axis=0)).to(torch.float32)
+        cov = torch.zeros(1, 7, 7, dtype=torch.float32)
+        cov[0, :6, :6] = torch.from_numpy(np.cov(coords.T)).to(torch.float32)
+        return cls(mu, cov, torch.tensor([energy], dtype=torch.float32),
+                   torch.tensor([charges.sum()], dtype=torch.float32), device=device)
 
     @classmethod
     def from_twiss(cls, beta_x=None, alpha_x=None, emittance_x=None, beta_y=None, alpha_y=None,

@@ -230,3 +230,37 @@ def test_reading_shows_beam_ares():
     reading = scr.reading
     assert tuple(reading.shape) == (1, 2040, 2448)
     assert bool((reading >= 0).all()) and bool((reading > 0).any())
+
+
+# ------------------------------------------------------------------ tests/test_astra_import.py
+def test_particle_beam_from_astra(tmp_path):
+    """tests/test_astra_import.py:27-44 on a synthetic file (the reference's sample is not in
+    its checkout): the device beam holds the reader's coordinates, a ones column, the charges."""
+    import numpy as np
+
+    from lynx_b200.astra import read_astra_beam
+
+    rng = np.random.default_rng(5)
+    n = 1001
+    rows = np.zeros((n, 10))
+    rows[:, 0:2] = rng.normal(0, 1.7e-4, (n, 2))
+    rows[:, 2] = rng.normal(0, 8e-6, n)
+    rows[:, 3:5] = rng.normal(0, 4e2, (n, 2))
+    rows[:, 5] = rng.normal(0, 2e5, n)
+    rows[0, :6] = (0, 0, 2.0, 0, 0, 1.0732e8)
+    rows[:, 7] = -5e-9
+    rows[:, 8], rows[:, 9] = 1, 5
+    rows[17, 9] = -3  # one lost particle
+    path = str(tmp_path / "beam.ini")
+    np.savetxt(path, rows, fmt="%.12e")
+
+    coords, energy, charges = read_astra_beam(path)
+    beam = lx.ParticleBeam.from_astra(path)
+    assert beam.num_particles == n - 1
+    got = beam.particles.cpu().numpy()
+    assert got.shape == (1, n - 1, 7)
+    np.testing.assert_array_equal(got[0, :, :6], coords.astype(np.float32))
+    assert (got[0, :, 6] == 1).all()
+    np.testing.assert_allclose(beam.energy.cpu().numpy(), [energy], rtol=1e-7)
+    np.testing.assert_allclose(beam.particle_charges.cpu().numpy()[0], charges, rtol=1e-6)
+    np.testing.assert_allclose(beam.sigma_x.cpu().numpy(), [coords[:, 0].std(ddof=1)], rtol=1e-4)
