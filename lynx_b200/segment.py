@@ -296,6 +296,13 @@ class Segment(Element):
         latticejson.save(self, filepath, title, info)
 
     @classmethod
+    def from_bmad(cls, bmad_lattice_file_path: str, environment_variables=None) -> "Segment":
+        """segment.py:281-299: Bmad lattice file (``lynx_b200/bmad.py``)."""
+        from . import bmad
+
+        return bmad.read_bmad_lattice(bmad_lattice_file_path, environment_variables)
+
+    @classmethod
     def from_nx_tables(cls, filepath) -> "Segment":
         """segment.py:301-313: ARES NX-tables component list (``lynx_b200/nxtables.py``)."""
         from . import nxtables
