@@ -276,7 +276,7 @@ class Solenoid(Element):
         self.k = _t(k, self.length)
         self.misalignment = (
             _t(misalignment) if misalignment is not None
-            else torch.zeros((*self.length.shape, 2))
+            else torch.zeros((*self.length.shape[:-1], 2))  # solenoid.py:55-59, as written
         )
         super().__init__(name)
 

@@ -296,6 +296,14 @@ class Segment(Element):
         latticejson.save(self, filepath, title, info)
 
     @classmethod
+    def from_ocelot(cls, cell, name: Optional[str] = None, warnings: bool = True, device=None,
+                    dtype=torch.float32, **kwargs) -> "Segment":
+        """segment.py:248-279: list of Ocelot elements (``lynx_b200/ocelot.py``)."""
+        from . import ocelot
+
+        return cls([ocelot.convert_element(e, warnings=warnings) for e in cell], name=name, **kwargs)
+
+    @classmethod
     def from_bmad(cls, bmad_lattice_file_path: str, environment_variables=None) -> "Segment":
         """segment.py:281-299: Bmad lattice file (``lynx_b200/bmad.py``)."""
         from . import bmad
