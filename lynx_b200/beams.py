@@ -200,6 +200,19 @@ class ParticleBeam(Beam):
         return cls.from_soa(soa, N, energy.to(device), charges)
 
     @classmethod
+    def from_ocelot(cls, parray, device=None, dtype=torch.float32) -> "ParticleBeam":
+        """particle_beam.py:545-561: an Ocelot ``ParticleArray`` (``rparticles`` (6, N), ``E`` in
+        GeV, ``q_array``); duck-typed, Ocelot is not imported."""
+        import numpy as np
+
+        coords = np.asarray(parray.rparticles, dtype=np.float64)
+        aos = torch.ones((1, coords.shape[1], 7), dtype=torch.float32)
+        aos[0, :, :6] = torch.from_numpy(coords.T.copy()).to(torch.float32)
+        charges = torch.as_tensor(np.asarray(parray.q_array), dtype=torch.float32).unsqueeze(0)
+        return cls(aos, torch.tensor([1e9 * float(parray.E)], dtype=torch.float32), charges,
+                   device=device)
+
+    @classmethod
     def from_astra(cls, path: str, device=None, dtype=torch.float32) -> "ParticleBeam":
         """particle_beam.py:563-578: ASTRA distribution file (``lynx_b200/astra.py``)."""
         from .astra import read_astra_beam
@@ -495,6 +508,19 @@ class ParameterBeam(Beam):
         for n, (i, j) in enumerate(((0, 1), (2, 3), (4, 5))):
             cov[..., i, j] = cov[..., j, i] = cor[n].float()
         return cls(mu, cov, d(energy, 1e8).float(), d(total_charge, 0.0).float(), device=device)
+
+    @classmethod
+    def from_ocelot(cls, parray, device=None, dtype=torch.float32) -> "ParameterBeam":
+        """parameter_beam.py:234-253: mean and ``np.cov`` of an Ocelot ``ParticleArray``."""
+        import numpy as np
+
+        coords = np.asarray(parray.rparticles, dtype=np.float64)
+        mu = torch.ones(1, 7, dtype=torch.float32)
+        mu[0, :6] = torch.from_numpy(coords.mean(axis=1)).to(torch.float32)
+        cov = torch.zeros(1, 7, 7, dtype=torch.float32)
+        cov[0, :6, :6] = torch.from_numpy(np.cov(coords)).to(torch.float32)
+        return cls(mu, cov, torch.tensor([1e9 * float(parray.E)], dtype=torch.float32),
+                   torch.tensor([float(np.sum(parray.q_array))], dtype=torch.float32), device=device)
 
     @classmethod
     def from_astra(cls, path: str, device=None, dtype=torch.float32) -> "ParameterBeam":

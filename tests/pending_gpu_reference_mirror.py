@@ -264,3 +264,20 @@ def test_particle_beam_from_astra(tmp_path):
     np.testing.assert_allclose(beam.energy.cpu().numpy(), [energy], rtol=1e-7)
     np.testing.assert_allclose(beam.particle_charges.cpu().numpy()[0], charges, rtol=1e-6)
     np.testing.assert_allclose(beam.sigma_x.cpu().numpy(), [coords[:, 0].std(ddof=1)], rtol=1e-4)
+
+
+def test_particle_beam_from_ocelot():
+    """particle_beam.py:545-561 with a stand-in ``ParticleArray``."""
+    import numpy as np
+
+    class ParticleArray:
+        rparticles = np.random.default_rng(3).normal(0, 1e-4, (6, 1003))
+        E = 0.1073
+        q_array = np.full(1003, 5e-18)
+
+    beam = lx.ParticleBeam.from_ocelot(ParticleArray)
+    got = beam.particles.cpu().numpy()
+    assert got.shape == (1, 1003, 7) and (got[0, :, 6] == 1).all()
+    np.testing.assert_array_equal(got[0, :, :6], ParticleArray.rparticles.T.astype(np.float32))
+    np.testing.assert_allclose(beam.energy.cpu().numpy(), [1.073e8], rtol=1e-7)
+    np.testing.assert_allclose(beam.particle_charges.cpu().numpy()[0], ParticleArray.q_array, rtol=1e-6)

@@ -120,3 +120,28 @@ def test_ares_cell_converts_to_the_reference_lattice_json(monkeypatch):
             # the reference's code today (screen.py:71-76) and this package use (2,)
             assert feats.pop("misalignment") == [g_feats.pop("misalignment")], key
         assert g_feats == feats, (key, g_feats, feats)
+
+
+class _ParticleArray:
+    """Ocelot's ``ParticleArray`` surface: ``rparticles`` (6, N), ``E`` [GeV], ``q_array`` [C]."""
+
+    def __init__(self, n, seed=3):
+        import numpy as np
+
+        rng = np.random.default_rng(seed)
+        self.rparticles = rng.normal(0, 1e-4, (6, n)) * np.array([[1.0], [0.02], [1.0], [0.02], [0.05], [10.0]])
+        self.E = 0.1073  # GeV
+        self.q_array = np.full(n, 5e-18)
+
+
+def test_parameter_beam_from_ocelot():
+    """parameter_beam.py:234-253."""
+    import numpy as np
+
+    parray = _ParticleArray(5000)
+    beam = lx.ParameterBeam.from_ocelot(parray, device="cpu")
+    np.testing.assert_allclose(beam._mu[0, :6].numpy(), parray.rparticles.mean(axis=1), rtol=1e-6, atol=1e-12)
+    np.testing.assert_allclose(beam._cov[0, :6, :6].numpy(), np.cov(parray.rparticles), rtol=1e-6, atol=1e-20)
+    assert float(beam._mu[0, 6]) == 1.0 and float(beam._cov[0, 6, 6]) == 0.0
+    np.testing.assert_allclose(beam.energy.numpy(), [1.073e8], rtol=1e-7)
+    np.testing.assert_allclose(torch.as_tensor(beam.total_charge).numpy(), [5000 * 5e-18], rtol=1e-6)
