@@ -1,0 +1,185 @@
+"""Golden vectors computed BY THE REFERENCE ITSELF (jank324/lynx in /root/reference), run on
+torch through tests/golden/reference_shim.py (read that file's header for what the shim is).
+
+    python tests/golden/make_reference_golden.py      # writes tests/golden/reference_*.npz
+
+Inputs are deterministic (numpy seeds below) and stored next to the outputs, so the tests need
+neither the reference nor this script.  Everything is fp32, as the reference computes.
+"""
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+for p in (ROOT, os.path.join(ROOT, "tests"), HERE):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import reference_shim  # noqa: E402
+from lynx_b200 import fixtures as F  # noqa: E402
+
+lynx = reference_shim.install()
+SMALL_SCREEN = {"resolution": (64, 48), "pixel_size": (4e-5, 4e-5), "binning": 1}
+
+
+def t(v):
+    return torch.tensor([v], dtype=torch.float32)
+
+
+def build(spec):
+    """Reference ``Segment`` from a lynx_b200.fixtures spec, through the reference's own
+    constructors."""
+    out = []
+    for kind, name, p in spec:
+        if kind == "marker":
+            el = lynx.Marker(name=name)
+        elif kind == "drift":
+            el = lynx.Drift(length=t(p["length"]), name=name)
+        elif kind == "quadrupole":
+            kw = {}
+            if "misalignment" in p:
+                kw["misalignment"] = torch.tensor([p["misalignment"]], dtype=torch.float32)
+            if "tilt" in p:
+                kw["tilt"] = t(p["tilt"])
+            el = lynx.Quadrupole(length=t(p["length"]), k1=t(p.get("k1", 0.0)), name=name, **kw)
+        elif kind in ("hcor", "vcor"):
+            cls = lynx.HorizontalCorrector if kind == "hcor" else lynx.VerticalCorrector
+            el = cls(length=t(p["length"]), angle=t(p.get("angle", 0.0)), name=name)
+        elif kind in ("dipole", "rbend"):
+            cls = lynx.Dipole if kind == "dipole" else lynx.RBend
+            el = cls(name=name, **{k: t(v) for k, v in p.items()})
+        elif kind == "cavity":
+            el = lynx.Cavity(length=t(p["length"]), voltage=t(p["voltage"]), phase=t(p["phase"]),
+                             frequency=t(p["frequency"]), name=name)
+        elif kind == "solenoid":
+            el = lynx.Solenoid(length=t(p["length"]), k=t(p["k"]), name=name)
+        elif kind == "undulator":
+            el = lynx.Undulator(length=t(p["length"]), name=name)
+        elif kind == "bpm":
+            el = lynx.BPM(is_active=p.get("is_active", False), name=name)
+        elif kind == "screen":
+            el = lynx.Screen(resolution=torch.tensor(p["resolution"]),
+                             pixel_size=torch.tensor(p["pixel_size"], dtype=torch.float32),
+                             binning=torch.tensor(p.get("binning", 1)),
+                             misalignment=torch.tensor([p.get("misalignment", (0.0, 0.0))],
+                                                       dtype=torch.float32),
+                             is_active=p.get("is_active", False), name=name)
+        else:
+            raise ValueError(kind)
+        out.append(el)
+    return lynx.Segment(out)
+
+
+def seeded_particles(n, seed):
+    """(1, n, 7) fp32 particles with the moments of the ASTRA beam the reference's tests use."""
+    rng = np.random.default_rng(seed)
+    a = np.ones((1, n, 7), dtype=np.float32)
+    a[0, :, :6] = (rng.standard_normal((n, 6)) * np.array(F.ASTRA_SIGMA) + np.array(F.ASTRA_MU)).astype(np.float32)
+    return torch.from_numpy(a)
+
+
+def element_maps():
+    """Every element's transfer_map at several energies / parameter sets (8a rows a1-a8)."""
+    E = torch.tensor([1.0732e8, 6.0e6, 1.0e9], dtype=torch.float32)
+    out = {"energy": E.numpy()}
+    cases = {
+        "drift": lambda e: lynx.Drift(length=t(0.7)).transfer_map(e),
+        "quadrupole": lambda e: lynx.Quadrupole(length=t(0.122), k1=t(7.3)).transfer_map(e),
+        "quadrupole_defocus": lambda e: lynx.Quadrupole(length=t(0.122), k1=t(-11.0)).transfer_map(e),
+        "quadrupole_tilt_mis": lambda e: lynx.Quadrupole(
+            length=t(0.2), k1=t(4.2), tilt=t(0.3),
+            misalignment=torch.tensor([[1e-3, -2e-3]])).transfer_map(e),
+        "hcor": lambda e: lynx.HorizontalCorrector(length=t(0.02), angle=t(1.5e-3)).transfer_map(e),
+        "vcor": lambda e: lynx.VerticalCorrector(length=t(0.02), angle=t(-2.5e-3)).transfer_map(e),
+        "dipole": lambda e: lynx.Dipole(length=t(0.5), angle=t(0.1), e1=t(0.05), e2=t(0.02),
+                                        fringe_integral=t(0.5), gap=t(0.03)).transfer_map(e),
+        "dipole_tilt": lambda e: lynx.Dipole(length=t(0.3), angle=t(-0.2), tilt=t(0.4),
+                                             fringe_integral=t(0.4), fringe_integral_exit=t(0.3),
+                                             gap=t(0.02)).transfer_map(e),
+        "rbend": lambda e: lynx.RBend(length=t(0.5), angle=t(0.1), fringe_integral=t(0.5),
+                                      gap=t(0.03)).transfer_map(e),
+        "solenoid": lambda e: lynx.Solenoid(length=t(0.5), k=t(0.3)).transfer_map(e),
+        "undulator": lambda e: lynx.Undulator(length=t(0.25)).transfer_map(e),
+        "cavity": lambda e: lynx.Cavity(length=t(1.0377), voltage=t(1.0e7), phase=t(30.0),
+                                        frequency=t(1.3e9)).transfer_map(e),
+        "cavity_decel": lambda e: lynx.Cavity(length=t(4.139), voltage=t(2.0e6), phase=t(160.0),
+                                              frequency=t(2.998e9)).transfer_map(e),
+    }
+    for name, fn in cases.items():
+        out[name] = np.stack([fn(e.reshape(1))[0].numpy() for e in E])
+    np.savez_compressed(os.path.join(HERE, "reference_element_maps.npz"), **out)
+    return out
+
+
+def ares_tracking():
+    """ARES EA (C6): merged map, particles, parameter beam, BPM-free screen reading."""
+    k1, vk, hk = (5.0, -5.0, 5.0), 1e-3, -2e-3
+    energy = t(F.ASTRA_ENERGY)
+    particles = seeded_particles(20001, seed=11)
+    out = {"k1": np.array(k1, np.float32), "vkick": np.float32(vk), "hkick": np.float32(hk),
+           "energy": energy.numpy(), "particles_in": particles.numpy()}
+    seg = build(F.ares_ea(k1=k1, vkick=vk, hkick=hk))
+    out["segment_map"] = seg.transfer_map(energy)[0].numpy()
+    beam = lynx.ParticleBeam(particles.clone(), energy.clone())
+    tracked = seg.track(beam)
+    out["particles_out"] = tracked.particles.numpy()
+    for name in ("mu_x", "mu_y", "sigma_x", "sigma_xp", "sigma_y", "sigma_yp", "sigma_s",
+                 "sigma_p", "sigma_xxp", "sigma_yyp"):
+        out["out_" + name] = getattr(tracked, name).numpy()
+    # parameter beam with the same first and second moments as the particle set
+    pb = lynx.ParameterBeam.from_parameters(
+        mu_x=t(F.ASTRA_MU[0]), mu_xp=t(F.ASTRA_MU[1]), mu_y=t(F.ASTRA_MU[2]), mu_yp=t(F.ASTRA_MU[3]),
+        sigma_x=t(F.ASTRA_SIGMA[0]), sigma_xp=t(F.ASTRA_SIGMA[1]), sigma_y=t(F.ASTRA_SIGMA[2]),
+        sigma_yp=t(F.ASTRA_SIGMA[3]), sigma_s=t(F.ASTRA_SIGMA[4]), sigma_p=t(F.ASTRA_SIGMA[5]),
+        energy=energy.clone())
+    out["pb_mu_in"], out["pb_cov_in"] = pb._mu.numpy(), pb._cov.numpy()
+    pb_out = seg.track(pb)
+    out["pb_mu_out"], out["pb_cov_out"] = pb_out._mu.numpy(), pb_out._cov.numpy()
+    # the screen, with a coarse camera so that the image stays small
+    seg = build(F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True, screen=SMALL_SCREEN))
+    empty = seg.track(lynx.ParticleBeam(particles.clone(), energy.clone()))
+    assert empty is lynx.ParticleBeam.empty or empty is lynx.particles.Beam.empty
+    out["screen_reading"] = seg.AREABSCR1.reading.numpy()
+    out["screen_resolution"] = np.array(SMALL_SCREEN["resolution"])
+    out["screen_pixel_size"] = np.array(SMALL_SCREEN["pixel_size"], np.float32)
+    np.savez_compressed(os.path.join(HERE, "reference_ares_ea.npz"), **out)
+    return out
+
+
+def cavity_line():
+    """Cavity + dipole + quadrupoles (config 4 lattice): the non-linear cavity pass."""
+    energy = t(6.0e6)
+    particles = seeded_particles(5001, seed=12)
+    seg = build(F.cavity_dipole_line(screen_active=False))
+    beam = lynx.ParticleBeam(particles.clone(), energy.clone())
+    tracked = seg.track(beam)
+    out = {"energy": energy.numpy(), "particles_in": particles.numpy(),
+           "particles_out": tracked.particles.numpy(), "energy_out": tracked.energy.numpy()}
+    np.savez_compressed(os.path.join(HERE, "reference_cavity_line.npz"), **out)
+    return out
+
+
+def bpm_line():
+    """SMATCH-like line with active BPMs: readings (bpm.py:48-58)."""
+    energy = t(F.ASTRA_ENERGY)
+    particles = seeded_particles(4001, seed=13)
+    seg = build(F.smatch(bpms_active=True, angles=(1e-3, -5e-4, 2e-4)))
+    tracked = seg.track(lynx.ParticleBeam(particles.clone(), energy.clone()))
+    out = {"energy": energy.numpy(), "particles_in": particles.numpy(),
+           "particles_out": tracked.particles.numpy()}
+    names = [e.name for e in seg.elements if isinstance(e, lynx.BPM)]
+    out["bpm_names"] = np.array(names)
+    out["bpm_readings"] = np.stack([getattr(seg, n).reading.numpy() for n in names])
+    np.savez_compressed(os.path.join(HERE, "reference_bpm_line.npz"), **out)
+    return out
+
+
+if __name__ == "__main__":
+    torch.manual_seed(0)
+    for fn in (element_maps, ares_tracking, cavity_line, bpm_line):
+        res = fn()
+        print(fn.__name__, {k: getattr(v, "shape", v) for k, v in res.items()})

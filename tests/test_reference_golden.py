@@ -1,0 +1,139 @@
+"""The oracle against vectors computed by THE REFERENCE ITSELF (tests/golden/reference_*.npz,
+written by tests/golden/make_reference_golden.py, which runs /root/reference on torch through
+tests/golden/reference_shim.py).  CPU only; needs neither the reference nor the script.
+
+This is what pins the oracle: in fp32 -- the reference's precision -- the
+restatement must reproduce the reference bit for bit wherever it follows the same operation
+order, and to a few ulp of the un-cancelled magnitude where DESIGN.md 1.4 / 1.5 say it does not.
+"""
+
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import oracle_elements
+from lynx_b200 import fixtures as F
+from oracle import lattice as O
+from oracle import element_map, screen_bin_edges, screen_reading_particles, segment_map
+from oracle.lattice import El
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+f32 = torch.float32
+
+
+def _load(name):
+    return np.load(os.path.join(GOLDEN, name))
+
+
+def t(v):
+    return torch.tensor([v], dtype=f32)
+
+
+def _el(kind, **p):
+    q = {k: (torch.tensor([v], dtype=f32) if k == "misalignment" else t(v)) for k, v in p.items()}
+    if kind in ("quadrupole", "solenoid") and "misalignment" not in q:
+        q["misalignment"] = torch.zeros(1, 2)
+    if kind == "quadrupole":
+        q.setdefault("tilt", t(0.0))
+    if kind in ("dipole", "rbend"):
+        for k in ("e1", "e2", "tilt", "fringe_integral", "gap"):
+            q.setdefault(k, t(0.0))
+        q.setdefault("fringe_integral_exit", q["fringe_integral"])
+    return El(kind, kind, q)
+
+
+ELEMENT_CASES = {
+    "drift": _el("drift", length=0.7),
+    "quadrupole": _el("quadrupole", length=0.122, k1=7.3),
+    "quadrupole_defocus": _el("quadrupole", length=0.122, k1=-11.0),
+    "quadrupole_tilt_mis": _el("quadrupole", length=0.2, k1=4.2, tilt=0.3, misalignment=(1e-3, -2e-3)),
+    "hcor": _el("hcor", length=0.02, angle=1.5e-3),
+    "vcor": _el("vcor", length=0.02, angle=-2.5e-3),
+    "dipole": _el("dipole", length=0.5, angle=0.1, e1=0.05, e2=0.02, fringe_integral=0.5, gap=0.03),
+    "dipole_tilt": _el("dipole", length=0.3, angle=-0.2, tilt=0.4, fringe_integral=0.4,
+                       fringe_integral_exit=0.3, gap=0.02),
+    "rbend": _el("rbend", length=0.5, angle=0.1, fringe_integral=0.5, gap=0.03),
+    "solenoid": _el("solenoid", length=0.5, k=0.3),
+    "undulator": _el("undulator", length=0.25),
+    "cavity": _el("cavity", length=1.0377, voltage=1.0e7, phase=30.0, frequency=1.3e9),
+    "cavity_decel": _el("cavity", length=4.139, voltage=2.0e6, phase=160.0, frequency=2.998e9),
+}
+
+
+@pytest.mark.parametrize("name", sorted(ELEMENT_CASES))
+def test_element_maps_are_the_reference_s(name):
+    """every element's ``transfer_map`` at three energies."""
+    g = _load("reference_element_maps.npz")
+    for i, energy in enumerate(g["energy"]):
+        got = element_map(ELEMENT_CASES[name], torch.tensor([energy], dtype=f32))[0].numpy()
+        np.testing.assert_array_equal(got, g[name][i], err_msg=f"{name} at {energy:g} eV")
+
+
+def _ares(g, dtype=f32, **kw):
+    k1, vk, hk = tuple(g["k1"].tolist()), float(g["vkick"]), float(g["hkick"])
+    return oracle_elements(F.ares_ea(k1=k1, vkick=vk, hkick=hk, **kw), dtype)
+
+
+def test_ares_ea_map_and_particles_bit_for_bit():
+    """a10 / a12 / a13: Segment.transfer_map and Segment.track of 20 001 particles."""
+    g = _load("reference_ares_ea.npz")
+    els, energy = _ares(g), torch.tensor(g["energy"], dtype=f32)
+    np.testing.assert_array_equal(segment_map(els, energy)[0].numpy(), g["segment_map"])
+    out = O.track(els, O.ParticleBeamO(torch.tensor(g["particles_in"]), energy))
+    np.testing.assert_array_equal(out.particles.numpy(), g["particles_out"])
+    moments = {"mu_x": out.mu(0), "mu_y": out.mu(2), "sigma_x": out.sigma(0), "sigma_xp": out.sigma(1),
+               "sigma_y": out.sigma(2), "sigma_yp": out.sigma(3), "sigma_s": out.sigma(4),
+               "sigma_p": out.sigma(5), "sigma_xxp": out.sigma_xxp, "sigma_yyp": out.sigma_yyp}
+    for name, got in moments.items():  # a17: the same torch reductions on the same bits
+        np.testing.assert_array_equal(got.numpy(), g["out_" + name], err_msg=name)
+
+
+def test_ares_ea_parameter_beam():
+    """a11: mu' = R mu, cov' = R cov R^T."""
+    g = _load("reference_ares_ea.npz")
+    els, energy = _ares(g), torch.tensor(g["energy"], dtype=f32)
+    beam = O.ParameterBeamO(torch.tensor(g["pb_mu_in"]), torch.tensor(g["pb_cov_in"]), energy)
+    out = O.track(els, beam)
+    np.testing.assert_array_equal(out.mu_.numpy(), g["pb_mu_out"])
+    np.testing.assert_array_equal(out.cov_.numpy(), g["pb_cov_out"])
+
+
+def test_ares_ea_screen_reading():
+    """a15 / a16: the 2-D histogram the reference's Screen.reading returns, every bin."""
+    g = _load("reference_ares_ea.npz")
+    screen = {"resolution": tuple(int(v) for v in g["screen_resolution"]),
+              "pixel_size": tuple(float(v) for v in g["screen_pixel_size"]), "binning": 1}
+    els = _ares(g, screen_active=True, screen=screen)
+    energy = torch.tensor(g["energy"], dtype=f32)
+    assert O.track(els, O.ParticleBeamO(torch.tensor(g["particles_in"]), energy)) is O.EMPTY
+    seen = [e for e in els if e.kind == "screen"][0].read_beam
+    ex, ey = screen_bin_edges(screen["resolution"], screen["pixel_size"], 1)
+    img = screen_reading_particles(seen.col(0), seen.col(2), ex, ey)  # (B, N) rows
+    want = g["screen_reading"]
+    assert tuple(want.shape[-2:]) == (48, 64) and want.sum() > 0
+    np.testing.assert_array_equal(np.asarray(img).reshape(want.shape), want)
+
+
+def test_cavity_dipole_line_particles():
+    """a8 / a9 / a7: the non-linear cavity pass, the dipole and the outgoing energy."""
+    g = _load("reference_cavity_line.npz")
+    els = oracle_elements(F.cavity_dipole_line(screen_active=False), f32)
+    energy = torch.tensor(g["energy"], dtype=f32)
+    out = O.track(els, O.ParticleBeamO(torch.tensor(g["particles_in"]), energy))
+    np.testing.assert_array_equal(out.energy.numpy(), g["energy_out"])
+    np.testing.assert_array_equal(out.particles.numpy(), g["particles_out"])
+
+
+def test_bpm_readings():
+    """a14: BPM.reading = (mu_x, mu_y) of the beam at the BPM."""
+    g = _load("reference_bpm_line.npz")
+    els = oracle_elements(F.smatch(bpms_active=True, angles=(1e-3, -5e-4, 2e-4)), f32)
+    energy = torch.tensor(g["energy"], dtype=f32)
+    out = O.track(els, O.ParticleBeamO(torch.tensor(g["particles_in"]), energy))
+    np.testing.assert_array_equal(out.particles.numpy(), g["particles_out"])
+    bpms = [e for e in els if e.kind == "bpm"]
+    assert [b.name for b in bpms] == list(g["bpm_names"])
+    for b, want in zip(bpms, g["bpm_readings"]):
+        np.testing.assert_allclose(np.asarray(b.reading).reshape(want.shape), want, rtol=2e-6, atol=1e-12)
