@@ -178,8 +178,55 @@ def bpm_line():
     return out
 
 
+def beam_ops():
+    """transformed_to (particle_beam.py:580-715), Aperture.track (aperture.py:69-109) and the
+    ASTRA reader (converters/astra.py:8-62)."""
+    import tempfile
+
+    energy = t(F.ASTRA_ENERGY)
+    particles = seeded_particles(3001, seed=14)
+    out = {"energy": energy.numpy(), "particles_in": particles.numpy()}
+    beam = lynx.ParticleBeam(particles.clone(), energy.clone(),
+                             particle_charges=torch.full((1, 3001), 1e-15))
+    target = dict(mu_x=t(1e-4), mu_y=t(-2e-4), mu_xp=t(1e-6), mu_yp=t(-3e-6), sigma_x=t(3e-4),
+                  sigma_y=t(1e-4), sigma_xp=t(5e-6), sigma_yp=t(2e-6), sigma_s=t(1e-5), sigma_p=t(1e-3))
+    moved = beam.transformed_to(**target)
+    out["transform_target"] = np.array([float(v) for v in target.values()], np.float32)
+    out["transform_target_names"] = np.array(list(target))
+    out["transformed"] = moved.particles.numpy()
+    for shape in ("rectangular", "elliptical"):
+        ap = lynx.Aperture(x_max=t(1.5e-4), y_max=t(2.0e-4), shape=shape, is_active=True)
+        kept = ap.track(lynx.ParticleBeam(particles.clone(), energy.clone(),
+                                          particle_charges=torch.full((1, 3001), 1e-15)))
+        out[f"aperture_{shape}_kept"] = kept.particles.numpy()
+        out[f"aperture_{shape}_lost"] = ap.lost_particles.numpy()
+    out["aperture_x_max"], out["aperture_y_max"] = np.float32(1.5e-4), np.float32(2.0e-4)
+    # ASTRA: a synthetic distribution file (the reference's sample is not in its checkout)
+    from lynx.converters.astra import from_astrabeam
+
+    rng = np.random.default_rng(15)
+    n = 2001
+    rows = np.zeros((n, 10))
+    rows[:, 0:2] = rng.normal(0, 1.7e-4, (n, 2))
+    rows[:, 2] = rng.normal(0, 8e-6, n)
+    rows[:, 3:5] = rng.normal(0, 4e2, (n, 2))
+    rows[:, 5] = rng.normal(0, 2e5, n)
+    rows[0, :6] = (0, 0, 2.0, 0, 0, 1.0732e8)
+    rows[:, 7], rows[:, 8], rows[:, 9] = -2.5e-7, 1, 5
+    rows[[17, 900], 9] = (-3, -1)  # two lost particles
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "beam.ini")
+        np.savetxt(path, rows, fmt="%.12e")
+        rows = np.loadtxt(path)  # what the file holds, to the printed precision
+        coords, e_ref, charges = from_astrabeam(path)
+    out["astra_rows"], out["astra_coords"] = rows, coords
+    out["astra_energy"], out["astra_charges"] = np.float64(e_ref), charges
+    np.savez_compressed(os.path.join(HERE, "reference_beam_ops.npz"), **out)
+    return out
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
-    for fn in (element_maps, ares_tracking, cavity_line, bpm_line):
+    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops):
         res = fn()
         print(fn.__name__, {k: getattr(v, "shape", v) for k, v in res.items()})

@@ -15,7 +15,8 @@ What the shim supplies (each item is an import-time or name-resolution matter, n
      ``lynx/accelerator/segment.py`` (``nn.ModuleList`` at :43 has no import).
   3. Module-level constants ``rest_energy`` / ``REST_ENERGY`` / ``electron_mass_eV`` are plain
      floats after the rename but are used as tensors (``rest_energy.to(device=...)``,
-     drift.py:52): wrapped as float32 tensors, the value unchanged.
+     drift.py:52): wrapped as float32 tensors, the value unchanged (not in lynx.converters,
+     which is numpy code and uses them as floats).
   4. ``matplotlib`` names used in annotations only (plotting is not exercised).
 
 Only tests/golden/make_reference_golden.py uses this, in the container that holds
@@ -91,6 +92,8 @@ def install():
 
     segment_module.nn = torch.nn
     for name, mod in list(sys.modules.items()):
+        if name.startswith("lynx.converters"):
+            continue  # numpy code: the constants are used as floats there
         if name == "lynx" or name.startswith("lynx."):
             for const in ("rest_energy", "REST_ENERGY", "electron_mass_eV"):
                 if isinstance(getattr(mod, const, None), float):

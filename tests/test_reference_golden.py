@@ -137,3 +137,54 @@ def test_bpm_readings():
     assert [b.name for b in bpms] == list(g["bpm_names"])
     for b, want in zip(bpms, g["bpm_readings"]):
         np.testing.assert_allclose(np.asarray(b.reading).reshape(want.shape), want, rtol=2e-6, atol=1e-12)
+
+
+# ------------------------------------------------------------------ beam-level operations
+def test_transformed_to_is_the_reference_s():
+    """particle_beam.py:580-715: statistics of the beam (torch fp32 mean / unbiased std, the s
+    and p means zeroed, :666-693), then ``(x - old_mu) / old_sigma * new_sigma + new_mu``."""
+    from oracle import beamops as OB
+
+    g = _load("reference_beam_ops.npz")
+    full = torch.tensor(g["particles_in"])  # (1, N, 7)
+    p = full[0, :, :6]
+    target = dict(zip(g["transform_target_names"].tolist(), g["transform_target"].tolist()))
+    # the beam's own statistics exactly as particle_beam.py:736-822 takes them: one strided
+    # column of the (1, N, 7) array at a time
+    old_mu = torch.stack([full[..., i].mean(dim=-1)[0] for i in range(6)])
+    old_sigma = torch.stack([full[..., i].std(dim=-1)[0] for i in range(6)])
+    old_mu[4:] = 0.0
+    coords = ("x", "xp", "y", "yp", "s", "p")
+    new_mu = np.array([target.get(f"mu_{c}", 0.0) for c in coords], np.float32)
+    new_sigma = np.array([target[f"sigma_{c}"] for c in coords], np.float32)
+    got = OB.transformed_to(p.numpy().T, old_mu.numpy(), old_sigma.numpy(), new_mu, new_sigma)
+    np.testing.assert_array_equal(got.T, g["transformed"][0, :, :6])
+    assert (g["transformed"][0, :, 6] == 1).all()
+
+
+@pytest.mark.parametrize("shape", ["rectangular", "elliptical"])
+def test_aperture_is_the_reference_s(shape):
+    """aperture.py:69-109: survivors and lost particles, both in incoming order."""
+    from oracle import beamops as OB
+
+    g = _load("reference_beam_ops.npz")
+    planes = g["particles_in"][0, :, :6].T
+    kept, lost, _, _ = OB.aperture_track(planes, g["aperture_x_max"], g["aperture_y_max"], shape)
+    np.testing.assert_array_equal(kept.T, g[f"aperture_{shape}_kept"][:, :6])
+    np.testing.assert_array_equal(lost.T, g[f"aperture_{shape}_lost"][:, :6])
+    assert 0 < kept.shape[1] < planes.shape[1]
+
+
+def test_astra_reader_is_the_reference_s(tmp_path):
+    """converters/astra.py:8-62 on a synthetic distribution with two lost particles: the
+    coordinates, the reference energy and the charges of lynx_b200.astra.read_astra_beam."""
+    from lynx_b200.astra import read_astra_beam
+
+    g = _load("reference_beam_ops.npz")
+    path = str(tmp_path / "beam.ini")
+    np.savetxt(path, g["astra_rows"], fmt="%.12e")
+    coords, energy, charges = read_astra_beam(path)
+    assert coords.shape == g["astra_coords"].shape == (1999, 6)
+    np.testing.assert_allclose(coords, g["astra_coords"], rtol=1e-12, atol=1e-15)  # delta cancels to ~1e-16
+    assert energy == float(g["astra_energy"])
+    np.testing.assert_array_equal(charges, g["astra_charges"])
