@@ -119,7 +119,7 @@ def ares_tracking():
     """ARES EA (C6): merged map, particles, parameter beam, BPM-free screen reading."""
     k1, vk, hk = (5.0, -5.0, 5.0), 1e-3, -2e-3
     energy = t(F.ASTRA_ENERGY)
-    particles = seeded_particles(20001, seed=11)
+    particles = seeded_particles(4001, seed=11)
     out = {"k1": np.array(k1, np.float32), "vkick": np.float32(vk), "hkick": np.float32(hk),
            "energy": energy.numpy(), "particles_in": particles.numpy()}
     seg = build(F.ares_ea(k1=k1, vkick=vk, hkick=hk))
@@ -153,7 +153,7 @@ def ares_tracking():
 def cavity_line():
     """Cavity + dipole + quadrupoles (config 4 lattice): the non-linear cavity pass."""
     energy = t(6.0e6)
-    particles = seeded_particles(5001, seed=12)
+    particles = seeded_particles(2001, seed=12)
     seg = build(F.cavity_dipole_line(screen_active=False))
     beam = lynx.ParticleBeam(particles.clone(), energy.clone())
     tracked = seg.track(beam)
@@ -166,7 +166,7 @@ def cavity_line():
 def bpm_line():
     """SMATCH-like line with active BPMs: readings (bpm.py:48-58)."""
     energy = t(F.ASTRA_ENERGY)
-    particles = seeded_particles(4001, seed=13)
+    particles = seeded_particles(2001, seed=13)
     seg = build(F.smatch(bpms_active=True, angles=(1e-3, -5e-4, 2e-4)))
     tracked = seg.track(lynx.ParticleBeam(particles.clone(), energy.clone()))
     out = {"energy": energy.numpy(), "particles_in": particles.numpy(),
@@ -184,10 +184,10 @@ def beam_ops():
     import tempfile
 
     energy = t(F.ASTRA_ENERGY)
-    particles = seeded_particles(3001, seed=14)
+    particles = seeded_particles(1501, seed=14)
     out = {"energy": energy.numpy(), "particles_in": particles.numpy()}
     beam = lynx.ParticleBeam(particles.clone(), energy.clone(),
-                             particle_charges=torch.full((1, 3001), 1e-15))
+                             particle_charges=torch.full((1, 1501), 1e-15))
     target = dict(mu_x=t(1e-4), mu_y=t(-2e-4), mu_xp=t(1e-6), mu_yp=t(-3e-6), sigma_x=t(3e-4),
                   sigma_y=t(1e-4), sigma_xp=t(5e-6), sigma_yp=t(2e-6), sigma_s=t(1e-5), sigma_p=t(1e-3))
     moved = beam.transformed_to(**target)
@@ -197,7 +197,7 @@ def beam_ops():
     for shape in ("rectangular", "elliptical"):
         ap = lynx.Aperture(x_max=t(1.5e-4), y_max=t(2.0e-4), shape=shape, is_active=True)
         kept = ap.track(lynx.ParticleBeam(particles.clone(), energy.clone(),
-                                          particle_charges=torch.full((1, 3001), 1e-15)))
+                                          particle_charges=torch.full((1, 1501), 1e-15)))
         out[f"aperture_{shape}_kept"] = kept.particles.numpy()
         out[f"aperture_{shape}_lost"] = ap.lost_particles.numpy()
     out["aperture_x_max"], out["aperture_y_max"] = np.float32(1.5e-4), np.float32(2.0e-4)
@@ -205,7 +205,7 @@ def beam_ops():
     from lynx.converters.astra import from_astrabeam
 
     rng = np.random.default_rng(15)
-    n = 2001
+    n = 501
     rows = np.zeros((n, 10))
     rows[:, 0:2] = rng.normal(0, 1.7e-4, (n, 2))
     rows[:, 2] = rng.normal(0, 8e-6, n)
@@ -213,7 +213,7 @@ def beam_ops():
     rows[:, 5] = rng.normal(0, 2e5, n)
     rows[0, :6] = (0, 0, 2.0, 0, 0, 1.0732e8)
     rows[:, 7], rows[:, 8], rows[:, 9] = -2.5e-7, 1, 5
-    rows[[17, 900], 9] = (-3, -1)  # two lost particles
+    rows[[17, 400], 9] = (-3, -1)  # two lost particles
     with tempfile.TemporaryDirectory() as d:
         path = os.path.join(d, "beam.ini")
         np.savetxt(path, rows, fmt="%.12e")

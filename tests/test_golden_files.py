@@ -62,8 +62,11 @@ def test_oracle_reproduces_golden_beam_ops():
 def test_golden_files_are_small_and_complete():
     names = sorted(f for f in os.listdir(G) if f.endswith(".npz"))
     assert names == ["ares_ea_gradients.npz", "ares_ea_parameter_beam.npz",
-                     "ares_ea_particles.npz", "beam_ops.npz", "cavity_dipole_line_particles.npz"]
-    assert all(os.path.getsize(os.path.join(G, n)) < 200_000 for n in names)
+                     "ares_ea_particles.npz", "beam_ops.npz", "cavity_dipole_line_particles.npz",
+                     # computed by the reference itself (tests/golden/make_reference_golden.py)
+                     "reference_ares_ea.npz", "reference_beam_ops.npz", "reference_bpm_line.npz",
+                     "reference_cavity_line.npz", "reference_element_maps.npz"]
+    assert all(os.path.getsize(os.path.join(G, n)) < 300_000 for n in names)
 
 
 def _rel(got, want, rtol, what):

@@ -77,7 +77,7 @@ def _ares(g, dtype=f32, **kw):
 
 
 def test_ares_ea_map_and_particles_bit_for_bit():
-    """a10 / a12 / a13: Segment.transfer_map and Segment.track of 20 001 particles."""
+    """a10 / a12 / a13: Segment.transfer_map and Segment.track of 4 001 particles."""
     g = _load("reference_ares_ea.npz")
     els, energy = _ares(g), torch.tensor(g["energy"], dtype=f32)
     np.testing.assert_array_equal(segment_map(els, energy)[0].numpy(), g["segment_map"])
@@ -184,7 +184,7 @@ def test_astra_reader_is_the_reference_s(tmp_path):
     path = str(tmp_path / "beam.ini")
     np.savetxt(path, g["astra_rows"], fmt="%.12e")
     coords, energy, charges = read_astra_beam(path)
-    assert coords.shape == g["astra_coords"].shape == (1999, 6)
+    assert coords.shape == g["astra_coords"].shape == (499, 6)
     np.testing.assert_allclose(coords, g["astra_coords"], rtol=1e-12, atol=1e-15)  # delta cancels to ~1e-16
     assert energy == float(g["astra_energy"])
     np.testing.assert_array_equal(charges, g["astra_charges"])
