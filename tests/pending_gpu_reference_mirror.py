@@ -281,3 +281,99 @@ def test_particle_beam_from_ocelot():
     np.testing.assert_array_equal(got[0, :, :6], ParticleArray.rparticles.T.astype(np.float32))
     np.testing.assert_allclose(beam.energy.cpu().numpy(), [1.073e8], rtol=1e-7)
     np.testing.assert_allclose(beam.particle_charges.cpu().numpy()[0], ParticleArray.q_array, rtol=1e-6)
+
+
+# ------------------------------------------------------------------ kernels vs the reference's own outputs
+def _ref(name):
+    import os
+
+    import numpy as np
+
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name))
+
+
+def _rel(got, want, rtol, what):
+    import numpy as np
+
+    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+    scale = np.sqrt(np.mean(want**2, axis=-1, keepdims=True)) + 1e-300
+    err = np.abs(got - want) / scale
+    assert err.max() <= rtol, f"{what}: worst err/rms {err.max():.3e} > {rtol}"
+
+
+def test_kernels_vs_reference_ares_ea():
+    """The CUDA path against tests/golden/reference_ares_ea.npz -- vectors computed by the
+    reference itself (tests/golden/make_reference_golden.py).  Tolerances as in
+    tests/test_golden_files.py: 2e-5 of a plane's rms for coordinates (the kernels compose the
+    lattice in a different, cancellation-free order), bins exact up to particles
+    within an ulp of an edge."""
+    import numpy as np
+
+    from lynx_b200 import fixtures as F
+
+    g = _ref("reference_ares_ea.npz")
+    k1, vk, hk = tuple(g["k1"].tolist()), float(g["vkick"]), float(g["hkick"])
+    energy = torch.tensor(g["energy"])
+    beam = lx.ParticleBeam(torch.from_numpy(g["particles_in"]), energy)
+    n = beam.num_particles
+    seg = F.build_segment(F.ares_ea(k1=k1, vkick=vk, hkick=hk))
+    out = seg.track(beam)
+    _rel(out.soa[0, :, :n].cpu().numpy(), g["particles_out"][0, :, :6].T, 2e-5, "particles")
+    for name in ("sigma_x", "sigma_y", "sigma_xp", "sigma_yp", "sigma_s", "sigma_p"):
+        np.testing.assert_allclose(getattr(out, name).cpu().numpy(), g["out_" + name], rtol=2e-5, err_msg=name)
+    tm = seg.transfer_map(energy.cuda())[0].cpu().numpy()
+    np.testing.assert_allclose(tm, g["segment_map"], rtol=2e-5, atol=1e-9)
+
+    pb = lx.ParameterBeam(torch.from_numpy(g["pb_mu_in"]), torch.from_numpy(g["pb_cov_in"]), energy)
+    pbo = seg.track(pb)
+    np.testing.assert_allclose(pbo._mu.cpu().numpy()[:, :4], g["pb_mu_out"][:, :4], rtol=3e-5, atol=1e-9)
+    d = np.sqrt(np.abs(np.einsum("bii->bi", g["pb_cov_out"].astype(np.float64))))
+    scale = d[:, :, None] * d[:, None, :] + 1e-300
+    assert (np.abs(pbo._cov.cpu().numpy() - g["pb_cov_out"]) / scale)[:, :6, :6].max() < 3e-5
+
+    screen = {"resolution": tuple(int(v) for v in g["screen_resolution"]),
+              "pixel_size": tuple(float(v) for v in g["screen_pixel_size"]), "binning": 1}
+    seg_s = F.build_segment(F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True, screen=screen))
+    assert seg_s.track(beam) is lx.Beam.empty
+    img, want = seg_s.AREABSCR1.reading[0].cpu().numpy(), g["screen_reading"][0]
+    assert img.shape == want.shape and img.sum() == want.sum()
+    assert np.abs(img - want).sum() <= 8
+
+
+def test_kernels_vs_reference_cavity_line_and_bpms():
+    import numpy as np
+
+    from lynx_b200 import fixtures as F
+
+    g = _ref("reference_cavity_line.npz")
+    beam = lx.ParticleBeam(torch.from_numpy(g["particles_in"]), torch.tensor(g["energy"]))
+    out = F.build_segment(F.cavity_dipole_line(False)).track(beam)
+    n = beam.num_particles
+    _rel(out.soa[0, :, :n].cpu().numpy(), g["particles_out"][0, :, :6].T, 5e-5, "cavity line")
+    np.testing.assert_allclose(out.energy.cpu().numpy(), g["energy_out"], rtol=1e-6)
+
+    g = _ref("reference_bpm_line.npz")
+    seg = F.build_segment(F.smatch(bpms_active=True, angles=(1e-3, -5e-4, 2e-4)))
+    seg.track(lx.ParticleBeam(torch.from_numpy(g["particles_in"]), torch.tensor(g["energy"])))
+    for name, want in zip(g["bpm_names"].tolist(), g["bpm_readings"]):
+        got = getattr(seg, name).reading.reshape(-1).cpu().numpy()
+        np.testing.assert_allclose(got, want.reshape(-1), rtol=2e-5, atol=2e-9, err_msg=name)
+
+
+def test_kernels_vs_reference_beam_ops():
+    import numpy as np
+
+    g = _ref("reference_beam_ops.npz")
+    energy = torch.tensor(g["energy"])
+    beam = lx.ParticleBeam(torch.from_numpy(g["particles_in"]), energy)
+    target = {k: torch.tensor([float(v)]) for k, v in zip(g["transform_target_names"].tolist(), g["transform_target"])}
+    moved = beam.transformed_to(**target)
+    # the device path takes the beam's statistics from double-precision sums (DESIGN.md K5), the
+    # reference from fp32 torch reductions: a few 1e-7 relative on old_mu / old_sigma
+    _rel(moved.particles[0, :, :6].T.cpu().numpy(), g["transformed"][0, :, :6].T, 1e-5, "transformed_to")
+    for shape in ("rectangular", "elliptical"):
+        ap = lx.Aperture(x_max=torch.tensor([float(g["aperture_x_max"])]),
+                         y_max=torch.tensor([float(g["aperture_y_max"])]), shape=shape, is_active=True)
+        kept = ap.track(lx.ParticleBeam(torch.from_numpy(g["particles_in"]), energy))
+        np.testing.assert_array_equal(kept.particles.reshape(-1, 7).cpu().numpy(), g[f"aperture_{shape}_kept"])
+        np.testing.assert_array_equal(ap.lost_particles.reshape(-1, 7).cpu().numpy(), g[f"aperture_{shape}_lost"])
