@@ -225,8 +225,60 @@ def beam_ops():
     return out
 
 
+def parameter_beam():
+    """ParameterBeam constructors / accessors (parameter_beam.py:47-433, beam.py:241-310), its
+    Screen.reading (screen.py:157-194) and a batch of settings through ARES EA (config 3)."""
+    out = {}
+    args = dict(mu_x=t(1e-4), mu_xp=t(-2e-6), mu_y=t(-3e-4), mu_yp=t(1e-6), sigma_x=t(2e-4),
+                sigma_xp=t(1e-5), sigma_y=t(1.5e-4), sigma_yp=t(8e-6), sigma_s=t(1e-5),
+                sigma_p=t(2e-3), cor_x=t(1e-9), cor_y=t(-5e-10), cor_s=t(2e-9), energy=t(1.2e8),
+                total_charge=t(1e-12))
+    pb = lynx.ParameterBeam.from_parameters(**args)
+    out["fp_names"] = np.array(list(args))
+    out["fp_values"] = np.array([float(v) for v in args.values()], np.float64)
+    out["fp_mu"], out["fp_cov"] = pb._mu.numpy(), pb._cov.numpy()
+    accessors = ("mu_x", "mu_xp", "mu_y", "mu_yp", "mu_s", "mu_p", "sigma_x", "sigma_xp", "sigma_y",
+                 "sigma_yp", "sigma_s", "sigma_p", "sigma_xxp", "sigma_yyp", "emittance_x",
+                 "emittance_y", "normalized_emittance_x", "normalized_emittance_y", "beta_x",
+                 "alpha_x", "beta_y", "alpha_y", "relativistic_gamma", "relativistic_beta")
+    out["accessor_names"] = np.array(accessors)
+    out["fp_accessors"] = np.array([float(getattr(pb, a)) for a in accessors], np.float64)
+    tw = dict(beta_x=t(5.0), alpha_x=t(-0.5), emittance_x=t(2e-8), beta_y=t(3.0), alpha_y=t(0.2),
+              emittance_y=t(1e-8), energy=t(1e8))
+    ptw = lynx.ParameterBeam.from_twiss(**tw)
+    out["tw_names"] = np.array(list(tw))
+    out["tw_values"] = np.array([float(v) for v in tw.values()], np.float64)
+    out["tw_mu"], out["tw_cov"] = ptw._mu.numpy(), ptw._cov.numpy()
+    out["tw_accessors"] = np.array([float(getattr(ptw, a)) for a in accessors], np.float64)
+    moved = pb.transformed_to(mu_x=t(1e-3), sigma_x=t(3e-4), sigma_yp=t(2e-6), energy=t(9e7))
+    out["tr_mu"], out["tr_cov"], out["tr_energy"] = moved._mu.numpy(), moved._cov.numpy(), moved.energy.numpy()
+    # Screen.reading of a ParameterBeam: pdf on the pixel grid
+    scr = lynx.Screen(resolution=torch.tensor(SMALL_SCREEN["resolution"]),
+                      pixel_size=torch.tensor(SMALL_SCREEN["pixel_size"]), binning=torch.tensor(1),
+                      misalignment=torch.tensor([[1e-4, -5e-5]]), is_active=True, name="scr")
+    seg = lynx.Segment([lynx.Drift(length=t(1.0)), scr])
+    seg.track(lynx.ParameterBeam.from_parameters(**args))
+    out["screen_pdf"] = seg.scr.reading.numpy()
+    # four settings of the three quadrupoles and two correctors through ARES EA
+    B = 4
+    rng = np.random.default_rng(16)
+    k1 = rng.uniform(-20, 20, (B, 3)).astype(np.float32)
+    ang = rng.uniform(-3e-3, 3e-3, (B, 2)).astype(np.float32)
+    seg = build(F.ares_ea()).broadcast((B,))
+    for i, q in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")):
+        getattr(seg, q).k1 = torch.from_numpy(k1[:, i].copy())
+    seg.AREAMCVM1.angle = torch.from_numpy(ang[:, 0].copy())
+    seg.AREAMCHM1.angle = torch.from_numpy(ang[:, 1].copy())
+    pbb = lynx.ParameterBeam.from_parameters(**{k: v for k, v in args.items()}).broadcast((B,))
+    res = seg.track(pbb)
+    out["batch_k1"], out["batch_angles"] = k1, ang
+    out["batch_mu"], out["batch_cov"] = res._mu.numpy(), res._cov.numpy()
+    np.savez_compressed(os.path.join(HERE, "reference_parameter_beam.npz"), **out)
+    return out
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
-    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops):
+    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam):
         res = fn()
         print(fn.__name__, {k: getattr(v, "shape", v) for k, v in res.items()})

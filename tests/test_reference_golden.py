@@ -188,3 +188,71 @@ def test_astra_reader_is_the_reference_s(tmp_path):
     np.testing.assert_allclose(coords, g["astra_coords"], rtol=1e-12, atol=1e-15)  # delta cancels to ~1e-16
     assert energy == float(g["astra_energy"])
     np.testing.assert_array_equal(charges, g["astra_charges"])
+
+
+# ------------------------------------------------------------------ ParameterBeam
+ACCESSOR_RTOL = 2e-6  # fp32 accessors; the host mirror builds mu / cov in float64 first
+
+
+def _kw(g, prefix):
+    return {k: torch.tensor([v], dtype=torch.float32)
+            for k, v in zip(g[prefix + "_names"].tolist(), g[prefix + "_values"].tolist())}
+
+
+def _accessors(beam, names):
+    return np.array([float(torch.as_tensor(getattr(beam, n)).reshape(-1)[0]) for n in names])
+
+
+def test_parameter_beam_host_mirror_is_the_reference_s():
+    """lynx_b200.ParameterBeam (host logic, CPU tensors) against the reference's
+    from_parameters / from_twiss / transformed_to and every accessor of beam.py:241-310 and
+    parameter_beam.py:371-425 (a18)."""
+    import lynx_b200 as lx
+
+    g = _load("reference_parameter_beam.npz")
+    names = g["accessor_names"].tolist()
+    pb = lx.ParameterBeam.from_parameters(device="cpu", **_kw(g, "fp"))
+    np.testing.assert_allclose(pb._mu.numpy(), g["fp_mu"], rtol=1e-7, atol=0)
+    np.testing.assert_allclose(pb._cov.numpy(), g["fp_cov"], rtol=2e-7, atol=0)
+    np.testing.assert_allclose(_accessors(pb, names), g["fp_accessors"], rtol=ACCESSOR_RTOL, err_msg=str(names))
+    tw = lx.ParameterBeam.from_twiss(device="cpu", **_kw(g, "tw"))
+    np.testing.assert_allclose(tw._mu.numpy(), g["tw_mu"], rtol=1e-7, atol=0)
+    np.testing.assert_allclose(tw._cov.numpy(), g["tw_cov"], rtol=2e-7, atol=1e-30)
+    np.testing.assert_allclose(_accessors(tw, names), g["tw_accessors"], rtol=ACCESSOR_RTOL, atol=1e-12, err_msg=str(names))
+    t1 = lambda v: torch.tensor([v], dtype=torch.float32)  # noqa: E731
+    moved = pb.transformed_to(mu_x=t1(1e-3), sigma_x=t1(3e-4), sigma_yp=t1(2e-6), energy=t1(9e7))
+    np.testing.assert_allclose(moved._mu.numpy(), g["tr_mu"], rtol=1e-7, atol=0)
+    np.testing.assert_allclose(moved._cov.numpy(), g["tr_cov"], rtol=2e-7, atol=0)
+    np.testing.assert_array_equal(moved.energy.numpy(), g["tr_energy"])
+
+
+def test_parameter_beam_screen_pdf_is_the_reference_s():
+    """8(f) row 1 / screen.py:157-194: the pdf image, its (B, W, H) layout and x flip (B8)."""
+    from oracle.lattice import ParameterBeamO, screen_reading_parameter_beam
+
+    g = _load("reference_parameter_beam.npz")
+    beam = ParameterBeamO(torch.tensor(g["fp_mu"]), torch.tensor(g["fp_cov"]), torch.tensor([1.2e8]))
+    scr = El("screen", "scr", {"misalignment": torch.tensor([[1e-4, -5e-5]]), "resolution": (64, 48),
+                               "pixel_size": (4e-5, 4e-5), "binning": 1}, is_active=True)
+    els = [El("drift", "d", {"length": t(1.0)}), scr]
+    assert O.track(els, beam) is O.EMPTY
+    seen = scr.read_beam
+    img = screen_reading_parameter_beam(seen.mu_, seen.cov_, (64, 48), (4e-5, 4e-5), 1)
+    assert tuple(img.shape) == tuple(g["screen_pdf"].shape) == (1, 64, 48)
+    np.testing.assert_array_equal(img.numpy(), g["screen_pdf"])
+
+
+def test_batched_settings_are_the_reference_s():
+    """Config 3 in small: four settings of three quadrupoles and two correctors (a19: elements
+    broadcast, then per-setting parameters) -- mu and cov per setting, bit for bit."""
+    g = _load("reference_parameter_beam.npz")
+    B = g["batch_k1"].shape[0]
+    over = {(q, "k1"): g["batch_k1"][:, i] for i, q in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3"))}
+    over[("AREAMCVM1", "angle")] = g["batch_angles"][:, 0]
+    over[("AREAMCHM1", "angle")] = g["batch_angles"][:, 1]
+    els = oracle_elements(F.ares_ea(), f32, batch=(B,), overrides=over)
+    beam = O.ParameterBeamO(torch.tensor(g["fp_mu"]).repeat(B, 1), torch.tensor(g["fp_cov"]).repeat(B, 1, 1),
+                            torch.full((B,), 1.2e8))
+    out = O.track(els, beam)
+    np.testing.assert_array_equal(out.mu_.numpy(), g["batch_mu"])
+    np.testing.assert_array_equal(out.cov_.numpy(), g["batch_cov"])
