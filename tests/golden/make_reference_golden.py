@@ -225,6 +225,30 @@ def beam_ops():
     return out
 
 
+def quirks():
+    """Behaviour the restatement reproduces on purpose: B1 -- a screen's y
+    misalignment is subtracted from column 1 (xp), screen.py:134-135; B6 -- a cavity with zero
+    voltage yields NaN, cavity.py:269; plus make_linspaced (particle_beam.py:385-470)."""
+    k1, vk, hk = (5.0, -5.0, 5.0), 1e-3, -2e-3
+    energy = t(F.ASTRA_ENERGY)
+    particles = seeded_particles(2001, seed=17)
+    screen = dict(SMALL_SCREEN, misalignment=(2e-4, -1.5e-4))
+    seg = build(F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True, screen=screen))
+    seg.track(lynx.ParticleBeam(particles.clone(), energy.clone()))
+    out = {"energy": energy.numpy(), "particles_in": particles.numpy(),
+           "k1": np.array(k1, np.float32), "vkick": np.float32(vk), "hkick": np.float32(hk),
+           "screen_misalignment": np.array(screen["misalignment"], np.float32),
+           "screen_reading_misaligned": seg.AREABSCR1.reading.numpy()}
+    cav = lynx.Cavity(length=t(1.0), voltage=t(0.0), phase=t(0.0), frequency=t(1.3e9))
+    out["cavity_v0_map"] = cav.transfer_map(t(1e8))[0].numpy()
+    lin = lynx.ParticleBeam.make_linspaced(
+        num_particles=11, mu_x=t(1e-4), mu_y=t(-1e-4), sigma_x=t(2e-4), sigma_y=t(1e-4),
+        sigma_xp=t(1e-5), sigma_yp=t(2e-5), sigma_s=t(1e-6), sigma_p=t(1e-3), energy=t(1e8))
+    out["linspaced"] = lin.particles.numpy()
+    np.savez_compressed(os.path.join(HERE, "reference_quirks.npz"), **out)
+    return out
+
+
 def parameter_beam():
     """ParameterBeam constructors / accessors (parameter_beam.py:47-433, beam.py:241-310), its
     Screen.reading (screen.py:157-194) and a batch of settings through ARES EA (config 3)."""
@@ -279,6 +303,6 @@ def parameter_beam():
 
 if __name__ == "__main__":
     torch.manual_seed(0)
-    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam):
+    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam, quirks):
         res = fn()
         print(fn.__name__, {k: getattr(v, "shape", v) for k, v in res.items()})

@@ -377,3 +377,31 @@ def test_kernels_vs_reference_beam_ops():
         kept = ap.track(lx.ParticleBeam(torch.from_numpy(g["particles_in"]), energy))
         np.testing.assert_array_equal(kept.particles.reshape(-1, 7).cpu().numpy(), g[f"aperture_{shape}_kept"])
         np.testing.assert_array_equal(ap.lost_particles.reshape(-1, 7).cpu().numpy(), g[f"aperture_{shape}_lost"])
+
+
+def test_make_linspaced_vs_reference():
+    """particle_beam.py:385-470 against the reference's own output (reference_quirks.npz)."""
+    import numpy as np
+
+    g = _ref("reference_quirks.npz")
+    lin = lx.ParticleBeam.make_linspaced(
+        num_particles=11, mu_x=T(1e-4), mu_y=T(-1e-4), sigma_x=T(2e-4), sigma_y=T(1e-4),
+        sigma_xp=T(1e-5), sigma_yp=T(2e-5), sigma_s=T(1e-6), sigma_p=T(1e-3), energy=T(1e8))
+    np.testing.assert_allclose(lin.particles.cpu().numpy(), g["linspaced"], rtol=1e-6, atol=1e-12)
+
+
+def test_screen_misalignment_quirk_b1_vs_reference():
+    """screen.py:134-135 as written (default) reproduces the reference's image."""
+    import numpy as np
+
+    from lynx_b200 import fixtures as F
+
+    g = _ref("reference_quirks.npz")
+    k1, vk, hk = tuple(g["k1"].tolist()), float(g["vkick"]), float(g["hkick"])
+    screen = {"resolution": (64, 48), "pixel_size": (4e-5, 4e-5), "binning": 1,
+              "misalignment": tuple(float(v) for v in g["screen_misalignment"])}
+    seg = F.build_segment(F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True, screen=screen))
+    beam = lx.ParticleBeam(torch.from_numpy(g["particles_in"]), torch.tensor(g["energy"]))
+    assert seg.track(beam) is lx.Beam.empty
+    img, want = seg.AREABSCR1.reading[0].cpu().numpy(), g["screen_reading_misaligned"][0]
+    assert img.sum() == want.sum() and np.abs(img - want).sum() <= 8

@@ -256,3 +256,44 @@ def test_batched_settings_are_the_reference_s():
     out = O.track(els, beam)
     np.testing.assert_array_equal(out.mu_.numpy(), g["batch_mu"])
     np.testing.assert_array_equal(out.cov_.numpy(), g["batch_cov"])
+
+
+# ------------------------------------------------------------------ quirks kept on purpose
+def test_screen_misalignment_quirk_b1_is_the_reference_s():
+    """screen.py:134-135 subtracts the y misalignment from column 1 (xp), so the image moves in
+    x only: the restatement with the quirk reproduces the reference's image bin for bin, the
+    physically meant variant does not."""
+    g = _load("reference_quirks.npz")
+    k1, vk, hk = tuple(g["k1"].tolist()), float(g["vkick"]), float(g["hkick"])
+    screen = {"resolution": (64, 48), "pixel_size": (4e-5, 4e-5), "binning": 1,
+              "misalignment": tuple(float(v) for v in g["screen_misalignment"])}
+    energy = torch.tensor(g["energy"], dtype=f32)
+    ex, ey = screen_bin_edges(screen["resolution"], screen["pixel_size"], 1)
+    images = {}
+    for quirk in (True, False):
+        els = oracle_elements(F.ares_ea(k1=k1, vkick=vk, hkick=hk, screen_active=True, screen=screen), f32)
+        O.track(els, O.ParticleBeamO(torch.tensor(g["particles_in"]), energy), screen_quirk_b1=quirk)
+        seen = [e for e in els if e.kind == "screen"][0].read_beam
+        images[quirk] = screen_reading_particles(seen.col(0), seen.col(2), ex, ey).numpy()
+    np.testing.assert_array_equal(images[True], g["screen_reading_misaligned"])
+    assert (images[False] != g["screen_reading_misaligned"]).any()
+
+
+def test_zero_voltage_cavity_quirk_b6_is_the_reference_s():
+    """cavity.py:269: 0 * inf -- the reference's map of a V = 0 cavity holds NaN in R12 / R34.
+    The restatement reproduces it as written; ``cavity_v0_as_drift`` (what the kernels do,
+    DESIGN.md 1.4) gives the drift map those entries converge to."""
+    g = _load("reference_quirks.npz")
+    cav = _el("cavity", length=1.0, voltage=0.0, phase=0.0, frequency=1.3e9)
+    e = torch.tensor([1e8], dtype=f32)
+    as_written = element_map(cav, e)[0].numpy()
+    want = g["cavity_v0_map"]
+    assert np.isnan(want[0, 1]) and np.isnan(want[2, 3]) and np.isnan(want).sum() == 2
+    np.testing.assert_array_equal(as_written, want)  # NaNs in the same places, the rest equal
+    repaired = element_map(cav, e, cavity_v0_as_drift=True)[0].numpy()
+    assert np.isfinite(repaired).all()
+    mask = ~np.isnan(want)
+    mask[4, 5] = False  # the drift carries R56 = -L / (beta gamma)^2 = -2.6e-5 here, the cavity formula 0
+    np.testing.assert_allclose(repaired[mask], want[mask], rtol=1e-6, atol=1e-12)
+    assert repaired[0, 1] == repaired[2, 3] == 1.0  # the drift's R12 = R34 = L
+    assert -3e-5 < repaired[4, 5] < -2e-5 and want[4, 5] == 0.0
