@@ -249,6 +249,47 @@ def quirks():
     return out
 
 
+def gradients():
+    """torch autograd THROUGH THE REFERENCE (it runs on torch here): d loss / d k1, d angle for a
+    particle beam and a parameter beam through ARES EA; loss as tests/test_differentiable.py
+    builds them from mu / sigma."""
+    energy = t(F.ASTRA_ENERGY)
+    particles = seeded_particles(2001, seed=18)
+    out = {"energy": energy.numpy(), "particles_in": particles.numpy()}
+    k1_0, ang_0 = [5.0, -5.0, 5.0], [1e-3, -2e-3]
+
+    def lattice():
+        seg = build(F.ares_ea())
+        k1 = torch.tensor(k1_0, requires_grad=True)
+        ang = torch.tensor(ang_0, requires_grad=True)
+        for i, q in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")):
+            getattr(seg, q).k1 = k1[i:i + 1]
+        seg.AREAMCVM1.angle, seg.AREAMCHM1.angle = ang[0:1], ang[1:2]
+        return seg, k1, ang
+
+    seg, k1, ang = lattice()
+    o = seg.track(lynx.ParticleBeam(particles.clone(), energy.clone()))
+    loss = (o.mu_x ** 2 + o.sigma_x ** 2 + o.mu_y ** 2 + o.sigma_y ** 2).sum() / 4
+    loss.backward()
+    out.update(k1=np.array(k1_0, np.float32), angles=np.array(ang_0, np.float32),
+               loss_particles=np.float32(loss.item()), g_k1_particles=k1.grad.numpy(),
+               g_angles_particles=ang.grad.numpy())
+    seg, k1, ang = lattice()
+    pb = lynx.ParameterBeam.from_parameters(
+        mu_x=t(F.ASTRA_MU[0]), mu_xp=t(F.ASTRA_MU[1]), mu_y=t(F.ASTRA_MU[2]), mu_yp=t(F.ASTRA_MU[3]),
+        sigma_x=t(F.ASTRA_SIGMA[0]), sigma_xp=t(F.ASTRA_SIGMA[1]), sigma_y=t(F.ASTRA_SIGMA[2]),
+        sigma_yp=t(F.ASTRA_SIGMA[3]), sigma_s=t(F.ASTRA_SIGMA[4]), sigma_p=t(F.ASTRA_SIGMA[5]),
+        energy=energy.clone())
+    out["pb_mu_in"], out["pb_cov_in"] = pb._mu.numpy(), pb._cov.numpy()
+    o = seg.track(pb)
+    loss = (o.mu_x ** 2 + o.sigma_x ** 2 + o.mu_y ** 2 + o.sigma_y ** 2).sum() / 4
+    loss.backward()
+    out.update(loss_parameter=np.float32(loss.item()), g_k1_parameter=k1.grad.numpy(),
+               g_angles_parameter=ang.grad.numpy())
+    np.savez_compressed(os.path.join(HERE, "reference_gradients.npz"), **out)
+    return out
+
+
 def parameter_beam():
     """ParameterBeam constructors / accessors (parameter_beam.py:47-433, beam.py:241-310), its
     Screen.reading (screen.py:157-194) and a batch of settings through ARES EA (config 3)."""
@@ -303,6 +344,6 @@ def parameter_beam():
 
 if __name__ == "__main__":
     torch.manual_seed(0)
-    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam, quirks):
+    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam, quirks, gradients):
         res = fn()
         print(fn.__name__, {k: getattr(v, "shape", v) for k, v in res.items()})

@@ -405,3 +405,33 @@ def test_screen_misalignment_quirk_b1_vs_reference():
     assert seg.track(beam) is lx.Beam.empty
     img, want = seg.AREABSCR1.reading[0].cpu().numpy(), g["screen_reading_misaligned"][0]
     assert img.sum() == want.sum() and np.abs(img - want).sum() <= 8
+
+
+@pytest.mark.parametrize("kind", ["particles", "parameter"])
+def test_adjoint_kernels_vs_reference_gradients(kind):
+    """K3 / K6-bwd against torch autograd through the reference itself
+    (tests/golden/reference_gradients.npz); tolerance as tests/test_golden_files.py (3e-5 of the
+    largest component) widened to the reference's own fp32 noise in d/dk1 (2e-3, see
+    tests/test_reference_golden.py)."""
+    import numpy as np
+
+    from lynx_b200 import fixtures as F
+
+    g = _ref("reference_gradients.npz")
+    seg = F.build_segment(F.ares_ea())
+    k1 = torch.tensor(g["k1"], requires_grad=True)
+    ang = torch.tensor(g["angles"], requires_grad=True)
+    for i, q in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")):
+        getattr(seg, q).k1 = k1[i:i + 1]
+    seg.AREAMCVM1.angle, seg.AREAMCHM1.angle = ang[0:1], ang[1:2]
+    energy = torch.tensor(g["energy"])
+    if kind == "particles":
+        beam = lx.ParticleBeam(torch.from_numpy(g["particles_in"]), energy)
+    else:
+        beam = lx.ParameterBeam(torch.from_numpy(g["pb_mu_in"]), torch.from_numpy(g["pb_cov_in"]), energy)
+    o = seg.track(beam)
+    loss = (o.mu_x ** 2 + o.sigma_x ** 2 + o.mu_y ** 2 + o.sigma_y ** 2).sum() / 4
+    loss.backward()
+    np.testing.assert_allclose(loss.item(), g[f"loss_{kind}"], rtol=3e-5)
+    np.testing.assert_allclose(k1.grad.numpy(), g[f"g_k1_{kind}"], rtol=3e-3)
+    np.testing.assert_allclose(ang.grad.numpy(), g[f"g_angles_{kind}"], rtol=1e-4)

@@ -297,3 +297,40 @@ def test_zero_voltage_cavity_quirk_b6_is_the_reference_s():
     np.testing.assert_allclose(repaired[mask], want[mask], rtol=1e-6, atol=1e-12)
     assert repaired[0, 1] == repaired[2, 3] == 1.0  # the drift's R12 = R34 = L
     assert -3e-5 < repaired[4, 5] < -2e-5 and want[4, 5] == 0.0
+
+
+# ------------------------------------------------------------------ gradients
+def _oracle_gradients(g, dtype, parameter_beam):
+    k1 = torch.tensor(g["k1"], dtype=dtype, requires_grad=True)
+    ang = torch.tensor(g["angles"], dtype=dtype, requires_grad=True)
+    els = oracle_elements(F.ares_ea(), dtype)
+    by_name = {e.name: e for e in els}
+    for i, q in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3")):
+        by_name[q].p["k1"] = k1[i:i + 1]
+    by_name["AREAMCVM1"].p["angle"], by_name["AREAMCHM1"].p["angle"] = ang[0:1], ang[1:2]
+    energy = torch.tensor(g["energy"], dtype=dtype)
+    if parameter_beam:
+        beam = O.ParameterBeamO(torch.tensor(g["pb_mu_in"], dtype=dtype),
+                                torch.tensor(g["pb_cov_in"], dtype=dtype), energy)
+    else:
+        beam = O.ParticleBeamO(torch.tensor(g["particles_in"], dtype=dtype), energy)
+    o = O.track(els, beam)
+    loss = (o.mu(0) ** 2 + o.sigma(0) ** 2 + o.mu(2) ** 2 + o.sigma(2) ** 2).sum() / 4
+    loss.backward()
+    return loss.item(), k1.grad.numpy(), ang.grad.numpy()
+
+
+@pytest.mark.parametrize("kind", ["particles", "parameter"])
+def test_gradients_are_the_reference_s(kind):
+    """torch autograd through the reference (tests/golden/make_reference_golden.py::gradients)
+    against torch autograd through the restatement -- the gradient oracle of the adjoint
+    kernels (tests/test_gpu_adjoint.py).  fp32: same operations, same graph -> 1e-5; the fp64
+    restatement bounds the fp32 noise of both."""
+    g = _load("reference_gradients.npz")
+    loss, g_k1, g_ang = _oracle_gradients(g, f32, kind == "parameter")
+    np.testing.assert_allclose(loss, g[f"loss_{kind}"], rtol=1e-6)
+    np.testing.assert_allclose(g_k1, g[f"g_k1_{kind}"], rtol=1e-5)
+    np.testing.assert_allclose(g_ang, g[f"g_angles_{kind}"], rtol=1e-5)
+    loss64, g_k1_64, g_ang_64 = _oracle_gradients(g, torch.float64, kind == "parameter")
+    np.testing.assert_allclose(g[f"g_k1_{kind}"], g_k1_64, rtol=2e-3)  # fp32 cancellation in sigma^2
+    np.testing.assert_allclose(g[f"g_angles_{kind}"], g_ang_64, rtol=1e-4)
