@@ -167,8 +167,9 @@ def run_reference(args, rank, world):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "ares_ea_1M_particles_screen_2448x2040", "elements": E_ARES,
                    "particles": n,
-                   "note": "torch-CPU restatement of the reference arithmetic (the "
-                           "reference itself cannot execute, SURVEY.md 0.1)"},
+                   "note": "torch-CPU restatement of the reference arithmetic, bit-identical "
+                           "to the reference's own outputs (tests/test_reference_golden.py); "
+                           "the Python reference cannot travel to the GPU box"},
         "cpu_baseline": {"value": val, "unit": "particle-element updates/s",
                          "cores": torch.get_num_threads(), "kind": "port",
                          "sample": f"{args.steps} full steps of {n} particles"},

@@ -2,12 +2,13 @@
 
     python tests/golden/make_golden.py
 
-The reference (jank324/lynx) cannot execute and pins no per-particle,
-histogram or gradient value, so these vectors come from the CPU restatement
-in ``oracle/`` (fp64) -- they pin the oracle against regressions and let the GPU tests
-compare against fixed files; they are NOT outputs of the reference itself.  The known
-answers that DO come from the reference's own tests / notebooks (C2-C5) are checked in
-tests/test_oracle_golden.py.
+These vectors come from the CPU restatement in ``oracle/`` (fp64): they pin the oracle against
+regressions and let the GPU tests compare against fixed files.  They are NOT outputs of the
+reference -- those are tests/golden/reference_*.npz, written by
+tests/golden/make_reference_golden.py (the reference run on torch through
+tests/golden/reference_shim.py), which the fp32 oracle reproduces bit for bit
+(tests/test_reference_golden.py).  The known answers from the reference's own tests /
+notebooks (C2-C5) are checked in tests/test_oracle_golden.py.
 """
 
 import os

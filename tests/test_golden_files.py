@@ -1,5 +1,6 @@
-"""Committed golden vectors (tests/golden/*.npz, generated from the fp64 oracle by
-tests/golden/make_golden.py -- NOT outputs of the reference, which cannot execute).
+"""Committed golden vectors tests/golden/{ares_ea,cavity,beam_ops}*.npz, generated from the fp64
+oracle by tests/golden/make_golden.py.  (The vectors computed by the reference itself are
+tests/golden/reference_*.npz, see tests/test_reference_golden.py.)
 
 CPU: the oracle still reproduces them (guards the checker against drift).
 GPU: the CUDA path, through the C ABI, against the fixed files (no oracle involved)."""
