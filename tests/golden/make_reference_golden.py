@@ -245,6 +245,18 @@ def quirks():
         num_particles=11, mu_x=t(1e-4), mu_y=t(-1e-4), sigma_x=t(2e-4), sigma_y=t(1e-4),
         sigma_xp=t(1e-5), sigma_yp=t(2e-5), sigma_s=t(1e-6), sigma_p=t(1e-3), energy=t(1e8))
     out["linspaced"] = lin.particles.numpy()
+    # split (drift.py:71-78, quadrupole.py:99-110, segment.py:310-315, horizontal_corrector.py:82-90)
+    res = torch.tensor(0.3)
+    out["split_drift"] = np.array([float(e.length) for e in lynx.Drift(length=t(2.0)).split(resolution=res)])
+    out["split_quadrupole"] = np.array([[float(e.length), float(e.k1)] for e in lynx.Quadrupole(
+        length=t(0.2), k1=t(4.2)).split(resolution=torch.tensor(0.03))])
+    seg = lynx.Segment([lynx.Drift(length=t(0.6)), lynx.Quadrupole(length=t(0.2), k1=t(0.0)),
+                        lynx.Marker(), lynx.Drift(length=t(0.4))])
+    out["split_segment"] = np.array([float(e.length) for e in seg.split(resolution=torch.tensor(0.25))])
+    # under torch, ``remaining = self.length; remaining -= resolution`` shrinks the corrector's
+    # own length while it is being split (an aliasing that immutable jnp arrays do not have)
+    out["split_hcor"] = np.array([[float(e.length), float(e.angle)] for e in lynx.HorizontalCorrector(
+        length=t(0.3), angle=t(3e-4)).split(resolution=torch.tensor(0.1))])
     np.savez_compressed(os.path.join(HERE, "reference_quirks.npz"), **out)
     return out
 

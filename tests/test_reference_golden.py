@@ -334,3 +334,30 @@ def test_gradients_are_the_reference_s(kind):
     loss64, g_k1_64, g_ang_64 = _oracle_gradients(g, torch.float64, kind == "parameter")
     np.testing.assert_allclose(g[f"g_k1_{kind}"], g_k1_64, rtol=2e-3)  # fp32 cancellation in sigma^2
     np.testing.assert_allclose(g[f"g_angles_{kind}"], g_ang_64, rtol=1e-4)
+
+
+def test_split_is_the_reference_s():
+    """Element.split / Segment.split of the host mirror against the reference's slices.  The
+    corrector is the exception: run on torch, the reference's ``remaining -= resolution``
+    (horizontal_corrector.py:84-89) also shrinks ``self.length`` -- the two names alias -- so its
+    slice angles come out as angle*l/(what is left); with immutable jnp arrays (the language the
+    reference declares) ``-=`` rebinds and every slice gets angle*l/length, which is what
+    lynx_b200 does.  The slice LENGTHS agree either way."""
+    import lynx_b200 as lx
+
+    g = _load("reference_quirks.npz")
+    got = [float(e.length) for e in lx.Drift(length=t(2.0)).split(resolution=torch.tensor(0.3))]
+    np.testing.assert_array_equal(np.array(got), g["split_drift"])
+    got = [[float(e.length), float(e.k1)] for e in
+           lx.Quadrupole(length=t(0.2), k1=t(4.2)).split(resolution=torch.tensor(0.03))]
+    np.testing.assert_array_equal(np.array(got), g["split_quadrupole"])
+    seg = lx.Segment([lx.Drift(length=t(0.6)), lx.Quadrupole(length=t(0.2), k1=t(0.0)), lx.Marker(),
+                      lx.Drift(length=t(0.4))])
+    got = [float(e.length) for e in seg.split(resolution=torch.tensor(0.25))]
+    np.testing.assert_array_equal(np.array(got), g["split_segment"])
+    hcor = lx.HorizontalCorrector(length=t(0.3), angle=t(3e-4))
+    slices = hcor.split(resolution=torch.tensor(0.1))
+    np.testing.assert_array_equal(np.array([float(e.length) for e in slices]), g["split_hcor"][:, 0])
+    np.testing.assert_allclose(g["split_hcor"][:3, 1], [1e-4, 1.5e-4, 3e-4], rtol=1e-6)  # the aliasing
+    np.testing.assert_allclose([float(e.angle) for e in slices[:3]], [1e-4] * 3, rtol=1e-6)
+    assert float(hcor.length) == np.float32(0.3)  # and the element itself is left intact
