@@ -302,6 +302,27 @@ def gradients():
     return out
 
 
+def converters():
+    """The reference's own lattice readers on its own resource files: element names, classes
+    and lengths (converters/nxtables.py, converters/bmad.py)."""
+    from pathlib import Path
+
+    out = {}
+    seg = lynx.Segment.from_nx_tables(Path("/root/reference/tests/resources/Stage4v3_9.txt"))
+    out["nx_names"] = np.array([e.name for e in seg.elements])
+    out["nx_classes"] = np.array([type(e).__name__ for e in seg.elements])
+    out["nx_lengths"] = np.array([float(e.length) for e in seg.elements], np.float32)
+    # (Segment.length itself raises here: the screens' default length has shape (), the other
+    #  elements' (1,), and segment.py:323 stacks them)
+    seg = lynx.Segment.from_bmad("/root/reference/tests/resources/bmad_tutorial_lattice.bmad")
+    out["bmad_names"] = np.array([e.name for e in seg.elements])
+    out["bmad_classes"] = np.array([type(e).__name__ for e in seg.elements])
+    out["bmad_lengths"] = np.array([float(e.length) for e in seg.elements], np.float32)
+    out["bmad_b_e1"], out["bmad_q_k1"] = seg.b.e1.numpy(), seg.q.k1.numpy()
+    np.savez_compressed(os.path.join(HERE, "reference_converters.npz"), **out)
+    return out
+
+
 def parameter_beam():
     """ParameterBeam constructors / accessors (parameter_beam.py:47-433, beam.py:241-310), its
     Screen.reading (screen.py:157-194) and a batch of settings through ARES EA (config 3)."""
@@ -356,6 +377,6 @@ def parameter_beam():
 
 if __name__ == "__main__":
     torch.manual_seed(0)
-    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam, quirks, gradients):
+    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam, quirks, gradients, converters):
         res = fn()
         print(fn.__name__, {k: getattr(v, "shape", v) for k, v in res.items()})

@@ -361,3 +361,25 @@ def test_split_is_the_reference_s():
     np.testing.assert_allclose(g["split_hcor"][:3, 1], [1e-4, 1.5e-4, 3e-4], rtol=1e-6)  # the aliasing
     np.testing.assert_allclose([float(e.angle) for e in slices[:3]], [1e-4] * 3, rtol=1e-6)
     assert float(hcor.length) == np.float32(0.3)  # and the element itself is left intact
+
+
+# ------------------------------------------------------------------ lattice readers
+@pytest.mark.skipif(not os.path.exists("/root/reference/tests/resources/Stage4v3_9.txt"),
+                    reason="the reference's resource files are only in the build container")
+def test_lattice_readers_are_the_reference_s():
+    """lynx_b200's NX-tables and Bmad readers on the reference's resource files against what
+    the reference's own readers return for them (reference_converters.npz): every element's
+    name, class and length."""
+    import lynx_b200 as lx
+
+    g = _load("reference_converters.npz")
+    seg = lx.Segment.from_nx_tables("/root/reference/tests/resources/Stage4v3_9.txt")
+    assert [e.name for e in seg.elements] == g["nx_names"].tolist()
+    assert [type(e).__name__ for e in seg.elements] == g["nx_classes"].tolist()
+    np.testing.assert_array_equal(np.array([float(e.length) for e in seg.elements], np.float32), g["nx_lengths"])
+    seg = lx.Segment.from_bmad("/root/reference/tests/resources/bmad_tutorial_lattice.bmad")
+    assert [e.name for e in seg.elements] == g["bmad_names"].tolist()
+    assert [type(e).__name__ for e in seg.elements] == g["bmad_classes"].tolist()
+    np.testing.assert_array_equal(np.array([float(e.length) for e in seg.elements], np.float32), g["bmad_lengths"])
+    np.testing.assert_array_equal(seg.b.e1.numpy(), g["bmad_b_e1"])
+    np.testing.assert_array_equal(seg.q.k1.numpy(), g["bmad_q_k1"])
