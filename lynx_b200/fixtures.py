@@ -80,6 +80,28 @@ def cavity_dipole_line(screen_active=True):
     ]
 
 
+def element_zoo():
+    """One of every map-bearing element kind with every optional parameter set (tilt,
+    misalignment, edge angles, fringe integrals): the lattice of the reference-generated vector
+    tests/golden/reference_zoo.npz."""
+    return [
+        ("drift", "D1", {"length": 0.3}),
+        ("quadrupole", "Q1", {"length": 0.122, "k1": 6.5, "tilt": 0.2, "misalignment": (2e-4, -1e-4)}),
+        ("solenoid", "S1", {"length": 0.09, "k": 0.8}),
+        ("hcor", "H1", {"length": 0.02, "angle": 1.2e-3}),
+        ("vcor", "V1", {"length": 0.02, "angle": -0.7e-3}),
+        ("dipole", "B1", {"length": 0.22, "angle": 0.05, "e1": 0.02, "e2": 0.03, "tilt": 0.1,
+                          "fringe_integral": 0.5, "fringe_integral_exit": 0.4, "gap": 0.03}),
+        ("drift", "D2", {"length": 0.25}),
+        ("rbend", "B2", {"length": 0.3, "angle": -0.04, "fringe_integral": 0.45, "gap": 0.02}),
+        ("undulator", "U1", {"length": 0.25}),
+        ("quadrupole", "Q2", {"length": 0.122, "k1": -8.0}),
+        ("cavity", "C1", {"length": 1.0377, "voltage": 8.0e6, "phase": -20.0, "frequency": 1.3e9}),
+        ("drift", "D3", {"length": 0.4}),
+        ("quadrupole", "Q3", {"length": 0.122, "k1": 3.0}),
+    ]
+
+
 def build_segment(spec, name=None):
     """lynx_b200 ``Segment`` from a spec."""
     from . import elements as E

@@ -163,6 +163,25 @@ def cavity_line():
     return out
 
 
+def zoo():
+    """Every map-bearing element kind with all its optional parameters, particles and a
+    parameter beam (lynx_b200.fixtures.element_zoo)."""
+    energy = t(2.0e7)
+    particles = seeded_particles(2001, seed=19)
+    seg = build(F.element_zoo())
+    tracked = seg.track(lynx.ParticleBeam(particles.clone(), energy.clone()))
+    out = {"energy": energy.numpy(), "particles_in": particles.numpy(),
+           "particles_out": tracked.particles.numpy(), "energy_out": tracked.energy.numpy()}
+    pb = lynx.ParameterBeam.from_parameters(
+        mu_x=t(1e-4), mu_y=t(-2e-4), sigma_x=t(2e-4), sigma_xp=t(1e-5), sigma_y=t(1.5e-4),
+        sigma_yp=t(8e-6), sigma_s=t(1e-5), sigma_p=t(2e-3), energy=energy.clone())
+    out["pb_mu_in"], out["pb_cov_in"] = pb._mu.numpy(), pb._cov.numpy()
+    res = build(F.element_zoo()).track(pb)
+    out["pb_mu_out"], out["pb_cov_out"], out["pb_energy_out"] = res._mu.numpy(), res._cov.numpy(), res.energy.numpy()
+    np.savez_compressed(os.path.join(HERE, "reference_zoo.npz"), **out)
+    return out
+
+
 def bpm_line():
     """SMATCH-like line with active BPMs: readings (bpm.py:48-58)."""
     energy = t(F.ASTRA_ENERGY)
@@ -377,6 +396,6 @@ def parameter_beam():
 
 if __name__ == "__main__":
     torch.manual_seed(0)
-    for fn in (element_maps, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam, quirks, gradients, converters):
+    for fn in (element_maps, zoo, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam, quirks, gradients, converters):
         res = fn()
         print(fn.__name__, {k: getattr(v, "shape", v) for k, v in res.items()})

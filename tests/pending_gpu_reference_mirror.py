@@ -435,3 +435,25 @@ def test_adjoint_kernels_vs_reference_gradients(kind):
     np.testing.assert_allclose(loss.item(), g[f"loss_{kind}"], rtol=3e-5)
     np.testing.assert_allclose(k1.grad.numpy(), g[f"g_k1_{kind}"], rtol=3e-3)
     np.testing.assert_allclose(ang.grad.numpy(), g[f"g_angles_{kind}"], rtol=1e-4)
+
+
+def test_kernels_vs_reference_element_zoo():
+    """One of every map-bearing element kind (fixtures.element_zoo) against the reference's own
+    particles, energy and parameter-beam moments."""
+    import numpy as np
+
+    from lynx_b200 import fixtures as F
+
+    g = _ref("reference_zoo.npz")
+    energy = torch.tensor(g["energy"])
+    beam = lx.ParticleBeam(torch.from_numpy(g["particles_in"]), energy)
+    out = F.build_segment(F.element_zoo()).track(beam)
+    _rel(out.soa[0, :, :beam.num_particles].cpu().numpy(), g["particles_out"][0, :, :6].T, 5e-5, "zoo particles")
+    np.testing.assert_allclose(out.energy.cpu().numpy(), g["energy_out"], rtol=1e-6)
+    pb = lx.ParameterBeam(torch.from_numpy(g["pb_mu_in"]), torch.from_numpy(g["pb_cov_in"]), energy)
+    res = F.build_segment(F.element_zoo()).track(pb)
+    np.testing.assert_allclose(res._mu.cpu().numpy()[:, :4], g["pb_mu_out"][:, :4], rtol=5e-5, atol=1e-9)
+    d = np.sqrt(np.abs(np.einsum("bii->bi", g["pb_cov_out"].astype(np.float64))))
+    scale = d[:, :, None] * d[:, None, :] + 1e-300
+    assert (np.abs(res._cov.cpu().numpy() - g["pb_cov_out"]) / scale)[:, :6, :6].max() < 5e-5
+    np.testing.assert_allclose(res.energy.cpu().numpy(), g["pb_energy_out"], rtol=1e-6)

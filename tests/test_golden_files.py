@@ -68,7 +68,7 @@ def test_golden_files_are_small_and_complete():
                      "reference_ares_ea.npz", "reference_beam_ops.npz", "reference_bpm_line.npz",
                      "reference_cavity_line.npz", "reference_converters.npz", "reference_element_maps.npz",
                      "reference_gradients.npz",
-                     "reference_parameter_beam.npz", "reference_quirks.npz"]
+                     "reference_parameter_beam.npz", "reference_quirks.npz", "reference_zoo.npz"]
     assert all(os.path.getsize(os.path.join(G, n)) < 300_000 for n in names)
 
 

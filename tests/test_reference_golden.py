@@ -383,3 +383,20 @@ def test_lattice_readers_are_the_reference_s():
     np.testing.assert_array_equal(np.array([float(e.length) for e in seg.elements], np.float32), g["bmad_lengths"])
     np.testing.assert_array_equal(seg.b.e1.numpy(), g["bmad_b_e1"])
     np.testing.assert_array_equal(seg.q.k1.numpy(), g["bmad_q_k1"])
+
+
+def test_element_zoo_is_the_reference_s():
+    """Every map-bearing element kind with all optional parameters in one line (tilted and
+    misaligned quadrupole, solenoid, both correctors, dipole with edges / fringe / tilt, rbend,
+    undulator, cavity): 2 001 particles and a parameter beam, bit for bit."""
+    g = _load("reference_zoo.npz")
+    energy = torch.tensor(g["energy"], dtype=f32)
+    els = oracle_elements(F.element_zoo(), f32)
+    out = O.track(els, O.ParticleBeamO(torch.tensor(g["particles_in"]), energy))
+    np.testing.assert_array_equal(out.energy.numpy(), g["energy_out"])
+    np.testing.assert_array_equal(out.particles.numpy(), g["particles_out"])
+    els = oracle_elements(F.element_zoo(), f32)
+    pb = O.track(els, O.ParameterBeamO(torch.tensor(g["pb_mu_in"]), torch.tensor(g["pb_cov_in"]), energy))
+    np.testing.assert_array_equal(pb.energy.numpy(), g["pb_energy_out"])
+    np.testing.assert_array_equal(pb.mu_.numpy(), g["pb_mu_out"])
+    np.testing.assert_array_equal(pb.cov_.numpy(), g["pb_cov_out"])
