@@ -264,6 +264,13 @@ def quirks():
         num_particles=11, mu_x=t(1e-4), mu_y=t(-1e-4), sigma_x=t(2e-4), sigma_y=t(1e-4),
         sigma_xp=t(1e-5), sigma_yp=t(2e-5), sigma_s=t(1e-6), sigma_p=t(1e-3), energy=t(1e8))
     out["linspaced"] = lin.particles.numpy()
+    # Screen geometry (screen.py:86-118) with 4x4 binning
+    scr = lynx.Screen(resolution=torch.tensor((2448, 2040)), pixel_size=torch.tensor((3.3198e-6, 2.4469e-6)),
+                      binning=torch.tensor(4), misalignment=torch.tensor([[0.0, 0.0]]))
+    out["screen_edges_x"], out["screen_edges_y"] = (e.numpy() for e in scr.pixel_bin_edges)
+    out["screen_extent"] = np.array([float(v) for v in scr.extent], np.float32)
+    out["screen_effective_resolution"] = scr.effective_resolution.numpy()
+    out["screen_effective_pixel_size"] = scr.effective_pixel_size.numpy()
     # split (drift.py:71-78, quadrupole.py:99-110, segment.py:310-315, horizontal_corrector.py:82-90)
     res = torch.tensor(0.3)
     out["split_drift"] = np.array([float(e.length) for e in lynx.Drift(length=t(2.0)).split(resolution=res)])

@@ -400,3 +400,24 @@ def test_element_zoo_is_the_reference_s():
     np.testing.assert_array_equal(pb.energy.numpy(), g["pb_energy_out"])
     np.testing.assert_array_equal(pb.mu_.numpy(), g["pb_mu_out"])
     np.testing.assert_array_equal(pb.cov_.numpy(), g["pb_cov_out"])
+
+
+def test_screen_geometry_is_the_reference_s():
+    """screen.py:86-118: bin edges (what the histogram kernel is handed), extent and the
+    effective resolution / pixel size with 4x4 binning -- host mirror and oracle, bit for bit."""
+    import lynx_b200 as lx
+
+    g = _load("reference_quirks.npz")
+    kw = dict(resolution=torch.tensor((2448, 2040)), pixel_size=torch.tensor((3.3198e-6, 2.4469e-6)),
+              binning=torch.tensor(4), misalignment=torch.tensor([[0.0, 0.0]]))
+    scr = lx.Screen(**kw)
+    ex, ey = scr.pixel_bin_edges
+    np.testing.assert_array_equal(ex.numpy(), g["screen_edges_x"])
+    np.testing.assert_array_equal(ey.numpy(), g["screen_edges_y"])
+    assert ex.numel() == 613 and ey.numel() == 511
+    np.testing.assert_array_equal(np.array([float(v) for v in scr.extent], np.float32), g["screen_extent"])
+    np.testing.assert_array_equal(scr.effective_resolution.numpy(), g["screen_effective_resolution"])
+    np.testing.assert_array_equal(scr.effective_pixel_size.numpy(), g["screen_effective_pixel_size"])
+    ox, oy = screen_bin_edges((2448, 2040), (3.3198e-6, 2.4469e-6), 4)
+    np.testing.assert_array_equal(ox.numpy(), g["screen_edges_x"])
+    np.testing.assert_array_equal(oy.numpy(), g["screen_edges_y"])
