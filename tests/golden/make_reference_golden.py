@@ -182,6 +182,31 @@ def zoo():
     return out
 
 
+def batched_particles():
+    """tests/test_dipole.py:25-44 and tests/test_quadrupole.py:78-99 with seeded particles: one
+    beam broadcast over three settings of a dipole / of a tilted quadrupole (config 5 in small)."""
+    energy = t(1e9)
+    particles = seeded_particles(1001, seed=20)
+    out = {"energy": energy.numpy(), "particles_in": particles.numpy()}
+    beam = lynx.ParticleBeam(particles.clone(), energy.clone()).broadcast((3,))
+    seg = lynx.Segment([
+        lynx.Dipole(length=torch.tensor([0.5, 0.5, 0.5]), angle=torch.tensor([0.1, 0.2, 0.1])),
+        lynx.Drift(length=t(0.5)).broadcast((3,)),
+    ])
+    out["dipole_angles"] = np.array([0.1, 0.2, 0.1], np.float32)
+    out["dipole_out"] = seg.track(beam).particles.numpy()
+    tilts = torch.tensor([np.pi / 4, np.pi / 2, np.pi * 5 / 4], dtype=torch.float32)
+    seg = lynx.Segment([
+        lynx.Quadrupole(length=torch.tensor([0.5, 0.5, 0.5]), k1=torch.tensor([1.0, 1.0, 1.0]), tilt=tilts),
+        lynx.Drift(length=t(0.5)).broadcast((3,)),
+    ])
+    beam = lynx.ParticleBeam(particles.clone(), energy.clone()).broadcast((3,))
+    out["quad_tilts"] = tilts.numpy()
+    out["quad_out"] = seg.track(beam).particles.numpy()
+    np.savez_compressed(os.path.join(HERE, "reference_batched_particles.npz"), **out)
+    return out
+
+
 def bpm_line():
     """SMATCH-like line with active BPMs: readings (bpm.py:48-58)."""
     energy = t(F.ASTRA_ENERGY)
@@ -403,6 +428,6 @@ def parameter_beam():
 
 if __name__ == "__main__":
     torch.manual_seed(0)
-    for fn in (element_maps, zoo, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam, quirks, gradients, converters):
+    for fn in (element_maps, zoo, batched_particles, ares_tracking, cavity_line, bpm_line, beam_ops, parameter_beam, quirks, gradients, converters):
         res = fn()
         print(fn.__name__, {k: getattr(v, "shape", v) for k, v in res.items()})

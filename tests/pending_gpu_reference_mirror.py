@@ -457,3 +457,23 @@ def test_kernels_vs_reference_element_zoo():
     scale = d[:, :, None] * d[:, None, :] + 1e-300
     assert (np.abs(res._cov.cpu().numpy() - g["pb_cov_out"]) / scale)[:, :6, :6].max() < 5e-5
     np.testing.assert_allclose(res.energy.cpu().numpy(), g["pb_energy_out"], rtol=1e-6)
+
+
+def test_kernels_vs_reference_batched_particle_settings():
+    """One beam x three settings (stride-0 beam, per-setting columns) against the reference's
+    own per-setting particles (reference_batched_particles.npz)."""
+    import numpy as np
+
+    g = _ref("reference_batched_particles.npz")
+    energy = torch.tensor(g["energy"])
+    n = g["particles_in"].shape[1]
+    for key, make in (
+        ("dipole_out", lambda: lx.Dipole(length=T(0.5, 0.5, 0.5), angle=torch.tensor(g["dipole_angles"]))),
+        ("quad_out", lambda: lx.Quadrupole(length=T(0.5, 0.5, 0.5), k1=T(1.0, 1.0, 1.0),
+                                           tilt=torch.tensor(g["quad_tilts"]))),
+    ):
+        beam = lx.ParticleBeam(torch.from_numpy(g["particles_in"]), energy).broadcast((3,))
+        seg = lx.Segment([make(), lx.Drift(length=T(0.5)).broadcast((3,))])
+        out = seg.track(beam)
+        for b in range(3):
+            _rel(out.soa[b, :, :n].cpu().numpy(), g[key][b, :, :6].T, 2e-5, f"{key}[{b}]")

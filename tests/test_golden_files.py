@@ -65,7 +65,8 @@ def test_golden_files_are_small_and_complete():
     assert names == ["ares_ea_gradients.npz", "ares_ea_parameter_beam.npz",
                      "ares_ea_particles.npz", "beam_ops.npz", "cavity_dipole_line_particles.npz",
                      # computed by the reference itself (tests/golden/make_reference_golden.py)
-                     "reference_ares_ea.npz", "reference_beam_ops.npz", "reference_bpm_line.npz",
+                     "reference_ares_ea.npz", "reference_batched_particles.npz",
+                     "reference_beam_ops.npz", "reference_bpm_line.npz",
                      "reference_cavity_line.npz", "reference_converters.npz", "reference_element_maps.npz",
                      "reference_gradients.npz",
                      "reference_parameter_beam.npz", "reference_quirks.npz", "reference_zoo.npz"]

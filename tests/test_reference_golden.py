@@ -421,3 +421,25 @@ def test_screen_geometry_is_the_reference_s():
     ox, oy = screen_bin_edges((2448, 2040), (3.3198e-6, 2.4469e-6), 4)
     np.testing.assert_array_equal(ox.numpy(), g["screen_edges_x"])
     np.testing.assert_array_equal(oy.numpy(), g["screen_edges_y"])
+
+
+def test_batched_particle_settings_are_the_reference_s():
+    """tests/test_dipole.py:25-44, tests/test_quadrupole.py:78-99 (config 5 in small): one beam
+    broadcast over three settings.  Note the reference takes the tilt sandwich for the whole
+    batch as soon as ANY setting is tilted (track_methods.py:100-104); here all three are."""
+    g = _load("reference_batched_particles.npz")
+    B = 3
+    energy = torch.full((B,), float(g["energy"][0]), dtype=f32)
+    p_in = torch.tensor(g["particles_in"]).repeat(B, 1, 1)
+    zeros = torch.zeros(B)
+    dip = El("dipole", "b", {"length": torch.full((B,), 0.5), "angle": torch.tensor(g["dipole_angles"]),
+                             "e1": zeros, "e2": zeros, "tilt": zeros, "fringe_integral": zeros,
+                             "fringe_integral_exit": zeros, "gap": zeros})
+    drift = El("drift", "d", {"length": torch.full((B,), 0.5)})
+    out = O.track([dip, drift], O.ParticleBeamO(p_in.clone(), energy))
+    np.testing.assert_array_equal(out.particles.numpy(), g["dipole_out"])
+    assert np.array_equal(g["dipole_out"][0], g["dipole_out"][2])
+    quad = El("quadrupole", "q", {"length": torch.full((B,), 0.5), "k1": torch.ones(B),
+                                  "tilt": torch.tensor(g["quad_tilts"]), "misalignment": torch.zeros(B, 2)})
+    out = O.track([quad, drift], O.ParticleBeamO(p_in.clone(), energy))
+    np.testing.assert_array_equal(out.particles.numpy(), g["quad_out"])
