@@ -306,11 +306,17 @@ class ParticleBeam(Beam):
         mus = [d(mu_x, 0.0), d(mu_xp, 0.0), d(mu_y, 0.0), d(mu_yp, 0.0), d(None, 0.0), d(None, 0.0)]
         sgs = [d(sigma_x, 175e-9), d(sigma_xp, 2e-7), d(sigma_y, 175e-9), d(sigma_yp, 2e-7),
                d(sigma_s, 0.0), d(sigma_p, 0.0)]
-        w = torch.linspace(-1.0, 1.0, n, device=device)
+        # torch.linspace(lo, hi, n) per beam row on the host, exactly as particle_beam.py:474-535
+        # spells it (linspace steps symmetrically from both ends, so mu + sigma * linspace(-1, 1)
+        # differs from it in the last bit; a handful of trace particles, not a hot path)
         ld = (n + 3) & ~3
-        soa = torch.zeros((*shape, 6, ld), device=device)
+        flat = int(torch.Size(shape).numel())
+        host = torch.zeros((flat, 6, ld), dtype=torch.float32)
         for k in range(6):
-            soa[..., k, :n] = mus[k].unsqueeze(-1) + sgs[k].unsqueeze(-1) * w
+            mu_k, sg_k = mus[k].reshape(-1).cpu(), sgs[k].reshape(-1).cpu()
+            for r in range(flat):
+                host[r, k, :n] = torch.linspace(float(mu_k[r] - sg_k[r]), float(mu_k[r] + sg_k[r]), n)
+        soa = host.reshape(*shape, 6, ld).to(device)
         charges = (d(total_charge, 0.0) / n).unsqueeze(-1).expand(*shape, n)
         return cls.from_soa(soa, n, d(energy, 1e8), charges)
 

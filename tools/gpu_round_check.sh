@@ -6,7 +6,7 @@ set -u
 out=gpurun_out/round_check
 mkdir -p "$out"
 timeout 120 python -m pytest tests -x -q -m gpu > "$out/pytest_gpu.log" 2>&1; echo "pytest rc=$?" | tee "$out/rc.txt"
-timeout 120 python -m pytest tests/pending_gpu_reference_mirror.py -q -m gpu > "$out/pytest_pending.log" 2>&1; echo "pending rc=$?" | tee -a "$out/rc.txt"
+timeout 120 python -m pytest tests/test_gpu_reference_mirror.py -q -m gpu > "$out/pytest_pending.log" 2>&1; echo "pending rc=$?" | tee -a "$out/rc.txt"
 timeout 120 python bench.py > "$out/bench_n1.json" 2> "$out/bench_n1.err"; echo "bench rc=$?" | tee -a "$out/rc.txt"
 timeout 60 python tools/track_call_overhead.py > "$out/track_call_overhead.txt" 2>&1; echo "overhead rc=$?" | tee -a "$out/rc.txt"
 timeout 60 python tools/e2e_breakdown.py > "$out/e2e_breakdown.txt" 2>&1; echo "e2e rc=$?" | tee -a "$out/rc.txt"
