@@ -145,7 +145,7 @@ __device__ __forceinline__ void cw_stage(const CWArgs& a, const WarpScratch& w, 
   }
 }
 
-template <bool K6>
+template <bool K6, int OPS>
 __global__ void __launch_bounds__(kCWThreads) compose_warp_kernel(CWArgs a) {
   extern __shared__ __align__(16) float cw_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -215,12 +215,14 @@ __global__ void __launch_bounds__(kCWThreads) compose_warp_kernel(CWArgs a) {
       map_identity(R);
       const Rel rel = make_rel(e_before);
       if (active_cav) {
-        CavityOut co;
-        cavity_setting(P(op.col), P(op.col + 1), P(op.col + 2), P(op.col + 3), e_before, R, co);
+        if constexpr ((OPS & op_bit(LYNX_OP_CAVITY)) != 0) {
+          CavityOut co;
+          cavity_setting(P(op.col), P(op.col + 1), P(op.col + 2), P(op.col + 3), e_before, R, co);
 #pragma unroll
-        for (int i = 0; i < kCavFloats; ++i) w.cav[lane * kCavFloats + i] = co.sc[i];
+          for (int i = 0; i < kCavFloats; ++i) w.cav[lane * kCavFloats + i] = co.sc[i];
+        }
       } else {
-        lm_linear_op<kOpsAll>(R, op, P, rel, e_before);
+        lm_linear_op<OPS>(R, op, P, rel, e_before);
       }
       float* d = w.maps + lane * kCWMap;
 #pragma unroll
@@ -345,7 +347,10 @@ static int cw_launch(const lynx_program_t* p, CWArgs& a, int which, cudaStream_t
     blocks += (unsigned)std::min<int64_t>(2 * p->sm_count, (a.zero_vec4 + kCWThreads - 1) / kCWThreads);
   {
     ProfileScope ps(which, st);
-    compose_warp_kernel<K6><<<blocks, kCWThreads, smem, st>>>(a);
+    if ((p->op_mask & ~kOpsLight) == 0)
+      compose_warp_kernel<K6, kOpsLight><<<blocks, kCWThreads, smem, st>>>(a);
+    else
+      compose_warp_kernel<K6, kOpsAll><<<blocks, kCWThreads, smem, st>>>(a);
   }
   count_launch();
   return cudaGetLastError() == cudaSuccess ? LYNX_OK : LYNX_E_LAUNCH;
