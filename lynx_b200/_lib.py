@@ -10,6 +10,8 @@ from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "lib" / "liblynx_b200.so"
+if os.environ.get("LYNX_B200_LIB"):  # a tuning build (python -m lynx_b200.build --experiments)
+    LIB_PATH = Path(os.environ["LYNX_B200_LIB"])
 
 OK = 0
 E_BADARG, E_BADPROGRAM, E_LAUNCH, E_NOMEM, E_NODEVICE = -1, -2, -3, -4, -5

@@ -12,7 +12,7 @@ from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
 ROOT = HERE.parent
-SRC = ["api.cu", "compose.cu", "compose_warp.cu", "track.cu", "track_pipe.cu", "adjoint.cu", "host.cu", "exchange.cu", "generate.cu", "beamops.cu", "along.cu"]
+SRC = ["api.cu", "compose.cu", "track.cu", "track_pipe.cu", "adjoint.cu", "host.cu", "exchange.cu", "generate.cu", "beamops.cu", "along.cu"]
 OUT = HERE / "lib" / "liblynx_b200.so"
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -28,12 +28,18 @@ def needs_build() -> bool:
     return any(d.stat().st_mtime > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
-    if not force and not needs_build():
+def build(force: bool = False, verbose: bool = False, experiments: bool = False) -> Path:
+    """``experiments``: a second library, ``liblynx_b200_exp.so``, compiled with
+    -DLYNX_EXPERIMENTS (tuning knobs read from the environment; select it with LYNX_B200_LIB).
+    The product library reads no environment variable."""
+    out = OUT.with_name("liblynx_b200_exp.so") if experiments else OUT
+    if not force and not experiments and not needs_build():
         return OUT
     OUT.parent.mkdir(parents=True, exist_ok=True)
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc, *FLAGS, f"-I{ROOT / 'include'}", "-o", str(OUT)]
+    cmd = [nvcc, *FLAGS, f"-I{ROOT / 'include'}", "-o", str(out)]
+    if experiments:
+        cmd += ["-DLYNX_EXPERIMENTS"]
     if verbose:
         cmd += ["-Xptxas", "-v"]
     cmd += [str(HERE / "csrc" / s) for s in SRC]
@@ -42,8 +48,9 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         raise RuntimeError(f"nvcc failed:\n{res.stdout}\n{res.stderr}")
     if verbose:
         print(res.stderr)
-    return OUT
+    return out
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv,
+                experiments="--experiments" in sys.argv))

@@ -1148,7 +1148,11 @@ extern "C" int lynx_track_particles_bwd(
   LYNX_CUDA_OK(cudaGetLastError());
 
   const bool collapse = p->n_cav == 0 && !d_g_out_soa && !d_g_in_soa;
-  static const bool no_collapse = [] { const char* e = getenv("LYNX_NO_COLLAPSE"); return e && e[0] == '1'; }();
+  bool no_collapse = false;
+#ifdef LYNX_EXPERIMENTS
+  static const bool env_nc = [] { const char* e = getenv("LYNX_NO_COLLAPSE"); return e && e[0] == '1'; }();
+  no_collapse = env_nc;
+#endif
   if (collapse && !no_collapse) {
     // one pass per beam row (not per setting): raw moment sums of the incoming beam
     LYNX_CUDA_OK(cudaMemsetAsync(w.in_sums, 0, sizeof(double) * 28 * Bb, st));
@@ -1196,7 +1200,11 @@ extern "C" int lynx_track_particles_bwd(
       sa.target = t;
       if (t > 0) sa.g_in = nullptr;  // written by the first pass only
       ProfileScope ps(3, st);
-      static const bool no_pipe = [] { const char* e = getenv("LYNX_K3"); return e && e[0] == 'l'; }();
+      bool no_pipe = false;
+#ifdef LYNX_EXPERIMENTS
+      static const bool env_np = [] { const char* e = getenv("LYNX_K3"); return e && e[0] == 'l'; }();
+      no_pipe = env_np;
+#endif
       cudaError_t pe = (no_pipe || B > 65535) ? cudaErrorNotSupported
                                               : adj_pipe_dispatch(sa, p->n_cav == 0, p->sm_count, st);
       if (pe == cudaErrorNotSupported) {  // grid-stride LDG variant

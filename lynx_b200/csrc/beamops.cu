@@ -430,15 +430,13 @@ extern "C" int lynx_beam_transform(const float* d_in_soa, int64_t in_row_stride,
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int64_t groups = (N + 3) >> 2;
-  static const int unroll = [] { const char* e = getenv("LYNX_XF_UNROLL"); return e ? atoi(e) : 2; }();
-  static const int ctas = [] { const char* e = getenv("LYNX_XF_CTAS"); return e ? atoi(e) : 8; }();
+  const int unroll = 2, ctas = 8;  // measured best on B200 (tools/beamops_sweep.py)
   const int64_t want = (groups + kXfTPB * unroll - 1) / (kXfTPB * unroll);
   const int64_t per_b = std::max<int64_t>(1, ((int64_t)ctas * sms + B - 1) / B);
   const dim3 grid((unsigned)std::max<int64_t>(1, std::min<int64_t>(want, per_b)), (unsigned)B);
   {
     ProfileScope ps(4, (cudaStream_t)stream);
-    auto kern = unroll == 1 ? beam_transform_kernel<1>
-                : unroll == 4 ? beam_transform_kernel<4> : beam_transform_kernel<2>;
+    auto kern = beam_transform_kernel<2>;
     kern<<<grid, kXfTPB, 0, (cudaStream_t)stream>>>(d_in_soa, in_row_stride, ld_in, N, d_table,
                                                     d_out_soa, ld_out);
   }
@@ -493,10 +491,11 @@ extern "C" int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N
   // persistent: as many CTAs as are resident (3 per SM), each loops over its tiles
   const dim3 sgrid((unsigned)std::max<int64_t>(1, std::min<int64_t>(n_tiles, (3LL * sms + R - 1) / R)),
                    (unsigned)R);
-  // Opt-in (LYNX_APERTURE_ONEPASS=1), a measured negative result: one launch and 48 B per
+  // Tuning builds only (-DLYNX_EXPERIMENTS, LYNX_APERTURE_ONEPASS=1), a measured negative result: one launch and 48 B per
   // particle, but 1.08 ms against 0.29 + 0.08 ms at 32 M particles.  With 1024-particle tiles
   // and 444 resident CTAs running in lock-step a tile's nearest published prefix is ~14
   // look-back windows (dependent L2 round trips) away, and the scatter cannot start before it.
+#ifdef LYNX_EXPERIMENTS
   static const bool onepass = [] { const char* e = getenv("LYNX_APERTURE_ONEPASS"); return e && e[0] == '1'; }();
   if (onepass) {
     // one launch: ticketed tiles + decoupled look-back (48 B per particle)
@@ -519,6 +518,7 @@ extern "C" int lynx_aperture_compact(const float* d_in_soa, int64_t R, int64_t N
     LYNX_CUDA_OK(cudaGetLastError());
     return LYNX_OK;
   }
+#endif
   // three launches: tile counts, scan, scatter (56 B per particle)
   uint32_t* tiles = reinterpret_cast<uint32_t*>(d_workspace);
   const int64_t per_r = std::max<int64_t>(1, (8LL * sms + R - 1) / R);

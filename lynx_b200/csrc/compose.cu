@@ -31,7 +31,6 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
   const int hist_blocks = a.hist_out ? 1 : 0;
   if (hist_blocks && blockIdx.x == gridDim.x - 1) {
     HistAxis* h = reinterpret_cast<HistAxis*>(a.hist_out);
-    if (threadIdx.x < 4) reinterpret_cast<int*>(a.hist_out)[32 + threadIdx.x] = 0;  // internal bbox cell
     if (a.bbox_clear && threadIdx.x < 4) a.bbox_clear[threadIdx.x] = 0;  // this call's cell
     hist_axis_setup(a.hist_ex, a.hist_W, h, threadIdx.x, kComposeTPB);
     hist_axis_setup(a.hist_ey, a.hist_H, h + 1, threadIdx.x, kComposeTPB);
@@ -215,18 +214,7 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   a.zero_rect = zero_rect;
   a.bbox_clear = bbox_clear;
   if (zero_rect && (!hist_out || !zero_ptr || (hist_W & 3))) return LYNX_E_BADARG;
-  // The warp-per-setting variant (compose_warp.cu) is opt-in: on B200 it did not beat
-  // the thread-per-setting walk at any measured B (both are bound by single-warp
-  // instruction latency / fetch, not by instruction count) -- see DESIGN.md.
-  static const bool use_warp = [] {
-    const char* e = getenv("LYNX_K1");
-    return e && e[0] == 'w';
-  }();
-  if (use_warp && !hist_out) {
-    const int r = compose_warp_launch(p, a, st);
-    if (r <= 0) return r;
-  }
-  static const int zero_blocks_per_sm = [] { const char* e = getenv("LYNX_ZERO_BLOCKS"); return e ? atoi(e) : 2; }();
+  const int zero_blocks_per_sm = 2;
   const int n_cols = (int)p->col_offset.size();
   const size_t budget = 40 * 1024;
   const size_t ops_bytes = a.n_ops * sizeof(DevOp);
@@ -300,14 +288,6 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
   a.cov_out = d_cov_out;
   a.bpm_out = d_bpm_out;
   a.energy_out = d_energy_out;
-  static const bool use_warp = [] {
-    const char* e = getenv("LYNX_K1");
-    return e && e[0] == 'w';
-  }();
-  if (use_warp) {
-    const int r = parambeam_warp_launch(p, a, (cudaStream_t)stream);
-    if (r <= 0) return r;
-  }
   const unsigned blocks = (unsigned)((B + kPBThreads - 1) / kPBThreads);
   const int n_cols = (int)p->col_offset.size();
   const size_t smem = a.n_ops * sizeof(DevOp) + (size_t)n_cols * kPBThreads * 4;

@@ -1,5 +1,5 @@
-// Argument blocks and sinks shared by the thread-per-setting (compose.cu) and
-// warp-per-setting (compose_warp.cu) variants of K1 / K6.
+// Argument blocks and sinks of K1 / K6 (compose.cu), also used by the along-s kernel and the
+// adjoint kernels.
 #pragma once
 #include "walk.cuh"
 
@@ -206,9 +206,5 @@ struct ParamBeamArgs {
   float* bpm_out;
   float* energy_out;
 };
-
-// warp-per-setting variants (compose_warp.cu) for small B; return 1 if not applicable
-int compose_warp_launch(const lynx_program_t* p, const ComposeArgs& a, cudaStream_t st);
-int parambeam_warp_launch(const lynx_program_t* p, const ParamBeamArgs& a, cudaStream_t st);
 
 }  // namespace lynx

@@ -10,9 +10,6 @@
 // Algorithmic HBM bytes: 24 B/particle read (+24 B written when outgoing particles are
 // requested); the per-setting record (<1 KB) is read once per CTA into shared memory.
 #include <algorithm>
-#include <mutex>
-#include <utility>
-#include <vector>
 #include <cstdlib>
 
 #include "walk.cuh"
@@ -36,7 +33,8 @@ __global__ void __launch_bounds__(kTPB, 2) track_fwd_kernel(TrackArgs a) {
   __shared__ HistAxis s_hx, s_hy;
 
   const int tid = threadIdx.x;
-  const int64_t b = blockIdx.y;
+  const int64_t b = blockIdx.x / (unsigned)a.ctas_per_row;
+  const int cta = (int)(blockIdx.x - b * a.ctas_per_row), n_cta = a.ctas_per_row;
   {
     const float* src = a.records + b * a.rec_floats;
     for (int i = tid; i < a.rec_floats; i += kTPB) rec[i] = src[i];
@@ -62,7 +60,7 @@ __global__ void __launch_bounds__(kTPB, 2) track_fwd_kernel(TrackArgs a) {
 
   const int64_t n_tiles = (a.N + kTile - 1) / kTile;
   int64_t n_mine = 0;
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  for (int64_t tile = cta; tile < n_tiles; tile += n_cta) {
     const int64_t base = tile * kTile + (int64_t)tid * kVec;
     n_mine += min((int64_t)kTile, a.N - tile * kTile);
     float v[6][kNP];
@@ -251,7 +249,7 @@ __global__ void __launch_bounds__(kTPB, 2) track_fwd_kernel(TrackArgs a) {
 }
 
 template <int MOM, bool HAS_OUT>
-static int launch_track(const TrackArgs& a, dim3 grid, size_t smem, cudaStream_t st) {
+static int launch_track(const TrackArgs& a, unsigned grid, size_t smem, cudaStream_t st) {
   auto k = track_fwd_kernel<MOM, HAS_OUT>;
   if (smem > 48 * 1024) {
     if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
@@ -321,59 +319,6 @@ extern "C" int lynx_track_particles_fwd_persistent(
                         epoch, stream);
 }
 
-// Library-owned scratch for the histogram replicas, one buffer per device,
-// grown on demand and zeroed once: hist_fold_kernel restores the all-zero invariant after
-// every use.  Returns nullptr when the request is over the cap or the allocation fails (the
-// caller then histograms without replicas).
-static float* replica_scratch(size_t bytes) {
-  static std::mutex mu;
-  static void* buf[64] = {nullptr};
-  static size_t cap[64] = {0};
-  constexpr size_t kMaxBytes = (size_t)2 << 30;
-  int dev = 0;
-  if (bytes > kMaxBytes || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  std::lock_guard<std::mutex> lk(mu);
-  if (cap[dev] < bytes) {
-    if (buf[dev]) {
-      cudaDeviceSynchronize();
-      cudaFree(buf[dev]);
-      buf[dev] = nullptr;
-      cap[dev] = 0;
-    }
-    void* q = nullptr;
-    if (cudaMalloc(&q, bytes) != cudaSuccess) {
-      cudaGetLastError();
-      return nullptr;
-    }
-    if (cudaMemset(q, 0, bytes) != cudaSuccess) {
-      cudaFree(q);
-      return nullptr;
-    }
-    buf[dev] = q;
-    cap[dev] = bytes;
-  }
-  return reinterpret_cast<float*>(buf[dev]);
-}
-
-// Persistent state of the fused kernel's grid barrier: 2 words per stream (launches on one
-// stream are serialised, so they can share it; the barrier leaves the state reusable).
-static unsigned int* grid_barrier_state(cudaStream_t st) {
-  static std::mutex mu;
-  static std::vector<std::pair<std::pair<int, cudaStream_t>, unsigned int*>> table;
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
-  std::lock_guard<std::mutex> lk(mu);
-  for (auto& e : table)
-    if (e.first.first == dev && e.first.second == st) return e.second;
-  void* q = nullptr;
-  if (cudaMalloc(&q, 256) != cudaSuccess || cudaMemset(q, 0, 256) != cudaSuccess) {
-    cudaGetLastError();
-    return nullptr;
-  }
-  table.push_back({{dev, st}, reinterpret_cast<unsigned int*>(q)});
-  return reinterpret_cast<unsigned int*>(q);
-}
-
 // d_img_state != nullptr: persistent screen image (lynx_track_particles_fwd_persistent) -- the
 // image is NOT zeroed as a whole; K1's extra blocks clear the rectangle the previous call lit
 // (bounding-box cell (epoch + 1) & 1 of the state), K2 records this call's box in cell epoch & 1.
@@ -399,7 +344,11 @@ static int track_fwd_impl(
 
   // one beam, B > 1 settings, only additive moment / BPM outputs, no cavity: stream the
   // beam once and push its moment sums through every setting's map (adjoint.cu)
-  static const bool no_collapse = [] { const char* e = getenv("LYNX_NO_COLLAPSE"); return e && e[0] == '1'; }();
+  bool no_collapse = false;
+#ifdef LYNX_EXPERIMENTS
+  static const bool env_nc = [] { const char* e = getenv("LYNX_NO_COLLAPSE"); return e && e[0] == '1'; }();
+  no_collapse = env_nc;
+#endif
   if (!no_collapse && in_row_stride == 0 && B > 1 && !d_out_soa && p->n_screen == 0 &&
       p->n_cav == 0 && (moment_mode != 0 || p->n_bpm_slots > 0)) {
     return fwd_collapse_launch(p, d_params, B, d_in_soa, ld_in, N, d_bpm_sums,
@@ -421,7 +370,6 @@ static int track_fwd_impl(
   // (exchange.cu): one fused zeroing range covers both
   const bool bbox_adjacent = d_screen_bbox && has_img && fuse_zero &&
                              (char*)d_screen_bbox + 64 == (char*)d_screen_img;
-  if (B > 65535) return LYNX_E_BADARG;
 
   TrackArgs a{};
   a.in = d_in_soa;
@@ -447,33 +395,9 @@ static int track_fwd_impl(
   a.stamp = bbox_adjacent ? reinterpret_cast<unsigned long long*>(d_screen_bbox + 8) : nullptr;
   a.mom = d_moment_sums;
   a.B = B;
-  static const int dbg = [] { const char* e = getenv("LYNX_DBG"); return e ? atoi(e) : 0; }();
-  a.dbg = dbg;
-  // fused composer fields (track_pipe_kernel<.., OPS>)
-  a.ops = p->d_ops;
-  a.n_ops = (int)p->dev_ops.size();
-  a.final_stage = p->final_stage;
-  a.n_cols = (int)p->col_offset.size();
-  a.col_offset = p->d_col_offset;
-  a.col_stride = p->d_col_stride;
-  a.params = d_params;
-  a.energy_in = d_energy_in;
-  a.energy_out = d_energy_out;
-  a.off_cav = p->off_cav;
-  a.off_centre = p->off_centre;
-  a.off_screen = p->off_screen;
-  // histogram replicas: LYNX_HIST_REPLICAS copies (default 8, 1 = off) once the launch has at
-  // least LYNX_HIST_REPLICAS_MIN particle rows x particles (the fold pass costs ~8 us)
-  static const int n_rep_env = [] { const char* e = getenv("LYNX_HIST_REPLICAS"); return e ? atoi(e) : 8; }();
-  static const long long rep_min = [] { const char* e = getenv("LYNX_HIST_REPLICAS_MIN"); return e ? atoll(e) : 4000000LL; }();
-  a.rep = nullptr;
-  a.n_rep = 1;
-  if (has_img && img_aligned && !(W & 3) && n_rep_env > 1 && n_rep_env <= 64 && B * N >= rep_min) {
-    a.rep = replica_scratch(img_bytes * (size_t)(n_rep_env - 1));
-    if (a.rep) a.n_rep = n_rep_env;
-  }
-  const bool internal_bbox = a.n_rep > 1 && !a.bbox;
-  if (internal_bbox) a.bbox = reinterpret_cast<int*>(hist_ws) + 32;
+  // one merged stage, then the terminal screen, and nothing else reads the beam
+  a.xy_only = (has_img && !d_out_soa && moment_mode == 0 && p->plan.size() == 2 &&
+               p->plan[0].kind == P_AFFINE && p->plan[1].kind == P_SCREEN) ? 1 : 0;
 
   // accumulators are cleared first so that the kernels stay adjacent in the stream
   if (p->n_bpm_slots > 0)
@@ -482,26 +406,11 @@ static int track_fwd_impl(
     LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
   if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
 
-  static const bool force_ldg = [] {
-    const char* e = getenv("LYNX_K2");
-    return e && e[0] == 'l';
-  }();
-  // ---- fused path: no K1 launch; every CTA composes its own setting (B <= SM count)
-  static const bool no_fused = [] { const char* e = getenv("LYNX_FUSED"); return !(e && e[0] == '1'); }();
-  if (!force_ldg && !no_fused && !persistent && B <= p->sm_count) {
-    a.zero_img = fuse_zero ? 1 : 0;
-    a.grid_bar = fuse_zero ? grid_barrier_state(st) : nullptr;
-    if (!fuse_zero || a.grid_bar) {
-      if (a.bbox && !a.zero_img) LYNX_CUDA_OK(cudaMemsetAsync(a.bbox, 0, 16, st));
-      const bool light = (p->op_mask & ~kOpsLight) == 0;
-      const int r = launch_track_pipe(a, moment_mode, d_out_soa != nullptr, p->sm_count, st,
-                                      light ? kOpsLight : kOpsAll);
-      if (r <= 0) return r;
-    }
-  }
-  a.zero_img = 0;
-  a.grid_bar = nullptr;
-
+  bool force_ldg = false;
+#ifdef LYNX_EXPERIMENTS
+  static const bool env_ldg = [] { const char* e = getenv("LYNX_K2"); return e && e[0] == 'l'; }();
+  force_ldg = env_ldg;
+#endif
   // ---- K1 (records, image zeroing, histogram geometry) then K2
   if (d_screen_bbox && !bbox_adjacent) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_bbox, 0, 16, st));
   int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
@@ -519,12 +428,12 @@ static int track_fwd_impl(
   // the bounding box (and with it the persistent image) is a feature of the pipelined kernel
   if (d_screen_bbox || persistent) return LYNX_E_BADPROGRAM;
   a.bbox = nullptr;
-  a.n_rep = 1;
   const int64_t n_tiles = (N + kTile - 1) / kTile;
   int64_t per_b = (2LL * p->sm_count + B - 1) / B;
   if (per_b < 1) per_b = 1;
-  if (B > 65535) return LYNX_E_BADARG;
-  dim3 grid((unsigned)std::min<int64_t>(n_tiles, per_b), (unsigned)B);
+  a.ctas_per_row = (int)std::min<int64_t>(n_tiles, per_b);
+  if ((int64_t)a.ctas_per_row * B > 0x7fffffffLL) return LYNX_E_BADARG;
+  const unsigned grid = (unsigned)((int64_t)a.ctas_per_row * B);
   size_t smem = sizeof(float) * p->rec_floats + sizeof(PlanItem) * p->plan.size() +
                 sizeof(double) * 2 * p->n_snap + 16;
   if (smem > 200 * 1024) return LYNX_E_BADPROGRAM;

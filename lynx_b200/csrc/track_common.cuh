@@ -8,7 +8,7 @@ namespace lynx {
 // Per-axis histogram geometry (hist_axis_setup): prepared by K1 for the pipelined kernel,
 // per CTA by the LDG kernel.
 struct HistAxis {
-  float e0, en, inv, margin;  // margin >= 0.5: the table is always consulted
+  float e0, en, inv, margin;  // inv = n / (en - e0); margin >= 0.5: the table is always consulted
 };
 
 struct TrackArgs {
@@ -30,25 +30,13 @@ struct TrackArgs {
   const float* ey;
   const HistAxis* hist;  // [2] x, y geometry written by K1 (pipelined kernel)
   unsigned long long* stamp;  // [4] debug %globaltimer cell in a symmetric slot's box, or null
-  int tile;     // particles per pipeline tile (K2 pipe variant; set by its launcher)
-  float* rep;   // histogram replicas 1..n_rep-1: [n_rep - 1][B][H][W], all zero on entry
-  int n_rep;    // CTA x histograms into replica x % n_rep (0 = img); folded by hist_fold_kernel
-  int* bbox;             // nullable: [4] max(W - ix), max(ix + 1), max(H - iy), max(iy + 1)
+  int tile;          // particles per pipeline tile (K2 pipe variant; set by its launcher)
+  int stages;        // ring depth of the pipelined kernel (2..4; the histogram tile takes the rest)
+  int ctas_per_row;  // CTAs that share one setting: b = blockIdx.x / ctas_per_row
+  int xy_only;       // the plan is [AFFINE, SCREEN] and nothing else reads the beam: rows x, y only
+  int* bbox;         // nullable: [4] max(W - ix), max(ix + 1), max(H - iy), max(iy + 1)
   double* mom;
   int64_t B;
-  int dbg;  // experiments only (LYNX_DBG): bit0 = skip the screen atomics
-  // ---- fused composer (track_pipe_kernel<.., OPS != 0>): every CTA walks its own setting's
-  //      lattice into the shared-memory record; no K1 launch, no record round trip
-  const DevOp* ops;
-  int n_ops, final_stage, n_cols;
-  const int64_t* col_offset;
-  const int32_t* col_stride;
-  const float* params;
-  const float* energy_in;
-  float* energy_out;
-  int off_cav, off_centre, off_screen;
-  unsigned int* grid_bar;  // [2] arrival count, generation (library-owned, self-resetting)
-  int zero_img;            // the kernel zeroes the image (+ bbox) itself, behind a grid barrier
 };
 
 __device__ __forceinline__ float4 ld_stream(const float* p) {
@@ -86,6 +74,30 @@ __device__ __forceinline__ void apply_affine(const float* __restrict__ m, float 
   }
 }
 
+// Rows 0 and 2 only: (x, y) of A v + c, in apply_affine's order of operations (bit-identical).
+// What a terminal screen needs of the last stage when nothing else reads the beam.
+template <int NP>
+__device__ __forceinline__ void apply_affine_xy(const float* __restrict__ m, const float (&v)[6][NP],
+                                                float (&x)[NP], float (&y)[NP]) {
+  float rx[7], ry[7];
+#pragma unroll
+  for (int k = 0; k < 7; ++k) {
+    rx[k] = m[k];
+    ry[k] = m[14 + k];
+  }
+#pragma unroll
+  for (int j = 0; j < NP; ++j) {
+    float ax = rx[6], ay = ry[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      ax = fmaf(rx[k], v[k][j], ax);
+      ay = fmaf(ry[k], v[k][j], ay);
+    }
+    x[j] = ax;
+    y[j] = ay;
+  }
+}
+
 // The linear map of an active cavity (cavity.py:248-325, maps.cuh cavity_setting) is three
 // 2x2 blocks on (x, xp), (y, yp), (s, p) with a zero kick column: 12 of the 42 entries.  Same
 // order of operations as apply_affine on the non-zero entries, so the result is bit-identical
@@ -118,8 +130,11 @@ __device__ __forceinline__ void apply_block2(const float* __restrict__ m, float 
 
 // Bin lookup against the reference's fp32 edge table: left-closed bins, last bin
 // right-closed, out-of-range dropped (torch.histogramdd semantics).
-// Slow path: the table decides (exact).
-static __device__ __noinline__ int find_bin_table(float x, const float* __restrict__ e, int n, int i) {
+// Slow path: the range check and the table decide (exact).  Out of line: it holds dependent
+// table loads and is taken by a few particles in a thousand.
+static __device__ __noinline__ int find_bin_slow(float x, const float* __restrict__ e, int n, int i,
+                                                 float e0, float en) {
+  if (!(x >= e0 && x <= en)) return -1;
   i = min(max(i, 0), n - 1);
   if (x < e[i]) {
     do { --i; } while (i > 0 && x < e[i]);
@@ -129,38 +144,53 @@ static __device__ __noinline__ int find_bin_table(float x, const float* __restri
   return i;
 }
 
-
-// Fast path: t = (x - e0) * n/(en - e0) names the bin outright unless its fractional
-// part is within `margin` of an edge; margin covers the fp32 error of t (<= ~3 eps n)
-// plus the verified deviation of the table from an ideal linspace (hist_axis_setup),
-// so every particle lands in exactly the bin the table would give.
+// Fast path: t = x * inv + off = (x - e0) * n / (en - e0) names the bin outright unless its
+// fractional part is within `margin` of an edge.  margin = d + delta (hist_axis_setup): d is the
+// MEASURED deviation of the table from the ideal linspace through its end points, in bins -- a
+// particle whose exact t* has frac(t*) in [d, 1 - d) lies in bin floor(t*) of the table -- and
+// delta >= |t - t*| bounds the fp32 error of t (n * 2^-21 for |e0|, |en| <= en - e0: the relative
+// errors of inv, of off and of the final rounding, each acting on a magnitude <= n).  So every
+// particle lands in exactly the bin the table would give.  8 instructions on the fast path.
+__device__ __forceinline__ int find_bin(float x, const float* __restrict__ e, int n, float inv,
+                                        float off, float margin, const HistAxis& h) {
+  const float t = fmaf(x, inv, off);
+  const int i = __float2int_rd(t);
+  const float fr = t - (float)i;  // exact
+  if ((unsigned)i < (unsigned)n && fabsf(fr - 0.5f) < 0.5f - margin) return i;
+  return find_bin_slow(x, e, n, i, h.e0, h.en);
+}
 __device__ __forceinline__ int find_bin(float x, const float* __restrict__ e, int n,
                                         const HistAxis& h) {
-  if (!(x >= h.e0 && x <= h.en)) return -1;
-  const float t = (x - h.e0) * h.inv;
-  const int i = (int)t;
-  const float fr = t - (float)i;
-  if (i < n && fr > h.margin && fr < 1.f - h.margin) return i;
-  return find_bin_table(x, e, n, i);
+  return find_bin(x, e, n, h.inv, -h.e0 * h.inv, h.margin, h);
 }
 
-// Cooperative (whole CTA) check that edge table `e` (n+1 values) deviates from the ideal
-// linspace by < 2^-10 of a bin; fills `h`.  Contains __syncthreads.
+// Cooperative (whole CTA) measurement of how far edge table `e` (n+1 values) deviates from the
+// ideal linspace through its end points; fills `h`.  Contains __syncthreads.
 __device__ __forceinline__ void hist_axis_setup(const float* __restrict__ e, int n, HistAxis* h,
                                                 int tid, int nthreads) {
+  __shared__ unsigned int s_dev;  // max deviation in bins (bits of a non-negative float)
+  if (tid == 0) s_dev = 0u;
+  __syncthreads();
   const double e0 = (double)e[0], en = (double)e[n];
   const double step = (en - e0) / n;
-  int bad = 0;
-  for (int i = tid; i <= n; i += nthreads)
-    bad |= fabs((double)e[i] - (e0 + step * i)) > step * (1.0 / 1024.0);
-  bad = __syncthreads_or(bad);
-  if (tid == 0) {
-    h->e0 = (float)e0;
-    h->en = (float)en;
-    h->inv = (float)n / ((float)en - (float)e0);
-    const float m = fmaxf(1.f / 256.f, (float)n * (1.f / 1048576.f));
-    h->margin = bad ? 1.f : m;
+  float dev = 0.f;
+  for (int i = tid; i <= n; i += nthreads) {
+    const float d = (float)(fabs((double)e[i] - (e0 + step * i)) / step);
+    dev = (d <= 1e30f) ? fmaxf(dev, d) : 2.f;  // NaN / inf in the table: never trust the fast path
   }
+  atomicMax(&s_dev, __float_as_uint(dev));
+  __syncthreads();
+  if (tid == 0) {
+    const float d = __uint_as_float(s_dev);
+    const float fe0 = (float)e0, fen = (float)en;
+    h->e0 = fe0;
+    h->en = fen;
+    h->inv = (float)n / (fen - fe0);
+    const bool ok = d < 0.25f && step > 0.0 && fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
+    // margin >= 0.5 means: the table is always consulted
+    h->margin = ok ? 1.25f * d + (float)n * (1.f / 2097152.f) + (1.f / 1048576.f) : 1.f;
+  }
+  __syncthreads();
 }
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -185,7 +215,7 @@ __host__ __device__ constexpr int tri(int i, int j) { return i * 6 - i * (i - 1)
 
 // TMA-bulk pipelined variant (track_pipe.cu); returns 1 if it cannot take the problem.
 int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_count,
-                      cudaStream_t st, int fused_ops = 0);
+                      cudaStream_t st);
 
 // Accumulate shifted first / second moments of one particle (d = v - centre).
 template <int MOM>

@@ -140,22 +140,6 @@ def test_aperture_compaction_is_byte_exact(shape, n):
         np.testing.assert_array_equal(ql[r, : n - m], lq)
 
 
-def test_aperture_one_pass_variant():
-    """The opt-in single-launch variant (ticketed tiles + decoupled look-back,
-    LYNX_APERTURE_ONEPASS=1) passes the same byte-exact tests (in a subprocess: the switch is
-    read once per process)."""
-    import os
-    import subprocess
-    import sys
-
-    env = dict(os.environ, LYNX_APERTURE_ONEPASS="1")
-    res = subprocess.run(
-        [sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", os.path.abspath(__file__), "-k",
-         "compaction_is_byte_exact or all_or_nothing or element_in_a_segment"],
-        env=env, capture_output=True, text=True, timeout=600)
-    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
-
-
 def test_aperture_all_or_nothing():
     x = _planes(10_000, seed=1)
     counts, kept, _, _, _ = _compact(x, np.inf, np.inf, "rectangular")

@@ -494,26 +494,49 @@ def test_parameter_beam_screen_reading():
     assert torch.equal(got.sum(dim=2).argmax(dim=1), want.sum(dim=2).argmax(dim=1))
 
 
-def test_screen_tests_with_histogram_replicas():
-    """The replicated-histogram path (csrc/track_pipe.cu hist_fold_kernel) only switches on
-    for launches of >= 4 M particles; rerun every screen test of this suite (and the host /
-    golden ones) in a subprocess with the threshold lowered to 1 so the small parity
-    cases exercise it, twice in one process so the 'replicas are zero again' invariant
-    is checked too."""
-    import os
-    import subprocess
-    import sys
-
-    env = dict(os.environ, LYNX_HIST_REPLICAS_MIN="1")
-    if env.get("LYNX_REPLICA_SUBPROCESS"):
-        pytest.skip("already inside the replica subprocess")
-    env["LYNX_REPLICA_SUBPROCESS"] = "1"
-    here = os.path.dirname(os.path.abspath(__file__))
-    cmd = [sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", "-k", "screen or host_buffer or golden",
-           os.path.join(here, "test_gpu_parity.py"), os.path.join(here, "test_golden_files.py"),
-           os.path.join(here, "test_gpu_parity.py")]
-    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+@pytest.mark.parametrize("case", ["centred", "corner", "pencil", "wide", "drifting", "odd_width", "three_settings"])
+def test_histogram_tile_placements(case):
+    """The shared-memory histogram tile of K2 (csrc/track_pipe.cu) is placed per CTA from the
+    statistics of the CTA's first pipeline tile; wherever it lands -- on the beam, against an image
+    border, on a beam narrower than a pixel or far wider than the tile, on a beam that moves away
+    while the CTA works through its tiles -- the image must equal torch.histogramdd of the same
+    coordinates bit for bit.  300 k particles so that every CTA gets a tile (>= ~1400 particles per
+    CTA); 'odd_width' has W % 4 != 0, which takes the path without the tile (16-byte rows are
+    needed for the bulk reduce)."""
+    n, W, H = 300_000, 640, 480
+    px = (1e-5, 1.25e-5)
+    rng = np.random.default_rng(123)
+    B = 3 if case == "three_settings" else 1
+    mis = torch.zeros(B, 2)
+    x = rng.normal(0.0, 40 * px[0], n)
+    y = rng.normal(0.0, 25 * px[1], n)
+    if case == "corner":  # the beam hangs over the lower left corner: tile clamped to the image
+        x += -W / 2 * px[0] + 10 * px[0]
+        y += -H / 2 * px[1] + 5 * px[1]
+    elif case == "pencil":
+        x, y = rng.normal(3.3 * px[0], 0.05 * px[0], n), rng.normal(-7.7 * px[1], 0.05 * px[1], n)
+    elif case == "wide":
+        x, y = rng.uniform(-W / 2 * px[0], W / 2 * px[0], n), rng.uniform(-H / 2 * px[1], H / 2 * px[1], n)
+    elif case == "drifting":  # the centre moves by 8 sigma over the particle index
+        x += np.linspace(-160, 160, n) * px[0]
+    elif case == "odd_width":
+        W = 642
+    elif case == "three_settings":
+        mis = torch.tensor([[0.0, 0.0], [1.2e-3, 0.0], [-2.0e-3, 0.0]])
+    p = torch.zeros(1, n, 7)
+    p[0, :, 0], p[0, :, 2], p[0, :, 6] = torch.from_numpy(x).float(), torch.from_numpy(y).float(), 1.0
+    scr = lx.Screen(resolution=torch.tensor([float(W), float(H)]), pixel_size=torch.tensor(px),
+                    misalignment=mis, is_active=True, name="s")
+    seg = lx.Segment([lx.Drift(torch.zeros(B)), scr])
+    beam = lx.ParticleBeam(p, torch.tensor([1e8]))
+    assert seg.track(beam.broadcast((B,)) if B > 1 else beam) is lx.Beam.empty
+    img = scr.reading.cpu()
+    assert tuple(img.shape) == (B, H, W)
+    ex, ey = screen_bin_edges((W, H), px)
+    xs = p[0, :, 0].unsqueeze(0) - mis[:, :1]
+    want = screen_reading_particles(xs, p[0, :, 2].unsqueeze(0).expand(B, -1), ex, ey)
+    assert torch.equal(img, want), f"{case}: {(img != want).sum().item()} pixels differ"
+    assert img.sum().item() > 0.3 * n * B
 
 
 def test_screen_exchange_kernel_single_rank():

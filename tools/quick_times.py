@@ -1,10 +1,10 @@
-"""Quick device timings of the workloads the docs quote (one line each), for A/B runs with
-environment switches:  python tools/quick_times.py [names...]
+"""Quick device timings of the workloads the docs quote (one line each), for A/B runs:
+    python tools/quick_times.py [names...]
 
     step1m   ARES EA 1 M particles + screen, whole step (K1 + K2), L2 flushed between steps
     scr32m   32 M particles, terminal screen
     out32m   32 M particles, outgoing particles
-    cfg4     config-4 shard (12.5 M, cavity + dipole), screen
+    cfg4     config-4 shard (12.5 M, cavity + dipole), screen / outgoing particles
     k6       ParameterBeam env-steps at B = 4096, 65536, 2^20
 """
 import os
@@ -41,10 +41,12 @@ def main():
     if "scr32m" in names:
         report("scr32m (screen, 24 B)", bench.ParticleWorkload(32_000_000, dev, 1002))
     if "out32m" in names:
-        report("out32m (particles, 48 B)", bench.ParticleWorkload(32_000_000, dev, 1002, screen=False, want_out=True))
+        report("out32m (particles, 48 B)",
+               bench.ParticleWorkload(32_000_000, dev, 1002, screen=False, want_out=True))
     if "cfg4" in names:
         report("cfg4 12.5M screen", bench.ParticleWorkload(12_500_000, dev, 1004, lattice="cfg4"))
-        report("cfg4 12.5M out", bench.ParticleWorkload(12_500_000, dev, 1004, lattice="cfg4", screen=False, want_out=True))
+        report("cfg4 12.5M out",
+               bench.ParticleWorkload(12_500_000, dev, 1004, lattice="cfg4", screen=False, want_out=True))
     if "k6" in names:
         for B in (4096, 65536, 1 << 20):
             report(f"k6 B={B}", bench.ParamBeamWorkload(B, dev), which=2)
