@@ -173,9 +173,11 @@ __device__ __forceinline__ void hist_axis_setup(const float* __restrict__ e, int
   __syncthreads();
   const double e0 = (double)e[0], en = (double)e[n];
   const double step = (en - e0) / n;
+  const double inv_step = 1.0 / step;  // one division, not one per table entry: this runs in K1's
+                                       // last block, on the critical path of the 1 M-particle step
   float dev = 0.f;
   for (int i = tid; i <= n; i += nthreads) {
-    const float d = (float)(fabs((double)e[i] - (e0 + step * i)) / step);
+    const float d = (float)(fabs((double)e[i] - (e0 + step * i)) * inv_step);
     dev = (d <= 1e30f) ? fmaxf(dev, d) : 2.f;  // NaN / inf in the table: never trust the fast path
   }
   atomicMax(&s_dev, __float_as_uint(dev));
