@@ -37,7 +37,9 @@ typedef enum {
   LYNX_E_BADPROGRAM = -2, /* unknown opcode, column out of range, bad slot        */
   LYNX_E_LAUNCH = -3,     /* CUDA reported an error while enqueueing              */
   LYNX_E_NOMEM = -4,      /* handle / workspace allocation failed                 */
-  LYNX_E_NODEVICE = -5    /* no CUDA device: there is NO CPU fallback             */
+  LYNX_E_NODEVICE = -5,   /* no CUDA device: there is NO CPU fallback             */
+  LYNX_E_TOOLARGE = -6    /* lynx_track_particles_fwd_noalloc: the problem needs more scratch
+                             than the library's static LYNX_NOALLOC_WORKSPACE_BYTES      */
 } lynx_status;
 
 /* Lattice program.  One op per reference element, in beam order.
@@ -178,6 +180,25 @@ int lynx_track_particles_fwd_persistent(const lynx_program_t*, const float* d_pa
                                         const float* d_energy_in, float* d_energy_out,
                                         void* d_workspace, int32_t* d_img_state, uint32_t epoch,
                                         lynx_stream_t stream);
+
+/* The same call for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * There is no workspace argument: the K1 -> K2 records live in
+ * a static device array of LYNX_NOALLOC_WORKSPACE_BYTES bytes that every GPU loading the
+ * library holds until exit; the call allocates nothing (no cudaMalloc / cudaFree).  Returns
+ * LYNX_E_TOOLARGE when lynx_workspace_bytes(prog, B) exceeds that size (ARES EA: B <= ~4000
+ * settings).  All calls on a device share the array: calls that overlap on the GPU (different
+ * streams, concurrently replayed graphs) race; calls on one stream do not.  Inputs and outputs
+ * are the caller's, exactly as for lynx_track_particles_fwd.                                  */
+#define LYNX_NOALLOC_WORKSPACE_BYTES (1 << 20)
+int lynx_track_particles_fwd_noalloc(const lynx_program_t*, const float* d_params, int64_t B,
+                                     const float* d_in_soa, int64_t in_row_stride, int64_t ld_in,
+                                     int64_t N, float* d_out_soa, int64_t ld_out,
+                                     double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H,
+                                     const float* d_edges_x, const float* d_edges_y,
+                                     double* d_moment_sums, int32_t moment_mode,
+                                     const float* d_energy_in, float* d_energy_out,
+                                     lynx_stream_t stream);
 
 /* Multi-GPU exchange step of the particle-sharded path (one process per GPU; the reference
  * has no distributed code): all-reduce (SUM) of the screen image over

@@ -14,7 +14,8 @@ if os.environ.get("LYNX_B200_LIB"):  # a tuning build (python -m lynx_b200.build
     LIB_PATH = Path(os.environ["LYNX_B200_LIB"])
 
 OK = 0
-E_BADARG, E_BADPROGRAM, E_LAUNCH, E_NOMEM, E_NODEVICE = -1, -2, -3, -4, -5
+E_BADARG, E_BADPROGRAM, E_LAUNCH, E_NOMEM, E_NODEVICE, E_TOOLARGE = -1, -2, -3, -4, -5, -6
+NOALLOC_WORKSPACE_BYTES = 1 << 20  # LYNX_NOALLOC_WORKSPACE_BYTES
 
 # opcodes / flags (mirror include/lynx_b200.h)
 OP_MARKER, OP_DRIFT, OP_QUAD, OP_HCOR, OP_VCOR, OP_DIPOLE = 0, 1, 2, 3, 4, 5
@@ -49,6 +50,11 @@ SIGNATURES = {
         C.c_int,
         [_vp, _vp, _i64, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _i32, _i32, _vp, _vp, _vp,
          _i32, _vp, _vp, _vp, _vp],
+    ),
+    "lynx_track_particles_fwd_noalloc": (
+        C.c_int,
+        [_vp, _vp, _i64, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _i32, _i32, _vp, _vp, _vp,
+         _i32, _vp, _vp, _vp],
     ),
     "lynx_track_particles_fwd_bbox": (
         C.c_int,

@@ -12,7 +12,7 @@ from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
 ROOT = HERE.parent
-SRC = ["api.cu", "compose.cu", "track.cu", "track_pipe.cu", "adjoint.cu", "host.cu", "exchange.cu", "generate.cu", "beamops.cu", "along.cu"]
+SRC = ["api.cu", "compose.cu", "track.cu", "track_pipe.cu", "adjoint.cu", "host.cu", "exchange.cu", "generate.cu", "beamops.cu", "along.cu", "noalloc.cu"]
 OUT = HERE / "lib" / "liblynx_b200.so"
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -103,6 +103,7 @@ extern "C" const char* lynx_status_str(int s) {
     case LYNX_E_LAUNCH: return "CUDA launch/enqueue error";
     case LYNX_E_NOMEM: return "out of memory";
     case LYNX_E_NODEVICE: return "no CUDA device (there is no CPU fallback)";
+    case LYNX_E_TOOLARGE: return "problem exceeds the static scratch of the no-allocation entry point (LYNX_NOALLOC_WORKSPACE_BYTES)";
     default: return "unknown";
   }
 }
