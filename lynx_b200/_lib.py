@@ -116,6 +116,17 @@ SIGNATURES = {
     ),
 }
 
+# Entry points that ENQUEUE device work on a caller-supplied stream: the set an XLA FFI shim has
+# to adapt (csrc/lynx_xla_ffi.cc; tests/test_xla_ffi_table.py keeps the two in step).
+STREAM_LAUNCHERS = (
+    "lynx_compose_maps", "lynx_track_particles_fwd", "lynx_track_particles_fwd_noalloc",
+    "lynx_track_particles_fwd_bbox", "lynx_track_particles_fwd_persistent",
+    "lynx_track_particles_bwd", "lynx_parambeam_fwd", "lynx_parambeam_bwd", "lynx_parambeam_along",
+    "lynx_screen_pdf", "lynx_beam_generate", "lynx_beam_generate_ellipsoid", "lynx_beam_transform",
+    "lynx_aperture_compact", "lynx_aos7_to_soa6", "lynx_soa6_to_aos7", "lynx_screen_allreduce",
+    "lynx_screen_allreduce_mc",
+)
+
 _lib = None
 
 
