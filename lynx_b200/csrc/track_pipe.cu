@@ -90,6 +90,16 @@ __device__ __forceinline__ void consumers_sync() { asm volatile("bar.sync 1, %0;
 __device__ __forceinline__ void red_add_f32(float* p, float v) {
   asm volatile("red.relaxed.gpu.global.add.f32 [%0], %1;" ::"l"(p), "f"(v));
 }
+__device__ __forceinline__ unsigned vmax_u16x2(unsigned a, unsigned b) {
+  unsigned r;
+  asm("max.u16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned vmin_u16x2(unsigned a, unsigned b) {
+  unsigned r;
+  asm("min.u16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
 __device__ __forceinline__ void bulk_reduce_add_f32(float* dst_gmem, const float* src_smem,
                                                     uint32_t bytes) {
   asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst_gmem),
@@ -244,7 +254,9 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
     // re-read where they are used (registers are the scarce resource here)
     const bool use_win = TILE && img_b && win_words > 0;
     bool win_set = false;
-    int bb0 = 0, bb1 = 0, bb2 = 0, bb3 = 0;  // bounding box of the touched bins (exchange.cu)
+    // bounding box of the touched bins (exchange.cu, persistent image), two u16 lanes per word:
+    // bb_max = max(ix + 1) | max(iy) << 16 over valid particles (0: none), bb_min = min(ix) | min(iy) << 16
+    unsigned bb_max = 0u, bb_min = 0xffffffffu;
 
     // Screen.track + Screen.reading for four particles (screen.py:126-141 + 195-211)
     auto screen4 = [&](const PlanItem& p, const float (&xv)[4], const float (&yv)[4],
@@ -253,34 +265,41 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
       const bool yfix = (p.c & LYNX_F_SCREEN_Y_FIX) != 0;
       const HistAxis hx = s_hist[0], hy = s_hist[1];
       const float offx = -hx.e0 * hx.inv, offy = -hy.e0 * hy.inv;
+      const bool regular = hx.margin < 0.5f && hy.margin < 0.5f;  // warp-uniform
       int pk[4];  // ix | iy << 16, or -1 (dead lane / outside the screen)
-      float c = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, syy = 0.f;
 #pragma unroll
       for (int l = 0; l < 4; ++l) {
         const float x = xv[l] - mx;
         const float y = yfix ? yv[l] - my : yv[l];
-        const int ix = find_bin(x, a.ex, a.W, hx.inv, offx, hx.margin, hx);
-        const int iy = find_bin(y, a.ey, a.H, hy.inv, offy, hy.margin, hy);
+        int ix, iy;
+        if (regular) {
+          ix = find_bin_regular(x, a.ex, a.W, hx.inv, offx, hx.margin, hx.e0, hx.en);
+          iy = find_bin_regular(y, a.ey, a.H, hy.inv, offy, hy.margin, hy.e0, hy.en);
+        } else {
+          ix = find_bin(x, a.ex, a.W, hx);
+          iy = find_bin(y, a.ey, a.H, hy);
+        }
         const bool ok = live[l] && ix >= 0 && iy >= 0;
         pk[l] = ok ? (ix | (iy << 16)) : -1;
-        if (ok) {
-          bb0 = max(bb0, a.W - ix);
-          bb1 = max(bb1, ix + 1);
-          bb2 = max(bb2, a.H - iy);
-          bb3 = max(bb3, iy + 1);
-        }
-        if (TILE && !win_set && ok) {
-          const float dx = (float)(ix - (a.W >> 1)), dy = (float)(iy - (a.H >> 1));
-          c += 1.f;
-          sx += dx;
-          sy += dy;
-          sxx = fmaf(dx, dx, sxx);
-          syy = fmaf(dy, dy, syy);
-        }
+        // invalid = 0xffffffff: neutral for the min; + 1 makes it 0, neutral for the max (a valid
+        // ix + 1 <= 65535 does not carry into the iy lane; W, H < 32768 is checked by the launcher)
+        bb_max = vmax_u16x2(bb_max, (unsigned)pk[l] + 1u);
+        bb_min = vmin_u16x2(bb_min, (unsigned)pk[l]);
       }
       if constexpr (TILE) {
-        if (use_win && !win_set) {
+        if (use_win && !win_set) {  // warp-uniform: the CTA's first pipeline tile only
           // place the tile on the beam: mean +- k sigma of this CTA's first pipeline tile
+          float c = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, syy = 0.f;
+#pragma unroll
+          for (int l = 0; l < 4; ++l)
+            if (pk[l] >= 0) {
+              const float dx = (float)((pk[l] & 0xffff) - (a.W >> 1)), dy = (float)((pk[l] >> 16) - (a.H >> 1));
+              c += 1.f;
+              sx += dx;
+              sy += dy;
+              sxx = fmaf(dx, dx, sxx);
+              syy = fmaf(dy, dy, syy);
+            }
           c = warp_sum(c);
           sx = warp_sum(sx);
           sy = warp_sum(sy);
@@ -322,18 +341,17 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
       }
       const HistWindow hw = s_win;
 #pragma unroll
-      for (int l = 0; l < 4; ++l)
-        if (pk[l] >= 0) {
-          const int ix = pk[l] & 0xffff, iy = pk[l] >> 16;
-          if constexpr (TILE) {
-            const unsigned dx = (unsigned)(ix - hw.x0), dy = (unsigned)(iy - hw.y0);
-            if (dx < (unsigned)hw.w && dy < (unsigned)hw.h) {
-              atomicAdd(win + dy * hw.w + dx, 1u);
-              continue;
-            }
-          }
-          red_add_f32(img_b + (int64_t)(a.H - 1 - iy) * a.W + ix, 1.0f);
+      for (int l = 0; l < 4; ++l) {
+        const bool ok = pk[l] >= 0;
+        const int ix = pk[l] & 0xffff, iy = pk[l] >> 16;
+        bool in = false;
+        if constexpr (TILE) {
+          const unsigned dx = (unsigned)(ix - hw.x0), dy = (unsigned)(iy - hw.y0);
+          in = ok && dx < (unsigned)hw.w && dy < (unsigned)hw.h;
+          if (in) atomicAdd(win + dy * hw.w + dx, 1u);
         }
+        if (ok && !in) red_add_f32(img_b + (unsigned)((a.H - 1 - iy) * a.W + ix), 1.0f);  // W H < 2^30
+      }
     };
 
     int s = 0;
@@ -472,11 +490,13 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
     if (a.bbox && img_b) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
-        bb0 = max(bb0, __shfl_xor_sync(0xffffffffu, bb0, o));
-        bb1 = max(bb1, __shfl_xor_sync(0xffffffffu, bb1, o));
-        bb2 = max(bb2, __shfl_xor_sync(0xffffffffu, bb2, o));
-        bb3 = max(bb3, __shfl_xor_sync(0xffffffffu, bb3, o));
+        bb_max = vmax_u16x2(bb_max, __shfl_xor_sync(0xffffffffu, bb_max, o));
+        bb_min = vmin_u16x2(bb_min, __shfl_xor_sync(0xffffffffu, bb_min, o));
       }
+      // cell layout: max(W - ix), max(ix + 1), max(H - iy), max(iy + 1); all 0 = nothing lit
+      const bool any = (bb_max & 0xffffu) != 0u;
+      const int bb0 = any ? a.W - (int)(bb_min & 0xffffu) : 0, bb1 = (int)(bb_max & 0xffffu);
+      const int bb2 = any ? a.H - (int)(bb_min >> 16) : 0, bb3 = any ? (int)(bb_max >> 16) + 1 : 0;
       // one set of global atomics per CTA, not per warp: 16 x 148 x 4 atomicMax on the same
       // four words were ~3 us of the 1 M-particle step (serialised in one L2 slice)
       if (lane == 0 && bb1 > 0) {
@@ -488,7 +508,9 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
       consumers_sync();
       if (cid < 4 && s_bb[1] > 0) atomicMax(a.bbox + cid, s_bb[cid]);
     }
-    if constexpr (TILE) bulk_wait_all();  // the tile's rows have been added (no-op without a flush)
+    // the tile's shared memory has been read by the bulk reduces (no-op without a flush); the
+    // additions themselves complete with the grid, which is what a dependent launch waits for
+    if constexpr (TILE) bulk_wait_read<0>();
     // Let a programmatically-serialized follower (multi-GPU exchange kernel) start launching
     // once the consumers of every CTA are through their tiles.  The first thread of a CTA to
     // execute this counts for the CTA, so it must not sit on a path the loader warp reaches
@@ -566,6 +588,7 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
                       cudaStream_t st) {
   const uint32_t cap = 227 * 1024 - 4096 - 1024;  // static shared memory takes the rest
   const bool hist = a.img != nullptr && !has_out;
+  if (a.img && (a.W >= 32768 || a.H >= 32768)) return 1;  // bins travel as two 15-bit lanes
   // grid: every CTA of a row gets the same number of tiles (1 M particles on 148 CTAs: 4 x 1696
   // each instead of 3 or 4 x 2048 -- the longest CTA sets the kernel time)
   int64_t per_b = (sm_count + a.B - 1) / a.B;
@@ -589,11 +612,16 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
   if (hist && !(a.W & 3) && !((uintptr_t)a.img & 15) && (((int64_t)a.W * a.H) & 3) == 0) {
     int px_per_particle = 3, min_stages = 2;
 #ifdef LYNX_EXPERIMENTS
+    int64_t max_words = 1 << 30;
     px_per_particle = env_int("LYNX_TILE_PXPP", px_per_particle);
     min_stages = env_int("LYNX_TILE_MIN_STAGES", min_stages);
+    max_words = env_int("LYNX_TILE_MAX_WORDS", 1 << 30);
 #endif
     const int64_t n_cta = (a.N + ctas_per_row - 1) / ctas_per_row;
     int64_t want = std::min<int64_t>(n_cta * px_per_particle, (int64_t)a.W * a.H);
+#ifdef LYNX_EXPERIMENTS
+    want = std::min<int64_t>(want, max_words);
+#endif
     if (want >= 4096) {
       for (stages = 4; stages > min_stages; --stages) {
         const uint32_t used = fixed + (uint32_t)stages * kStageFloats * 4u;
