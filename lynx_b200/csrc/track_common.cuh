@@ -160,18 +160,33 @@ static __device__ __noinline__ int find_bin_slow(float x, const float* __restric
 // 100 instructions per warp and tile, measured); doing the near-edge work branch-free for every
 // lane cost 29 instructions per lookup (measured as well).  x in [e0, en] implies floor(t) in
 // [-1, n] and j in [0, n], so nothing needs clamping.
-__device__ __forceinline__ int find_bin_regular(float x, const float* __restrict__ e, int n,
-                                                float inv, float off, float margin, float e0,
-                                                float en) {
+// Two-step form, so that a thread can do the cheap part for all its lookups first and then take
+// ONE branch for the rare near-edge cases (a branch per lookup cost ~9 instructions each in
+// reconvergence bookkeeping, measured):
+//   bin_guess: floor(t), or -1 outside [e0, en]; `near` = the table has to decide
+//   bin_near_edge: the decision
+__device__ __forceinline__ int bin_guess(float x, float inv, float off, float margin, float e0,
+                                         float en, bool& near, float& fr_out) {
   const float t = fmaf(x, inv, off);
   const int i = __float2int_rd(t);
   const float fr = t - (float)i;
   const bool valid = x >= e0 && x <= en;  // NaN fails both
-  int b = valid ? i : -1;
-  if (valid && !(fabsf(fr - 0.5f) < 0.5f - margin)) {
-    const int j = i + (fr > 0.5f ? 1 : 0);  // the nearest edge
-    b = min(x >= __ldg(e + j) ? j : j - 1, n - 1);  // x == en: the last bin is right-closed
-  }
+  near = valid && !(fabsf(fr - 0.5f) < 0.5f - margin);
+  fr_out = fr;
+  return valid ? i : -1;
+}
+__device__ __forceinline__ int bin_near_edge(float x, const float* __restrict__ e, int n, int i,
+                                             float fr) {
+  const int j = i + (fr > 0.5f ? 1 : 0);  // the nearest edge
+  return min(x >= __ldg(e + j) ? j : j - 1, n - 1);  // x == en: the last bin is right-closed
+}
+__device__ __forceinline__ int find_bin_regular(float x, const float* __restrict__ e, int n,
+                                                float inv, float off, float margin, float e0,
+                                                float en) {
+  bool near;
+  float fr;
+  int b = bin_guess(x, inv, off, margin, e0, en, near, fr);
+  if (near) b = bin_near_edge(x, e, n, b, fr);
   return b;
 }
 

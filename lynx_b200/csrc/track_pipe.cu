@@ -100,6 +100,9 @@ __device__ __forceinline__ unsigned vmin_u16x2(unsigned a, unsigned b) {
   asm("min.u16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
   return r;
 }
+__device__ __forceinline__ void reds_add_u32(uint32_t smem_addr, uint32_t v) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(smem_addr), "r"(v) : "memory");
+}
 __device__ __forceinline__ void bulk_reduce_add_f32(float* dst_gmem, const float* src_smem,
                                                     uint32_t bytes) {
   asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst_gmem),
@@ -267,20 +270,40 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
       const float offx = -hx.e0 * hx.inv, offy = -hy.e0 * hy.inv;
       const bool regular = hx.margin < 0.5f && hy.margin < 0.5f;  // warp-uniform
       int pk[4];  // ix | iy << 16, or -1 (dead lane / outside the screen)
+      if (regular) {
+        float xs[4], ys[4], frx[4], fry[4];
+        int ix[4], iy[4];
+        bool nx[4], ny[4], any_near = false;
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+          xs[l] = xv[l] - mx;
+          ys[l] = yfix ? yv[l] - my : yv[l];
+          ix[l] = bin_guess(xs[l], hx.inv, offx, hx.margin, hx.e0, hx.en, nx[l], frx[l]);
+          iy[l] = bin_guess(ys[l], hy.inv, offy, hy.margin, hy.e0, hy.en, ny[l], fry[l]);
+          any_near = any_near || nx[l] || ny[l];
+        }
+        if (any_near) {  // a few lookups in a thousand: the edge table decides
+#pragma unroll
+          for (int l = 0; l < 4; ++l) {
+            if (nx[l]) ix[l] = bin_near_edge(xs[l], a.ex, a.W, ix[l], frx[l]);
+            if (ny[l]) iy[l] = bin_near_edge(ys[l], a.ey, a.H, iy[l], fry[l]);
+          }
+        }
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+          const bool ok = live[l] && (ix[l] | iy[l]) >= 0;
+          pk[l] = ok ? (ix[l] | (iy[l] << 16)) : -1;
+        }
+      } else {
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+          const int ix = find_bin(xv[l] - mx, a.ex, a.W, hx);
+          const int iy = find_bin(yfix ? yv[l] - my : yv[l], a.ey, a.H, hy);
+          pk[l] = (live[l] && (ix | iy) >= 0) ? (ix | (iy << 16)) : -1;
+        }
+      }
 #pragma unroll
       for (int l = 0; l < 4; ++l) {
-        const float x = xv[l] - mx;
-        const float y = yfix ? yv[l] - my : yv[l];
-        int ix, iy;
-        if (regular) {
-          ix = find_bin_regular(x, a.ex, a.W, hx.inv, offx, hx.margin, hx.e0, hx.en);
-          iy = find_bin_regular(y, a.ey, a.H, hy.inv, offy, hy.margin, hy.e0, hy.en);
-        } else {
-          ix = find_bin(x, a.ex, a.W, hx);
-          iy = find_bin(y, a.ey, a.H, hy);
-        }
-        const bool ok = live[l] && ix >= 0 && iy >= 0;
-        pk[l] = ok ? (ix | (iy << 16)) : -1;
         // invalid = 0xffffffff: neutral for the min; + 1 makes it 0, neutral for the max (a valid
         // ix + 1 <= 65535 does not carry into the iy lane; W, H < 32768 is checked by the launcher)
         bb_max = vmax_u16x2(bb_max, (unsigned)pk[l] + 1u);
@@ -340,6 +363,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
         }
       }
       const HistWindow hw = s_win;
+      const uint32_t win_s = smem_u32(win);
 #pragma unroll
       for (int l = 0; l < 4; ++l) {
         const bool ok = pk[l] >= 0;
@@ -348,7 +372,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
         if constexpr (TILE) {
           const unsigned dx = (unsigned)(ix - hw.x0), dy = (unsigned)(iy - hw.y0);
           in = ok && dx < (unsigned)hw.w && dy < (unsigned)hw.h;
-          if (in) atomicAdd(win + dy * hw.w + dx, 1u);
+          if (in) reds_add_u32(win_s + 4u * (dy * (unsigned)hw.w + dx), 1u);
         }
         if (ok && !in) red_add_f32(img_b + (unsigned)((a.H - 1 - iy) * a.W + ix), 1.0f);  // W H < 2^30
       }
@@ -477,13 +501,20 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
         // image (row iy of the tile is image row H - 1 - iy: flipud(hist.T), screen.py:206)
         consumers_sync();
         float* f = reinterpret_cast<float*>(win);
-        const int npx = hw.w * hw.h;
-        for (int i = cid; i < npx; i += kConsumers) f[i] = (float)win[i];
+        const int n4 = (hw.w * hw.h) >> 2;  // w is a multiple of 4
+        uint4* w4 = reinterpret_cast<uint4*>(win);
+        for (int i = cid; i < n4; i += kConsumers) {
+          const uint4 c = w4[i];
+          reinterpret_cast<float4*>(f)[i] = make_float4((float)c.x, (float)c.y, (float)c.z, (float)c.w);
+        }
         fence_proxy_async();
         consumers_sync();
-        for (int r = cid; r < hw.h; r += kConsumers)
-          bulk_reduce_add_f32(img_b + (int64_t)(a.H - 1 - (hw.y0 + r)) * a.W + hw.x0, f + r * hw.w,
-                              (uint32_t)hw.w * 4u);
+        // one elected lane per warp issues its rows: a bulk operation is issued per THREAD, and
+        // 32 lanes of a warp doing so serialise (8 % of the 1 M-particle kernel's instructions)
+        if (lane == 0)
+          for (int r = cw; r < hw.h; r += kConsumerWarps)
+            bulk_reduce_add_f32(img_b + (int64_t)(a.H - 1 - (hw.y0 + r)) * a.W + hw.x0, f + r * hw.w,
+                                (uint32_t)hw.w * 4u);
         bulk_commit();
       }
     }

@@ -25,7 +25,9 @@ for l in dis[start + 1:]:
     if re.match(r"\s+/\*[0-9a-f]{4,6}\*/\s+\S", l):
         lines.append(cur)
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
-blk = out.split('"Kernel Name"')[1]
+blks = out.split('"Kernel Name"')[1:]
+base = re.sub(r"^_ZN4lynx\d+", "", kern).split("I")[0].split("E")[0]  # e.g. track_pipe_kernel
+blk = next((b for b in blks if base in b.splitlines()[0]), blks[0])
 rows = list(csv.reader(io.StringIO("\n".join(blk.splitlines()[1:]))))
 hdr = rows[0]
 E, S = hdr.index("Instructions Executed"), hdr.index("# Samples")
