@@ -57,6 +57,16 @@ def peaks():
         return 6650.0, "fallback"
 
 
+def traffic_of(kernel, workload, n):
+    """Measured DRAM bytes per launch from the committed table (profiles/traffic.json), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            e = json.load(f).get(f"{kernel}/{workload}/{n}")
+        return (e["traffic"], e["source"]) if e else (None, None)
+    except Exception:
+        return None, None
+
+
 class ClockSampler:
     """SM clock / throttle reasons DURING the timed region: an NVML polling thread (the
     timed region is a few ms, far shorter than nvidia-smi's sampling period), with
@@ -153,6 +163,28 @@ def time_cpu(n, steps, warmup):
     return (time.perf_counter() - t0) / steps
 
 
+def time_cpu_parambeam(B, steps, warmup=1):
+    """Config 3 in the restated reference arithmetic: ONE vectorised Segment.track of a
+    ParameterBeam over B settings (lynx/accelerator/element.py:71-82), torch CPU, fp32."""
+    from helpers import oracle_elements
+    from lynx_b200 import fixtures as F
+    from oracle import lattice as O
+
+    k1, ang = F.random_settings(B)
+    ov = {(nm, "k1"): k1[:, i] for i, nm in enumerate(("AREAMQZM1", "AREAMQZM2", "AREAMQZM3"))}
+    ov[("AREAMCVM1", "angle")], ov[("AREAMCHM1", "angle")] = ang[:, 0], ang[:, 1]
+    els = oracle_elements(F.ares_ea(), torch.float32, (B,), ov)
+    pb = O.ParameterBeamO.from_parameters(F.ASTRA_MU[:4], F.ASTRA_SIGMA, F.ASTRA_ENERGY)
+    pb = O.ParameterBeamO(pb.mu_.expand(B, 7).clone(), pb.cov_.expand(B, 7, 7).clone(),
+                          pb.energy.expand(B).clone())
+    for _ in range(warmup):
+        O.track(els, pb)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        O.track(els, pb)
+    return (time.perf_counter() - t0) / steps
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -176,6 +208,11 @@ def run_reference(args, rank, world):
         "e2e": {"value": val, "unit": "particle-element updates/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
     }
+    # the second half of the metric on the same cores: ParameterBeam env-steps/s (config 3)
+    psec = time_cpu_parambeam(args.settings, max(3, min(args.steps, 20)))
+    line["env_steps"] = {"value": args.settings / psec, "unit": "env-steps/s",
+                         "settings": args.settings, "ms_per_step": psec * 1e3,
+                         "cores": torch.get_num_threads(), "kind": "port"}
     print(json.dumps(line), flush=True)
 
 
@@ -448,14 +485,13 @@ def run_ours(args, rank, world, local_rank):
     lib = L.lib()
     peak, peak_src = peaks()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+    from lynx_b200.sharding import ScreenExchange
 
     wl = ParticleWorkload(args.particles, device, seed=1002 + rank, screen=True)
     post = None
     step_fn = wl.step
     exchange_kind = None
     if world > 1:  # the one exchange step of the path: the screen image (north star)
-        from lynx_b200.sharding import ScreenExchange
-
         if args.exchange == "nccl":
             post = lambda: dist.all_reduce(wl.img)  # noqa: E731
             exchange_kind = "dense NCCL all-reduce of the 20 MB image"
@@ -495,7 +531,6 @@ def run_ours(args, rank, world, local_rank):
             exch.reduce = real_reduce
             sys.stderr.write(f"[rank {rank}] no exchange: local image {np.mean(ms_local) * 1e3:.2f} us, "
                              f"symmetric slot {np.mean(ms_symm) * 1e3:.2f} us\n")
-        sys.stderr.write(f"[rank {rank}] sharded step kernels: K1 {k1 * 1e3:.2f} us, K2 {k2 * 1e3:.2f} us\n")
     launches = lib.lynx_launch_count() - 0
     launches_timed = launches * args.steps // (args.steps + args.warmup)
     torch.cuda.synchronize()
@@ -547,6 +582,109 @@ def run_ours(args, rank, world, local_rank):
     h2d = 4 * (6 * wl.ld + wl.params_host.numel() + 1)
     d2h = 4 * rect + 16
 
+    def max_over_ranks(x):
+        t = torch.tensor([x], device=device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    def timed_collective(fn, steps, warmup):
+        """barrier, per-step events with the L2 flush, MAX over ranks of the mean step (ms)."""
+        if world > 1:
+            dist.barrier()
+        return max_over_ranks(float(np.mean(timed_steps(fn, steps, warmup, flush))))
+
+    # ---- (iv) the exchange step against NCCL, outside any timed region: the fused kernel's
+    #      image must equal dist.all_reduce of the ranks' local images bit for bit
+    exchange_check = None
+    if world > 1 and args.exchange == "fused":
+        wl.step()  # local image of this rank's shard into wl.img
+        want = wl.img.clone()
+        dist.all_reduce(want)
+        wl.sharded_step(exch)
+        torch.cuda.synchronize()
+        same = torch.equal(exch.out, want) and want.sum().item() == world * args.particles
+        flag = torch.tensor([1.0 if same else 0.0], device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        exchange_check = "bit-exact" if flag.item() == 1.0 else "MISMATCH"
+
+    # ---- (i) the second half of the metric: ParameterBeam env-steps/s, settings sharded over
+    #      the ranks (args.settings per GPU; no collective on the path, SURVEY 8e)
+    pw = ParamBeamWorkload(args.settings, device, seed=1003 + rank)
+    pb_ms = timed_collective(pw.step, args.steps, args.warmup)
+    env_steps = {"value": world * args.settings / (pb_ms * 1e-3), "unit": "env-steps/s",
+                 "settings_per_gpu": args.settings, "n_gpus": world, "ms_per_step": pb_ms,
+                 "scaling": "weak", "sharding": "settings axis, no collective",
+                 "workload": "ares_ea_parameterbeam_random_k1_angles (BASELINE.json configs[2])"}
+    if not args.no_extras:
+        bigB = 1 << 20
+        pw2 = ParamBeamWorkload(bigB, device, seed=2003 + rank)
+        big_ms = timed_collective(pw2.step, 10, 3)
+        env_steps["at_scale"] = {"settings_per_gpu": bigB, "ms_per_step": big_ms,
+                                 "value": world * bigB / (big_ms * 1e-3)}
+        if rank == 0:
+            k6b = kernel_ms(pw2.step, 2, 10, flush, lib)
+            a6 = pw2.algorithmic_bytes() / (k6b * 1e-3) / 1e9
+            env_steps["roofline"] = {"bound": "hbm", "kernel": "parambeam_fwd_kernel (K6)",
+                                     "settings": bigB, "kernel_ms": k6b, "achieved": a6,
+                                     "peak": peak, "unit": "GB/s", "frac": a6 / peak,
+                                     "algorithmic_bytes_per_launch": pw2.algorithmic_bytes()}
+        del pw2
+
+    # ---- (ii) BASELINE.json configs[3]: 100 M particles through Cavity + Dipole + quadrupoles
+    #      over 8 GPUs = 12.5 M per rank (weak-scaled to the ranks present), screen image
+    #      exchanged by the fused kernel
+    cfg4 = None
+    if not args.no_extras:
+        n4 = 12_500_000
+        w4 = ParticleWorkload(n4, device, seed=1004 + rank, lattice="cfg4")
+        local_ms = timed_collective(w4.step, 10, 3)
+        cfg4 = {"particles_per_gpu": n4, "elements": w4.n_elements, "n_gpus": world,
+                "local_step_ms": local_ms}
+        if world > 1 and args.exchange == "fused":
+            ex4 = ScreenExchange(1, w4.W, w4.H, device)
+            sh_ms = timed_collective(lambda: w4.sharded_step(ex4), 10, 3)
+            w4.step()
+            want4 = w4.img.clone()
+            dist.all_reduce(want4)
+            w4.sharded_step(ex4)
+            torch.cuda.synchronize()
+            ok4 = torch.tensor([1.0 if torch.equal(ex4.out, want4) else 0.0], device=device)
+            dist.all_reduce(ok4, op=dist.ReduceOp.MIN)
+            cfg4.update({"step_ms": sh_ms, "efficiency_vs_local_shard": local_ms / sh_ms,
+                         "exchange_check": "bit-exact" if ok4.item() == 1.0 else "MISMATCH",
+                         "particle_element_updates_per_s": world * n4 * w4.n_elements / (sh_ms * 1e-3)})
+            del ex4
+        else:
+            cfg4["particle_element_updates_per_s"] = world * n4 * w4.n_elements / (local_ms * 1e-3)
+        del w4
+
+    # ---- (iii) the same step through the PYTHON surface: host particles (N, 7) ->
+    #      lx.ParticleBeam -> Segment.track -> Screen.reading -> host image
+    import lynx_b200 as lx
+    from lynx_b200 import fixtures as F
+
+    aos_host = torch.from_numpy(F.soa_to_aos7(wl.soa_host[:, :args.particles].numpy())).unsqueeze(0).pin_memory()
+    api_seg = F.build_segment(F.ares_ea(k1=K1, vkick=VKICK, hkick=HKICK, screen_active=True,
+                                        screen=F.TEST_SCREEN))
+    api_energy = torch.tensor([F.ASTRA_ENERGY])
+
+    def api_step():
+        beam = lx.ParticleBeam(aos_host, api_energy)
+        api_seg.track(beam)
+        return api_seg.AREABSCR1.reading.cpu()
+
+    api_img = api_step()
+    api_ok = torch.equal(api_img.reshape(-1), dense_img.reshape(-1))
+    for _ in range(2):
+        api_step()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(max(3, args.steps // 10)):
+        api_step()
+    api_s = max_over_ranks((time.perf_counter() - t0) / max(3, args.steps // 10))
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -556,19 +694,20 @@ def run_ours(args, rank, world, local_rank):
     k2_ms = kernel_ms(wl.step, 1, args.steps, flush, lib)
     alg = wl.algorithmic_bytes()
     ach = alg / (k2_ms * 1e-3) / 1e9 if k2_ms else None
-    roofline = {"bound": "hbm", "kernel": "track_fwd_kernel (K2)", "achieved": ach, "peak": peak,
-                "unit": "GB/s", "frac": (ach / peak) if ach else None,
+    traffic, traffic_src = traffic_of("track_pipe_kernel", "ares_screen", args.particles)
+    roofline = {"bound": "hbm", "kernel": "track_pipe_kernel<0, false, true> (K2, screen variant)",
+                "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None,
                 # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel on this
-                # workload, from profiles/r1e_k2_screen1m.txt (ncu --set full; the image is
-                # zeroed and accumulated in L2, its write-back happens after the kernel)
-                "traffic": 24355840 if args.particles == 1_000_000 else None,
-                "traffic_source": "profiles/r1e_k2_screen1m.txt",
+                # workload (ncu --set full), from the committed table profiles/traffic.json; the
+                # image is zeroed and accumulated in L2, its write-back happens after the kernel
+                "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs, burst copy)",
                 "algorithmic_bytes_per_launch": alg, "kernel_ms": k2_ms,
                 "frac_of_8000": (ach / 8000.0) if ach else None,
-                "regime": "L2-atomic / latency-bound at 1M particles: 1 M RED.ADD.F32 at the "
-                          "focused-beam rate of the L2 (~75 G/s, profiles/r1b_atomic_bench.txt) "
-                          "are ~13 us of the kernel; 44 MB are 6.8 us at the HBM peak"}
+                "regime": "latency / issue-bound at 1 M particles: 4 pipeline tiles per CTA, "
+                          "~500 warp instructions per 128 particles at 4 warps per scheduler "
+                          "(profiles/r2e_k2_screen32m_lines.txt); 44 MB are 6.8 us at the HBM "
+                          "peak.  The same kernel at 32 M particles: extras.at_scale_screen_24B"}
     line = {
         "metric": "particle_element_updates_per_s", "value": value,
         "unit": "particle-element updates/s", "n_gpus": world, "steps": args.steps,
@@ -591,7 +730,18 @@ def run_ours(args, rank, world, local_rank):
                                    "ms_per_step": e2e_dense_s.item() * 1e3,
                                    "d2h_bytes_per_step": 4 * wl.W * wl.H}},
         "roofline": roofline,
+        "env_steps": env_steps,
+        "api_e2e": {"value": world * args.particles * E_ARES / api_s, "unit": "particle-element updates/s",
+                    "ms_per_step": api_s * 1e3, "h2d_bytes_per_step": 28 * args.particles,
+                    "d2h_bytes_per_step": 4 * wl.W * wl.H, "image_equals_c_abi_path": bool(api_ok),
+                    "path": "pinned host (1, N, 7) particles -> lx.ParticleBeam -> lx.Segment.track "
+                            "-> Screen.reading.cpu(): AoS upload, AoS->SoA kernel, K1, K2, dense "
+                            "20 MB image read-back, all through the Python surface"},
     }
+    if exchange_check is not None:
+        line["exchange_check"] = exchange_check
+    if cfg4 is not None:
+        line["cfg4_100M_sharded"] = cfg4
 
     if world == 1:
         # ---- CPU baseline: the oracle port on this box's cores, bounded sample
@@ -602,12 +752,17 @@ def run_ours(args, rank, world, local_rank):
             "cores": torch.get_num_threads(), "kind": "port",
             "sample": f"8 full steps of {args.particles} particles (torch-CPU restatement)",
             "ms_per_step": sec * 1e3}
+        psec = time_cpu_parambeam(args.settings, 20, 2)
+        env_steps["cpu_baseline"] = {
+            "value": args.settings / psec, "unit": "env-steps/s", "cores": torch.get_num_threads(),
+            "kind": "port", "ms_per_step": psec * 1e3,
+            "sample": f"20 vectorised Segment.track(ParameterBeam) calls over {args.settings} "
+                      "settings (torch-CPU restatement of lynx/accelerator/element.py:71-82)"}
 
     if world == 1 and not args.no_extras:
         extras = {}
         # ParameterBeam env-steps/s (configs[2])
-        pw = ParamBeamWorkload(args.settings, device)
-        pms = timed_steps(pw.step, args.steps, args.warmup, flush)
+        pms = [pb_ms]
         for _ in range(3):
             pw.host_step(ctx)
         t0 = time.perf_counter()
@@ -621,15 +776,6 @@ def run_ours(args, rank, world, local_rank):
             "e2e_value": args.settings / pe2e, "kernel_ms": k6,
             "achieved_gbs": pw.algorithmic_bytes() / (k6 * 1e-3) / 1e9 if k6 else None,
             "regime": "launch-latency-bound (1 MB per launch)"}
-        # large-B point where HBM is the limiter
-        bigB = 1 << 20
-        pw2 = ParamBeamWorkload(bigB, device)
-        k6b = kernel_ms(pw2.step, 2, 10, flush, lib)
-        extras["parameterbeam_at_scale"] = {
-            "settings": bigB, "value": bigB / (k6b * 1e-3), "unit": "env-steps/s",
-            "kernel_ms": k6b, "achieved_gbs": pw2.algorithmic_bytes() / (k6b * 1e-3) / 1e9,
-            "frac": pw2.algorithmic_bytes() / (k6b * 1e-3) / 1e9 / peak}
-        del pw2
         # streaming roofline points at N = scale_particles
         ns = args.scale_particles
         for name, kw in (("track_out_48B", dict(screen=False, want_out=True)),
@@ -638,8 +784,10 @@ def run_ours(args, rank, world, local_rank):
             w2 = ParticleWorkload(ns, device, seed=7, **kw)
             km = kernel_ms(w2.step, 1, 10, flush, lib)
             a2 = w2.algorithmic_bytes() / (km * 1e-3) / 1e9
+            tr2 = traffic_of("track_pipe_kernel", "ares_screen" if kw.get("screen") else "ares_out", ns)[0]
             extras[f"at_scale_{name}"] = {
                 "particles": ns, "kernel_ms": km, "achieved_gbs": a2, "frac": a2 / peak,
+                "traffic": tr2 if not kw.get("moments") else None,
                 "frac_of_8000": a2 / 8000.0,
                 "particle_element_updates_per_s": ns * E_ARES / (km * 1e-3)}
             del w2
