@@ -6,6 +6,7 @@
 #include <cstdlib>
 
 #include "compose_common.cuh"
+#include "pipe.cuh"
 #include "track_common.cuh"
 
 namespace lynx {
@@ -93,7 +94,7 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
   float energy = a.energy_in[b];
   if (STAGED) {
     SmemParamView P{s_vals, S, (int)threadIdx.x};
-    walk_program<OPS>(s_ops, a.n_ops, a.final_stage, P, energy, sink);
+    walk_program<OPS, (OPS & ~kOpsLight) == 0>(s_ops, a.n_ops, a.final_stage, P, energy, sink);
   } else {
     ParamView P{a.params, a.col_offset, a.col_stride, b};
     walk_program<OPS>(a.ops, a.n_ops, a.final_stage, P, energy, sink);
@@ -106,30 +107,51 @@ __global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int
 
 constexpr int kPBThreads = 64;
 
-template <bool STAGED, int OPS>
-__global__ void __launch_bounds__(kPBThreads) parambeam_fwd_kernel(ParamBeamArgs a, int n_cols) {
-  // staging tile so the [B][7] / [B][7][7] outputs leave the SM as full coalesced rows
-  __shared__ float tile[kPBThreads * 49];
+// Program tables small enough to ride in the kernel's parameter space (constant bank): the
+// ops and the column tables are then there when the block starts, and the only cold loads
+// of the kernel -- parameters, beam, energy -- are all issued at once (one DRAM round trip).
+constexpr int kTabOps = 48, kTabCols = 96;
+struct ProgramTables {
+  DevOp ops[kTabOps];
+  int64_t col_offset[kTabCols];
+  int32_t col_stride[kTabCols];
+};
+
+// One thread owns one setting.  TAB: ops / column tables from the parameter space, else from
+// global memory (ops staged in shared memory).  OPS within kOpsLight: the merged map is a
+// light map (maps.cuh).
+template <bool TAB, int OPS>
+__global__ void __launch_bounds__(kPBThreads)
+parambeam_fwd_kernel(ParamBeamArgs a, int n_cols, const __grid_constant__ ProgramTables tab) {
+  constexpr bool LT = (OPS & ~kOpsLight) == 0;
+  // staging tile so the [B][7] / [B][7][7] outputs leave the SM as whole rows (bulk copy)
+  __shared__ __align__(16) float tile_cov[kPBThreads * 49];
+  __shared__ __align__(16) float tile_mu[kPBThreads * 7];
   extern __shared__ __align__(16) float pb_smem[];
   const int64_t b0 = (int64_t)blockIdx.x * kPBThreads;
   const int64_t b = b0 + threadIdx.x;
   const bool live = b < a.B;
-  DevOp* s_ops = reinterpret_cast<DevOp*>(pb_smem);
-  float* s_vals = pb_smem + a.n_ops * (sizeof(DevOp) / sizeof(float));
-  if (STAGED) {  // one parallel round of loads instead of a dependent chain per column
-    const int ns = (int)min((int64_t)kPBThreads, a.B - b0);
+  const int nb = (int)min((int64_t)kPBThreads, a.B - b0);
+  float* s_vals = pb_smem;
+  const DevOp* ops = tab.ops;
+  if (!TAB) {
+    DevOp* s_ops = reinterpret_cast<DevOp*>(pb_smem + n_cols * kPBThreads);
     for (int i = threadIdx.x; i < a.n_ops * (int)(sizeof(DevOp) / 4); i += kPBThreads)
-      pb_smem[i] = reinterpret_cast<const float*>(a.ops)[i];
-    for (int i = threadIdx.x; i < n_cols * ns; i += kPBThreads) {
-      const int c = i / ns, sl = i - c * ns;
-      s_vals[c * kPBThreads + sl] = __ldg(a.params + __ldg(a.col_offset + c) +
-                                          (b0 + sl) * (int64_t)__ldg(a.col_stride + c));
-    }
-    __syncthreads();
+      reinterpret_cast<float*>(s_ops)[i] = reinterpret_cast<const float*>(a.ops)[i];
+    ops = s_ops;
   }
   MomentSink sink;
   float energy = 0.f;
   if (live) {
+    // this setting's parameter columns: thread = setting, so every load of a per-setting
+    // column is coalesced across the warp, a shared column is a broadcast, and nobody else
+    // reads this thread's slots (no barrier)
+#pragma unroll 4
+    for (int c = 0; c < n_cols; ++c) {
+      const int64_t off = TAB ? tab.col_offset[c] : __ldg(a.col_offset + c);
+      const int64_t st = TAB ? tab.col_stride[c] : __ldg(a.col_stride + c);
+      s_vals[c * kPBThreads + threadIdx.x] = __ldg(a.params + off + b * st);
+    }
     const float* mi = a.mu_in + b * a.beam_stride * 7;
     const float* ci = a.cov_in + b * a.beam_stride * 49;
 #pragma unroll
@@ -142,32 +164,36 @@ __global__ void __launch_bounds__(kPBThreads) parambeam_fwd_kernel(ParamBeamArgs
     sink.B = a.B;
     sink.b = b;
     energy = a.energy_in[b];
-    if (STAGED) {
-      SmemParamView P{s_vals, kPBThreads, (int)threadIdx.x};
-      walk_program<OPS>(s_ops, a.n_ops, a.final_stage, P, energy, sink);
-    } else {
-      ParamView P{a.params, a.col_offset, a.col_stride, b};
-      walk_program<OPS>(a.ops, a.n_ops, a.final_stage, P, energy, sink);
-    }
+  }
+  if (!TAB) __syncthreads();
+  if (live) {
+    SmemParamView P{s_vals, kPBThreads, (int)threadIdx.x};
+    walk_program<OPS, LT>(ops, a.n_ops, a.final_stage, P, energy, sink);
     if (a.energy_out) a.energy_out[b] = energy;
-  }
-  const int nb = (int)min((int64_t)kPBThreads, a.B - b0);
-  // mu: [nb][7]
-  if (live) {
 #pragma unroll
-    for (int i = 0; i < 7; ++i) tile[threadIdx.x * 7 + i] = sink.mu[i];
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < nb * 7; i += kPBThreads) a.mu_out[b0 * 7 + i] = tile[i];
-  __syncthreads();
-  if (live) {
+    for (int i = 0; i < 7; ++i) tile_mu[threadIdx.x * 7 + i] = sink.mu[i];
 #pragma unroll
     for (int i = 0; i < 7; ++i)
 #pragma unroll
-      for (int j = 0; j < 7; ++j) tile[threadIdx.x * 49 + i * 7 + j] = sink.cov[i][j];
+      for (int j = 0; j < 7; ++j) tile_cov[threadIdx.x * 49 + i * 7 + j] = sink.cov[i][j];
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < nb * 49; i += kPBThreads) a.cov_out[b0 * 49 + i] = tile[i];
+  // rows [b0, b0 + nb) of mu_out / cov_out are contiguous: one bulk copy each when their
+  // byte counts and addresses are multiples of 16 (nb % 4 == 0, 16-byte aligned outputs)
+  const bool bulk = (nb & 3) == 0 && (((uintptr_t)a.mu_out | (uintptr_t)a.cov_out) & 15) == 0;
+  if (bulk) {
+    fence_proxy_async();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      bulk_s2g(a.cov_out + b0 * 49, tile_cov, (uint32_t)nb * 196u);
+      bulk_s2g(a.mu_out + b0 * 7, tile_mu, (uint32_t)nb * 28u);
+      bulk_commit();
+      bulk_wait_read<0>();
+    }
+  } else {
+    __syncthreads();
+    for (int i = threadIdx.x; i < nb * 7; i += kPBThreads) a.mu_out[b0 * 7 + i] = tile_mu[i];
+    for (int i = threadIdx.x; i < nb * 49; i += kPBThreads) a.cov_out[b0 * 49 + i] = tile_cov[i];
+  }
 }
 
 }  // namespace lynx
@@ -290,16 +316,29 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
   a.energy_out = d_energy_out;
   const unsigned blocks = (unsigned)((B + kPBThreads - 1) / kPBThreads);
   const int n_cols = (int)p->col_offset.size();
-  const size_t smem = a.n_ops * sizeof(DevOp) + (size_t)n_cols * kPBThreads * 4;
+  const bool tabbed = a.n_ops <= kTabOps && n_cols <= kTabCols;
+  const size_t smem = (size_t)n_cols * kPBThreads * 4 + (tabbed ? 0 : a.n_ops * sizeof(DevOp));
+  if (smem > 200 * 1024) return LYNX_E_TOOLARGE;  // > 800 parameter columns
+  ProgramTables tab;
+  if (tabbed) {
+    std::copy(p->dev_ops.begin(), p->dev_ops.end(), tab.ops);
+    std::copy(p->col_offset.begin(), p->col_offset.end(), tab.col_offset);
+    std::copy(p->col_stride.begin(), p->col_stride.end(), tab.col_stride);
+  }
   {
     ProfileScope ps(2, (cudaStream_t)stream);
     const bool light = (p->op_mask & ~kOpsLight) == 0;
-    if (smem <= 32 * 1024 && light)
-      parambeam_fwd_kernel<true, kOpsLight><<<blocks, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols);
-    else if (smem <= 32 * 1024)
-      parambeam_fwd_kernel<true, kOpsAll><<<blocks, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols);
+    auto launch = [&](auto kern) {
+      if (smem > 48 * 1024)
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      kern<<<blocks, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols, tab);
+    };
+    if (tabbed && light)
+      launch(parambeam_fwd_kernel<true, kOpsLight>);
+    else if (tabbed)
+      launch(parambeam_fwd_kernel<true, kOpsAll>);
     else
-      parambeam_fwd_kernel<false, kOpsAll><<<blocks, kPBThreads, 0, (cudaStream_t)stream>>>(a, n_cols);
+      launch(parambeam_fwd_kernel<false, kOpsAll>);
   }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());

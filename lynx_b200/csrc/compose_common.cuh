@@ -15,7 +15,8 @@ struct RecordSinkT {
   int off_cav, off_centre, off_screen;
   float ctr[6];
 
-  __device__ __forceinline__ void write_map(const Map& M, int idx) {
+  template <bool LT>
+  __device__ __forceinline__ void write_map(const MapT<float, LT>& M, int idx) {
     float* d = rec + idx * kMapStride;
 #pragma unroll
     for (int i = 0; i < 6; ++i)
@@ -31,16 +32,21 @@ struct RecordSinkT {
       for (int j = 0; j < 7; ++j) o[42 + j] = (j == 6) ? 1.f : 0.f;
     }
   }
-  __device__ __forceinline__ void push_centre(const Map& M, float* lin) {
+  // structural entries of a light map are skipped where the dense sum is unchanged by them
+  // (0 * ctr added to a non-zero partial sum); rows 4 / 5 keep the dense order of operations
+  template <bool LT>
+  __device__ __forceinline__ void push_centre(const MapT<float, LT>& M, float* lin) {
 #pragma unroll
     for (int i = 0; i < 6; ++i) {
       float a = M.m[i][6];
 #pragma unroll
-      for (int j = 0; j < 6; ++j) a = fmaf(M.m[i][j], ctr[j], a);
+      for (int j = 0; j < 6; ++j)
+        if (map_live<LT>(i, j) || i == j) a = fmaf(M.m[i][j], ctr[j], a);
       lin[i] = a;
     }
   }
-  __device__ __forceinline__ void stage(const Map& M, int idx) {
+  template <bool LT>
+  __device__ __forceinline__ void stage(const MapT<float, LT>& M, int idx) {
     write_map(M, idx);
     float lin[6];
     push_centre(M, lin);
@@ -63,15 +69,18 @@ struct RecordSinkT {
     for (int i = 0; i < 6; ++i) ctr[i] = lin[i];
   }
   __device__ __forceinline__ bool flush_before(const DevOp& op) const { return op.flush_stage >= 0; }
-  __device__ __forceinline__ void finish(const Map& M, int final_stage) {
+  template <bool LT>
+  __device__ __forceinline__ void finish(const MapT<float, LT>& M, int final_stage) {
     if (final_stage >= 0) stage(M, final_stage);
   }
-  __device__ __forceinline__ void bpm(const Map&, int, int snap) {
+  template <bool LT>
+  __device__ __forceinline__ void bpm(const MapT<float, LT>&, int, int snap) {
     float* d = rec + off_centre + snap * 6;
 #pragma unroll
     for (int i = 0; i < 6; ++i) d[i] = ctr[i];
   }
-  __device__ __forceinline__ void screen(const Map&, int, int sidx, float mx, float my, int) {
+  template <bool LT>
+  __device__ __forceinline__ void screen(const MapT<float, LT>&, int, int sidx, float mx, float my, int) {
     rec[off_screen + sidx * 2 + 0] = mx;
     rec[off_screen + sidx * 2 + 1] = my;
   }
@@ -115,46 +124,48 @@ struct MomentSinkT {
   T* bpm_out;
   int64_t B, b;
 
-  // element.py:73-74 with R = [M; e6]
-  __device__ __forceinline__ void apply(const MapT<T>& M) {
+  // element.py:73-74 with R = [M; e6].  A light map (maps.cuh) skips the products with its
+  // structural zeros and ones: 315 fma instead of 686, the same bits.
+  template <bool LT>
+  __device__ __forceinline__ void apply(const MapT<T, LT>& M) {
     T t[7];
+    // t = R[0..5] v for a 7-vector v (mu or a column of cov), dense order of summation
+    auto rows_times = [&](auto&& v) {
 #pragma unroll
-    for (int i = 0; i < 6; ++i) {
-      T acc = T(0.f);
+      for (int i = 0; i < 6; ++i) {
+        if (LT && i == 5) {
+          t[5] = v(5);
+        } else if (LT && i == 4) {
+          t[4] = fma_(M.m[4][5], v(5), v(4));
+        } else {
+          T acc = T(0.f);
 #pragma unroll
-      for (int j = 0; j < 7; ++j) acc = fma_(M.m[i][j], mu[j], acc);
-      t[i] = acc;
-    }
+          for (int j = 0; j < 7; ++j)
+            if (map_live<LT>(i, j)) acc = fma_(M.m[i][j], v(j), acc);
+          t[i] = acc;
+        }
+      }
+    };
+    rows_times([&](int j) { return mu[j]; });
 #pragma unroll
     for (int i = 0; i < 6; ++i) mu[i] = t[i];
     // cov <- R cov  (column by column, in place)
 #pragma unroll
     for (int k = 0; k < 7; ++k) {
-#pragma unroll
-      for (int i = 0; i < 6; ++i) {
-        T acc = T(0.f);
-#pragma unroll
-        for (int j = 0; j < 7; ++j) acc = fma_(M.m[i][j], cov[j][k], acc);
-        t[i] = acc;
-      }
+      rows_times([&](int j) { return cov[j][k]; });
 #pragma unroll
       for (int i = 0; i < 6; ++i) cov[i][k] = t[i];
     }
     // cov <- cov R^T  (row by row, in place)
 #pragma unroll
     for (int i = 0; i < 7; ++i) {
-#pragma unroll
-      for (int l = 0; l < 6; ++l) {
-        T acc = T(0.f);
-#pragma unroll
-        for (int k = 0; k < 7; ++k) acc = fma_(cov[i][k], M.m[l][k], acc);
-        t[l] = acc;
-      }
+      rows_times([&](int k) { return cov[i][k]; });
 #pragma unroll
       for (int l = 0; l < 6; ++l) cov[i][l] = t[l];
     }
   }
-  __device__ __forceinline__ void stage(const MapT<T>& M, int) { apply(M); }
+  template <bool LT>
+  __device__ __forceinline__ void stage(const MapT<T, LT>& M, int) { apply(M); }
   // cavity.py:113-140, 202-218 (ParameterBeam branch; overwrites as written, quirk B5)
   __device__ __forceinline__ void cavity(const MapT<T>& C, const CavityOutT<T>& co, int, int) {
     const T mu4 = mu[4], mu5 = mu[5];
@@ -174,16 +185,19 @@ struct MomentSinkT {
     }
   }
   __device__ __forceinline__ bool flush_before(const DevOp& op) const { return op.flush_stage >= 0; }
-  __device__ __forceinline__ void finish(const MapT<T>& M, int final_stage) {
+  template <bool LT>
+  __device__ __forceinline__ void finish(const MapT<T, LT>& M, int final_stage) {
     if (final_stage >= 0) apply(M);
   }
-  __device__ __forceinline__ void bpm(const MapT<T>&, int slot, int) {
+  template <bool LT>
+  __device__ __forceinline__ void bpm(const MapT<T, LT>&, int slot, int) {
     if (bpm_out) {
       bpm_out[(slot * B + b) * 2 + 0] = mu[0];  // bpm.py:52
       bpm_out[(slot * B + b) * 2 + 1] = mu[2];
     }
   }
-  __device__ __forceinline__ void screen(const MapT<T>&, int, int, T mx, T my, int) {
+  template <bool LT>
+  __device__ __forceinline__ void screen(const MapT<T, LT>&, int, int, T mx, T my, int) {
     mu[0] -= mx;  // screen.py:131-132
     mu[2] -= my;
   }

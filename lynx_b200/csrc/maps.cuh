@@ -20,14 +20,26 @@
 
 namespace lynx {
 
-template <typename T>
+// LT ("light"): the map of a run made only of kOpsLight elements (walk.cuh: drifts, quadrupoles,
+// correctors, undulators, markers).  No such element reads rows 4 / 5 into rows 0..3 (no
+// dispersion) or writes row 5, so columns 4 and 5 of rows 0..3 stay zero, row 4 stays
+// e4 + r56 e5 and row 5 stays e5.  The row primitives skip those entries and every consumer
+// skips the products with them: the results are the bits the dense arithmetic produces (an fma
+// with a structural zero is exact), at 21 live entries instead of 42.
+template <typename T, bool LT = false>
 struct MapT {
   T m[6][7];
 };
 using Map = MapT<float>;
 
-template <typename T>
-__device__ __forceinline__ void map_identity(MapT<T>& M) {
+// is entry (i, j) of a map carried as a variable (true) or a structural 0 / 1 (false)
+template <bool LT>
+__host__ __device__ constexpr bool map_live(int i, int j) {
+  return !LT || (i < 4 && j != 4 && j != 5) || (i == 4 && j == 5);
+}
+
+template <typename T, bool LT>
+__device__ __forceinline__ void map_identity(MapT<T, LT>& M) {
 #pragma unroll
   for (int i = 0; i < 6; ++i)
 #pragma unroll
@@ -35,17 +47,19 @@ __device__ __forceinline__ void map_identity(MapT<T>& M) {
 }
 
 // row_a += f * row_b
-template <typename T>
-__device__ __forceinline__ void row_axpy(MapT<T>& M, int a, T f, int b) {
+template <typename T, bool LT>
+__device__ __forceinline__ void row_axpy(MapT<T, LT>& M, int a, T f, int b) {
 #pragma unroll
-  for (int j = 0; j < 7; ++j) M.m[a][j] = fma_(f, M.m[b][j], M.m[a][j]);
+  for (int j = 0; j < 7; ++j)
+    if (map_live<LT>(a, j)) M.m[a][j] = fma_(f, M.m[b][j], M.m[a][j]);
 }
 
 // [row_a; row_b] <- [[p, q], [r, s]] [row_a; row_b]
-template <typename T>
-__device__ __forceinline__ void rows_2x2(MapT<T>& M, int a, int b, T p, T q, T r, T s) {
+template <typename T, bool LT>
+__device__ __forceinline__ void rows_2x2(MapT<T, LT>& M, int a, int b, T p, T q, T r, T s) {
 #pragma unroll
   for (int j = 0; j < 7; ++j) {
+    if (!map_live<LT>(a, j)) continue;
     T x = M.m[a][j], y = M.m[b][j];
     M.m[a][j] = fma_(p, x, q * y);
     M.m[b][j] = fma_(r, x, s * y);
@@ -124,8 +138,8 @@ __device__ __forceinline__ void disp_fns(T t, T& g, T& h) {
 }
 
 // rotation_matrix(a) applied from the left, track_methods.py:14-34
-template <typename T>
-__device__ __forceinline__ void lm_rotation(MapT<T>& M, T a) {
+template <typename T, bool LT>
+__device__ __forceinline__ void lm_rotation(MapT<T, LT>& M, T a) {
   T sn, cs;
   sincos_(a, &sn, &cs);
   rows_2x2(M, 0, 2, cs, sn, -sn, cs);
@@ -133,8 +147,8 @@ __device__ __forceinline__ void lm_rotation(MapT<T>& M, T a) {
 }
 
 // drift.py:57-60 (also correctors, undulator with its own r56)
-template <typename T>
-__device__ __forceinline__ void lm_drift(MapT<T>& M, T L, T r56) {
+template <typename T, bool LT>
+__device__ __forceinline__ void lm_drift(MapT<T, LT>& M, T L, T r56) {
   row_axpy(M, 0, L, 1);
   row_axpy(M, 2, L, 3);
   row_axpy(M, 4, r56, 5);
@@ -146,8 +160,8 @@ __device__ __forceinline__ T drift_r56(T L, const RelT<T>& rel) {
 }
 
 // base_rmatrix(length, k1, hx, tilt=0, energy), track_methods.py:37-98 (tilt by caller)
-template <typename T>
-__device__ __forceinline__ void lm_base(MapT<T>& M, T L, T k1, T hx, const RelT<T>& rel) {
+template <typename T, bool LT>
+__device__ __forceinline__ void lm_base(MapT<T, LT>& M, T L, T k1, T hx, const RelT<T>& rel) {
   // :67-68 (k1 == 0 -> 1e-12).  The reference does this with a masked write, which also
   // zeroes d/dk1 at exactly k1 == 0; the tangent is kept here.
   if (val(k1) == 0.f) k1 = k1 + 1e-12f;
@@ -159,7 +173,7 @@ __device__ __forceinline__ void lm_base(MapT<T>& M, T L, T k1, T hx, const RelT<
   sx = sx * L;
   sy = sy * L;
   T r56 = -L * rel.inv_beta2_base * rel.igamma2_base;
-  if (nz(hx)) {
+  if (!LT && nz(hx)) {  // dispersion: dipoles only, never part of a light run
     T g, h;
     disp_fns(kx2 * L2, g, h);
     T dxb = hx * L2 * g * rel.inv_beta_base;   // dx / beta
@@ -181,8 +195,8 @@ __device__ __forceinline__ void lm_base(MapT<T>& M, T L, T k1, T hx, const RelT<
 }
 
 // quadrupole.py:66-80
-template <typename T>
-__device__ __forceinline__ void lm_quad(MapT<T>& M, T L, T k1, T mx, T my, T tilt,
+template <typename T, bool LT>
+__device__ __forceinline__ void lm_quad(MapT<T, LT>& M, T L, T k1, T mx, T my, T tilt,
                                          const RelT<T>& rel) {
   // R_exit . [rot(-tilt) . base . rot(tilt)] . R_entry   (right-most acts first)
   M.m[0][6] -= mx;  // R_entry, track_methods.py:118-120

@@ -47,8 +47,8 @@ constexpr int kOpsLight = op_bit(LYNX_OP_MARKER) | op_bit(LYNX_OP_DRIFT) | op_bi
                           op_bit(LYNX_OP_HCOR) | op_bit(LYNX_OP_VCOR) | op_bit(LYNX_OP_UNDULATOR) |
                           op_bit(LYNX_OP_BPM) | op_bit(LYNX_OP_SCREEN);
 
-template <int OPS, typename T, typename PV>
-__device__ __forceinline__ bool lm_linear_op(MapT<T>& M, const DevOp& op, const PV& P,
+template <int OPS, typename T, bool LT, typename PV>
+__device__ __forceinline__ bool lm_linear_op(MapT<T, LT>& M, const DevOp& op, const PV& P,
                                              const RelT<T>& rel, T energy) {
   const int c = op.col;
   switch (op.opcode) {
@@ -103,11 +103,14 @@ __device__ __forceinline__ bool lm_linear_op(MapT<T>& M, const DevOp& op, const 
   }
 }
 
-template <int OPS, typename T, typename Sink, typename PV>
+// LT: carry the merged map as a light map (maps.cuh); only for OPS within kOpsLight, and
+// only with sinks whose stage / bpm / screen / finish accept MapT<T, true>.
+template <int OPS, bool LT = false, typename T, typename Sink, typename PV>
 __device__ __forceinline__ void walk_program(const DevOp* __restrict__ ops, int n_ops,
                                              int final_stage, const PV& P,
                                              T& energy, Sink& sink) {
-  MapT<T> M;
+  static_assert(!LT || (OPS & ~kOpsLight) == 0, "light maps need a light opcode set");
+  MapT<T, LT> M;
   map_identity(M);
   RelT<T> rel = make_rel(energy);
   for (int i = 0; i < n_ops; ++i) {

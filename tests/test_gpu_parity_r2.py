@@ -321,3 +321,52 @@ def test_config5_256_settings_1m_particles_vs_oracle():
         worst[nm] = err.max()
         assert err.max() <= 3e-5, f"d loss / d {nm}: worst err / max|g| of a setting {err.max():.3e}"
     print(f"config 5, 256 x 1 M: worst gradient error / largest component of the setting: {worst}")
+
+
+# ------------------------------------------------------------------ light maps (maps.cuh)
+@pytest.mark.parametrize("B", [1, 42, 1002, 4096])
+def test_light_map_kernels_equal_the_dense_kernels(B):
+    """A lattice made only of drifts / quadrupoles / correctors runs the light-map variants of
+    K1 and K6 (21 live map entries, maps.cuh); the same lattice with an identity
+    ``CustomTransferMap`` in its merged run runs the dense ones.  The light variants skip only
+    products with structural zeros and ones, so both must agree to the bit -- tilted and
+    misaligned quadrupoles, ragged last block (B % 4 != 0: no bulk store) included."""
+    rng = np.random.default_rng(B)
+
+    def lattice(dense):
+        t = lambda v: torch.tensor(np.asarray(v, dtype=np.float32).reshape(-1))  # noqa: E731
+        els = [lx.Drift(length=torch.tensor([0.17])),
+               lx.Quadrupole(length=torch.tensor([0.12]), k1=t(rng.uniform(-30, 30, B)),
+                             misalignment=torch.from_numpy(
+                                 rng.normal(0, 1e-4, (B, 2)).astype(np.float32)),
+                             tilt=t(rng.uniform(-0.3, 0.3, B)), name="Q1"),
+               lx.Drift(length=torch.tensor([0.43])),
+               lx.VerticalCorrector(length=torch.tensor([0.02]), angle=t(rng.uniform(-6e-3, 6e-3, B))),
+               lx.Quadrupole(length=torch.tensor([0.12]), k1=t(rng.uniform(-30, 30, B)), name="Q2"),
+               lx.HorizontalCorrector(length=torch.tensor([0.02]), angle=t(rng.uniform(-6e-3, 6e-3, B))),
+               lx.Quadrupole(length=torch.tensor([0.12]), k1=torch.tensor([0.0]), name="Q3"),
+               lx.Drift(length=torch.tensor([0.45]))]
+        if dense:
+            els.insert(3, lx.CustomTransferMap(torch.eye(7).unsqueeze(0), length=torch.tensor([0.0])))
+        return lx.Segment(els)
+
+    rng = np.random.default_rng(B)
+    light = lattice(False)
+    rng = np.random.default_rng(B)
+    dense = lattice(True)
+    t = lambda v: torch.tensor([v])  # noqa: E731
+    pb = lx.ParameterBeam.from_parameters(
+        mu_x=t(F.ASTRA_MU[0]), mu_xp=t(F.ASTRA_MU[1]), mu_y=t(F.ASTRA_MU[2]), mu_yp=t(F.ASTRA_MU[3]),
+        sigma_x=t(F.ASTRA_SIGMA[0]), sigma_xp=t(F.ASTRA_SIGMA[1]), sigma_y=t(F.ASTRA_SIGMA[2]),
+        sigma_yp=t(F.ASTRA_SIGMA[3]), sigma_s=t(F.ASTRA_SIGMA[4]), sigma_p=t(F.ASTRA_SIGMA[5]),
+        cor_x=t(0.3 * F.ASTRA_SIGMA[0] * F.ASTRA_SIGMA[1]),
+        cor_s=t(-0.2 * F.ASTRA_SIGMA[4] * F.ASTRA_SIGMA[5]), energy=t(F.ASTRA_ENERGY))
+    a, b = light.track(pb), dense.track(pb)
+    assert a._mu.shape == (B, 7) and torch.equal(a._mu, b._mu)
+    assert torch.equal(a._cov, b._cov)
+    assert torch.isfinite(a._cov).all() and (a._cov[:, 0, 0] > 0).all()
+    # K1's records through the particle kernel: outgoing particles of a small beam
+    n = 4099
+    beam = _gpu_beam(F.gaussian_beam_soa(n, seed=5), F.ASTRA_ENERGY)
+    pa, pd = light.track(beam), dense.track(beam)
+    assert pa.soa.shape[0] == B and torch.equal(pa.soa[..., :n], pd.soa[..., :n])

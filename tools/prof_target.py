@@ -31,6 +31,18 @@ elif a.mode == "none1m":
     w = bench.ParticleWorkload(1_000_000, dev, seed=7, screen=False)
 elif a.mode == "pb4096":
     w = bench.ParamBeamWorkload(4096, dev)
+elif a.mode == "pbboth":  # launches 1-2: B = 4096, launches 3-4: B = 2^20
+    w1, w2 = bench.ParamBeamWorkload(4096, dev), bench.ParamBeamWorkload(1 << 20, dev)
+
+    class _W2:
+        i = 0
+
+        def step(self):
+            (w1 if self.i < 2 else w2).step()
+            self.i += 1
+
+    w = _W2()
+    a.steps = 2
 elif a.mode == "pb1m":
     w = bench.ParamBeamWorkload(1 << 20, dev)
 elif a.mode == "adj32m":
