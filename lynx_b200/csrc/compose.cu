@@ -115,70 +115,29 @@ struct ProgramTables {
   DevOp ops[kTabOps];
   int64_t col_offset[kTabCols];
   int32_t col_stride[kTabCols];
+  // shared-memory slot of column c: word col_slot[c] + (thread & col_mask[c]); a column shared
+  // by all settings (stride 0) has ONE slot per block, a per-setting column one per thread
+  int32_t col_slot[kTabCols];
+  int32_t col_mask[kTabCols];
+  int32_t var_cols[kTabCols];  // the per-setting columns
+  int32_t n_var, smem_words;
 };
 
-// One thread owns one setting.  TAB: ops / column tables from the parameter space, else from
-// global memory (ops staged in shared memory).  OPS within kOpsLight: the merged map is a
-// light map (maps.cuh).
-template <bool TAB, int OPS>
-__global__ void __launch_bounds__(kPBThreads)
-parambeam_fwd_kernel(ParamBeamArgs a, int n_cols, const __grid_constant__ ProgramTables tab) {
-  constexpr bool LT = (OPS & ~kOpsLight) == 0;
-  // staging tile so the [B][7] / [B][7][7] outputs leave the SM as whole rows (bulk copy)
-  __shared__ __align__(16) float tile_cov[kPBThreads * 49];
-  __shared__ __align__(16) float tile_mu[kPBThreads * 7];
-  extern __shared__ __align__(16) float pb_smem[];
-  const int64_t b0 = (int64_t)blockIdx.x * kPBThreads;
-  const int64_t b = b0 + threadIdx.x;
-  const bool live = b < a.B;
-  const int nb = (int)min((int64_t)kPBThreads, a.B - b0);
-  float* s_vals = pb_smem;
-  const DevOp* ops = tab.ops;
-  if (!TAB) {
-    DevOp* s_ops = reinterpret_cast<DevOp*>(pb_smem + n_cols * kPBThreads);
-    for (int i = threadIdx.x; i < a.n_ops * (int)(sizeof(DevOp) / 4); i += kPBThreads)
-      reinterpret_cast<float*>(s_ops)[i] = reinterpret_cast<const float*>(a.ops)[i];
-    ops = s_ops;
+struct SlotParamView {
+  const float* vals;
+  const ProgramTables& tab;
+  int s;
+  __device__ __forceinline__ float operator()(int col) const {
+    return vals[tab.col_slot[col] + (s & tab.col_mask[col])];
   }
-  MomentSink sink;
-  float energy = 0.f;
-  if (live) {
-    // this setting's parameter columns: thread = setting, so every load of a per-setting
-    // column is coalesced across the warp, a shared column is a broadcast, and nobody else
-    // reads this thread's slots (no barrier)
-#pragma unroll 4
-    for (int c = 0; c < n_cols; ++c) {
-      const int64_t off = TAB ? tab.col_offset[c] : __ldg(a.col_offset + c);
-      const int64_t st = TAB ? tab.col_stride[c] : __ldg(a.col_stride + c);
-      s_vals[c * kPBThreads + threadIdx.x] = __ldg(a.params + off + b * st);
-    }
-    const float* mi = a.mu_in + b * a.beam_stride * 7;
-    const float* ci = a.cov_in + b * a.beam_stride * 49;
-#pragma unroll
-    for (int i = 0; i < 7; ++i) sink.mu[i] = __ldg(mi + i);
-#pragma unroll
-    for (int i = 0; i < 7; ++i)
-#pragma unroll
-      for (int j = 0; j < 7; ++j) sink.cov[i][j] = __ldg(ci + i * 7 + j);
-    sink.bpm_out = a.bpm_out;
-    sink.B = a.B;
-    sink.b = b;
-    energy = a.energy_in[b];
-  }
-  if (!TAB) __syncthreads();
-  if (live) {
-    SmemParamView P{s_vals, kPBThreads, (int)threadIdx.x};
-    walk_program<OPS, LT>(ops, a.n_ops, a.final_stage, P, energy, sink);
-    if (a.energy_out) a.energy_out[b] = energy;
-#pragma unroll
-    for (int i = 0; i < 7; ++i) tile_mu[threadIdx.x * 7 + i] = sink.mu[i];
-#pragma unroll
-    for (int i = 0; i < 7; ++i)
-#pragma unroll
-      for (int j = 0; j < 7; ++j) tile_cov[threadIdx.x * 49 + i * 7 + j] = sink.cov[i][j];
-  }
-  // rows [b0, b0 + nb) of mu_out / cov_out are contiguous: one bulk copy each when their
-  // byte counts and addresses are multiples of 16 (nb % 4 == 0, 16-byte aligned outputs)
+};
+
+// Tile epilogue shared by the K6 kernels: rows [b0, b0 + nb) of mu_out / cov_out are contiguous,
+// one bulk copy each when their byte counts and addresses are multiples of 16 (nb % 4 == 0,
+// 16-byte aligned outputs), else a coalesced copy loop.  The caller owns the barrier BEFORE the
+// tiles are written again (bulk: tile_release()).
+__device__ __forceinline__ bool tile_store(const ParamBeamArgs& a, int64_t b0, int nb,
+                                           const float* tile_mu, const float* tile_cov) {
   const bool bulk = (nb & 3) == 0 && (((uintptr_t)a.mu_out | (uintptr_t)a.cov_out) & 15) == 0;
   if (bulk) {
     fence_proxy_async();
@@ -187,13 +146,145 @@ parambeam_fwd_kernel(ParamBeamArgs a, int n_cols, const __grid_constant__ Progra
       bulk_s2g(a.cov_out + b0 * 49, tile_cov, (uint32_t)nb * 196u);
       bulk_s2g(a.mu_out + b0 * 7, tile_mu, (uint32_t)nb * 28u);
       bulk_commit();
-      bulk_wait_read<0>();
     }
   } else {
     __syncthreads();
     for (int i = threadIdx.x; i < nb * 7; i += kPBThreads) a.mu_out[b0 * 7 + i] = tile_mu[i];
     for (int i = threadIdx.x; i < nb * 49; i += kPBThreads) a.cov_out[b0 * 49 + i] = tile_cov[i];
   }
+  return bulk;
+}
+// the bulk copies of the previous tile_store have finished READING the tiles
+__device__ __forceinline__ void tile_release() {
+  if (threadIdx.x == 0) bulk_wait_read<0>();
+  __syncthreads();
+}
+
+__device__ __forceinline__ void load_beam(const ParamBeamArgs& a, int64_t b, MomentSink& sink) {
+  const float* mi = a.mu_in + b * a.beam_stride * 7;
+  const float* ci = a.cov_in + b * a.beam_stride * 49;
+#pragma unroll
+  for (int i = 0; i < 7; ++i) sink.mu[i] = __ldg(mi + i);
+#pragma unroll
+  for (int i = 0; i < 7; ++i)
+#pragma unroll
+    for (int j = 0; j < 7; ++j) sink.cov[i][j] = __ldg(ci + i * 7 + j);
+  sink.bpm_out = a.bpm_out;
+  sink.B = a.B;
+  sink.b = b;
+}
+
+__device__ __forceinline__ void tile_fill(const MomentSink& sink, float* tile_mu, float* tile_cov) {
+#pragma unroll
+  for (int i = 0; i < 7; ++i) tile_mu[threadIdx.x * 7 + i] = sink.mu[i];
+#pragma unroll
+  for (int i = 0; i < 7; ++i)
+#pragma unroll
+    for (int j = 0; j < 7; ++j) tile_cov[threadIdx.x * 49 + i * 7 + j] = sink.cov[i][j];
+}
+
+// K6, the usual case: the program tables ride in the parameter space.  One thread owns one
+// setting of a 64-setting tile; a block walks tiles blockIdx.x, + gridDim.x, ... and fetches the
+// NEXT tile's per-setting parameters and energy into registers before it walks the current one,
+// so that after the first tile no DRAM latency sits on a thread's path (the shared-beam moments
+// are L1 hits, the outputs leave by bulk copy).  OPS within kOpsLight: light map (maps.cuh).
+constexpr int kPrefetchCols = 8;
+
+template <int OPS>
+__global__ void __launch_bounds__(kPBThreads)
+parambeam_fwd_kernel(ParamBeamArgs a, int n_cols, const __grid_constant__ ProgramTables tab) {
+  constexpr bool LT = (OPS & ~kOpsLight) == 0;
+  __shared__ __align__(16) float tile_cov[kPBThreads * 49];
+  __shared__ __align__(16) float tile_mu[kPBThreads * 7];
+  extern __shared__ __align__(16) float pb_smem[];
+  float* s_vals = pb_smem;
+  const int tid = threadIdx.x;
+  const int64_t n_tiles = (a.B + kPBThreads - 1) / kPBThreads;
+  const int n_var = tab.n_var;
+
+  float pre[kPrefetchCols], e_pre = 0.f;
+  auto fetch = [&](int64_t b) {  // all loads issued back to back, nothing waits on them here
+    const bool lv = b < a.B;
+#pragma unroll
+    for (int v = 0; v < kPrefetchCols; ++v) {
+      pre[v] = 0.f;
+      if (lv && v < n_var) {
+        const int c = tab.var_cols[v];
+        pre[v] = __ldg(a.params + tab.col_offset[c] + b * (int64_t)tab.col_stride[c]);
+      }
+    }
+    e_pre = lv ? __ldg(a.energy_in + b) : 0.f;
+  };
+  fetch((int64_t)blockIdx.x * kPBThreads + tid);
+  // columns shared by all settings: thread c fetches column c once for the block
+  for (int c = tid; c < n_cols; c += kPBThreads)
+    if (tab.col_stride[c] == 0) s_vals[tab.col_slot[c]] = __ldg(a.params + tab.col_offset[c]);
+  __syncthreads();
+
+  bool bulk_pending = false;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t b0 = tile * kPBThreads, b = b0 + tid;
+    const bool live = b < a.B;
+    const int nb = (int)min((int64_t)kPBThreads, a.B - b0);
+    // this tile's per-setting columns: a thread's slots are read by that thread only
+#pragma unroll
+    for (int v = 0; v < kPrefetchCols; ++v)
+      if (v < n_var) s_vals[tab.col_slot[tab.var_cols[v]] + tid] = pre[v];
+    float energy = e_pre;
+    if (live)
+      for (int v = kPrefetchCols; v < n_var; ++v) {  // more per-setting columns than registers
+        const int c = tab.var_cols[v];
+        s_vals[tab.col_slot[c] + tid] =
+            __ldg(a.params + tab.col_offset[c] + b * (int64_t)tab.col_stride[c]);
+      }
+    fetch(b + (int64_t)gridDim.x * kPBThreads);  // the next tile of this block
+    MomentSink sink;
+    if (live) {
+      load_beam(a, b, sink);
+      SlotParamView P{s_vals, tab, tid};
+      walk_program<OPS, LT>(tab.ops, a.n_ops, a.final_stage, P, energy, sink);
+      if (a.energy_out) a.energy_out[b] = energy;
+    }
+    if (bulk_pending) tile_release();
+    if (live) tile_fill(sink, tile_mu, tile_cov);
+    bulk_pending = tile_store(a, b0, nb, tile_mu, tile_cov);
+    if (!bulk_pending) __syncthreads();
+  }
+  if (bulk_pending && tid == 0) bulk_wait_read<0>();
+}
+
+// K6 for programs too large for the parameter space (> kTabOps ops or > kTabCols columns):
+// one tile per block, ops staged in shared memory, column tables read from global memory.
+__global__ void __launch_bounds__(kPBThreads) parambeam_fwd_big_kernel(ParamBeamArgs a, int n_cols) {
+  __shared__ __align__(16) float tile_cov[kPBThreads * 49];
+  __shared__ __align__(16) float tile_mu[kPBThreads * 7];
+  extern __shared__ __align__(16) float pb_smem[];
+  const int64_t b0 = (int64_t)blockIdx.x * kPBThreads;
+  const int64_t b = b0 + threadIdx.x;
+  const bool live = b < a.B;
+  const int nb = (int)min((int64_t)kPBThreads, a.B - b0);
+  float* s_vals = pb_smem;
+  DevOp* s_ops = reinterpret_cast<DevOp*>(pb_smem + n_cols * kPBThreads);
+  for (int i = threadIdx.x; i < a.n_ops * (int)(sizeof(DevOp) / 4); i += kPBThreads)
+    reinterpret_cast<float*>(s_ops)[i] = reinterpret_cast<const float*>(a.ops)[i];
+  MomentSink sink;
+  float energy = 0.f;
+  if (live) {
+#pragma unroll 4
+    for (int c = 0; c < n_cols; ++c)
+      s_vals[c * kPBThreads + threadIdx.x] =
+          __ldg(a.params + __ldg(a.col_offset + c) + b * (int64_t)__ldg(a.col_stride + c));
+    load_beam(a, b, sink);
+    energy = a.energy_in[b];
+  }
+  __syncthreads();
+  if (live) {
+    SmemParamView P{s_vals, kPBThreads, (int)threadIdx.x};
+    walk_program<kOpsAll>(s_ops, a.n_ops, a.final_stage, P, energy, sink);
+    if (a.energy_out) a.energy_out[b] = energy;
+    tile_fill(sink, tile_mu, tile_cov);
+  }
+  if (tile_store(a, b0, nb, tile_mu, tile_cov) && threadIdx.x == 0) bulk_wait_read<0>();
 }
 
 }  // namespace lynx
@@ -317,28 +408,39 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
   const unsigned blocks = (unsigned)((B + kPBThreads - 1) / kPBThreads);
   const int n_cols = (int)p->col_offset.size();
   const bool tabbed = a.n_ops <= kTabOps && n_cols <= kTabCols;
-  const size_t smem = (size_t)n_cols * kPBThreads * 4 + (tabbed ? 0 : a.n_ops * sizeof(DevOp));
-  if (smem > 200 * 1024) return LYNX_E_TOOLARGE;  // > 800 parameter columns
   ProgramTables tab;
+  tab.n_var = tab.smem_words = 0;
   if (tabbed) {
     std::copy(p->dev_ops.begin(), p->dev_ops.end(), tab.ops);
     std::copy(p->col_offset.begin(), p->col_offset.end(), tab.col_offset);
     std::copy(p->col_stride.begin(), p->col_stride.end(), tab.col_stride);
+    for (int c = 0; c < n_cols; ++c) {
+      const bool var = p->col_stride[c] != 0;
+      tab.col_slot[c] = tab.smem_words;
+      tab.col_mask[c] = var ? -1 : 0;
+      tab.smem_words += var ? kPBThreads : 1;
+      if (var) tab.var_cols[tab.n_var++] = c;
+    }
   }
+  const size_t smem = tabbed ? (size_t)tab.smem_words * 4
+                             : (size_t)n_cols * kPBThreads * 4 + a.n_ops * sizeof(DevOp);
+  if (smem > 200 * 1024) return LYNX_E_TOOLARGE;  // > 800 parameter columns
   {
     ProfileScope ps(2, (cudaStream_t)stream);
     const bool light = (p->op_mask & ~kOpsLight) == 0;
-    auto launch = [&](auto kern) {
+    auto launch = [&](auto kern, unsigned grid, auto... extra) {
       if (smem > 48 * 1024)
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      kern<<<blocks, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols, tab);
+      kern<<<grid, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols, extra...);
     };
+    // persistent above 8 resident blocks per SM (the register budget of the light kernel)
+    const unsigned grid = std::min<unsigned>(blocks, 8u * (unsigned)p->sm_count);
     if (tabbed && light)
-      launch(parambeam_fwd_kernel<true, kOpsLight>);
+      launch(parambeam_fwd_kernel<kOpsLight>, grid, tab);
     else if (tabbed)
-      launch(parambeam_fwd_kernel<true, kOpsAll>);
+      launch(parambeam_fwd_kernel<kOpsAll>, grid, tab);
     else
-      launch(parambeam_fwd_kernel<false, kOpsAll>);
+      launch(parambeam_fwd_big_kernel, blocks);
   }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());

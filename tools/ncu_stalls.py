@@ -1,5 +1,5 @@
 """Summarise an ncu report's source page: top SASS instructions by stall samples and the
-breakdown of stall reasons.  usage: python tools/ncu_stalls.py report.ncu-rep [top]"""
+breakdown of stall reasons.  usage: python tools/ncu_stalls.py report.ncu-rep [top] [launch]"""
 import csv
 import io
 import subprocess
@@ -9,7 +9,7 @@ rep = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 25
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 blocks = out.split('"Kernel Name"')
-blk = '"Kernel Name"' + blocks[1]
+blk = '"Kernel Name"' + blocks[int(sys.argv[3]) if len(sys.argv) > 3 else 1]
 lines = blk.splitlines()
 rows = list(csv.reader(io.StringIO("\n".join(lines[1:]))))
 hdr = rows[0]
