@@ -110,16 +110,18 @@ constexpr int kPBThreads = 64;
 // Program tables small enough to ride in the kernel's parameter space (constant bank): the
 // ops and the column tables are then there when the block starts, and the only cold loads
 // of the kernel -- parameters, beam, energy -- are all issued at once (one DRAM round trip).
-constexpr int kTabOps = 48, kTabCols = 96;
+constexpr int kTabOps = 40, kTabCols = 64;  // 3.6 KB of the 4 KB classic parameter space
 struct ProgramTables {
   DevOp ops[kTabOps];
   int64_t col_offset[kTabCols];
   int32_t col_stride[kTabCols];
-  // shared-memory slot of column c: word col_slot[c] + (thread & col_mask[c]); a column shared
-  // by all settings (stride 0) has ONE slot per block, a per-setting column one per thread
-  int32_t col_slot[kTabCols];
-  int32_t col_mask[kTabCols];
-  int32_t var_cols[kTabCols];  // the per-setting columns
+  // shared-memory slot of column c: word slot + (thread & mask); a column shared by all
+  // settings (stride 0) has ONE slot per block (mask 0), a per-setting column one per thread
+  int2 col_slot_mask[kTabCols];
+  // the per-setting columns: offset, stride and slot again, packed for the prefetch
+  int64_t var_offset[kTabCols];
+  int32_t var_stride[kTabCols];
+  int32_t var_slot[kTabCols];
   int32_t n_var, smem_words;
 };
 
@@ -128,7 +130,8 @@ struct SlotParamView {
   const ProgramTables& tab;
   int s;
   __device__ __forceinline__ float operator()(int col) const {
-    return vals[tab.col_slot[col] + (s & tab.col_mask[col])];
+    const int2 sm = tab.col_slot_mask[col];
+    return vals[sm.x + (s & sm.y)];
   }
 };
 
@@ -202,45 +205,48 @@ parambeam_fwd_kernel(ParamBeamArgs a, int n_cols, const __grid_constant__ Progra
   const int64_t n_tiles = (a.B + kPBThreads - 1) / kPBThreads;
   const int n_var = tab.n_var;
 
+  // per-setting parameters and energy of settings [b0, b0 + 64): all loads issued back to back,
+  // nothing waits on them here (settings are indexed in 32 bits: B < 2^31, the launcher checks)
   float pre[kPrefetchCols], e_pre = 0.f;
-  auto fetch = [&](int64_t b) {  // all loads issued back to back, nothing waits on them here
-    const bool lv = b < a.B;
+  auto fetch = [&](int64_t b0) {
+    const uint32_t b = (uint32_t)b0 + tid;
+    if (b < (uint32_t)a.B) {
 #pragma unroll
-    for (int v = 0; v < kPrefetchCols; ++v) {
-      pre[v] = 0.f;
-      if (lv && v < n_var) {
-        const int c = tab.var_cols[v];
-        pre[v] = __ldg(a.params + tab.col_offset[c] + b * (int64_t)tab.col_stride[c]);
-      }
+      for (int v = 0; v < kPrefetchCols; ++v)
+        if (v < n_var)
+          pre[v] = __ldg(a.params + (tab.var_offset[v] + (uint64_t)b * (uint32_t)tab.var_stride[v]));
+      e_pre = __ldg(a.energy_in + b);
     }
-    e_pre = lv ? __ldg(a.energy_in + b) : 0.f;
   };
-  fetch((int64_t)blockIdx.x * kPBThreads + tid);
+#pragma unroll
+  for (int v = 0; v < kPrefetchCols; ++v) pre[v] = 0.f;
+  int64_t tile = blockIdx.x;
+  fetch(tile * kPBThreads);
+  MomentSink sink;
+  if (tile * kPBThreads + tid < a.B) load_beam(a, tile * kPBThreads + tid, sink);  // in flight too
   // columns shared by all settings: thread c fetches column c once for the block
   for (int c = tid; c < n_cols; c += kPBThreads)
-    if (tab.col_stride[c] == 0) s_vals[tab.col_slot[c]] = __ldg(a.params + tab.col_offset[c]);
+    if (tab.col_stride[c] == 0) s_vals[tab.col_slot_mask[c].x] = __ldg(a.params + tab.col_offset[c]);
   __syncthreads();
 
   bool bulk_pending = false;
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  for (; tile < n_tiles; tile += gridDim.x) {
     const int64_t b0 = tile * kPBThreads, b = b0 + tid;
     const bool live = b < a.B;
     const int nb = (int)min((int64_t)kPBThreads, a.B - b0);
+    if (live && tile != blockIdx.x) load_beam(a, b, sink);  // L1 hits for a shared beam
     // this tile's per-setting columns: a thread's slots are read by that thread only
 #pragma unroll
     for (int v = 0; v < kPrefetchCols; ++v)
-      if (v < n_var) s_vals[tab.col_slot[tab.var_cols[v]] + tid] = pre[v];
+      if (v < n_var) s_vals[tab.var_slot[v] + tid] = pre[v];
     float energy = e_pre;
     if (live)
-      for (int v = kPrefetchCols; v < n_var; ++v) {  // more per-setting columns than registers
-        const int c = tab.var_cols[v];
-        s_vals[tab.col_slot[c] + tid] =
-            __ldg(a.params + tab.col_offset[c] + b * (int64_t)tab.col_stride[c]);
-      }
-    fetch(b + (int64_t)gridDim.x * kPBThreads);  // the next tile of this block
-    MomentSink sink;
+      for (int v = kPrefetchCols; v < n_var; ++v)  // more per-setting columns than registers
+        s_vals[tab.var_slot[v] + tid] =
+            __ldg(a.params + (tab.var_offset[v] + (uint64_t)(uint32_t)b * (uint32_t)tab.var_stride[v]));
+    const int64_t next_b0 = b0 + (int64_t)gridDim.x * kPBThreads;  // the next tile of this block
+    if (next_b0 < a.B) fetch(next_b0);
     if (live) {
-      load_beam(a, b, sink);
       SlotParamView P{s_vals, tab, tid};
       walk_program<OPS, LT>(tab.ops, a.n_ops, a.final_stage, P, energy, sink);
       if (a.energy_out) a.energy_out[b] = energy;
@@ -389,6 +395,7 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
       B <= 0 || (beam_stride != 0 && beam_stride != 1))
     return LYNX_E_BADARG;
   if (p->n_bpm_slots > 0 && !d_bpm_out) return LYNX_E_BADARG;
+  if (B >= ((int64_t)1 << 31)) return LYNX_E_TOOLARGE;  // 0.5 TB of moments
   ParamBeamArgs a;
   a.ops = p->d_ops;
   a.n_ops = (int)p->dev_ops.size();
@@ -416,10 +423,14 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
     std::copy(p->col_stride.begin(), p->col_stride.end(), tab.col_stride);
     for (int c = 0; c < n_cols; ++c) {
       const bool var = p->col_stride[c] != 0;
-      tab.col_slot[c] = tab.smem_words;
-      tab.col_mask[c] = var ? -1 : 0;
+      if (var && p->col_stride[c] < 0) return LYNX_E_BADARG;
+      tab.col_slot_mask[c] = make_int2(tab.smem_words, var ? -1 : 0);
+      if (var) {
+        tab.var_offset[tab.n_var] = p->col_offset[c];
+        tab.var_stride[tab.n_var] = p->col_stride[c];
+        tab.var_slot[tab.n_var++] = tab.smem_words;
+      }
       tab.smem_words += var ? kPBThreads : 1;
-      if (var) tab.var_cols[tab.n_var++] = c;
     }
   }
   const size_t smem = tabbed ? (size_t)tab.smem_words * 4
@@ -433,8 +444,8 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       kern<<<grid, kPBThreads, smem, (cudaStream_t)stream>>>(a, n_cols, extra...);
     };
-    // persistent above 8 resident blocks per SM (the register budget of the light kernel)
-    const unsigned grid = std::min<unsigned>(blocks, 8u * (unsigned)p->sm_count);
+    // persistent above the resident blocks per SM (the register budgets of the two variants)
+    const unsigned grid = std::min<unsigned>(blocks, (light ? 8u : 5u) * (unsigned)p->sm_count);
     if (tabbed && light)
       launch(parambeam_fwd_kernel<kOpsLight>, grid, tab);
     else if (tabbed)
