@@ -15,96 +15,6 @@ namespace lynx {
 // loads (a lone thread chasing col_offset -> params per column pays ~1 us of dependent
 // latency per column, which is the whole kernel at B = 1), then walk from shared memory.
 constexpr int kComposeTPB = 128;
-
-template <bool STAGED, int OPS, bool MAPS = false>
-__global__ void __launch_bounds__(kComposeTPB) compose_kernel(ComposeArgs a, int n_cols, int S) {
-  extern __shared__ __align__(16) float cs_smem[];
-  // Programmatic dependent launch: let the particle kernel start its prologue (barrier
-  // init, TMA requests for its first tiles) now; it waits (griddepcontrol.wait) for this
-  // grid to finish before it reads the records or touches the zeroed image.
-  asm volatile("griddepcontrol.launch_dependents;");
-  if (a.hist_out && blockIdx.x == 0 && threadIdx.x == 0) {  // debug stamp (exchange trace)
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    reinterpret_cast<unsigned long long*>(a.hist_out)[8] = t;  // K1 block 0 starts
-  }
-  // the last block validates the screen's edge tables and writes the bin-lookup geometry
-  const int hist_blocks = a.hist_out ? 1 : 0;
-  if (hist_blocks && blockIdx.x == gridDim.x - 1) {
-    HistAxis* h = reinterpret_cast<HistAxis*>(a.hist_out);
-    if (a.bbox_clear && threadIdx.x < 4) a.bbox_clear[threadIdx.x] = 0;  // this call's cell
-    hist_axis_setup(a.hist_ex, a.hist_W, h, threadIdx.x, kComposeTPB);
-    hist_axis_setup(a.hist_ey, a.hist_H, h + 1, threadIdx.x, kComposeTPB);
-    return;
-  }
-  // blocks beyond the compose range only zero caller buffers (image / sums)
-  const int compose_blocks = (int)((a.B + S - 1) / S);
-  if ((int)blockIdx.x >= compose_blocks) {
-    const int zb = blockIdx.x - compose_blocks, nzb = gridDim.x - compose_blocks - hist_blocks;
-    float4* z = reinterpret_cast<float4*>(a.zero_ptr);
-    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (a.zero_rect) {
-      // persistent image: rows [H - v3, v2) x columns [W - v0, v1) of every setting's image
-      // (the cell holds max(W - ix), max(ix + 1), max(H - iy), max(iy + 1); all 0 = nothing lit)
-      const int v0 = __ldg(a.zero_rect), v1 = __ldg(a.zero_rect + 1), v2 = __ldg(a.zero_rect + 2),
-                v3 = __ldg(a.zero_rect + 3);
-      if (v1 <= 0 || v3 <= 0) return;
-      const int r0 = a.hist_H - v3, nr = v2 - r0;
-      const int c0 = (a.hist_W - v0) & ~3, nv = (min((v1 + 3) & ~3, a.hist_W) - c0) >> 2;
-      const int64_t per_img = (int64_t)nr * nv, total = a.B * per_img;
-      for (int64_t i = (int64_t)zb * kComposeTPB + threadIdx.x; i < total;
-           i += (int64_t)nzb * kComposeTPB) {
-        const int64_t b = i / per_img, rem = i - b * per_img;
-        const int r = (int)(rem / nv), cv = (int)(rem - (int64_t)r * nv);
-        *reinterpret_cast<float4*>(a.zero_ptr + ((b * a.hist_H + r0 + r) * (int64_t)a.hist_W + c0 +
-                                                 4 * cv)) = zero;
-      }
-      return;
-    }
-    for (int64_t i = (int64_t)zb * kComposeTPB + threadIdx.x; i < a.zero_vec4;
-         i += (int64_t)nzb * kComposeTPB)
-      z[i] = zero;
-    return;
-  }
-  const int64_t b0 = (int64_t)blockIdx.x * S;
-  const int ns = (int)min((int64_t)S, a.B - b0);
-  DevOp* s_ops = reinterpret_cast<DevOp*>(cs_smem);
-  float* s_vals = cs_smem + a.n_ops * (sizeof(DevOp) / sizeof(float));
-  if (STAGED) {
-    for (int i = threadIdx.x; i < a.n_ops * (int)(sizeof(DevOp) / 4); i += kComposeTPB)
-      cs_smem[i] = reinterpret_cast<const float*>(a.ops)[i];
-    for (int i = threadIdx.x; i < n_cols * ns; i += kComposeTPB) {
-      const int c = i / ns, sl = i - c * ns;
-      s_vals[c * S + sl] = __ldg(a.params + __ldg(a.col_offset + c) +
-                                 (b0 + sl) * (int64_t)__ldg(a.col_stride + c));
-    }
-    __syncthreads();
-  }
-  if ((int)threadIdx.x >= ns) return;
-  const int64_t b = b0 + threadIdx.x;
-  RecordSinkT<MAPS> sink;
-  sink.rec = a.records + b * a.rec_floats;
-  sink.maps_out = a.maps_out ? a.maps_out + b * (int64_t)a.n_stages * 49 : nullptr;
-  sink.off_cav = a.off_cav;
-  sink.off_centre = a.off_centre;
-  sink.off_screen = a.off_screen;
-#pragma unroll
-  for (int i = 0; i < 6; ++i)
-    sink.ctr[i] = a.seed ? __ldg(a.seed + b * a.seed_row_stride + i * a.seed_ld) : 0.f;
-  float energy = a.energy_in[b];
-  if (STAGED) {
-    SmemParamView P{s_vals, S, (int)threadIdx.x};
-    walk_program<OPS, (OPS & ~kOpsLight) == 0>(s_ops, a.n_ops, a.final_stage, P, energy, sink);
-  } else {
-    ParamView P{a.params, a.col_offset, a.col_stride, b};
-    walk_program<OPS>(a.ops, a.n_ops, a.final_stage, P, energy, sink);
-  }
-  float* fc = sink.rec + a.final_centre;
-#pragma unroll
-  for (int i = 0; i < 6; ++i) fc[i] = sink.ctr[i];
-  if (a.energy_out) a.energy_out[b] = energy;
-}
-
 constexpr int kPBThreads = 64;
 
 // Program tables small enough to ride in the kernel's parameter space (constant bank): the
@@ -134,6 +44,140 @@ struct SlotParamView {
     return vals[sm.x + (s & sm.y)];
   }
 };
+
+
+// STAGED: 0 = ops / column tables / parameters read from global memory as the walk needs them,
+// 1 = staged in shared memory from global memory, 2 = ops and column tables from the parameter
+// space (ProgramTables), parameters staged in shared memory.
+template <int STAGED, int OPS, bool MAPS = false>
+__global__ void __launch_bounds__(kComposeTPB)
+compose_kernel(ComposeArgs a, int n_cols, int S, const __grid_constant__ ProgramTables tab) {
+  extern __shared__ __align__(16) float cs_smem[];
+  // Programmatic dependent launch: let the particle kernel start its prologue (barrier
+  // init, TMA requests for its first tiles) now; it waits (griddepcontrol.wait) for this
+  // grid to finish before it reads the records or touches the zeroed image.
+  asm volatile("griddepcontrol.launch_dependents;");
+  if (a.hist_out && blockIdx.x == 0 && threadIdx.x == 0) {  // debug stamp (exchange trace)
+#ifdef LYNX_EXPERIMENTS
+    reinterpret_cast<unsigned long long*>(a.hist_out)[11] = 0ull;
+#endif
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    reinterpret_cast<unsigned long long*>(a.hist_out)[8] = t;  // K1 block 0 starts
+  }
+  // the FIRST block validates the screen's edge tables and writes the bin-lookup geometry (it
+  // and the compose blocks are the long poles of the launch; the zeroing blocks come last)
+  const int hist_blocks = a.hist_out ? 1 : 0;
+  if (hist_blocks && blockIdx.x == 0) {
+    HistAxis* h = reinterpret_cast<HistAxis*>(a.hist_out);
+    if (a.bbox_clear && threadIdx.x < 4) a.bbox_clear[threadIdx.x] = 0;  // this call's cell
+    hist_axes_setup(a.hist_ex, a.hist_W, a.hist_ey, a.hist_H, h, threadIdx.x, kComposeTPB);
+#ifdef LYNX_EXPERIMENTS
+    if (threadIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      reinterpret_cast<unsigned long long*>(a.hist_out)[10] = t;  // histogram block done
+    }
+#endif
+    return;
+  }
+  // blocks beyond the compose range only zero caller buffers (image / sums)
+  const int first_compose = hist_blocks;
+  const int compose_blocks = (int)((a.B + S - 1) / S);
+  if ((int)blockIdx.x >= first_compose + compose_blocks) {
+    const int zb = blockIdx.x - compose_blocks - first_compose, nzb = gridDim.x - compose_blocks - hist_blocks;
+    float4* z = reinterpret_cast<float4*>(a.zero_ptr);
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.zero_rect) {
+      // persistent image: rows [H - v3, v2) x columns [W - v0, v1) of every setting's image
+      // (the cell holds max(W - ix), max(ix + 1), max(H - iy), max(iy + 1); all 0 = nothing lit)
+      const int v0 = __ldg(a.zero_rect), v1 = __ldg(a.zero_rect + 1), v2 = __ldg(a.zero_rect + 2),
+                v3 = __ldg(a.zero_rect + 3);
+      if (v1 <= 0 || v3 <= 0) return;
+      const int r0 = a.hist_H - v3, nr = v2 - r0;
+      const int c0 = (a.hist_W - v0) & ~3, nv = (min((v1 + 3) & ~3, a.hist_W) - c0) >> 2;
+      const int64_t per_img = (int64_t)nr * nv, total = a.B * per_img;
+      for (int64_t i = (int64_t)zb * kComposeTPB + threadIdx.x; i < total;
+           i += (int64_t)nzb * kComposeTPB) {
+        const int64_t b = i / per_img, rem = i - b * per_img;
+        const int r = (int)(rem / nv), cv = (int)(rem - (int64_t)r * nv);
+        *reinterpret_cast<float4*>(a.zero_ptr + ((b * a.hist_H + r0 + r) * (int64_t)a.hist_W + c0 +
+                                                 4 * cv)) = zero;
+      }
+    } else {
+      for (int64_t i = (int64_t)zb * kComposeTPB + threadIdx.x; i < a.zero_vec4;
+           i += (int64_t)nzb * kComposeTPB)
+        z[i] = zero;
+    }
+#ifdef LYNX_EXPERIMENTS
+    if (threadIdx.x == 0 && a.hist_out) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      atomicMax(reinterpret_cast<unsigned long long*>(a.hist_out) + 11, t);  // last zeroing block done
+    }
+#endif
+    return;
+  }
+  if (blockIdx.x == first_compose) LYNX_TSTAMP(a.hist_out, 17);
+  const int64_t b0 = (int64_t)(blockIdx.x - first_compose) * S;
+  const int ns = (int)min((int64_t)S, a.B - b0);
+  const int64_t b = b0 + threadIdx.x;
+  const bool mine = (int)threadIdx.x < ns;
+  DevOp* s_ops = reinterpret_cast<DevOp*>(cs_smem);
+  float* s_vals = cs_smem + (STAGED == 1 ? a.n_ops * (sizeof(DevOp) / sizeof(float)) : 0);
+  // every cold load of the block is issued before anything waits: the seed centre and the energy
+  // of this thread's setting, then the tile's parameters (after a flush of L2 each first touch
+  // of a buffer is a DRAM and page-table miss of a microsecond or more; chained, they were
+  // most of K1 at B = 1)
+  RecordSinkT<MAPS> sink;
+  float energy = 0.f;
+  if (mine) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+      sink.ctr[i] = a.seed ? __ldg(a.seed + b * a.seed_row_stride + i * a.seed_ld) : 0.f;
+    energy = __ldg(a.energy_in + b);
+  }
+  if (STAGED == 1) {
+    for (int i = threadIdx.x; i < a.n_ops * (int)(sizeof(DevOp) / 4); i += kComposeTPB)
+      cs_smem[i] = reinterpret_cast<const float*>(a.ops)[i];
+  }
+  if (STAGED) {
+    for (int i = threadIdx.x; i < n_cols * ns; i += kComposeTPB) {
+      const int c = i / ns, sl = i - c * ns;
+      const int64_t off = STAGED == 2 ? tab.col_offset[c] : __ldg(a.col_offset + c);
+      const int64_t st = STAGED == 2 ? tab.col_stride[c] : __ldg(a.col_stride + c);
+      s_vals[c * S + sl] = __ldg(a.params + off + (b0 + sl) * st);
+    }
+    __syncthreads();
+  }
+  if (!mine) return;
+  if (b == 0) LYNX_TSTAMP(a.hist_out, 15);
+  sink.rec = a.records + b * a.rec_floats;
+  sink.maps_out = a.maps_out ? a.maps_out + b * (int64_t)a.n_stages * 49 : nullptr;
+  sink.off_cav = a.off_cav;
+  sink.off_centre = a.off_centre;
+  sink.off_screen = a.off_screen;
+  constexpr bool LT = (OPS & ~kOpsLight) == 0;
+  if (STAGED) {
+    SmemParamView P{s_vals, S, (int)threadIdx.x};
+    walk_program<OPS, LT>(STAGED == 2 ? tab.ops : s_ops, a.n_ops, a.final_stage, P, energy, sink);
+  } else {
+    ParamView P{a.params, a.col_offset, a.col_stride, b};
+    walk_program<OPS, LT>(a.ops, a.n_ops, a.final_stage, P, energy, sink);
+  }
+  if (b == 0) LYNX_TSTAMP(a.hist_out, 16);
+  float* fc = sink.rec + a.final_centre;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) fc[i] = sink.ctr[i];
+  if (a.energy_out) a.energy_out[b] = energy;
+#ifdef LYNX_EXPERIMENTS
+  if (b == 0 && a.hist_out) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    reinterpret_cast<unsigned long long*>(a.hist_out)[9] = t;  // walker of setting 0 done
+  }
+#endif
+}
 
 // Tile epilogue shared by the K6 kernels: rows [b0, b0 + nb) of mu_out / cov_out are contiguous,
 // one bulk copy each when their byte counts and addresses are multiples of 16 (nb % 4 == 0,
@@ -295,6 +339,29 @@ __global__ void __launch_bounds__(kPBThreads) parambeam_fwd_big_kernel(ParamBeam
 
 }  // namespace lynx
 
+namespace lynx {
+// false: the program does not fit the parameter space (the kernels then read global tables)
+static bool fill_tables(const lynx_program_t* p, ProgramTables& tab) {
+  const int n_ops = (int)p->dev_ops.size(), n_cols = (int)p->col_offset.size();
+  tab.n_var = tab.smem_words = 0;
+  if (n_ops > kTabOps || n_cols > kTabCols) return false;
+  std::copy(p->dev_ops.begin(), p->dev_ops.end(), tab.ops);
+  std::copy(p->col_offset.begin(), p->col_offset.end(), tab.col_offset);
+  std::copy(p->col_stride.begin(), p->col_stride.end(), tab.col_stride);
+  for (int c = 0; c < n_cols; ++c) {
+    const bool var = p->col_stride[c] != 0;
+    tab.col_slot_mask[c] = make_int2(tab.smem_words, var ? -1 : 0);
+    if (var) {
+      tab.var_offset[tab.n_var] = p->col_offset[c];
+      tab.var_stride[tab.n_var] = p->col_stride[c];
+      tab.var_slot[tab.n_var++] = tab.smem_words;
+    }
+    tab.smem_words += var ? kPBThreads : 1;
+  }
+  return true;
+}
+}  // namespace lynx
+
 using namespace lynx;
 
 namespace lynx {
@@ -337,10 +404,19 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   a.zero_rect = zero_rect;
   a.bbox_clear = bbox_clear;
   if (zero_rect && (!hist_out || !zero_ptr || (hist_W & 3))) return LYNX_E_BADARG;
-  const int zero_blocks_per_sm = 2;
+#ifdef LYNX_EXPERIMENTS  // timing decomposition of K1 (results are garbage)
+  if (getenv("LYNX_K1_NOZERO")) a.zero_vec4 = 0;
+  if (getenv("LYNX_K1_NOWALK")) a.n_ops = 0;
+#endif
+  int zero_blocks_per_sm = 2;
+#ifdef LYNX_EXPERIMENTS
+  if (const char* e = getenv("LYNX_K1_ZBLOCKS")) zero_blocks_per_sm = atoi(e);
+#endif
   const int n_cols = (int)p->col_offset.size();
   const size_t budget = 40 * 1024;
-  const size_t ops_bytes = a.n_ops * sizeof(DevOp);
+  ProgramTables tab;
+  const bool tabbed = fill_tables(p, tab);
+  const size_t ops_bytes = tabbed ? 0 : a.n_ops * sizeof(DevOp);
   int S = kComposeTPB;
   bool staged = false;
   if (ops_bytes + (size_t)std::max(n_cols, 1) * 4 <= budget) {
@@ -358,17 +434,31 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   {
     ProfileScope ps(0, st);
     const bool light = (p->op_mask & ~kOpsLight) == 0;
+    auto launch = [&](auto kern) {
+      // the histogram block's static chunk buffers (32 KB) + the staged parameters exceed the
+      // 48 KB a kernel gets without opting in
+      static bool attr_set = false;  // per instantiation
+      if (!attr_set) {
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        attr_set = true;
+      }
+      kern<<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S, tab);
+    };
     if (d_maps_out) {  // public lynx_compose_maps: records + 7x7 stage maps
-      if (staged)
-        compose_kernel<true, kOpsAll, true><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);
+      if (staged && tabbed)
+        launch(compose_kernel<2, kOpsAll, true>);
+      else if (staged)
+        launch(compose_kernel<1, kOpsAll, true>);
       else
-        compose_kernel<false, kOpsAll, true><<<blocks, kComposeTPB, 0, st>>>(a, n_cols, S);
-    } else if (staged && light)
-      compose_kernel<true, kOpsLight><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);
+        launch(compose_kernel<0, kOpsAll, true>);
+    } else if (staged && tabbed && light)
+      launch(compose_kernel<2, kOpsLight>);
+    else if (staged && tabbed)
+      launch(compose_kernel<2, kOpsAll>);
     else if (staged)
-      compose_kernel<true, kOpsAll><<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S);
+      launch(compose_kernel<1, kOpsAll>);
     else
-      compose_kernel<false, kOpsAll><<<blocks, kComposeTPB, 0, st>>>(a, n_cols, S);
+      launch(compose_kernel<0, kOpsAll>);
   }
   count_launch();
   LYNX_CUDA_OK(cudaGetLastError());
@@ -414,25 +504,10 @@ extern "C" int lynx_parambeam_fwd(const lynx_program_t* p, const float* d_params
   a.energy_out = d_energy_out;
   const unsigned blocks = (unsigned)((B + kPBThreads - 1) / kPBThreads);
   const int n_cols = (int)p->col_offset.size();
-  const bool tabbed = a.n_ops <= kTabOps && n_cols <= kTabCols;
   ProgramTables tab;
-  tab.n_var = tab.smem_words = 0;
-  if (tabbed) {
-    std::copy(p->dev_ops.begin(), p->dev_ops.end(), tab.ops);
-    std::copy(p->col_offset.begin(), p->col_offset.end(), tab.col_offset);
-    std::copy(p->col_stride.begin(), p->col_stride.end(), tab.col_stride);
-    for (int c = 0; c < n_cols; ++c) {
-      const bool var = p->col_stride[c] != 0;
-      if (var && p->col_stride[c] < 0) return LYNX_E_BADARG;
-      tab.col_slot_mask[c] = make_int2(tab.smem_words, var ? -1 : 0);
-      if (var) {
-        tab.var_offset[tab.n_var] = p->col_offset[c];
-        tab.var_stride[tab.n_var] = p->col_stride[c];
-        tab.var_slot[tab.n_var++] = tab.smem_words;
-      }
-      tab.smem_words += var ? kPBThreads : 1;
-    }
-  }
+  const bool tabbed = fill_tables(p, tab);
+  for (int c = 0; c < n_cols; ++c)
+    if (p->col_stride[c] < 0) return LYNX_E_BADARG;
   const size_t smem = tabbed ? (size_t)tab.smem_words * 4
                              : (size_t)n_cols * kPBThreads * 4 + a.n_ops * sizeof(DevOp);
   if (smem > 200 * 1024) return LYNX_E_TOOLARGE;  // > 800 parameter columns

@@ -233,6 +233,89 @@ __device__ __forceinline__ void hist_axis_setup(const float* __restrict__ e, int
   __syncthreads();
 }
 
+// Both axes at once for K1's histogram block, in fp32 and without a division routine.  The
+// tables are staged in shared memory by cp.async -- every element in flight at once, ONE DRAM
+// round trip per 4096-entry chunk pair -- where hist_axis_setup's loop paid one cold miss per
+// iteration, and its fp64 divisions a few microseconds of cold instruction fetches: the block
+// was K1's critical path (8-9 us of the 1 M-particle step, tools/k2_timeline.py).
+// The fp32 evaluation of d = |e[i] - (e0 + step i)| / step is off by at most
+// n 2^-22 (step's rounding, acting over n bins) + 2^-12 (the fma's and e0's roundings at
+// |e| <= en - e0, the reciprocal's 2 ulp); twice that is added to the measured deviation, so
+// the margin stays an upper bound and the lookup exact (track_common.cuh, bin_guess).
+// Contains __syncthreads.
+constexpr int kHistChunk = 4096;
+#ifdef LYNX_EXPERIMENTS
+#define LYNX_TSTAMP(ptr, i)                                             \
+  do {                                                                  \
+    if (threadIdx.x == 0 && (ptr)) {                                    \
+      unsigned long long t_;                                            \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));            \
+      reinterpret_cast<unsigned long long*>(ptr)[i] = t_;               \
+    }                                                                   \
+  } while (0)
+#else
+#define LYNX_TSTAMP(ptr, i) do {} while (0)
+#endif
+__device__ __forceinline__ void hist_axes_setup(const float* __restrict__ ex, int W,
+                                                const float* __restrict__ ey, int H, HistAxis* h,
+                                                int tid, int nthreads) {
+  __shared__ float s_e[2][kHistChunk];
+  __shared__ unsigned int s_dev[2];
+  if (tid < 2) s_dev[tid] = 0u;
+  const float* e[2] = {ex, ey};
+  const int n[2] = {W, H};
+  // the end points, in flight together with the first chunks
+  const float f0[2] = {__ldg(ex), __ldg(ey)}, fn[2] = {__ldg(ex + W), __ldg(ey + H)};
+  float dev[2] = {0.f, 0.f}, step[2], inv_step[2];
+  const int chunks = (max(W, H) + kHistChunk) / kHistChunk;  // covers n + 1 entries
+  for (int c = 0; c < chunks; ++c) {
+    const int base = c * kHistChunk;
+#pragma unroll
+    for (int x = 0; x < 2; ++x)
+      for (int i = tid; i < kHistChunk && base + i <= n[x]; i += nthreads)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(
+                         (uint32_t)__cvta_generic_to_shared(&s_e[x][i])),
+                     "l"(e[x] + base + i)
+                     : "memory");
+    LYNX_TSTAMP(h, 12);
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();
+    LYNX_TSTAMP(h, 13);
+    if (c == 0) {
+#pragma unroll
+      for (int x = 0; x < 2; ++x) {
+        inv_step[x] = (float)n[x] * __frcp_rn(fn[x] - f0[x]);
+        step[x] = (fn[x] - f0[x]) * __frcp_rn((float)n[x]);
+      }
+    }
+#pragma unroll
+    for (int x = 0; x < 2; ++x)
+      for (int i = tid; i < kHistChunk && base + i <= n[x]; i += nthreads) {
+        const float d = fabsf(s_e[x][i] - fmaf(step[x], (float)(base + i), f0[x])) * inv_step[x];
+        dev[x] = (d <= 1e30f) ? fmaxf(dev[x], d) : 2.f;  // NaN / inf: never trust the fast path
+      }
+    __syncthreads();  // the chunk buffers are refilled next
+  }
+  LYNX_TSTAMP(h, 14);
+  atomicMax(&s_dev[0], __float_as_uint(dev[0]));
+  atomicMax(&s_dev[1], __float_as_uint(dev[1]));
+  __syncthreads();
+  if (tid < 2) {
+    const int x = tid;
+    const float fe0 = f0[x], fen = fn[x];
+    const int nn = x ? H : W;
+    const float d = __uint_as_float(s_dev[x]) + (float)nn * (1.f / 2097152.f) + (1.f / 2048.f);
+    HistAxis r;
+    r.e0 = fe0;
+    r.en = fen;
+    r.inv = (float)nn / (fen - fe0);
+    const float m = 1.25f * d + (float)nn * (1.f / 2097152.f) + (1.f / 1048576.f);
+    const bool ok = d < 0.2f && m < 0.25f && fen > fe0 && fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
+    r.margin = ok ? m : 1.f;  // margin >= 0.5 means: irregular table, always searched
+    h[x] = r;
+  }
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -110,6 +110,22 @@ __device__ __forceinline__ void bulk_reduce_add_f32(float* dst_gmem, const float
                : "memory");
 }
 
+#ifdef LYNX_EXPERIMENTS
+// phase stamps of CTA `g_k2_trace_cta`'s first consumer thread (tools/k2_timeline.py)
+__device__ unsigned long long g_k2_trace[16];
+__device__ int g_k2_trace_cta = 0;
+#define K2_STAMP(i)                                                              \
+  do {                                                                           \
+    if ((int)blockIdx.x == g_k2_trace_cta && threadIdx.x == 32 * (HAS_OUT ? 2 : 0)) { \
+      unsigned long long t_;                                                     \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                     \
+      g_k2_trace[i] = t_;                                                        \
+    }                                                                            \
+  } while (0)
+#else
+#define K2_STAMP(i) do {} while (0)
+#endif
+
 // TILE: the screen variant with the shared-memory histogram tile (win_words > 0).
 template <int MOM, bool HAS_OUT, bool TILE>
 __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(TrackArgs a, uint32_t win_words) {
@@ -137,6 +153,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
+  K2_STAMP(0);
   // grid: a.ctas_per_row consecutive CTAs share a setting (no 65 535 limit of gridDim.y)
   const int64_t b = blockIdx.x / (unsigned)a.ctas_per_row;
   const int cta = (int)(blockIdx.x - b * a.ctas_per_row), n_cta = a.ctas_per_row;
@@ -181,7 +198,9 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
   }
   // ... then wait for the K1 grid (records + histogram geometry written, image zeroed) --
   // a no-op unless this kernel was launched with programmatic stream serialization
+  K2_STAMP(1);
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  K2_STAMP(2);
   if (a.stamp && tid == 0 && blockIdx.x == 0) {  // exchange trace (exchange.cu)
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -194,6 +213,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
     if (a.img && tid < 2) s_hist[tid] = a.hist[tid];
   }
   __syncthreads();
+  K2_STAMP(3);
 
   MomAcc<MOM> acc;
 #pragma unroll
@@ -386,6 +406,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
       n_mine += cnt;
       float* st = stages + s * kStageFloats + cid * 4;
       mbar_wait(full + s, u & 1);
+      if (t == cta) K2_STAMP(4);
       float v[6][4];
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
@@ -489,11 +510,13 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
           mom_accumulate(acc, d);
         }
       }
+      if (t == cta) K2_STAMP(5);
       if (++s == STAGES) {
         s = 0;
         ++u;
       }
     }
+    K2_STAMP(6);
     if constexpr (TILE) {
       const HistWindow hw = s_win;
       if (use_win && win_set && hw.w > 0) {
@@ -509,6 +532,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
         }
         fence_proxy_async();
         consumers_sync();
+        K2_STAMP(7);
         // one elected lane per warp issues its rows: a bulk operation is issued per THREAD, and
         // 32 lanes of a warp doing so serialise (8 % of the 1 M-particle kernel's instructions)
         if (lane == 0)
@@ -518,6 +542,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
         bulk_commit();
       }
     }
+    K2_STAMP(8);
     if (a.bbox && img_b) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
@@ -541,7 +566,9 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
     }
     // the tile's shared memory has been read by the bulk reduces (no-op without a flush); the
     // additions themselves complete with the grid, which is what a dependent launch waits for
+    K2_STAMP(9);
     if constexpr (TILE) bulk_wait_read<0>();
+    K2_STAMP(10);
     // Let a programmatically-serialized follower (multi-GPU exchange kernel) start launching
     // once the consumers of every CTA are through their tiles.  The first thread of a CTA to
     // execute this counts for the CTA, so it must not sit on a path the loader warp reaches
@@ -607,6 +634,12 @@ static int launch_pipe(const TrackArgs& a, unsigned grid, size_t smem, uint32_t 
 }
 
 #ifdef LYNX_EXPERIMENTS
+}  // namespace lynx
+extern "C" int lynx_dbg_k2_trace(unsigned long long* host16, int cta) {
+  if (cudaMemcpyFromSymbol(host16, lynx::g_k2_trace, sizeof(lynx::g_k2_trace)) != cudaSuccess) return -1;
+  return cudaMemcpyToSymbol(lynx::g_k2_trace_cta, &cta, sizeof(int)) == cudaSuccess ? 0 : -1;
+}
+namespace lynx {
 static int env_int(const char* name, int dflt) {
   const char* e = getenv(name);
   return e ? atoi(e) : dflt;
@@ -641,7 +674,7 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
   const uint32_t fixed = pipe_layout(0, a.rec_floats, a.n_plan, a.n_snap, 0).total;
   if (fixed + 2u * kStageFloats * 4u > cap) return 1;
   if (hist && !(a.W & 3) && !((uintptr_t)a.img & 15) && (((int64_t)a.W * a.H) & 3) == 0) {
-    int px_per_particle = 3, min_stages = 2;
+    int px_per_particle = 1, min_stages = 2;  // swept at 1 M particles: 1-2 best (profiles/r2j_sweeps.txt)
 #ifdef LYNX_EXPERIMENTS
     int64_t max_words = 1 << 30;
     px_per_particle = env_int("LYNX_TILE_PXPP", px_per_particle);

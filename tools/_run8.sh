@@ -1,3 +1,4 @@
 set -u
-out=gpurun_out/r2h; mkdir -p $out
-python tools/prof_target.py --mode pbboth > $out/plain_pb.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:"parambeam" -c 4 -f -o $out/k6b python tools/prof_target.py --mode pbboth > $out/ncu_pb.log 2>&1; echo "ncu rc=$?"
+out=gpurun_out/r2i; mkdir -p $out
+m=screen1m
+python tools/prof_target.py --mode $m --steps 3 > $out/plain_$m.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:"track_pipe|compose" -s 4 -c 2 -f -o $out/k_$m python tools/prof_target.py --mode $m --steps 3 > $out/ncu_$m.log 2>&1; echo "ncu $m rc=$?"

@@ -25,19 +25,20 @@ def main():
     from lynx_b200 import _lib as L
 
     lib = L.lib()
+    PEAK = bench.peaks()[0]
 
     def report(name, w, steps=30, which=1):
         ms = bench.timed_steps(w.step, steps, 5, flush)
         k = bench.kernel_ms(w.step, which, 10, flush, lib)
         ab = w.algorithmic_bytes()
-        print(f"{name:28s} step {np.median(ms) * 1e3:8.1f} us  kernel {k * 1e3:8.1f} us  "
-              f"{ab / k / 1e6:7.0f} GB/s alg  frac {ab / k / 1e6 / 6547.8:.3f}", flush=True)
+        print(f"{name:28s} step {np.mean(ms) * 1e3:8.2f} us (median {np.median(ms) * 1e3:.1f})  kernel {k * 1e3:8.1f} us  "
+              f"{ab / k / 1e6:7.0f} GB/s alg  frac {ab / k / 1e6 / PEAK:.3f}", flush=True)
 
     if "step1m" in names:
         w = bench.ParticleWorkload(1_000_000, dev, 1002)
         report("step1m (K1+K2, screen)", w, steps=100)
         ms = bench.timed_steps(w.persistent_step, 100, 5, flush)
-        print(f"{'step1m persistent image':28s} step {np.median(ms) * 1e3:8.1f} us", flush=True)
+        print(f"{'step1m persistent image':28s} step {np.mean(ms) * 1e3:8.2f} us (median {np.median(ms) * 1e3:.1f})", flush=True)
     if "scr32m" in names:
         report("scr32m (screen, 24 B)", bench.ParticleWorkload(32_000_000, dev, 1002))
     if "out32m" in names:
