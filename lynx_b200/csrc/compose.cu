@@ -71,7 +71,7 @@ compose_kernel(ComposeArgs a, int n_cols, int S, const __grid_constant__ Program
   if (hist_blocks && blockIdx.x == 0) {
     HistAxis* h = reinterpret_cast<HistAxis*>(a.hist_out);
     if (a.bbox_clear && threadIdx.x < 4) a.bbox_clear[threadIdx.x] = 0;  // this call's cell
-    hist_axes_setup(a.hist_ex, a.hist_W, a.hist_ey, a.hist_H, h, threadIdx.x, kComposeTPB);
+    hist_axes_setup(a.hist_ex, a.hist_W, a.hist_ey, a.hist_H, h, threadIdx.x, kComposeTPB, cs_smem);
 #ifdef LYNX_EXPERIMENTS
     if (threadIdx.x == 0) {
       unsigned long long t;
@@ -424,7 +424,9 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
     if (n_cols > 0) S = (int)std::min<size_t>(kComposeTPB, (budget - ops_bytes) / (4 * (size_t)n_cols));
     S = (int)std::min<int64_t>(S, std::max<int64_t>(B, 1));
   }
-  const size_t smem = staged ? ops_bytes + (size_t)n_cols * S * 4 : 0;
+  // the histogram block stages the edge tables in the same dynamic region (2 x 16 KB)
+  const size_t smem = std::max<size_t>(staged ? ops_bytes + (size_t)n_cols * S * 4 : 0,
+                                       hist_out ? 2 * kHistChunk * sizeof(float) : 0);
   unsigned blocks = (unsigned)((B + S - 1) / S);
   if (zero_rect)
     blocks += (unsigned)p->sm_count;  // the rectangle's size is only known on the device
@@ -434,16 +436,7 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   {
     ProfileScope ps(0, st);
     const bool light = (p->op_mask & ~kOpsLight) == 0;
-    auto launch = [&](auto kern) {
-      // the histogram block's static chunk buffers (32 KB) + the staged parameters exceed the
-      // 48 KB a kernel gets without opting in
-      static bool attr_set = false;  // per instantiation
-      if (!attr_set) {
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        attr_set = true;
-      }
-      kern<<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S, tab);
-    };
+    auto launch = [&](auto kern) { kern<<<blocks, kComposeTPB, smem, st>>>(a, n_cols, S, tab); };
     if (d_maps_out) {  // public lynx_compose_maps: records + 7x7 stage maps
       if (staged && tabbed)
         launch(compose_kernel<2, kOpsAll, true>);

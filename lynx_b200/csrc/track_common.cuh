@@ -233,16 +233,13 @@ __device__ __forceinline__ void hist_axis_setup(const float* __restrict__ e, int
   __syncthreads();
 }
 
-// Both axes at once for K1's histogram block, in fp32 and without a division routine.  The
-// tables are staged in shared memory by cp.async -- every element in flight at once, ONE DRAM
-// round trip per 4096-entry chunk pair -- where hist_axis_setup's loop paid one cold miss per
-// iteration, and its fp64 divisions a few microseconds of cold instruction fetches: the block
-// was K1's critical path (8-9 us of the 1 M-particle step, tools/k2_timeline.py).
-// The fp32 evaluation of d = |e[i] - (e0 + step i)| / step is off by at most
-// n 2^-22 (step's rounding, acting over n bins) + 2^-12 (the fma's and e0's roundings at
-// |e| <= en - e0, the reciprocal's 2 ulp); twice that is added to the measured deviation, so
-// the margin stays an upper bound and the lookup exact (track_common.cuh, bin_guess).
-// Contains __syncthreads.
+// Both axes at once for K1's histogram block.  The tables are staged in shared memory by
+// cp.async -- every element in flight at once, ONE DRAM round trip per 4096-entry chunk pair --
+// where hist_axis_setup's loop paid one cold miss per iteration (20 per axis on the 2448 x 2040
+// screen; the block was K1's critical path, tools/k2_timeline.py).  Same arithmetic, hence the
+// same margins, as two calls of hist_axis_setup: the deviation is measured in fp64 -- an fp32
+// measurement needs ~0.002 bins of extra margin, which doubles the near-edge lookups of the
+// particle kernel and cost it 5 % at 32 M particles.  Contains __syncthreads.
 constexpr int kHistChunk = 4096;
 #ifdef LYNX_EXPERIMENTS
 #define LYNX_TSTAMP(ptr, i)                                             \
@@ -258,15 +255,16 @@ constexpr int kHistChunk = 4096;
 #endif
 __device__ __forceinline__ void hist_axes_setup(const float* __restrict__ ex, int W,
                                                 const float* __restrict__ ey, int H, HistAxis* h,
-                                                int tid, int nthreads) {
-  __shared__ float s_e[2][kHistChunk];
+                                                int tid, int nthreads, float* scratch) {
+  float (*s_e)[kHistChunk] = reinterpret_cast<float (*)[kHistChunk]>(scratch);  // [2][kHistChunk]
   __shared__ unsigned int s_dev[2];
   if (tid < 2) s_dev[tid] = 0u;
   const float* e[2] = {ex, ey};
   const int n[2] = {W, H};
   // the end points, in flight together with the first chunks
   const float f0[2] = {__ldg(ex), __ldg(ey)}, fn[2] = {__ldg(ex + W), __ldg(ey + H)};
-  float dev[2] = {0.f, 0.f}, step[2], inv_step[2];
+  float dev[2] = {0.f, 0.f};
+  double e0[2], step[2], inv_step[2];
   const int chunks = (max(W, H) + kHistChunk) / kHistChunk;  // covers n + 1 entries
   for (int c = 0; c < chunks; ++c) {
     const int base = c * kHistChunk;
@@ -284,14 +282,15 @@ __device__ __forceinline__ void hist_axes_setup(const float* __restrict__ ex, in
     if (c == 0) {
 #pragma unroll
       for (int x = 0; x < 2; ++x) {
-        inv_step[x] = (float)n[x] * __frcp_rn(fn[x] - f0[x]);
-        step[x] = (fn[x] - f0[x]) * __frcp_rn((float)n[x]);
+        e0[x] = (double)f0[x];
+        step[x] = ((double)fn[x] - e0[x]) / n[x];
+        inv_step[x] = 1.0 / step[x];
       }
     }
 #pragma unroll
     for (int x = 0; x < 2; ++x)
       for (int i = tid; i < kHistChunk && base + i <= n[x]; i += nthreads) {
-        const float d = fabsf(s_e[x][i] - fmaf(step[x], (float)(base + i), f0[x])) * inv_step[x];
+        const float d = (float)(fabs((double)s_e[x][i] - (e0[x] + step[x] * (base + i))) * inv_step[x]);
         dev[x] = (d <= 1e30f) ? fmaxf(dev[x], d) : 2.f;  // NaN / inf: never trust the fast path
       }
     __syncthreads();  // the chunk buffers are refilled next
@@ -304,13 +303,13 @@ __device__ __forceinline__ void hist_axes_setup(const float* __restrict__ ex, in
     const int x = tid;
     const float fe0 = f0[x], fen = fn[x];
     const int nn = x ? H : W;
-    const float d = __uint_as_float(s_dev[x]) + (float)nn * (1.f / 2097152.f) + (1.f / 2048.f);
+    const float d = __uint_as_float(s_dev[x]);
     HistAxis r;
     r.e0 = fe0;
     r.en = fen;
     r.inv = (float)nn / (fen - fe0);
     const float m = 1.25f * d + (float)nn * (1.f / 2097152.f) + (1.f / 1048576.f);
-    const bool ok = d < 0.2f && m < 0.25f && fen > fe0 && fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
+    const bool ok = d < 0.2f && m < 0.25f && step[x] > 0.0 && fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
     r.margin = ok ? m : 1.f;  // margin >= 0.5 means: irregular table, always searched
     h[x] = r;
   }

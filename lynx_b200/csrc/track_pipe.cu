@@ -331,6 +331,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
       }
       if constexpr (TILE) {
         if (use_win && !win_set) {  // warp-uniform: the CTA's first pipeline tile only
+          K2_STAMP(11);
           // place the tile on the beam: mean +- k sigma of this CTA's first pipeline tile
           float c = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, syy = 0.f;
 #pragma unroll
@@ -353,6 +354,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
             d[0] = c; d[1] = sx; d[2] = sy; d[3] = sxx; d[4] = syy;
           }
           consumers_sync();
+          K2_STAMP(12);
           if (cid == 0) {
             float tc = 0.f, tx = 0.f, ty = 0.f, txx = 0.f, tyy = 0.f;
             for (int w = 0; w < kConsumerWarps; ++w) {
@@ -379,6 +381,7 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
             s_win = nw;
           }
           consumers_sync();
+          K2_STAMP(13);
           win_set = true;
         }
       }

@@ -31,7 +31,8 @@ buf = (C.c_uint64 * 16)()
 fn(buf, cta)
 names = ["entry", "prologue done", "K1 complete (griddep wait)", "records in smem", "tile 1 landed",
          "tile 1 done", "tile loop done", "window converted", "bulk reduces issued", "bbox done",
-         "bulk read done"]
+         "bulk read done", "tile 1: bins known, placement starts", "tile 1: warp statistics exchanged",
+         "tile 1: window placed"]
 rows = []
 for i in range(60):
     if not os.environ.get('LYNX_NOFLUSH'):
@@ -42,7 +43,7 @@ for i in range(60):
     t = np.array(list(buf), dtype=np.float64)
     hist = w.ws[-256:].view(torch.int64).cpu().numpy().astype(np.float64)
     if i >= 10:
-        rows.append(np.concatenate([t[:11] - t[0], hist[8:18] - t[0]]))
+        rows.append(np.concatenate([t[:14] - t[0], hist[8:12] - t[0]]))
 m = np.mean(rows, axis=0) / 1e3
-for n, v in zip(names + ["K1 block 0 start", "K1 walker done", "K1 histogram block done", "K1 last zeroing block done", "K1 hist: loads issued", "K1 hist: tables in smem", "K1 hist: deviations done", "K1 walker: parameters in smem", "K1 walker: walk done", "K1 walker block entry"], m):
+for n, v in zip(names + ["K1 block 0 start", "K1 walker done", "K1 histogram block done", "K1 last zeroing block done"], m):
     print(f"{n:32s} {v:8.2f} us")
