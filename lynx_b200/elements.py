@@ -401,30 +401,36 @@ class Aperture(Element):
         R = 1
         for s_ in incoming.batch_shape:
             R *= s_
-        if R != 1 or self.x_max.numel() != 1 or self.y_max.numel() != 1:
-            # every beam row keeps a different number of particles: not one ParticleBeam
-            # (the reference's mask indexing flattens the batch in that case)
-            raise NotImplementedError("Aperture.track: one beam row (batch size 1) only")
+        lim_rows = max(self.x_max.numel(), self.y_max.numel())
+        if lim_rows not in (1, R):
+            raise ValueError(f"Aperture limits have {lim_rows} settings, the beam has {R} rows")
         soa = soa if soa.is_contiguous() else soa.contiguous()
         N, ld = incoming.num_particles, incoming.ld
-        xm = self.x_max.reshape(1).to(device=dev, dtype=torch.float32)
-        ym = self.y_max.reshape(1).to(device=dev, dtype=torch.float32)
+        soa_r = soa.reshape(R, 6, ld)
+        lim_stride = 1 if lim_rows > 1 else 0
+        xm = self.x_max.reshape(-1).expand(lim_rows).to(device=dev, dtype=torch.float32).contiguous()
+        ym = self.y_max.reshape(-1).expand(lim_rows).to(device=dev, dtype=torch.float32).contiguous()
         pc = incoming.particle_charges
         uniform_pc = pc is not None and pc.stride(-1) == 0
-        q_in = pc.reshape(1, N).contiguous() if (pc is not None and not uniform_pc) else None
-        kept = torch.empty_like(soa)
-        lost = torch.empty_like(soa)
-        q_kept = torch.empty((1, ld), device=dev) if q_in is not None else None
-        q_lost = torch.empty((1, ld), device=dev) if q_in is not None else None
-        counts = torch.empty(1, dtype=torch.int64, device=dev)
-        ws = torch.empty(max(L.lib().lynx_aperture_workspace_bytes(1, N), 16), dtype=torch.uint8,
+        q_in = (pc.expand(*incoming.batch_shape, N).reshape(R, N).contiguous()
+                if (pc is not None and (not uniform_pc or R > 1)) else None)
+        kept = torch.empty_like(soa_r)
+        lost = torch.empty_like(soa_r)
+        q_kept = torch.empty((R, ld), device=dev) if q_in is not None else None
+        q_lost = torch.empty((R, ld), device=dev) if q_in is not None else None
+        counts = torch.empty(R, dtype=torch.int64, device=dev)
+        ws = torch.empty(max(L.lib().lynx_aperture_workspace_bytes(R, N), 16), dtype=torch.uint8,
                          device=dev)
         L.check(L.lib().lynx_aperture_compact(
-            soa.data_ptr(), 1, N, ld, L.ptr(q_in), N if q_in is not None else 0, xm.data_ptr(),
-            ym.data_ptr(), 0, 0 if self.shape == "rectangular" else 1, kept.data_ptr(),
+            soa_r.data_ptr(), R, N, ld, L.ptr(q_in), N if q_in is not None else 0, xm.data_ptr(),
+            ym.data_ptr(), lim_stride, 0 if self.shape == "rectangular" else 1, kept.data_ptr(),
             lost.data_ptr(), ld, L.ptr(q_kept), L.ptr(q_lost), counts.data_ptr(), ws.data_ptr(),
             L.current_stream()), "lynx_aperture_compact")
-        n = int(counts.item())  # the boolean-mask indexing of the reference syncs here too
+        cnt = counts.tolist()  # the boolean-mask indexing of the reference syncs here too
+        if R > 1:
+            return self._finish_flattened(incoming, kept, lost, q_kept, q_lost, cnt, N, pc)
+        n = cnt[0]
+        kept, lost = kept.reshape(soa.shape), lost.reshape(soa.shape)
         bshape = incoming.batch_shape
 
         def charges(buf, m):
@@ -451,6 +457,40 @@ class Aperture(Element):
             return ParticleBeam.empty  # aperture.py:98-108
         kept[..., n:(n + 3) & ~3] = 0  # padding lanes [N, round4(N)) of the SoA contract
         return ParticleBeam.from_soa(kept, n, incoming.energy, charges(q_kept, n))
+
+    def _finish_flattened(self, incoming, kept, lost, q_kept, q_lost, cnt, N, pc):
+        """A beam with R > 1 rows: the reference's ``incoming.particles[survived_mask]``
+        (aperture.py:89-97) indexes (R, N, 7) with an (R, N) mask, which FLATTENS the batch -- the
+        outgoing beam is one row of all rows' survivors in row order (its energy keeps the
+        incoming batch shape, as written there).  The rows were compacted on the device in one
+        launch; here they are joined."""
+        dev = kept.device
+
+        def join(planes, q, counts):
+            total = sum(counts)
+            ld = (total + 3) & ~3
+            out = torch.zeros((6, ld), device=dev)
+            qo = torch.empty(total, device=dev) if q is not None else None
+            o = 0
+            for r, m in enumerate(counts):
+                out[:, o:o + m] = planes[r, :, :m]
+                if q is not None:
+                    qo[o:o + m] = q[r, :m]
+                o += m
+            return out, qo, total
+
+        k_soa, k_q, n = join(kept, q_kept, cnt)
+        l_soa, l_q, n_lost = join(lost, q_lost, [N - m for m in cnt])
+        if n_lost > 0:
+            self._lost_beam = ParticleBeam.from_soa(l_soa, n_lost, incoming.energy, None)
+            self._lost_aos = None
+        else:
+            self._lost_beam = None
+            self._lost_aos = torch.empty((0, 7), device=dev)
+        self.lost_particle_charges = l_q if pc is not None else None
+        if n == 0:
+            return ParticleBeam.empty
+        return ParticleBeam.from_soa(k_soa, n, incoming.energy, k_q)
 
     def broadcast(self, shape):
         new = self.__class__(x_max=self.x_max.repeat(shape), y_max=self.y_max.repeat(shape),

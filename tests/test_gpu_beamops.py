@@ -307,3 +307,33 @@ def test_split_matches_unsplit_track():
     a = seg.transfer_map(e).cpu().numpy()
     b = lx.Segment(parts).transfer_map(e).cpu().numpy()
     np.testing.assert_allclose(b, a, rtol=2e-5, atol=2e-7)
+
+
+def test_aperture_element_on_a_batched_beam():
+    """Three beam rows through one Aperture with a limit per row: the reference's mask indexing
+    (aperture.py:89-97) flattens the batch -- the survivors of all rows, in row order, form ONE
+    beam; the lost particles likewise."""
+    n, R = 20_003, 3
+    rows = np.stack([F.gaussian_beam_soa(n, seed=30 + r) for r in range(R)])
+    aos = torch.from_numpy(np.stack([F.soa_to_aos7(rows[r]) for r in range(R)]))
+    charges = torch.arange(R * n, dtype=torch.float32).reshape(R, n)
+    beam = lx.ParticleBeam(aos, torch.full((R,), F.ASTRA_ENERGY), particle_charges=charges)
+    xmax = torch.tensor([1e-4, 2e-4, 3e-4])
+    for shape in ("rectangular", "elliptical"):
+        ap = lx.Aperture(x_max=xmax, y_max=torch.tensor(2e-4), shape=shape, name="ap")
+        out = ap.track(beam)
+        kept, lost, kq, lq = [], [], [], []
+        for r in range(R):
+            k, l_, a, b = BO.aperture_track(rows[r], float(xmax[r]), 2e-4, shape, charges[r].numpy())
+            kept.append(k)
+            lost.append(l_)
+            kq.append(a)
+            lq.append(b)
+        kept, lost = np.concatenate(kept, axis=1), np.concatenate(lost, axis=1)
+        m = kept.shape[1]
+        assert 0 < m < R * n and out.num_particles == m and out.soa.shape[0] == 6
+        np.testing.assert_array_equal(out.soa[:, :m].cpu().numpy(), kept)
+        np.testing.assert_array_equal(out.particle_charges.cpu().numpy(), np.concatenate(kq))
+        assert ap.lost_particles.shape == (R * n - m, 7)
+        np.testing.assert_array_equal(ap.lost_particles[:, :6].T.cpu().numpy(), lost)
+        np.testing.assert_array_equal(ap.lost_particle_charges.cpu().numpy(), np.concatenate(lq))

@@ -199,13 +199,21 @@ def test_screen_histogram_exact_and_vs_oracle():
     ex, ey = screen_bin_edges(F.TEST_SCREEN["resolution"], F.TEST_SCREEN["pixel_size"])
     own = screen_reading_particles(read.xs.cpu(), read.ys.cpu(), ex, ey)
     assert torch.equal(img.cpu(), own)
-    # (b) vs the oracle end to end: only particles within a few ulp of an edge may move
-    els, _ = _oracle_track(spec, soa, F.ASTRA_ENERGY, torch.float32)
-    rb = els[-1].read_beam
-    want = screen_reading_particles(rb.col(0), rb.col(2), ex, ey)
-    moved = (img.cpu() - want).abs().sum().item() / 2
-    assert img.sum().item() == want.sum().item() or moved <= 1e-3 * n
-    assert moved <= 2e-3 * n, moved
+    # (b) vs the oracle end to end, particle by particle: a particle may sit in another bin than
+    # the oracle's only if its coordinate is within the coordinate tolerance of that bin edge
+    from test_gpu_parity_r2 import check_bins_particle_by_particle
+
+    res = {}
+    for d in (torch.float32, torch.float64):
+        els, _ = _oracle_track(spec, soa, F.ASTRA_ENERGY, d)
+        res[d] = els[-1].read_beam
+    o32, o64 = res[torch.float32], res[torch.float64]
+    moved = check_bins_particle_by_particle(
+        read.xs.cpu().numpy()[0], read.ys.cpu().numpy()[0], o32.col(0)[0].numpy(),
+        o32.col(2)[0].numpy(), o64.col(0)[0].numpy(), o64.col(2)[0].numpy(), ex, ey, "config 2 screen")
+    want = screen_reading_particles(o32.col(0), o32.col(2), ex, ey)
+    assert (img.cpu() - want).abs().sum().item() <= 2 * moved
+    assert moved <= 1e-3 * n, moved
 
 
 def test_screen_edge_semantics_device():
