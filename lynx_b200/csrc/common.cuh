@@ -92,6 +92,20 @@ int fwd_collapse_launch(const lynx_program_t* p, const float* d_params, int64_t 
                         double* d_moment_sums, const float* d_energy_in, float* d_energy_out,
                         void* d_workspace, cudaStream_t st);
 
+// The forward launcher behind lynx_track_particles_fwd / _bbox / _persistent.  `accumulate`:
+// a further particle range of the SAME call (host.cu tracks a beam in chunks as they arrive over
+// PCIe): no K1, nothing cleared -- records, histogram geometry, the zeroed image and the sums
+// of the first range's launch are in place -- only the particle kernel runs and adds.
+int track_fwd_impl(const lynx_program_t* p, const float* d_params, int64_t B, const float* d_in_soa,
+                   int64_t in_row_stride, int64_t ld_in, int64_t N, float* d_out_soa, int64_t ld_out,
+                   double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H,
+                   const float* d_edges_x, const float* d_edges_y, double* d_moment_sums,
+                   int32_t moment_mode, const float* d_energy_in, float* d_energy_out,
+                   void* d_workspace, int32_t* d_screen_bbox, int32_t* d_img_state, uint32_t epoch,
+                   lynx_stream_t stream, bool accumulate);
+bool fwd_collapses(const lynx_program_t* p, int64_t B, int64_t in_row_stride, bool has_out,
+                   int moment_mode);
+
 // optional event bracketing of the dominant kernels (bench roofline)
 struct ProfileScope {
   int which;

@@ -2,15 +2,22 @@
 // Segment.track makes.  Copies inputs host->device on the context's stream, runs the
 // device launchers, copies results back, synchronises.  Device scratch is cached on the
 // context and only grows.
+#include <algorithm>
 #include <cstring>
 #include <new>
 #include <vector>
 
 #include "common.cuh"
 
+constexpr int kMaxChunks = 8;
+
 struct lynx_host_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
+  // the beam crosses PCIe in chunks on its own stream; chunk c is tracked (on `stream`) while
+  // chunk c + 1 is still arriving
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t chunk_ready[kMaxChunks] = {};
   struct Buf {
     void* p = nullptr;
     size_t cap = 0;
@@ -50,6 +57,8 @@ struct lynx_host_ctx {
   }
 };
 
+extern "C" void lynx_host_ctx_destroy(lynx_host_ctx_t* c);
+
 extern "C" int lynx_host_ctx_create(int device, lynx_host_ctx_t** out) {
   if (!out) return LYNX_E_BADARG;
   *out = nullptr;
@@ -60,8 +69,12 @@ extern "C" int lynx_host_ctx_create(int device, lynx_host_ctx_t** out) {
   lynx_host_ctx* c = new (std::nothrow) lynx_host_ctx();
   if (!c) return LYNX_E_NOMEM;
   c->device = device;
-  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
-    delete c;
+  bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+  for (int i = 0; ok && i < kMaxChunks; ++i)
+    ok = cudaEventCreateWithFlags(&c->chunk_ready[i], cudaEventDisableTiming) == cudaSuccess;
+  if (!ok) {
+    lynx_host_ctx_destroy(c);
     return LYNX_E_LAUNCH;
   }
   *out = c;
@@ -76,6 +89,9 @@ extern "C" void lynx_host_ctx_destroy(lynx_host_ctx_t* c) {
                                &c->bpm_f,  &c->bbox,  &c->img_state};
   if (c->h_bbox) cudaFreeHost(c->h_bbox);
   for (auto* b : all) c->release(*b);
+  for (auto& e : c->chunk_ready)
+    if (e) cudaEventDestroy(e);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -114,16 +130,24 @@ extern "C" int lynx_host_track_particles(
   const int n_bpm = lynx_program_num_bpm(p);
   const bool has_screen = screen_img && lynx_program_num_screens(p) > 0;
 
+  // The beam (24 B per particle, the bulk of the call) goes first and in chunks on the copy
+  // stream: the particle kernel of chunk k runs while chunk k + 1 is on the bus, so that only
+  // the last chunk's kernel and the read-back are not hidden behind PCIe.  Chunks are whole
+  // multiples of 4 particles (16-byte aligned planes); the collapsed moment path (one beam,
+  // many settings, adjoint.cu) streams the beam once and is not chunked.
+  if (!c->grow(c->in, sizeof(float) * Bb * 6 * ld)) return LYNX_E_NOMEM;
+  int n_chunks = N >= (1 << 19) ? 4 : (N >= (1 << 17) ? 2 : 1);
+  if (lynx::fwd_collapses(p, B, (Bb == B) ? 1 : 0, out_soa != nullptr, moment_mode)) n_chunks = 1;
+  const int64_t chunk = (((N + n_chunks - 1) / n_chunks) + 3) & ~(int64_t)3;
+  for (int k = 0; k < n_chunks; ++k) {
+    const int64_t p0 = k * chunk, cnt = std::min<int64_t>(chunk, N - p0);
+    LYNX_CUDA_OK(cudaMemcpy2DAsync((float*)c->in.p + p0, sizeof(float) * ld, in_soa + p0,
+                                   sizeof(float) * N, sizeof(float) * cnt, Bb * 6,
+                                   cudaMemcpyHostToDevice, c->copy_stream));
+    LYNX_CUDA_OK(cudaEventRecord(c->chunk_ready[k], c->copy_stream));
+  }
   H2D(c->params, params, sizeof(float) * n_param_floats);
   H2D(c->energy_in, energy_in, sizeof(float) * B);
-  if (!c->grow(c->in, sizeof(float) * Bb * 6 * ld)) return LYNX_E_NOMEM;
-  if (ld == N) {
-    LYNX_CUDA_OK(cudaMemcpyAsync(c->in.p, in_soa, sizeof(float) * Bb * 6 * N,
-                                 cudaMemcpyHostToDevice, st));
-  } else {
-    LYNX_CUDA_OK(cudaMemcpy2DAsync(c->in.p, sizeof(float) * ld, in_soa, sizeof(float) * N,
-                                   sizeof(float) * N, Bb * 6, cudaMemcpyHostToDevice, st));
-  }
   if (out_soa && !c->grow(c->out, sizeof(float) * B * 6 * ld)) return LYNX_E_NOMEM;
   if (!c->grow(c->energy_out, sizeof(float) * B)) return LYNX_E_NOMEM;
   if (n_bpm > 0 && !c->grow(c->bpm, sizeof(double) * 2 * n_bpm * B)) return LYNX_E_NOMEM;
@@ -152,6 +176,7 @@ extern "C" int lynx_host_track_particles(
   bool dev_persistent = has_screen && c->img_persistent_ok && !(W & 3);
   const int32_t* d_box = sparse_img ? (const int32_t*)c->bbox.p : nullptr;
   int rc = LYNX_OK;
+  uint32_t epoch = 0;
   if (dev_persistent) {
     if (!c->grow(c->img_state, 32)) return LYNX_E_NOMEM;
     if (c->img_geom[0] != W || c->img_geom[1] != H || c->img_geom[2] != B) {
@@ -163,29 +188,34 @@ extern "C" int lynx_host_track_particles(
       c->img_geom[2] = B;
       c->img_epoch = 0;
     }
-    const uint32_t epoch = c->img_epoch++;
-    rc = lynx_track_particles_fwd_persistent(
-        p, (const float*)c->params.p, B, (const float*)c->in.p, (Bb == B) ? 1 : 0, ld, N,
-        out_soa ? (float*)c->out.p : nullptr, ld, (double*)c->bpm.p, (float*)c->img.p, W, H,
-        (const float*)c->ex.p, (const float*)c->ey.p, moment_mode ? (double*)c->mom.p : nullptr,
-        moment_mode, (const float*)c->energy_in.p, (float*)c->energy_out.p, c->ws.p,
-        (int32_t*)c->img_state.p, epoch, (lynx_stream_t)st);
+    epoch = c->img_epoch++;
     d_box = (const int32_t*)c->img_state.p + 4 * (epoch & 1u);
-    if (rc == LYNX_E_BADPROGRAM) {  // lattice outside the pipelined kernel: plain path from now on
+  }
+  // particle range [p0, p0 + cnt) of every beam row; ranges after the first only add
+  auto track_range = [&](int64_t p0, int64_t cnt, bool accumulate) {
+    return lynx::track_fwd_impl(
+        p, (const float*)c->params.p, B, (const float*)c->in.p + p0, (Bb == B) ? 1 : 0, ld, cnt,
+        out_soa ? (float*)c->out.p + p0 : nullptr, ld, (double*)c->bpm.p,
+        has_screen ? (float*)c->img.p : nullptr, W, H, (const float*)c->ex.p, (const float*)c->ey.p,
+        moment_mode ? (double*)c->mom.p : nullptr, moment_mode, (const float*)c->energy_in.p,
+        (float*)c->energy_out.p, c->ws.p,
+        dev_persistent ? nullptr : (sparse_img ? (int32_t*)c->bbox.p : nullptr),
+        dev_persistent ? (int32_t*)c->img_state.p : nullptr, epoch, (lynx_stream_t)st, accumulate);
+  };
+  for (int k = 0; k < n_chunks; ++k) {
+    const int64_t p0 = k * chunk, cnt = std::min<int64_t>(chunk, N - p0);
+    LYNX_CUDA_OK(cudaStreamWaitEvent(st, c->chunk_ready[k], 0));
+    rc = track_range(p0, cnt, k > 0);
+    if (k == 0 && dev_persistent && rc == LYNX_E_BADPROGRAM) {
+      // lattice outside the pipelined kernel: plain path from now on
       c->img_persistent_ok = false;
       c->img_geom[0] = c->img_geom[1] = c->img_geom[2] = 0;
       dev_persistent = false;
       d_box = sparse_img ? (const int32_t*)c->bbox.p : nullptr;
+      rc = track_range(p0, cnt, false);
     }
+    if (rc != LYNX_OK) break;
   }
-  if (!dev_persistent)
-    rc = lynx_track_particles_fwd_bbox(
-        p, (const float*)c->params.p, B, (const float*)c->in.p, (Bb == B) ? 1 : 0,
-        ld, N, out_soa ? (float*)c->out.p : nullptr, ld, (double*)c->bpm.p,
-        has_screen ? (float*)c->img.p : nullptr, W, H, (const float*)c->ex.p,
-        (const float*)c->ey.p, moment_mode ? (double*)c->mom.p : nullptr, moment_mode,
-        (const float*)c->energy_in.p, (float*)c->energy_out.p, c->ws.p,
-        sparse_img ? (int32_t*)c->bbox.p : nullptr, (lynx_stream_t)st);
   if (rc != LYNX_OK) return rc;
   // Sparse read-back of the persistent host image.  Invariant: the host image is zero
   // outside last_rect.  The device image is exact everywhere (zero outside this call's

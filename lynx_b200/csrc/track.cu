@@ -287,10 +287,14 @@ extern "C" int lynx_track_particles_fwd(
                                        d_workspace, nullptr, stream);
 }
 
-static int track_fwd_impl(const lynx_program_t*, const float*, int64_t, const float*, int64_t,
-                          int64_t, int64_t, float*, int64_t, double*, float*, int32_t, int32_t,
-                          const float*, const float*, double*, int32_t, const float*, float*,
-                          void*, int32_t*, int32_t*, uint32_t, lynx_stream_t);
+using lynx::track_fwd_impl;
+
+// does this launch take the collapsed path (one beam, B > 1 settings, additive outputs only)?
+bool lynx::fwd_collapses(const lynx_program_t* p, int64_t B, int64_t in_row_stride, bool has_out,
+                         int moment_mode) {
+  return in_row_stride == 0 && B > 1 && !has_out && p->n_screen == 0 && p->n_cav == 0 &&
+         (moment_mode != 0 || p->n_bpm_slots > 0);
+}
 
 extern "C" int lynx_track_particles_fwd_bbox(
     const lynx_program_t* p, const float* d_params, int64_t B, const float* d_in_soa,
@@ -302,7 +306,7 @@ extern "C" int lynx_track_particles_fwd_bbox(
   return track_fwd_impl(p, d_params, B, d_in_soa, in_row_stride, ld_in, N, d_out_soa, ld_out,
                         d_bpm_sums, d_screen_img, W, H, d_edges_x, d_edges_y, d_moment_sums,
                         moment_mode, d_energy_in, d_energy_out, d_workspace, d_screen_bbox, nullptr,
-                        0u, stream);
+                        0u, stream, false);
 }
 
 extern "C" int lynx_track_particles_fwd_persistent(
@@ -316,19 +320,19 @@ extern "C" int lynx_track_particles_fwd_persistent(
   return track_fwd_impl(p, d_params, B, d_in_soa, in_row_stride, ld_in, N, d_out_soa, ld_out,
                         d_bpm_sums, d_screen_img, W, H, d_edges_x, d_edges_y, d_moment_sums,
                         moment_mode, d_energy_in, d_energy_out, d_workspace, nullptr, d_img_state,
-                        epoch, stream);
+                        epoch, stream, false);
 }
 
 // d_img_state != nullptr: persistent screen image (lynx_track_particles_fwd_persistent) -- the
 // image is NOT zeroed as a whole; K1's extra blocks clear the rectangle the previous call lit
 // (bounding-box cell (epoch + 1) & 1 of the state), K2 records this call's box in cell epoch & 1.
-static int track_fwd_impl(
+int lynx::track_fwd_impl(
     const lynx_program_t* p, const float* d_params, int64_t B, const float* d_in_soa,
     int64_t in_row_stride, int64_t ld_in, int64_t N, float* d_out_soa, int64_t ld_out,
     double* d_bpm_sums, float* d_screen_img, int32_t W, int32_t H, const float* d_edges_x,
     const float* d_edges_y, double* d_moment_sums, int32_t moment_mode,
     const float* d_energy_in, float* d_energy_out, void* d_workspace, int32_t* d_screen_bbox,
-    int32_t* d_img_state, uint32_t epoch, lynx_stream_t stream) {
+    int32_t* d_img_state, uint32_t epoch, lynx_stream_t stream, bool accumulate) {
   if (!p || !d_params || !d_in_soa || !d_energy_in || !d_workspace || B <= 0 || N <= 0)
     return LYNX_E_BADARG;
   if ((ld_in & 3) || ld_in < N || ((uintptr_t)d_in_soa & 15)) return LYNX_E_BADARG;
@@ -349,8 +353,9 @@ static int track_fwd_impl(
   static const bool env_nc = [] { const char* e = getenv("LYNX_NO_COLLAPSE"); return e && e[0] == '1'; }();
   no_collapse = env_nc;
 #endif
-  if (!no_collapse && in_row_stride == 0 && B > 1 && !d_out_soa && p->n_screen == 0 &&
-      p->n_cav == 0 && (moment_mode != 0 || p->n_bpm_slots > 0)) {
+  if (accumulate && fwd_collapses(p, B, in_row_stride, d_out_soa != nullptr, moment_mode))
+    return LYNX_E_BADARG;  // the collapsed path has no continuation (callers ask fwd_collapses first)
+  if (!no_collapse && fwd_collapses(p, B, in_row_stride, d_out_soa != nullptr, moment_mode)) {
     return fwd_collapse_launch(p, d_params, B, d_in_soa, ld_in, N, d_bpm_sums,
                                moment_mode ? d_moment_sums : nullptr, d_energy_in, d_energy_out,
                                d_workspace, st);
@@ -400,11 +405,15 @@ static int track_fwd_impl(
                p->plan[0].kind == P_AFFINE && p->plan[1].kind == P_SCREEN) ? 1 : 0;
 
   // accumulators are cleared first so that the kernels stay adjacent in the stream
-  if (p->n_bpm_slots > 0)
-    LYNX_CUDA_OK(cudaMemsetAsync(d_bpm_sums, 0, sizeof(double) * 2 * p->n_bpm_slots * B, st));
-  if (has_img && !fuse_zero && !persistent)
-    LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
-  if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
+  // (accumulate: a further range of the SAME beam -- records, zeroed image and sums of the
+  // first range's call are in place, only the particle kernel runs)
+  if (!accumulate) {
+    if (p->n_bpm_slots > 0)
+      LYNX_CUDA_OK(cudaMemsetAsync(d_bpm_sums, 0, sizeof(double) * 2 * p->n_bpm_slots * B, st));
+    if (has_img && !fuse_zero && !persistent)
+      LYNX_CUDA_OK(cudaMemsetAsync(d_screen_img, 0, img_bytes, st));
+    if (moment_mode) LYNX_CUDA_OK(cudaMemsetAsync(d_moment_sums, 0, sizeof(double) * 28 * B, st));
+  }
 
   bool force_ldg = false;
 #ifdef LYNX_EXPERIMENTS
@@ -412,8 +421,9 @@ static int track_fwd_impl(
   force_ldg = env_ldg;
 #endif
   // ---- K1 (records, image zeroing, histogram geometry) then K2
-  if (d_screen_bbox && !bbox_adjacent) LYNX_CUDA_OK(cudaMemsetAsync(d_screen_bbox, 0, 16, st));
-  int rc = compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
+  if (d_screen_bbox && !bbox_adjacent && !accumulate)
+    LYNX_CUDA_OK(cudaMemsetAsync(d_screen_bbox, 0, 16, st));
+  int rc = accumulate ? LYNX_OK : compose_launch(p, d_params, B, d_energy_in, d_in_soa, in_row_stride * 6 * ld_in, ld_in,
                           records, nullptr, d_energy_out,
                           fuse_zero ? (bbox_adjacent ? (void*)d_screen_bbox : (void*)d_screen_img)
                                     : (persistent ? (void*)d_screen_img : nullptr),

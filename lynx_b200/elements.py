@@ -40,6 +40,25 @@ class Element:
     """lynx/accelerator/element.py:23-149."""
 
     _params = ()  # names of the tensor attributes that ``broadcast`` tiles
+    # attributes a track WRITES (readings, diagnostics): setting them does not change the lattice
+    _outputs = frozenset(("reading", "cached_reading", "lost_particle_charges"))
+    _ver = 0
+
+    def __setattr__(self, name, value):
+        # every (re)assignment of a public attribute -- a parameter tensor, is_active, binning ...
+        # -- bumps the element's version; Segment.track keys its cache of the encoded lattice
+        # (program handle + packed device parameters) on it and on the tensors' own in-place
+        # version counters (_stamp below)
+        object.__setattr__(self, name, value)
+        if name[0] != "_" and name not in self._outputs or name == "_transfer_map":
+            object.__setattr__(self, "_ver", self._ver + 1)
+
+    def _stamp(self):
+        """Changes whenever something ``_encode`` reads may have changed: an attribute was
+        assigned, or a parameter tensor was modified in place (``Tensor._version``; writes
+        through ``.data`` are invisible to it -- assign the attribute instead)."""
+        d = self.__dict__
+        return (id(self), self._ver) + tuple(d[n]._version for n in self._params if n in d)
 
     def __init__(self, name: Optional[str] = None) -> None:
         self.name = name if name is not None else generate_unique_name()
@@ -307,6 +326,9 @@ class CustomTransferMap(Element):
     """custom_transfer_map.py:22-116."""
 
     _params = ("length",)
+
+    def _stamp(self):
+        return super()._stamp() + (self._transfer_map._version,)
 
     def __init__(self, transfer_map, length=None, name=None, device=None, dtype=torch.float32):
         assert isinstance(transfer_map, torch.Tensor)

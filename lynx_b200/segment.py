@@ -92,6 +92,33 @@ def _prep_particle_beam(beam: ParticleBeam, batch_shape):
     return soa.expand(*batch_shape, *soa.shape[-2:]).contiguous(), False
 
 
+# Encoded lattices of the last few Segment.track calls: (elements kept alive, Encoded, Program,
+# packed device parameters).  encode + Program.get + pack_params are ~0.25 ms of Python and one
+# H2D copy per call -- ten times the kernels of a 1 M-particle ARES step -- and a tracking loop
+# calls track on an unchanged lattice most of the time.  A hit costs one _stamp() per element.
+_LATTICE_CACHE = {}
+_LATTICE_CACHE_MAX = 16
+
+
+def _encoded_lattice(flat, energy_shape, beam_batch_shape, device):
+    key = (tuple(e._stamp() for e in flat), tuple(energy_shape), tuple(beam_batch_shape), str(device))
+    hit = _LATTICE_CACHE.get(key)
+    if hit is not None:
+        return hit[1], hit[2], hit[3]
+    enc = encode(flat, energy_shape)
+    bshape = enc.batch_shape
+    if bshape != tuple(beam_batch_shape):
+        bshape = broadcast_shapes(bshape, beam_batch_shape)
+    enc.batch_shape = bshape
+    prog = Program.get(enc)
+    params = pack_params(enc, device)
+    if not params.requires_grad:  # a differentiable packing belongs to its autograd graph
+        if len(_LATTICE_CACHE) >= _LATTICE_CACHE_MAX:
+            _LATTICE_CACHE.pop(next(iter(_LATTICE_CACHE)))
+        _LATTICE_CACHE[key] = (list(flat), enc, prog, params)  # the elements stay alive: ids stay unique
+    return enc, prog, params
+
+
 def track_elements(elements, incoming, *, particles: bool = True, moments: int = 1):
     """Segment.track (segment.py:340-356) for a flat or nested element list.
 
@@ -116,14 +143,9 @@ def track_elements(elements, incoming, *, particles: bool = True, moments: int =
         return track_elements(flat[cut + 1:], beam, particles=particles, moments=moments)
     device = incoming.soa.device
     _require_cuda(device)
-    enc = encode(flat, incoming.energy.shape)
+    enc, prog, params = _encoded_lattice(flat, incoming.energy.shape, incoming.batch_shape, device)
     bshape = enc.batch_shape
-    if bshape != incoming.batch_shape:
-        bshape = broadcast_shapes(bshape, incoming.batch_shape)
-    enc.batch_shape = bshape
     B = enc.B
-    prog = Program.get(enc)
-    params = pack_params(enc, device)
     e_in = incoming.energy.to(device).expand(bshape).reshape(B).contiguous()
     soa, shared = _prep_particle_beam(incoming, bshape)
     N, ld = incoming.num_particles, incoming.ld
@@ -190,12 +212,10 @@ def beam_moment_sums(beam: ParticleBeam) -> torch.Tensor:
 def _track_parameter_beam(flat, incoming: ParameterBeam):
     device = incoming._mu.device
     _require_cuda(device)
-    enc = encode(flat, incoming.energy.shape)
-    bshape = broadcast_shapes(enc.batch_shape, tuple(incoming._mu.shape[:-1]))
-    enc.batch_shape = bshape
+    enc, prog, params = _encoded_lattice(flat, incoming.energy.shape,
+                                         tuple(incoming._mu.shape[:-1]), device)
+    bshape = enc.batch_shape
     B = enc.B
-    prog = Program.get(enc)
-    params = pack_params(enc, device)
     e_in = incoming.energy.to(device).expand(bshape).reshape(B).contiguous()
     mu, cov = incoming._mu, incoming._cov
     nb = mu.dim() - 1

@@ -430,6 +430,58 @@ def test_host_buffer_abi_matches_device_path():
     L.lib().lynx_host_ctx_destroy(ctx)
 
 
+@pytest.mark.parametrize("n", [131_075, 700_001])
+def test_host_buffer_abi_chunked_overlap(n):
+    """Above 128 K particles the host entry point sends the beam in 2 (>= 128 K) or 4 (>= 512 K)
+    chunks and tracks each as it lands (csrc/host.cu): image and outgoing particles must be the
+    device path's bit for bit, the moment sums equal up to the order of their additions."""
+    import ctypes as C
+
+    from lynx_b200 import _lib as L
+    from lynx_b200.program import Program, encode, pack_params
+
+    soa = F.gaussian_beam_soa(n, seed=5)
+    e_in = np.array([F.ASTRA_ENERGY], dtype=np.float32)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    ctx = C.c_void_p()
+    L.check(L.lib().lynx_host_ctx_create(0, C.byref(ctx)))
+    soa_c = np.ascontiguousarray(soa)
+    for screen_on in (True, False):
+        spec = F.ares_ea(k1=(5.0, -5.0, 5.0), vkick=1e-3, hkick=-2e-3, screen_active=screen_on,
+                         screen=F.TEST_SCREEN)
+        seg = F.build_segment(spec)
+        out_dev = seg.track(_gpu_beam(soa, F.ASTRA_ENERGY))
+        enc = encode(seg.elements, (1,))
+        prog = Program.get(enc)
+        params = pack_params(enc, "cpu").numpy()
+        mom = np.empty((1, 28), dtype=np.float64)
+        if screen_on:
+            want = seg.AREABSCR1.reading.cpu().numpy()
+            ex, ey = (e.numpy() for e in seg.AREABSCR1.pixel_bin_edges)
+            W, H = ex.size - 1, ey.size - 1
+            for persistent in (0, 1, 1):
+                L.check(L.lib().lynx_host_ctx_set_option(ctx, 1, persistent))
+                img = np.zeros((1, H, W), dtype=np.float32)
+                L.check(L.lib().lynx_host_track_particles(
+                    ctx, prog.handle, vp(params), params.size, 1, vp(soa_c), 1, n, vp(e_in), None,
+                    None, vp(img), W, H, vp(ex), vp(ey), vp(mom), 2, None))
+                assert np.array_equal(img, want)
+                assert mom[0, 0] == n
+        else:
+            out = np.empty((1, 6, n), dtype=np.float32)
+            L.check(L.lib().lynx_host_track_particles(
+                ctx, prog.handle, vp(params), params.size, 1, vp(soa_c), 1, n, vp(e_in), vp(out),
+                None, None, 0, 0, None, None, vp(mom), 2, None))
+            assert np.array_equal(out[0], out_dev.soa[0, :, :n].cpu().numpy())
+            sums = out_dev.moment_sums().cpu().numpy().reshape(28)
+            assert mom[0, 0] == n == sums[0]
+            diag = [7 + d for d in (0, 6, 11, 15, 18, 20)]  # sum v_i^2: no cancellation
+            np.testing.assert_allclose(mom[0, diag], sums[diag], rtol=1e-5)
+            sd = np.sqrt(sums[diag] / n)
+            np.testing.assert_allclose(mom[0, 1:7] / n, sums[1:7] / n, atol=1e-5 * sd.max(), rtol=1e-4)
+    L.lib().lynx_host_ctx_destroy(ctx)
+
+
 def test_forward_moment_collapse_matches_streaming():
     """One beam shared by B settings, moments / BPM readings only: the collapse path
     (beam streamed once, sums pushed through each setting's map) must agree with the
