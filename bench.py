@@ -523,6 +523,24 @@ def run_ours(args, rank, world, local_rank):
         sys.stderr.write(f"[rank {rank}] us after K1 done: K2 CTA0 done {rel[5]:.2f}, EX resident "
                          f"{rel[0]:.2f}, K2 complete {rel[1]:.2f}, peers arrived {rel[2]:.2f}, "
                          f"written {rel[3]:.2f}, last CTA {rel[7]:.2f}; step mean {sum(ms) / len(ms) * 1e3:.2f}\n")
+        # where the rest of the step goes: stamp kernels in front of and behind the step
+        st2 = torch.zeros(2, dtype=torch.int64, device=device)
+        lib.lynx_exchange_trace(trace.data_ptr())
+        gaps = []
+        for i in range(60):
+            flush.zero_()
+            lib.lynx_debug_stamp(st2.data_ptr(), L.current_stream())
+            step_fn()
+            lib.lynx_debug_stamp(st2.data_ptr() + 8, L.current_stream())
+            torch.cuda.synchronize()
+            row = trace.view(1024, 8)[exch.step & 1023].tolist()
+            t0, t1 = st2.tolist()
+            if i >= 10 and row[0] > 0:
+                gaps.append(((row[6] - t0) / 1e3, (t1 - row[7]) / 1e3, (t1 - t0) / 1e3))
+        lib.lynx_exchange_trace(None)
+        g = np.mean(gaps, axis=0)
+        sys.stderr.write(f"[rank {rank}] stamp kernel -> K1 block 0 starts {g[0]:.2f} us; EX last CTA -> "
+                         f"stamp kernel {g[1]:.2f} us; stamp to stamp {g[2]:.2f} us\n")
         ms_local = timed_steps(wl.step, 50, 5, flush)
         if hasattr(exch, "reduce"):
             real_reduce = exch.reduce
@@ -607,9 +625,24 @@ def run_ours(args, rank, world, local_rank):
         if not same:
             sys.stderr.write(f"[rank {rank}] exchange check: {(exch.out != want).sum().item()} pixels differ, "
                              f"sums {exch.out.sum().item()} / {want.sum().item()}\n")
+        # ... and over many back-to-back steps with a different beam each (the message that
+        # publishes a rank's image is a relaxed system-scope store, exchange.cu: a stale read
+        # would drop counts silently, so the sum is checked against NCCL every time)
+        n_stress = 0 if args.no_extras else 40
+        for k in range(n_stress):
+            wl.soa[:, : wl.n].mul_(1.0 + 1e-3 * ((k + rank) % 5))
+            wl.step()
+            w2 = wl.img.clone()
+            dist.all_reduce(w2)
+            wl.sharded_step(exch)
+            wl.sharded_step(exch)  # twice: both slots, no host synchronisation in between
+            torch.cuda.synchronize()
+            same = same and torch.equal(exch.out, w2)
+        wl.soa.copy_(wl.soa_host, non_blocking=False)
         flag = torch.tensor([1.0 if same else 0.0], device=device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        exchange_check = "bit-exact" if flag.item() == 1.0 else "MISMATCH"
+        exchange_check = ("bit-exact" if flag.item() == 1.0 else "MISMATCH") + (
+            f" ({2 * n_stress + 1} exchanges against dist.all_reduce)" if n_stress else "")
 
     # ---- (i) the second half of the metric: ParameterBeam env-steps/s, settings sharded over
     #      the ranks (args.settings per GPU; no collective on the path)
