@@ -614,7 +614,7 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- (iv) the exchange step against NCCL, outside any timed region: the fused kernel's
     #      image must equal dist.all_reduce of the ranks' local images bit for bit
-    exchange_check = None
+    exchange_check, exchange_check_n = None, 0
     if world > 1 and args.exchange == "fused":
         wl.step()  # local image of this rank's shard into wl.img
         want = wl.img.clone()
@@ -641,8 +641,8 @@ def run_ours(args, rank, world, local_rank):
         wl.soa.copy_(wl.soa_host, non_blocking=False)
         flag = torch.tensor([1.0 if same else 0.0], device=device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        exchange_check = ("bit-exact" if flag.item() == 1.0 else "MISMATCH") + (
-            f" ({2 * n_stress + 1} exchanges against dist.all_reduce)" if n_stress else "")
+        exchange_check = "bit-exact" if flag.item() == 1.0 else "MISMATCH"
+        exchange_check_n = 2 * n_stress + 1
 
     # ---- (i) the second half of the metric: ParameterBeam env-steps/s, settings sharded over
     #      the ranks (args.settings per GPU; no collective on the path)
@@ -776,6 +776,7 @@ def run_ours(args, rank, world, local_rank):
     }
     if exchange_check is not None:
         line["exchange_check"] = exchange_check
+        line["exchange_check_exchanges"] = exchange_check_n  # each against dist.all_reduce of the local images
     if cfg4 is not None:
         line["cfg4_100M_sharded"] = cfg4
 
