@@ -661,9 +661,11 @@ def run_ours(args, rank, world, local_rank):
         if rank == 0:
             k6b = kernel_ms(pw2.step, 2, 10, flush, lib)
             a6 = pw2.algorithmic_bytes() / (k6b * 1e-3) / 1e9
-            env_steps["roofline"] = {"bound": "hbm", "kernel": "parambeam_fwd_kernel (K6)",
+            tr6, tr6_src = traffic_of("parambeam_fwd_kernel", "ares_ea", bigB)
+            env_steps["roofline"] = {"bound": "hbm", "kernel": "parambeam_fwd_kernel<light> (K6)",
                                      "settings": bigB, "kernel_ms": k6b, "achieved": a6,
                                      "peak": peak, "unit": "GB/s", "frac": a6 / peak,
+                                     "traffic": tr6, "traffic_source": tr6_src,
                                      "algorithmic_bytes_per_launch": pw2.algorithmic_bytes()}
         del pw2
 

@@ -324,13 +324,14 @@ def test_config5_256_settings_1m_particles_vs_oracle():
 
 
 # ------------------------------------------------------------------ light maps (maps.cuh)
-@pytest.mark.parametrize("B", [1, 42, 1002, 4096])
+@pytest.mark.parametrize("B", [1, 42, 1002, 4096, 20_001])
 def test_light_map_kernels_equal_the_dense_kernels(B):
     """A lattice made only of drifts / quadrupoles / correctors runs the light-map variants of
     K1 and K6 (21 live map entries, maps.cuh); the same lattice with an identity
     ``CustomTransferMap`` in its merged run runs the dense ones.  The light variants skip only
     products with structural zeros and ones, so both must agree to the bit -- tilted and
-    misaligned quadrupoles, ragged last block (B % 4 != 0: no bulk store) included."""
+    misaligned quadrupoles, ragged last block (B % 4 != 0: no bulk store) and several tiles per
+    block (B = 20 001) included."""
     rng = np.random.default_rng(B)
 
     def lattice(dense):
@@ -366,7 +367,7 @@ def test_light_map_kernels_equal_the_dense_kernels(B):
     assert torch.equal(a._cov, b._cov)
     assert torch.isfinite(a._cov).all() and (a._cov[:, 0, 0] > 0).all()
     # K1's records through the particle kernel: outgoing particles of a small beam
-    n = 4099
+    n = 4099 if B <= 4096 else 259
     beam = _gpu_beam(F.gaussian_beam_soa(n, seed=5), F.ASTRA_ENERGY)
     pa, pd = light.track(beam), dense.track(beam)
     assert pa.soa.shape[0] == B and torch.equal(pa.soa[..., :n], pd.soa[..., :n])
