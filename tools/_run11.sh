@@ -1,9 +1,10 @@
 set -u
-out=gpurun_out/r2k; mkdir -p $out
-export LYNX_B200_LIB=lynx_b200/lib/liblynx_b200_exp.so
-for m in push pull; do
-echo "== $m"
-if [ $m = pull ]; then export LYNX_EX_PULL=1; fi
-LYNX_EX_TRACE=1 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 100 --warmup 10 --no-extras > $out/bench_n2_$m.json 2> $out/bench_n2.err; grep "rank 0" $out/bench_n2.err | grep "us after\|stamp kernel" | sed 's/.*\(us after\)/\1/'; python -c "
-import json;s=open('$out/bench_n2_$m.json').read();d=json.loads(s[s.index('{'):]);print('step',d['ms_per_step']*1e3,'check',d.get('exchange_check'))"
-done
+N=$1
+out=gpurun_out/r2n; mkdir -p $out
+LYNX_EX_TRACE=1 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 100 --warmup 10 > $out/bench_n$N.json 2> $out/bench_n$N.err; echo "bench n$N rc=$?"; grep "rank 0" $out/bench_n$N.err | tail -4; grep -i "Traceback" -A8 $out/bench_n$N.err | head -20
+python - <<PY
+import json
+d=json.load(open('$out/bench_n$N.json'))
+for k in ('value','ms_per_step','e2e','exchange_check','exchange_check_exchanges','env_steps','api_e2e','cfg4_100M_sharded','gpu_launches'):
+    print(k, json.dumps(d.get(k))[:420])
+PY
