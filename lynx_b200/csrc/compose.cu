@@ -25,8 +25,9 @@ struct ProgramTables {
   DevOp ops[kTabOps];
   int64_t col_offset[kTabCols];
   int32_t col_stride[kTabCols];
-  // shared-memory slot of column c: word slot + (thread & mask); a column shared by all
-  // settings (stride 0) has ONE slot per block (mask 0), a per-setting column one per thread
+  // shared-memory slot of column c: word slot + thread * per_thread; a column shared by all
+  // settings (stride 0) has ONE slot per block (per_thread 0), a per-setting column one per
+  // thread (per_thread 1)
   int2 col_slot_mask[kTabCols];
   // the per-setting columns: offset, stride and slot again, packed for the prefetch
   int64_t var_offset[kTabCols];
@@ -41,7 +42,7 @@ struct SlotParamView {
   int s;
   __device__ __forceinline__ float operator()(int col) const {
     const int2 sm = tab.col_slot_mask[col];
-    return vals[sm.x + (s & sm.y)];
+    return vals[sm.x + s * sm.y];
   }
 };
 
@@ -208,14 +209,41 @@ __device__ __forceinline__ void tile_release() {
 }
 
 __device__ __forceinline__ void load_beam(const ParamBeamArgs& a, int64_t b, MomentSink& sink) {
-  const float* mi = a.mu_in + b * a.beam_stride * 7;
-  const float* ci = a.cov_in + b * a.beam_stride * 49;
+  if (a.beam_stride == 0 && ((((uintptr_t)a.cov_in) | ((uintptr_t)a.mu_in)) & 15) == 0) {
+    // one beam for all settings, 16-byte aligned: 15 broadcast loads instead of 56
+    float c[52], m[8];
 #pragma unroll
-  for (int i = 0; i < 7; ++i) sink.mu[i] = __ldg(mi + i);
+    for (int q = 0; q < 12; ++q) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(a.cov_in) + q);
+      c[4 * q] = v.x;
+      c[4 * q + 1] = v.y;
+      c[4 * q + 2] = v.z;
+      c[4 * q + 3] = v.w;
+    }
+    c[48] = __ldg(a.cov_in + 48);
+    const float4 m0 = __ldg(reinterpret_cast<const float4*>(a.mu_in));
+    m[0] = m0.x;
+    m[1] = m0.y;
+    m[2] = m0.z;
+    m[3] = m0.w;
 #pragma unroll
-  for (int i = 0; i < 7; ++i)
+    for (int i = 4; i < 7; ++i) m[i] = __ldg(a.mu_in + i);
 #pragma unroll
-    for (int j = 0; j < 7; ++j) sink.cov[i][j] = __ldg(ci + i * 7 + j);
+    for (int i = 0; i < 7; ++i) sink.mu[i] = m[i];
+#pragma unroll
+    for (int i = 0; i < 7; ++i)
+#pragma unroll
+      for (int j = 0; j < 7; ++j) sink.cov[i][j] = c[i * 7 + j];
+  } else {
+    const float* mi = a.mu_in + b * a.beam_stride * 7;
+    const float* ci = a.cov_in + b * a.beam_stride * 49;
+#pragma unroll
+    for (int i = 0; i < 7; ++i) sink.mu[i] = __ldg(mi + i);
+#pragma unroll
+    for (int i = 0; i < 7; ++i)
+#pragma unroll
+      for (int j = 0; j < 7; ++j) sink.cov[i][j] = __ldg(ci + i * 7 + j);
+  }
   sink.bpm_out = a.bpm_out;
   sink.B = a.B;
   sink.b = b;
@@ -350,7 +378,7 @@ static bool fill_tables(const lynx_program_t* p, ProgramTables& tab) {
   std::copy(p->col_stride.begin(), p->col_stride.end(), tab.col_stride);
   for (int c = 0; c < n_cols; ++c) {
     const bool var = p->col_stride[c] != 0;
-    tab.col_slot_mask[c] = make_int2(tab.smem_words, var ? -1 : 0);
+    tab.col_slot_mask[c] = make_int2(tab.smem_words, var ? 1 : 0);
     if (var) {
       tab.var_offset[tab.n_var] = p->col_offset[c];
       tab.var_stride[tab.n_var] = p->col_stride[c];

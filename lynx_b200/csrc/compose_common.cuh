@@ -1,6 +1,7 @@
 // Argument blocks and sinks of K1 / K6 (compose.cu), also used by the along-s kernel and the
 // adjoint kernels.
 #pragma once
+#include <type_traits>
 #include "walk.cuh"
 
 namespace lynx {
@@ -125,14 +126,24 @@ struct MomentSinkT {
   int64_t B, b;
 
   // element.py:73-74 with R = [M; e6].  A light map (maps.cuh) skips the products with its
-  // structural zeros and ones: 315 fma instead of 686, the same bits.
+  // structural zeros and ones, the same bits as the dense arithmetic.  The second product
+  // cov R^T is evaluated for the upper triangle only and mirrored: R cov R^T of a symmetric
+  // cov is symmetric, the reference's full product differs from its own transpose by rounding
+  // (an input that is NOT symmetric -- not a covariance -- comes out symmetrised here).
+  // 686 fma dense / 315 light for the full product, 539 / 223 with the triangle.  The
+  // dual-number instantiation (K6-bwd) keeps the full product: its tangent seeds ONE entry of
+  // cov, which is not a symmetric direction, and d / d cov[i][j] must stay what autograd through
+  // the reference's matmul gives.
+  static constexpr bool kSymmetric = std::is_same<T, float>::value;
   template <bool LT>
   __device__ __forceinline__ void apply(const MapT<T, LT>& M) {
     T t[7];
-    // t = R[0..5] v for a 7-vector v (mu or a column of cov), dense order of summation
-    auto rows_times = [&](auto&& v) {
+    // t[i] = (R v)[i] for i in [lo, 6) and a 7-vector v (mu, a column or a row of cov), dense
+    // order of summation
+    auto rows_times = [&](auto&& v, int lo) {
 #pragma unroll
       for (int i = 0; i < 6; ++i) {
+        if (i < lo) continue;
         if (LT && i == 5) {
           t[5] = v(5);
         } else if (LT && i == 4) {
@@ -146,22 +157,39 @@ struct MomentSinkT {
         }
       }
     };
-    rows_times([&](int j) { return mu[j]; });
+    rows_times([&](int j) { return mu[j]; }, 0);
 #pragma unroll
     for (int i = 0; i < 6; ++i) mu[i] = t[i];
     // cov <- R cov  (column by column, in place)
 #pragma unroll
     for (int k = 0; k < 7; ++k) {
-      rows_times([&](int j) { return cov[j][k]; });
+      rows_times([&](int j) { return cov[j][k]; }, 0);
 #pragma unroll
       for (int i = 0; i < 6; ++i) cov[i][k] = t[i];
     }
-    // cov <- cov R^T  (row by row, in place)
+    if constexpr (kSymmetric) {
+      // cov <- cov R^T: entries (i, l >= i) row by row, in place (row i only reads row i) ...
 #pragma unroll
-    for (int i = 0; i < 7; ++i) {
-      rows_times([&](int k) { return cov[i][k]; });
+      for (int i = 0; i < 6; ++i) {
+        rows_times([&](int k) { return cov[i][k]; }, i);
 #pragma unroll
-      for (int l = 0; l < 6; ++l) cov[i][l] = t[l];
+        for (int l = 0; l < 6; ++l)
+          if (l >= i) cov[i][l] = t[l];
+      }
+      // ... and the mirror image (column 6 of the product is column 6 of R cov)
+#pragma unroll
+      for (int i = 0; i < 7; ++i)
+#pragma unroll
+        for (int l = 0; l < 7; ++l)
+          if (l > i) cov[l][i] = cov[i][l];
+    } else {
+      // cov <- cov R^T  (row by row, in place)
+#pragma unroll
+      for (int i = 0; i < 7; ++i) {
+        rows_times([&](int k) { return cov[i][k]; }, 0);
+#pragma unroll
+        for (int l = 0; l < 6; ++l) cov[i][l] = t[l];
+      }
     }
   }
   template <bool LT>
