@@ -403,6 +403,12 @@ int lynx::track_fwd_impl(
   // one merged stage, then the terminal screen, and nothing else reads the beam
   a.xy_only = (has_img && !d_out_soa && moment_mode == 0 && p->plan.size() == 2 &&
                p->plan[0].kind == P_AFFINE && p->plan[1].kind == P_SCREEN) ? 1 : 0;
+  {
+    const size_t np_ = p->plan.size();
+    a.xy_tail = (has_img && !d_out_soa && moment_mode == 0 && np_ > 2 && img_bytes &&
+                 p->plan[np_ - 2].kind == P_AFFINE && p->plan[np_ - 1].kind == P_SCREEN)
+                    ? (int)np_ - 2 : -1;
+  }
 
   // accumulators are cleared first so that the kernels stay adjacent in the stream
   // (accumulate: a further range of the SAME beam -- records, zeroed image and sums of the

@@ -34,6 +34,8 @@ struct TrackArgs {
   int stages;        // ring depth of the pipelined kernel (2..4; the histogram tile takes the rest)
   int ctas_per_row;  // CTAs that share one setting: b = blockIdx.x / ctas_per_row
   int xy_only;       // the plan is [AFFINE, SCREEN] and nothing else reads the beam: rows x, y only
+  int xy_tail;       // longer plans ending [.., AFFINE, SCREEN] with nothing else reading the beam:
+                     // plan index of that last stage (x, y rows only), else -1
   int* bbox;         // nullable: [4] max(W - ix), max(ix + 1), max(H - iy), max(iy + 1)
   double* mom;
   int64_t B;

@@ -459,6 +459,14 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
       for (int pi = 0; pi < a.n_plan; ++pi) {
         const PlanItem p = plan[pi];
         if (p.kind == P_AFFINE) {
+          if constexpr (!HAS_OUT && MOM == 0) {
+            if (pi == a.xy_tail) {  // the last stage in front of the terminal screen: x, y rows only
+              float xv[4], yv[4];
+              apply_affine_xy(rec + p.a, v, xv, yv);
+              screen4(plan[pi + 1], xv, yv, live);
+              break;
+            }
+          }
           apply_affine(rec + p.a, v);
         } else if (p.kind == P_CAVITY) {
           float s0[4], q0[4];
