@@ -272,7 +272,13 @@ extern "C" int lynx_screen_allreduce_mc(void* const* peer_bases, void* multicast
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   // the rectangle is only known on the device: a fixed grid strides over it
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3((unsigned)(2 * sms));
+  unsigned ex_grid = (unsigned)(2 * sms);
+  bool ex_pdl = true;
+#ifdef LYNX_EXPERIMENTS
+  if (const char* e = getenv("LYNX_EX_GRID")) ex_grid = (unsigned)atoi(e);
+  if (getenv("LYNX_EX_NOPDL")) ex_pdl = false;
+#endif
+  cfg.gridDim = dim3(ex_grid);
   cfg.blockDim = dim3(kExTPB);
   cfg.dynamicSmemBytes = 0;
   cfg.stream = (cudaStream_t)stream;
@@ -280,7 +286,7 @@ extern "C" int lynx_screen_allreduce_mc(void* const* peer_bases, void* multicast
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = ex_pdl ? 1 : 0;
   const cudaError_t err = cudaLaunchKernelEx(&cfg, screen_allreduce_kernel, a);
   count_launch();
   return err == cudaSuccess ? LYNX_OK : LYNX_E_LAUNCH;
