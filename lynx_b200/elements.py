@@ -629,7 +629,16 @@ class Screen(Element):
         if isinstance(beam, ParameterBeam):
             self.cached_reading = self._parameter_beam_image(beam)
             return self.cached_reading
-        raise RuntimeError("screen reading is produced by Segment.track; none cached")
+        # a ParticleBeam set through set_read_beam: histogram its x, y as they are
+        # (screen.py:195-211 reads read_beam.xs / ys; the misalignment was applied by track)
+        from .segment import track_elements
+
+        probe = Screen(resolution=self.resolution, pixel_size=self.pixel_size, binning=self.binning,
+                       misalignment=torch.zeros_like(self.misalignment), is_active=True,
+                       name=f"{self.name}_probe")
+        track_elements([probe], beam)
+        self.cached_reading = probe.cached_reading
+        return self.cached_reading
 
     def _parameter_beam_image(self, beam: ParameterBeam) -> torch.Tensor:
         """screen.py:157-194 on the device (K7): (..., W_eff, H_eff) as the reference

@@ -50,7 +50,10 @@ def _is_shared(t: torch.Tensor, nbatch_dims: int) -> bool:
 def compose_transfer_map(elements, energy: torch.Tensor) -> Optional[torch.Tensor]:
     """Segment.transfer_map (segment.py:329-338): product of the elements' maps."""
     flat = _flatten(elements)
-    if not all(e.is_skippable for e in flat):
+    # a lone active cavity: its own linear map (cavity.py:248-325, Cavity.transfer_map) is the
+    # one stage K1 emits for it; any other non-skippable element has no map (segment.py:329-338)
+    lone_cavity = len(flat) == 1 and type(flat[0]).__name__ == "Cavity"
+    if not lone_cavity and not all(e.is_skippable for e in flat):
         return None
     energy = torch.as_tensor(energy, dtype=torch.float32)
     device = energy.device if energy.device.type == "cuda" else torch.device("cuda")
@@ -158,6 +161,9 @@ def track_elements(elements, incoming, *, particles: bool = True, moments: int =
         el.reading = (bpm[slot] / N).to(torch.float32).T.reshape(2, *bshape)
     if enc.screen_element is not None:
         scr = enc.screen_element
+        for el in flat[flat.index(scr) + 1:]:  # they see Beam.empty (screen.py:139, bpm.py:50-52)
+            if type(el).__name__ == "BPM" and el.is_active:
+                el.reading = None
         upto = flat[: flat.index(scr)]
         scr._read = lambda: _beam_at_screen(upto, incoming, scr)
         scr.cached_reading = img

@@ -476,3 +476,56 @@ def test_kernels_vs_reference_batched_particle_settings():
         out = seg.track(beam)
         for b in range(3):
             _rel(out.soa[b, :, :n].cpu().numpy(), g[key][b, :, :6].T, 2e-5, f"{key}[{b}]")
+
+
+# ------------------------------------------------------------------ API-surface corner cases
+def test_active_cavity_transfer_map_and_user_set_screen_beam_and_bpm_behind_screen():
+    """Three places where the host mirror used to deviate from the reference's surface:
+    ``Cavity.transfer_map`` of an ACTIVE cavity returns its linear map (cavity.py:248-325), not
+    None; ``Screen.reading`` histograms a ParticleBeam set through ``set_read_beam``
+    (screen.py:195-211); an active BPM behind an active screen sees ``Beam.empty`` and reads None
+    (bpm.py:50-52)."""
+    import numpy as np
+    import torch
+
+    import lynx_b200 as lx
+    from lynx_b200 import fixtures as F
+    from oracle import lattice as O
+    from oracle import screen_bin_edges, screen_reading_particles
+
+    # 1. active cavity
+    energy = torch.tensor([6e6, 1e8])
+    cav = lx.Cavity(length=torch.tensor([1.0377, 0.5]), voltage=torch.tensor([0.01815975e9, -3e6]),
+                    phase=torch.tensor([0.0, 30.0]), frequency=torch.tensor([1.3e9, 1.3e9]))
+    assert cav.is_active
+    got = cav.transfer_map(energy.cuda())
+    assert got is not None and tuple(got.shape) == (2, 7, 7)
+    want = O.element_map(O.El("cavity", "c", {"length": cav.length.double(), "voltage": cav.voltage.double(),
+                                              "phase": cav.phase.double(), "frequency": cav.frequency.double()}),
+                         energy.double())
+    np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=2e-5, atol=1e-7)
+    assert lx.Segment([lx.Drift(torch.tensor([0.1])), cav]).transfer_map(energy.cuda()) is None
+
+    # 2. a ParticleBeam handed to the screen by the user
+    n = 30_000
+    soa = F.gaussian_beam_soa(n, seed=9)
+    soa[0] *= 3.0  # wider than the tracked test beams
+    beam = lx.ParticleBeam(torch.from_numpy(F.soa_to_aos7(soa)).unsqueeze(0), torch.tensor([F.ASTRA_ENERGY]))
+    scr = lx.Screen(resolution=torch.tensor(F.TEST_SCREEN["resolution"]),
+                    pixel_size=torch.tensor(F.TEST_SCREEN["pixel_size"]), is_active=True,
+                    misalignment=torch.tensor([1e-4, -2e-4]), name="S")
+    scr.set_read_beam(beam)
+    ex, ey = screen_bin_edges(F.TEST_SCREEN["resolution"], F.TEST_SCREEN["pixel_size"])
+    want_img = screen_reading_particles(beam.xs.cpu(), beam.ys.cpu(), ex, ey)
+    assert torch.equal(scr.reading.cpu(), want_img)  # no misalignment applied: track does that
+
+    # 3. BPM behind the terminal screen
+    bpm = lx.BPM(is_active=True, name="B")
+    bpm.reading = torch.ones(2, 1)  # stale
+    seg = lx.Segment([lx.Drift(torch.tensor([0.2])),
+                      lx.Screen(resolution=torch.tensor(F.TEST_SCREEN["resolution"]),
+                                pixel_size=torch.tensor(F.TEST_SCREEN["pixel_size"]), is_active=True,
+                                name="S2"),
+                      lx.Drift(torch.tensor([0.2])), bpm])
+    assert seg.track(beam) is lx.Beam.empty
+    assert bpm.reading is None
