@@ -153,9 +153,11 @@ def track_elements(elements, incoming, *, particles: bool = True, moments: int =
     soa, shared = _prep_particle_beam(incoming, bshape)
     N, ld = incoming.num_particles, incoming.ld
     want_out = particles and not prog.terminal
+    # behind a terminal screen there is no outgoing beam (Beam.empty, screen.py:139): nobody
+    # reads its moments, and the moment-free screen variant of K2 is the fast one
     out, bpm, img, mom, e_out = launch_track_particles(
-        prog, params, B, soa, shared, ld, N, e_in, want_out=want_out, moment_mode=moments,
-        screen=enc.screen_element, batch_shape=bshape)
+        prog, params, B, soa, shared, ld, N, e_in, want_out=want_out,
+        moment_mode=0 if prog.terminal else moments, screen=enc.screen_element, batch_shape=bshape)
     for slot, el in enumerate(enc.bpm_elements):  # bpm.py:54
         el._bpm_sums = bpm[slot]  # additive over particle shards (sharding.py)
         el.reading = (bpm[slot] / N).to(torch.float32).T.reshape(2, *bshape)
