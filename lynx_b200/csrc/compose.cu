@@ -458,8 +458,16 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
   unsigned blocks = (unsigned)((B + S - 1) / S);
   if (zero_rect)
     blocks += (unsigned)p->sm_count;  // the rectangle's size is only known on the device
-  else if (a.zero_vec4 > 0)
-    blocks += (unsigned)std::min<int64_t>(zero_blocks_per_sm * p->sm_count, (a.zero_vec4 + kComposeTPB - 1) / kComposeTPB);
+  else if (a.zero_vec4 > 0) {
+    // While the compose and histogram blocks are fewer than the SMs, the launch is exactly one
+    // block per SM: a zeroing block that shares an SM with the walker or the histogram block
+    // keeps that SM's store path busy and holds their loads back until it is done (both sat
+    // 2.5 us at their first loads, tools/k2_timeline.py) -- and they are the launch's long poles.
+    int64_t zb = std::min<int64_t>(zero_blocks_per_sm * p->sm_count, (a.zero_vec4 + kComposeTPB - 1) / kComposeTPB);
+    const int64_t others = (int64_t)blocks + (hist_out ? 1 : 0);
+    if (others < p->sm_count) zb = std::min<int64_t>(zb, p->sm_count - others);
+    blocks += (unsigned)zb;
+  }
   if (hist_out) blocks += 1;
   {
     ProfileScope ps(0, st);

@@ -301,19 +301,22 @@ __device__ __forceinline__ void hist_axes_setup(const float* __restrict__ ex, in
   atomicMax(&s_dev[0], __float_as_uint(dev[0]));
   atomicMax(&s_dev[1], __float_as_uint(dev[1]));
   __syncthreads();
+  // (selects, not array indexing by the thread index: that would put the arrays in local
+  // memory, whose first touch is a page-table and DRAM miss on this block's critical path)
   if (tid < 2) {
-    const int x = tid;
-    const float fe0 = f0[x], fen = fn[x];
-    const int nn = x ? H : W;
-    const float d = __uint_as_float(s_dev[x]);
+    const bool y = tid == 1;
+    const float fe0 = y ? f0[1] : f0[0], fen = y ? fn[1] : fn[0];
+    const int nn = y ? H : W;
+    const float d = __uint_as_float(y ? s_dev[1] : s_dev[0]);
     HistAxis r;
     r.e0 = fe0;
     r.en = fen;
     r.inv = (float)nn / (fen - fe0);
     const float m = 1.25f * d + (float)nn * (1.f / 2097152.f) + (1.f / 1048576.f);
-    const bool ok = d < 0.2f && m < 0.25f && step[x] > 0.0 && fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
+    const bool ok = d < 0.2f && m < 0.25f && (y ? step[1] : step[0]) > 0.0 &&
+                    fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
     r.margin = ok ? m : 1.f;  // margin >= 0.5 means: irregular table, always searched
-    h[x] = r;
+    h[tid] = r;
   }
 }
 
