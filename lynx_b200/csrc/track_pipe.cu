@@ -15,8 +15,8 @@
 //
 // In-flight bytes are set by shared memory (a ring of 48 KB stages), not by registers x
 // occupancy, so the whole 1M-particle beam is requested in the first microsecond and large
-// beams stream at copy speed.  SASS: UBLKCP (bulk copies), SYNCS (mbarrier), UBLKRED (bulk
-// reduce).  Same arithmetic and outputs as track_fwd_kernel (track.cu).
+// beams stream at copy speed.  SASS: UBLKCP (bulk copies), SYNCS (mbarrier).  Same arithmetic
+// and outputs as track_fwd_kernel (track.cu).
 //
 // Screen histogram (K4).  One global RED.ADD.F32 per particle runs at the focused-beam atomic
 // rate of the L2 (64-75 G updates/s for a sigma = 40 px spot, profiles/r2_hist_bench_c.txt): 32 M
@@ -25,9 +25,13 @@
 // profiles/r2_hist_bench_b.txt) -- so every CTA keeps a private u32 TILE of the image in shared
 // memory, placed on the beam from the statistics of the CTA's first pipeline tile (mean +- k
 // sigma, k as large as the tile's capacity allows).  In-tile particles cost one ATOMS, the tails
-// go to global memory as before (few, and spread out: no hot L2 lines), and at the end the tile
-// is converted to fp32 in place and added into the image with ONE cp.reduce.async.bulk per tile
-// row.  The ring gives the tile its shared memory: 2-4 stages, chosen by the launcher.
+// go to global memory as before (few, and spread out: no hot L2 lines), and at the end every
+// thread converts its quads of the tile to fp32 and adds the non-empty ones into the image with
+// one 16-byte vector reduction each (red.global.add.v4.f32).  A first version converted in
+// place and issued one cp.reduce.async.bulk per tile row: a bulk operation is issued per
+// thread through uniform registers, the rows' issue loop and the extra barrier + async-proxy
+// fence cost 0.8 us of the 1 M-particle step more than the vector reductions do (no difference
+// at 32 M).  The ring gives the tile its shared memory: 2-4 stages, chosen by the launcher.
 // Counts are integers, so the image is bit-identical whatever the placement.
 //
 // Fast path (a.xy_only): when the plan is one merged stage followed by the terminal screen and
@@ -78,7 +82,7 @@ __host__ __device__ inline PipeSmemLayout pipe_layout(int stages, int rec_floats
 }
 
 // CTA-private image tile (bin coordinates): [x0, x0+w) x [y0, y0+h), one u32 counter per bin,
-// row-major by iy; x0 and w are multiples of 4 (16-byte rows for the bulk reduce).
+// row-major by iy; x0 and w are multiples of 4 (16-byte quads for the vector reduction).
 struct HistWindow {
   int x0, y0, w, h;
 };
@@ -102,12 +106,6 @@ __device__ __forceinline__ unsigned vmin_u16x2(unsigned a, unsigned b) {
 }
 __device__ __forceinline__ void reds_add_u32(uint32_t smem_addr, uint32_t v) {
   asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(smem_addr), "r"(v) : "memory");
-}
-__device__ __forceinline__ void bulk_reduce_add_f32(float* dst_gmem, const float* src_smem,
-                                                    uint32_t bytes) {
-  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst_gmem),
-               "r"(smem_u32(src_smem)), "r"(bytes)
-               : "memory");
 }
 
 #ifdef LYNX_EXPERIMENTS
@@ -531,26 +529,24 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
     if constexpr (TILE) {
       const HistWindow hw = s_win;
       if (use_win && win_set && hw.w > 0) {
-        // flush: u32 counts -> fp32 in place, then one bulk reduce-add per tile row into the
-        // image (row iy of the tile is image row H - 1 - iy: flipud(hist.T), screen.py:206)
+        // flush: every thread converts its quads of u32 counts and adds the non-empty ones
+        // straight into the image with ONE 16-byte vector reduction each (row iy of the tile is
+        // image row H - 1 - iy: flipud(hist.T), screen.py:206; x0 and w are multiples of 4 and
+        // the image rows 16-byte aligned, so a quad never straddles a row)
         consumers_sync();
-        float* f = reinterpret_cast<float*>(win);
-        const int n4 = (hw.w * hw.h) >> 2;  // w is a multiple of 4
-        uint4* w4 = reinterpret_cast<uint4*>(win);
+        const int w4n = hw.w >> 2, n4 = w4n * hw.h;
+        const uint4* w4 = reinterpret_cast<const uint4*>(win);
         for (int i = cid; i < n4; i += kConsumers) {
           const uint4 c = w4[i];
-          reinterpret_cast<float4*>(f)[i] = make_float4((float)c.x, (float)c.y, (float)c.z, (float)c.w);
+          if ((c.x | c.y | c.z | c.w) != 0u) {
+            const int r = i / w4n, q = i - r * w4n;
+            float* dst = img_b + (int64_t)(a.H - 1 - (hw.y0 + r)) * a.W + hw.x0 + 4 * q;
+            asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst),
+                         "f"((float)c.x), "f"((float)c.y), "f"((float)c.z), "f"((float)c.w)
+                         : "memory");
+          }
         }
-        fence_proxy_async();
-        consumers_sync();
         K2_STAMP(7);
-        // one elected lane per warp issues its rows: a bulk operation is issued per THREAD, and
-        // 32 lanes of a warp doing so serialise (8 % of the 1 M-particle kernel's instructions)
-        if (lane == 0)
-          for (int r = cw; r < hw.h; r += kConsumerWarps)
-            bulk_reduce_add_f32(img_b + (int64_t)(a.H - 1 - (hw.y0 + r)) * a.W + hw.x0, f + r * hw.w,
-                                (uint32_t)hw.w * 4u);
-        bulk_commit();
       }
     }
     K2_STAMP(8);
@@ -575,10 +571,6 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
       consumers_sync();
       if (cid < 4 && s_bb[1] > 0) atomicMax(a.bbox + cid, s_bb[cid]);
     }
-    // the tile's shared memory has been read by the bulk reduces (no-op without a flush); the
-    // additions themselves complete with the grid, which is what a dependent launch waits for
-    K2_STAMP(9);
-    if constexpr (TILE) bulk_wait_read<0>();
     K2_STAMP(10);
     // Let a programmatically-serialized follower (multi-GPU exchange kernel) start launching
     // once the consumers of every CTA are through their tiles.  The first thread of a CTA to
@@ -678,7 +670,7 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
   if (ctas_per_row * a.B > 0x7fffffffLL) return 1;
 
   // Histogram tile (see the head of this file): the image rows must be 16-byte aligned for the
-  // bulk reduce.  Its size follows the particles a CTA will see -- flushing costs time per
+  // vector reductions.  Its size follows the particles a CTA will see -- flushing costs time per
   // tile byte, the atomics it saves come per particle -- and the ring shrinks to make room.
   int stages = 4;
   uint32_t win_words = 0;

@@ -30,8 +30,8 @@ else:
 buf = (C.c_uint64 * 16)()
 fn(buf, cta)
 names = ["entry", "prologue done", "K1 complete (griddep wait)", "records in smem", "tile 1 landed",
-         "tile 1 done", "tile loop done", "window converted", "bulk reduces issued", "bbox done",
-         "bulk read done", "tile 1: bins known, placement starts", "tile 1: warp statistics exchanged",
+         "tile 1 done", "tile loop done", "tile flushed (vector reductions issued)", "(same)", "(unused)",
+         "bounding box merged", "tile 1: bins known, placement starts", "tile 1: warp statistics exchanged",
          "tile 1: window placed"]
 rows = []
 for i in range(60):
