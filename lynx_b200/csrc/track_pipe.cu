@@ -677,7 +677,11 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
   const uint32_t fixed = pipe_layout(0, a.rec_floats, a.n_plan, a.n_snap, 0).total;
   if (fixed + 2u * kStageFloats * 4u > cap) return 1;
   if (hist && !(a.W & 3) && !((uintptr_t)a.img & 15) && (((int64_t)a.W * a.H) & 3) == 0) {
-    int px_per_particle = 1, min_stages = 2;  // swept at 1 M particles: 1-2 best (profiles/r2j_sweeps.txt)
+    // words of tile per particle of the CTA: with the per-row bulk-reduce flush 1-2 was best at
+    // 1 M particles (27.6 us against 29.6 at 3 and 31.7 at 6); with the vector-reduction flush,
+    // which skips empty quads, 1 / 2 / 4 are within noise at 1, 2, 4 and 8 M particles
+    // (profiles/r2j_k2_timeline.txt)
+    int px_per_particle = 1, min_stages = 2;
 #ifdef LYNX_EXPERIMENTS
     int64_t max_words = 1 << 30;
     px_per_particle = env_int("LYNX_TILE_PXPP", px_per_particle);
