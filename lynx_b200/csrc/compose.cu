@@ -61,23 +61,27 @@ compose_kernel(ComposeArgs a, int n_cols, int S, const __grid_constant__ Program
   if (a.hist_out && blockIdx.x == 0 && threadIdx.x == 0) {  // debug stamp (exchange trace)
 #ifdef LYNX_EXPERIMENTS
     reinterpret_cast<unsigned long long*>(a.hist_out)[11] = 0ull;
+    reinterpret_cast<unsigned long long*>(a.hist_out)[10] = 0ull;
 #endif
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     reinterpret_cast<unsigned long long*>(a.hist_out)[8] = t;  // K1 block 0 starts
   }
-  // the FIRST block validates the screen's edge tables and writes the bin-lookup geometry (it
-  // and the compose blocks are the long poles of the launch; the zeroing blocks come last)
-  const int hist_blocks = a.hist_out ? 1 : 0;
-  if (hist_blocks && blockIdx.x == 0) {
+  // the FIRST TWO blocks validate the screen's edge tables (x, y) and write the bin-lookup
+  // geometry (they and the compose blocks are the long poles of the launch; the zeroing blocks
+  // come last)
+  const int hist_blocks = a.hist_out ? 2 : 0;
+  if ((int)blockIdx.x < hist_blocks) {
     HistAxis* h = reinterpret_cast<HistAxis*>(a.hist_out);
-    if (a.bbox_clear && threadIdx.x < 4) a.bbox_clear[threadIdx.x] = 0;  // this call's cell
-    hist_axes_setup(a.hist_ex, a.hist_W, a.hist_ey, a.hist_H, h, threadIdx.x, kComposeTPB, cs_smem);
+    const bool y = blockIdx.x == 1;
+    if (!y && a.bbox_clear && threadIdx.x < 4) a.bbox_clear[threadIdx.x] = 0;  // this call's cell
+    hist_axis_setup_staged(y ? a.hist_ey : a.hist_ex, y ? a.hist_H : a.hist_W, h + (y ? 1 : 0),
+                           threadIdx.x, kComposeTPB, cs_smem, y ? nullptr : a.hist_out);
 #ifdef LYNX_EXPERIMENTS
     if (threadIdx.x == 0) {
       unsigned long long t;
       asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-      reinterpret_cast<unsigned long long*>(a.hist_out)[10] = t;  // histogram block done
+      atomicMax(reinterpret_cast<unsigned long long*>(a.hist_out) + 10, t);  // histogram blocks done
     }
 #endif
     return;
@@ -452,9 +456,9 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
     if (n_cols > 0) S = (int)std::min<size_t>(kComposeTPB, (budget - ops_bytes) / (4 * (size_t)n_cols));
     S = (int)std::min<int64_t>(S, std::max<int64_t>(B, 1));
   }
-  // the histogram block stages the edge tables in the same dynamic region (2 x 16 KB)
+  // a histogram block stages its edge table in the same dynamic region (16 KB)
   const size_t smem = std::max<size_t>(staged ? ops_bytes + (size_t)n_cols * S * 4 : 0,
-                                       hist_out ? 2 * kHistChunk * sizeof(float) : 0);
+                                       hist_out ? kHistChunk * sizeof(float) : 0);
   unsigned blocks = (unsigned)((B + S - 1) / S);
   if (zero_rect)
     blocks += (unsigned)p->sm_count;  // the rectangle's size is only known on the device
@@ -464,11 +468,11 @@ int compose_launch(const lynx_program_t* p, const float* d_params, int64_t B,
     // keeps that SM's store path busy and holds their loads back until it is done (both sat
     // 2.5 us at their first loads, tools/k2_timeline.py) -- and they are the launch's long poles.
     int64_t zb = std::min<int64_t>(zero_blocks_per_sm * p->sm_count, (a.zero_vec4 + kComposeTPB - 1) / kComposeTPB);
-    const int64_t others = (int64_t)blocks + (hist_out ? 1 : 0);
+    const int64_t others = (int64_t)blocks + (hist_out ? 2 : 0);
     if (others < p->sm_count) zb = std::min<int64_t>(zb, p->sm_count - others);
     blocks += (unsigned)zb;
   }
-  if (hist_out) blocks += 1;
+  if (hist_out) blocks += 2;
   {
     ProfileScope ps(0, st);
     const bool light = (p->op_mask & ~kOpsLight) == 0;

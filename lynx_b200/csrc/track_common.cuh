@@ -235,13 +235,14 @@ __device__ __forceinline__ void hist_axis_setup(const float* __restrict__ e, int
   __syncthreads();
 }
 
-// Both axes at once for K1's histogram block.  The tables are staged in shared memory by
-// cp.async -- every element in flight at once, ONE DRAM round trip per 4096-entry chunk pair --
-// where hist_axis_setup's loop paid one cold miss per iteration (20 per axis on the 2448 x 2040
-// screen; the block was K1's critical path, tools/k2_timeline.py).  Same arithmetic, hence the
-// same margins, as two calls of hist_axis_setup: the deviation is measured in fp64 -- an fp32
-// measurement needs ~0.002 bins of extra margin, which doubles the near-edge lookups of the
-// particle kernel and cost it 5 % at 32 M particles.  Contains __syncthreads.
+// One axis by one block of K1 (two histogram blocks per launch, x and y side by side).  The
+// table is staged in shared memory by cp.async -- every element in flight at once, ONE DRAM
+// round trip per 4096-entry chunk -- where hist_axis_setup's loop paid one cold miss per
+// iteration (20 per axis on the 2448 x 2040 screen; the block was K1's critical path,
+// tools/k2_timeline.py).  Same arithmetic, hence the same margin, as hist_axis_setup: the
+// deviation is measured in fp64 -- an fp32 measurement needs ~0.002 bins of extra margin, which
+// doubles the near-edge lookups of the particle kernel and cost it 5 % at 32 M particles.
+// Contains __syncthreads.
 constexpr int kHistChunk = 4096;
 #ifdef LYNX_EXPERIMENTS
 #define LYNX_TSTAMP(ptr, i)                                             \
@@ -255,68 +256,50 @@ constexpr int kHistChunk = 4096;
 #else
 #define LYNX_TSTAMP(ptr, i) do {} while (0)
 #endif
-__device__ __forceinline__ void hist_axes_setup(const float* __restrict__ ex, int W,
-                                                const float* __restrict__ ey, int H, HistAxis* h,
-                                                int tid, int nthreads, float* scratch) {
-  float (*s_e)[kHistChunk] = reinterpret_cast<float (*)[kHistChunk]>(scratch);  // [2][kHistChunk]
-  __shared__ unsigned int s_dev[2];
-  if (tid < 2) s_dev[tid] = 0u;
-  const float* e[2] = {ex, ey};
-  const int n[2] = {W, H};
-  // the end points, in flight together with the first chunks
-  const float f0[2] = {__ldg(ex), __ldg(ey)}, fn[2] = {__ldg(ex + W), __ldg(ey + H)};
-  float dev[2] = {0.f, 0.f};
-  double e0[2], step[2], inv_step[2];
-  const int chunks = (max(W, H) + kHistChunk) / kHistChunk;  // covers n + 1 entries
+__device__ __forceinline__ void hist_axis_setup_staged(const float* __restrict__ e, int n,
+                                                       HistAxis* h, int tid, int nthreads,
+                                                       float* s_e /* [kHistChunk] */, void* stamps) {
+  __shared__ unsigned int s_dev;
+  if (tid == 0) s_dev = 0u;
+  const float f0 = __ldg(e), fn = __ldg(e + n);  // in flight together with the first chunk
+  float dev = 0.f;
+  double e0 = 0.0, step = 0.0, inv_step = 0.0;
+  const int chunks = (n + kHistChunk) / kHistChunk;  // covers n + 1 entries
   for (int c = 0; c < chunks; ++c) {
     const int base = c * kHistChunk;
-#pragma unroll
-    for (int x = 0; x < 2; ++x)
-      for (int i = tid; i < kHistChunk && base + i <= n[x]; i += nthreads)
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(
-                         (uint32_t)__cvta_generic_to_shared(&s_e[x][i])),
-                     "l"(e[x] + base + i)
-                     : "memory");
-    LYNX_TSTAMP(h, 12);
+    for (int i = tid; i < kHistChunk && base + i <= n; i += nthreads)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(
+                       (uint32_t)__cvta_generic_to_shared(&s_e[i])),
+                   "l"(e + base + i)
+                   : "memory");
+    LYNX_TSTAMP(stamps, 12);
     asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
-    LYNX_TSTAMP(h, 13);
+    LYNX_TSTAMP(stamps, 13);
     if (c == 0) {
-#pragma unroll
-      for (int x = 0; x < 2; ++x) {
-        e0[x] = (double)f0[x];
-        step[x] = ((double)fn[x] - e0[x]) / n[x];
-        inv_step[x] = 1.0 / step[x];
-      }
+      e0 = (double)f0;
+      step = ((double)fn - e0) / n;
+      inv_step = 1.0 / step;
     }
-#pragma unroll
-    for (int x = 0; x < 2; ++x)
-      for (int i = tid; i < kHistChunk && base + i <= n[x]; i += nthreads) {
-        const float d = (float)(fabs((double)s_e[x][i] - (e0[x] + step[x] * (base + i))) * inv_step[x]);
-        dev[x] = (d <= 1e30f) ? fmaxf(dev[x], d) : 2.f;  // NaN / inf: never trust the fast path
-      }
-    __syncthreads();  // the chunk buffers are refilled next
+    for (int i = tid; i < kHistChunk && base + i <= n; i += nthreads) {
+      const float d = (float)(fabs((double)s_e[i] - (e0 + step * (base + i))) * inv_step);
+      dev = (d <= 1e30f) ? fmaxf(dev, d) : 2.f;  // NaN / inf: never trust the fast path
+    }
+    __syncthreads();  // the chunk buffer is refilled next
   }
-  LYNX_TSTAMP(h, 14);
-  atomicMax(&s_dev[0], __float_as_uint(dev[0]));
-  atomicMax(&s_dev[1], __float_as_uint(dev[1]));
+  LYNX_TSTAMP(stamps, 14);
+  atomicMax(&s_dev, __float_as_uint(dev));
   __syncthreads();
-  // (selects, not array indexing by the thread index: that would put the arrays in local
-  // memory, whose first touch is a page-table and DRAM miss on this block's critical path)
-  if (tid < 2) {
-    const bool y = tid == 1;
-    const float fe0 = y ? f0[1] : f0[0], fen = y ? fn[1] : fn[0];
-    const int nn = y ? H : W;
-    const float d = __uint_as_float(y ? s_dev[1] : s_dev[0]);
+  if (tid == 0) {
+    const float d = __uint_as_float(s_dev);
     HistAxis r;
-    r.e0 = fe0;
-    r.en = fen;
-    r.inv = (float)nn / (fen - fe0);
-    const float m = 1.25f * d + (float)nn * (1.f / 2097152.f) + (1.f / 1048576.f);
-    const bool ok = d < 0.2f && m < 0.25f && (y ? step[1] : step[0]) > 0.0 &&
-                    fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
+    r.e0 = f0;
+    r.en = fn;
+    r.inv = (float)n / (fn - f0);
+    const float m = 1.25f * d + (float)n * (1.f / 2097152.f) + (1.f / 1048576.f);
+    const bool ok = d < 0.2f && m < 0.25f && step > 0.0 && fmaxf(fabsf(f0), fabsf(fn)) <= fn - f0;
     r.margin = ok ? m : 1.f;  // margin >= 0.5 means: irregular table, always searched
-    h[tid] = r;
+    *h = r;
   }
 }
 

@@ -43,7 +43,7 @@ for i in range(60):
     t = np.array(list(buf), dtype=np.float64)
     hist = w.ws[-256:].view(torch.int64).cpu().numpy().astype(np.float64)
     if i >= 10:
-        rows.append(np.concatenate([t[:14] - t[0], hist[8:12] - t[0]]))
+        rows.append(np.concatenate([t[:14] - t[0], hist[8:18] - t[0]]))
 m = np.mean(rows, axis=0) / 1e3
-for n, v in zip(names + ["K1 block 0 start", "K1 walker done", "K1 histogram block done", "K1 last zeroing block done"], m):
+for n, v in zip(names + ["K1 block 0 start", "K1 walker done", "K1 histogram block done", "K1 last zeroing block done", "K1 hist: copies issued", "K1 hist: tables in smem", "K1 hist: deviations done", "K1 walker: parameters in smem", "K1 walker: walk done", "K1 walker block entry"], m):
     print(f"{n:32s} {v:8.2f} us")
