@@ -371,3 +371,48 @@ def test_light_map_kernels_equal_the_dense_kernels(B):
     beam = _gpu_beam(F.gaussian_beam_soa(n, seed=5), F.ASTRA_ENERGY)
     pa, pd = light.track(beam), dense.track(beam)
     assert pa.soa.shape[0] == B and torch.equal(pa.soa[..., :n], pd.soa[..., :n])
+
+
+# ------------------------------------------------------------------ sizes at the edges
+def test_more_than_65535_settings_and_tiny_beams():
+    """B = 70 001 settings (round 1's grids put the setting on gridDim.y: at most 65 535) of a
+    quadrupole line over ONE shared 130-particle beam, outgoing particles and a screen image per
+    setting: first, last and a middle setting must equal the same setting tracked alone, bit for
+    bit.  Then beams of 1, 2, 3 and 5 particles (ragged below one float4)."""
+    B, n = 70_001, 130
+    rng = np.random.default_rng(3)
+    k1 = rng.uniform(-20, 20, B).astype(np.float32)
+    soa = F.gaussian_beam_soa(n, seed=6)
+
+    def line(k, screen):
+        els = [lx.Drift(torch.tensor([0.3])), lx.Quadrupole(torch.tensor([0.12]), torch.from_numpy(k)),
+               lx.Drift(torch.tensor([0.5]))]
+        if screen:
+            els.append(lx.Screen(resolution=torch.tensor((64.0, 48.0)), pixel_size=torch.tensor((4e-5, 5e-5)),
+                                 is_active=True, name="S"))
+        return lx.Segment(els)
+
+    beam = _gpu_beam(soa, F.ASTRA_ENERGY)
+    out = line(k1, False).track(beam)
+    assert out.soa.shape[0] == B
+    seg = line(k1, True)
+    assert seg.track(beam) is lx.Beam.empty
+    img = seg.S.reading
+    assert tuple(img.shape) == (B, 48, 64)
+    for b in (0, 33_333, 65_535, 65_536, B - 1):
+        one = line(k1[b:b + 1], False).track(beam)
+        assert torch.equal(out.soa[b, :, :n], one.soa[0, :, :n]), b
+        s1 = line(k1[b:b + 1], True)
+        s1.track(beam)
+        assert torch.equal(img[b], s1.S.reading[0]), b
+    assert (img.sum(dim=(1, 2)) <= n).all() and img.sum().item() > 0.5 * n * B
+
+    for m in (1, 2, 3, 5):
+        small = _gpu_beam(soa[:, :m].copy(), F.ASTRA_ENERGY)
+        o = line(k1[:4], False).track(small)
+        _, t64 = _oracle_track([("drift", "a", {"length": 0.3}),
+                                ("quadrupole", "q", {"length": 0.12, "k1": 0.0}),
+                                ("drift", "b", {"length": 0.5})], soa[:, :m], F.ASTRA_ENERGY,
+                               torch.float64, (4,), {("q", "k1"): k1[:4]})
+        want = t64.particles[:, :, :6].permute(0, 2, 1).numpy()
+        np.testing.assert_allclose(o.soa[:, :, :m].cpu().numpy(), want, rtol=2e-5, atol=1e-9)
