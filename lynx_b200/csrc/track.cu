@@ -387,6 +387,7 @@ int lynx::track_fwd_impl(
   a.rec_floats = p->rec_floats;
   a.plan = p->d_plan;
   a.n_plan = (int)p->plan.size();
+  for (size_t i = 0; i < p->plan.size() && i < 8; ++i) a.plan_inline[i] = p->plan[i];
   a.n_snap = p->n_snap;
   a.final_centre = p->final_centre;
   a.bpm_sums = d_bpm_sums;

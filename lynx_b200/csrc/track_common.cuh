@@ -20,6 +20,7 @@ struct TrackArgs {
   const float* records;
   int rec_floats;
   const PlanItem* plan;
+  PlanItem plan_inline[8];  // the first plan items by value: short plans need no global load in the prologue
   int n_plan;
   int n_snap;
   int final_centre;

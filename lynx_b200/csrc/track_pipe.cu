@@ -188,7 +188,11 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
     for (int s = 0; s < kMaxStages; ++s) s_freed[s] = 0u;
   }
   // ---- everyone: plan, cleared tile (independent of K1) ...
-  for (int i = tid; i < a.n_plan; i += kPipeThreads) plan[i] = a.plan[i];
+  if (a.n_plan <= 8) {  // from the kernel's parameter space: no cold load
+    if (tid < a.n_plan) plan[tid] = a.plan_inline[tid];
+  } else {
+    for (int i = tid; i < a.n_plan; i += kPipeThreads) plan[i] = a.plan[i];
+  }
   for (int i = tid; i < a.n_snap * 2; i += kPipeThreads) s_bpm[i] = 0.0;
   if (TILE) {
     uint4* w4 = reinterpret_cast<uint4*>(win);
