@@ -359,6 +359,9 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
           K2_STAMP(12);
           if (cid == 0) {
             float tc = 0.f, tx = 0.f, ty = 0.f, txx = 0.f, tyy = 0.f;
+            // not unrolled: with all 80 loads hoisted this once-per-CTA block set the whole
+            // kernel's register count (124; the tile loop itself needs ~80)
+#pragma unroll 1
             for (int w = 0; w < kConsumerWarps; ++w) {
               tc += s_wstat[w][0]; tx += s_wstat[w][1]; ty += s_wstat[w][2];
               txx += s_wstat[w][3]; tyy += s_wstat[w][4];
