@@ -733,7 +733,7 @@ def run_ours(args, rank, world, local_rank):
     alg = wl.algorithmic_bytes()
     ach = alg / (k2_ms * 1e-3) / 1e9 if k2_ms else None
     traffic, traffic_src = traffic_of("track_pipe_kernel", "ares_screen", args.particles)
-    roofline = {"bound": "hbm", "kernel": "track_pipe_kernel<0, false, true> (K2, screen variant)",
+    roofline = {"bound": "hbm", "kernel": "track_pipe_kernel<0, false, true, 24> (K2, screen variant)",
                 "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None,
                 # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel on this
                 # workload (ncu --set full), from the committed table profiles/traffic.json; the

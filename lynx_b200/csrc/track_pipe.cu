@@ -47,12 +47,12 @@
 
 namespace lynx {
 
-constexpr int kPipeTile = 2048;                    // particles per stage
-constexpr int kConsumerWarps = 16;
-constexpr int kConsumers = kConsumerWarps * 32;    // 512 threads x 4 particles = tile
-constexpr int kPipeThreadsOut = kConsumers + 64;   // + producer warp + storer warp
-__host__ __device__ constexpr int pipe_threads(bool has_out) { return has_out ? kPipeThreadsOut : kConsumers; }
-constexpr int kStageFloats = 6 * kPipeTile;
+// Consumer warps per CTA are a template parameter CW (each thread carries 4 particles, so a
+// pipeline tile is 128 particles per consumer warp).  The moment-free screen variant needs 80
+// registers per thread and runs 24 warps -- six per scheduler instead of four, for a kernel bound
+// by instruction issue latency; the moment-free outgoing-particles variant (90 -> 80 registers)
+// runs 20 + 2 role warps; the moment variants (96-120 registers) run 16.
+__host__ __device__ constexpr int pipe_threads(int cw, bool has_out) { return cw * 32 + (has_out ? 64 : 0); }
 constexpr int kMaxStages = 4;
 
 struct PipeSmemLayout {
@@ -60,10 +60,10 @@ struct PipeSmemLayout {
   uint32_t rec, plan, bpm, bars, win, total;
 };
 
-__host__ __device__ inline PipeSmemLayout pipe_layout(int stages, int rec_floats, int n_plan,
-                                                      int n_snap, uint32_t win_words) {
+__host__ __device__ inline PipeSmemLayout pipe_layout(int stages, int stage_floats, int rec_floats,
+                                                      int n_plan, int n_snap, uint32_t win_words) {
   PipeSmemLayout L;
-  uint32_t o = (uint32_t)(sizeof(float) * kStageFloats * stages);
+  uint32_t o = (uint32_t)(sizeof(float) * stage_floats * stages);
   L.rec = o;
   o += 4u * rec_floats;
   o = (o + 15u) & ~15u;
@@ -87,7 +87,8 @@ struct HistWindow {
   int x0, y0, w, h;
 };
 
-__device__ __forceinline__ void consumers_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory"); }
+template <int THREADS>
+__device__ __forceinline__ void consumers_sync_n() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); }
 
 // Histogram update as an explicit reduction (nvcc lowers a result-less atomicAdd to ATOMG
 // instead of REDG in kernels that also contain acquire / release code: -35 %, found in SASS).
@@ -125,13 +126,19 @@ __device__ int g_k2_trace_cta = 0;
 #endif
 
 // TILE: the screen variant with the shared-memory histogram tile (win_words > 0).
-template <int MOM, bool HAS_OUT, bool TILE>
-__global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(TrackArgs a, uint32_t win_words) {
+template <int MOM, bool HAS_OUT, bool TILE, int CW>
+__global__ void __launch_bounds__(pipe_threads(CW, HAS_OUT), 1)
+track_pipe_kernel(TrackArgs a, uint32_t win_words) {
   extern __shared__ __align__(128) unsigned char psm[];
-  constexpr int kPipeThreads = pipe_threads(HAS_OUT);
+  constexpr int kConsumerWarps = CW;
+  constexpr int kConsumers = kConsumerWarps * 32;
+  constexpr int kPipeTile = kConsumers * 4;     // particles per stage (capacity and plane stride)
+  constexpr int kStageFloats = 6 * kPipeTile;
+  constexpr int kPipeThreads = pipe_threads(kConsumerWarps, HAS_OUT);
+  auto consumers_sync = [] { consumers_sync_n<kConsumers>(); };
   constexpr int kRoleWarps = HAS_OUT ? 2 : 0;  // producer + storer
   const int STAGES = a.stages;
-  const PipeSmemLayout L = pipe_layout(STAGES, a.rec_floats, a.n_plan, a.n_snap, win_words);
+  const PipeSmemLayout L = pipe_layout(STAGES, kStageFloats, a.rec_floats, a.n_plan, a.n_snap, win_words);
   float* stages = reinterpret_cast<float*>(psm);
   float* rec = reinterpret_cast<float*>(psm + L.rec);
   PlanItem* plan = reinterpret_cast<PlanItem*>(psm + L.plan);
@@ -613,10 +620,10 @@ __global__ void __launch_bounds__(pipe_threads(HAS_OUT), 1) track_pipe_kernel(Tr
   }
 }
 
-template <int MOM, bool HAS_OUT, bool TILE>
+template <int MOM, bool HAS_OUT, bool TILE, int CW = 16>
 static int launch_pipe(const TrackArgs& a, unsigned grid, size_t smem, uint32_t win_words,
                        cudaStream_t st) {
-  auto k = track_pipe_kernel<MOM, HAS_OUT, TILE>;
+  auto k = track_pipe_kernel<MOM, HAS_OUT, TILE, CW>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096) !=
@@ -626,7 +633,7 @@ static int launch_pipe(const TrackArgs& a, unsigned grid, size_t smem, uint32_t 
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(pipe_threads(HAS_OUT));
+  cfg.blockDim = dim3(pipe_threads(CW, HAS_OUT));
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -658,8 +665,12 @@ static int env_int(const char* name, int dflt) {
 
 // Returns LYNX_OK after enqueueing, or 1 if this variant cannot take the problem (the
 // caller then uses the LDG kernel).
-int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_count,
-                      cudaStream_t st) {
+// cw consumer warps; returns -100 when more than 16 were asked for a screen without a histogram
+// tile (the wider screen kernel exists only as the tiled variant): the caller retries with 16.
+static int launch_track_pipe_cw(const TrackArgs& a, int moment_mode, bool has_out, int cw,
+                                int sm_count, cudaStream_t st) {
+  const int kPipeTile = cw * 128;
+  const uint32_t kStageFloats = 6u * (uint32_t)kPipeTile;
   const uint32_t cap = 227 * 1024 - 4096 - 1024;  // static shared memory takes the rest
   const bool hist = a.img != nullptr && !has_out;
   if (a.img && (a.W >= 32768 || a.H >= 32768)) return 1;  // bins travel as two 15-bit lanes
@@ -681,7 +692,7 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
   // tile byte, the atomics it saves come per particle -- and the ring shrinks to make room.
   int stages = 4;
   uint32_t win_words = 0;
-  const uint32_t fixed = pipe_layout(0, a.rec_floats, a.n_plan, a.n_snap, 0).total;
+  const uint32_t fixed = pipe_layout(0, 0, a.rec_floats, a.n_plan, a.n_snap, 0).total;
   if (fixed + 2u * kStageFloats * 4u > cap) return 1;
   if (hist && !(a.W & 3) && !((uintptr_t)a.img & 15) && (((int64_t)a.W * a.H) & 3) == 0) {
     // words of tile per particle of the CTA: with the per-row bulk-reduce flush 1-2 was best at
@@ -713,7 +724,8 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
     stages = 4;
     while (stages > 2 && fixed + (uint32_t)stages * kStageFloats * 4u > cap) --stages;
   }
-  const PipeSmemLayout L = pipe_layout(stages, a.rec_floats, a.n_plan, a.n_snap, win_words);
+  if (cw != 16 && !win_words && !has_out) return -100;
+  const PipeSmemLayout L = pipe_layout(stages, (int)kStageFloats, a.rec_floats, a.n_plan, a.n_snap, win_words);
   if (L.total > cap) return 1;
   TrackArgs at = a;
   at.tile = (int)tile;
@@ -722,19 +734,45 @@ int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_
   const unsigned grid = (unsigned)(ctas_per_row * a.B);
   if (win_words) {
     switch (moment_mode) {
-      case 0: return launch_pipe<0, false, true>(at, grid, L.total, win_words, st);
+      case 0:
+        if (cw == 24) return launch_pipe<0, false, true, 24>(at, grid, L.total, win_words, st);
+#ifdef LYNX_EXPERIMENTS
+        if (cw == 28) return launch_pipe<0, false, true, 28>(at, grid, L.total, win_words, st);
+#endif
+        return launch_pipe<0, false, true>(at, grid, L.total, win_words, st);
       case 1: return launch_pipe<1, false, true>(at, grid, L.total, win_words, st);
       default: return launch_pipe<2, false, true>(at, grid, L.total, win_words, st);
     }
   }
   switch (moment_mode * 2 + (has_out ? 1 : 0)) {
     case 0: return launch_pipe<0, false, false>(at, grid, L.total, 0, st);
-    case 1: return launch_pipe<0, true, false>(at, grid, L.total, 0, st);
+    case 1:
+      if (cw == 20) return launch_pipe<0, true, false, 20>(at, grid, L.total, 0, st);
+      return launch_pipe<0, true, false>(at, grid, L.total, 0, st);
     case 2: return launch_pipe<1, false, false>(at, grid, L.total, 0, st);
     case 3: return launch_pipe<1, true, false>(at, grid, L.total, 0, st);
     case 4: return launch_pipe<2, false, false>(at, grid, L.total, 0, st);
     default: return launch_pipe<2, true, false>(at, grid, L.total, 0, st);
   }
+}
+
+int launch_track_pipe(const TrackArgs& a, int moment_mode, bool has_out, int sm_count,
+                      cudaStream_t st) {
+  // Consumer warps, measured on B200 (profiles/r2j_k2_timeline.txt): the moment-free screen
+  // variant 16 / 20 / 24 / 28 / 32 warps -> cfg4 screen 143.4 / 137.6 / 131.9 / 129.7 / 135.6 us
+  // and 32 M particles 175 / 171.5 / 169 / 167.7 / 265 us, but the 1 M step 25.6 us at 24 and
+  // 27.5 at 28; the moment-free outgoing-particles variant 16 / 20 / 22 -> 32 M particles
+  // 254 / 244.5 / 248.6 us.
+  int cw = 16;
+  if (moment_mode == 0) cw = has_out ? 20 : (a.img != nullptr ? 24 : 16);
+#ifdef LYNX_EXPERIMENTS
+  if (cw == 24) cw = env_int("LYNX_K2_CW", cw);
+  if (cw == 20) cw = env_int("LYNX_K2_CW_OUT", cw);
+#endif
+  int rc = launch_track_pipe_cw(a, moment_mode, has_out, cw, sm_count, st);
+  if ((rc == -100 || rc == 1) && cw != 16)  // no room for the wider tile: the 16-warp kernel
+    rc = launch_track_pipe_cw(a, moment_mode, has_out, 16, sm_count, st);
+  return rc;
 }
 
 }  // namespace lynx
