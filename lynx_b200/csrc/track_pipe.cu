@@ -87,6 +87,11 @@ struct HistWindow {
   int x0, y0, w, h;
 };
 
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 template <int THREADS>
 __device__ __forceinline__ void consumers_sync_n() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); }
 
@@ -148,7 +153,8 @@ track_pipe_kernel(TrackArgs a, uint32_t win_words) {
   uint64_t* done = empty + kMaxStages;
   uint32_t* win = reinterpret_cast<uint32_t*>(psm + L.win);
   __shared__ double s_red[kConsumerWarps][28];
-  __shared__ float s_wstat[kConsumerWarps][5];
+  __shared__ int s_stat[3];                   // tile placement: count, sum dx, sum dy of the first tile
+  __shared__ unsigned long long s_stat2[2];   // ... sum dx^2, sum dy^2
   __shared__ float s_chk[kConsumerWarps];  // sink of the load-completion dependency (see below)
   __shared__ int s_bb[4];                  // CTA bounding box of the touched bins
   if (threadIdx.x < 4) s_bb[threadIdx.x] = 0;  // ordered before its use by the CTA barriers below
@@ -192,6 +198,8 @@ track_pipe_kernel(TrackArgs a, uint32_t win_words) {
     int it = 0;
     for (int64_t t = cta; t < n_tiles && it < STAGES; t += n_cta, ++it) issue_tile(it, t);
     s_win = HistWindow{0, 0, 0, 0};
+    s_stat[0] = s_stat[1] = s_stat[2] = 0;
+    s_stat2[0] = s_stat2[1] = 0ull;
     for (int s = 0; s < kMaxStages; ++s) s_freed[s] = 0u;
   }
   // ---- everyone: plan, cleared tile (independent of K1) ...
@@ -341,53 +349,64 @@ track_pipe_kernel(TrackArgs a, uint32_t win_words) {
       if constexpr (TILE) {
         if (use_win && !win_set) {  // warp-uniform: the CTA's first pipeline tile only
           K2_STAMP(11);
-          // place the tile on the beam: mean +- k sigma of this CTA's first pipeline tile
-          float c = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, syy = 0.f;
+          // place the tile on the beam: mean +- k sigma of this CTA's first pipeline tile.
+          // Exact integer sums of the bin offsets (|dx|, |dy| < 2^15): warp reductions by
+          // redux.sync (the squares as two 16-bit halves, 4 x 2^28 per thread does not survive
+          // a 32-lane sum in 32 bits), then one shared-memory atomic per warp and statistic.
+          int c = 0, sx = 0, sy = 0;
+          unsigned int sxx = 0u, syy = 0u;
 #pragma unroll
           for (int l = 0; l < 4; ++l)
             if (pk[l] >= 0) {
-              const float dx = (float)((pk[l] & 0xffff) - (a.W >> 1)), dy = (float)((pk[l] >> 16) - (a.H >> 1));
-              c += 1.f;
+              const int dx = (pk[l] & 0xffff) - (a.W >> 1), dy = (pk[l] >> 16) - (a.H >> 1);
+              c += 1;
               sx += dx;
               sy += dy;
-              sxx = fmaf(dx, dx, sxx);
-              syy = fmaf(dy, dy, syy);
+              sxx += (unsigned)(dx * dx);
+              syy += (unsigned)(dy * dy);
             }
-          c = warp_sum(c);
-          sx = warp_sum(sx);
-          sy = warp_sum(sy);
-          sxx = warp_sum(sxx);
-          syy = warp_sum(syy);
+          c = __reduce_add_sync(0xffffffffu, c);
+          sx = __reduce_add_sync(0xffffffffu, sx);
+          sy = __reduce_add_sync(0xffffffffu, sy);
+          const unsigned long long qx =
+              ((unsigned long long)__reduce_add_sync(0xffffffffu, sxx >> 16) << 16) +
+              __reduce_add_sync(0xffffffffu, sxx & 0xffffu);
+          const unsigned long long qy =
+              ((unsigned long long)__reduce_add_sync(0xffffffffu, syy >> 16) << 16) +
+              __reduce_add_sync(0xffffffffu, syy & 0xffffu);
           if (lane == 0) {
-            float* d = s_wstat[cw];
-            d[0] = c; d[1] = sx; d[2] = sy; d[3] = sxx; d[4] = syy;
+            atomicAdd(&s_stat[0], c);
+            atomicAdd(&s_stat[1], sx);
+            atomicAdd(&s_stat[2], sy);
+            atomicAdd(&s_stat2[0], qx);
+            atomicAdd(&s_stat2[1], qy);
           }
           consumers_sync();
           K2_STAMP(12);
           if (cid == 0) {
-            float tc = 0.f, tx = 0.f, ty = 0.f, txx = 0.f, tyy = 0.f;
-            // not unrolled: with all 80 loads hoisted this once-per-CTA block set the whole
-            // kernel's register count (124; the tile loop itself needs ~80)
-#pragma unroll 1
-            for (int w = 0; w < kConsumerWarps; ++w) {
-              tc += s_wstat[w][0]; tx += s_wstat[w][1]; ty += s_wstat[w][2];
-              txx += s_wstat[w][3]; tyy += s_wstat[w][4];
-            }
+            // (approximate reciprocals and roots: the placement only has to be sensible, and one
+            // thread decides it for the CTA)
+            const long long ci = s_stat[0], sxi = s_stat[1], syi = s_stat[2];
+            const float tc = (float)(int)ci;
+            const float itc = __fdividef(1.f, tc);
+            // n^2 var = n sum d^2 - (sum d)^2, exact in 64 bits (n <= 2^12, sum d^2 < 2^40)
+            const float vx = (float)(ci * (long long)s_stat2[0] - sxi * sxi) * (itc * itc);
+            const float vy = (float)(ci * (long long)s_stat2[1] - syi * syi) * (itc * itc);
             HistWindow nw{0, 0, 0, 0};
             const float cap = (float)win_words;
-            if (tc >= 32.f) {
-              const float mxb = tx / tc, myb = ty / tc;
-              const float sgx = fmaxf(sqrtf(fmaxf(txx / tc - mxb * mxb, 0.f)), 0.5f);
-              const float sgy = fmaxf(sqrtf(fmaxf(tyy / tc - myb * myb, 0.f)), 0.5f);
-              const float k = fminf(sqrtf(cap / (4.f * sgx * sgy)), 5.f);
+            if (ci >= 32) {
+              const float mxb = (float)(int)sxi * itc, myb = (float)(int)syi * itc;
+              const float sgx = fmaxf(sqrt_approx(fmaxf(vx, 0.f)), 0.5f);
+              const float sgy = fmaxf(sqrt_approx(fmaxf(vy, 0.f)), 0.5f);
+              const float k = fminf(sqrt_approx(__fdividef(cap, 4.f * sgx * sgy)), 5.f);
               int w2 = min((2 * (int)ceilf(k * sgx) + 5) & ~3, a.W);
               int h2 = min(2 * (int)ceilf(k * sgy) + 2, a.H);
-              if ((float)w2 * (float)h2 > cap) h2 = (int)(cap / (float)w2);
+              if ((unsigned)(w2 * h2) > win_words) h2 = (int)(win_words / (unsigned)w2);  // exact: the tile's size
               if (h2 > 0 && w2 > 0) {
                 nw.w = w2;
                 nw.h = h2;
-                nw.x0 = min(max((int)lrintf(mxb) + (a.W >> 1) - (w2 >> 1), 0), a.W - w2) & ~3;
-                nw.y0 = min(max((int)lrintf(myb) + (a.H >> 1) - (h2 >> 1), 0), a.H - h2);
+                nw.x0 = min(max(__float2int_rn(mxb) + (a.W >> 1) - (w2 >> 1), 0), a.W - w2) & ~3;
+                nw.y0 = min(max(__float2int_rn(myb) + (a.H >> 1) - (h2 >> 1), 0), a.H - h2);
               }
             }
             s_win = nw;
