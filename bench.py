@@ -742,9 +742,9 @@ def run_ours(args, rank, world, local_rank):
                 "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs, burst copy)",
                 "algorithmic_bytes_per_launch": alg, "kernel_ms": k2_ms,
                 "frac_of_8000": (ach / 8000.0) if ach else None,
-                "regime": "latency / issue-bound at 1 M particles: 4 pipeline tiles per CTA, "
-                          "~500 warp instructions per 128 particles at 4 warps per scheduler "
-                          "(profiles/r2e_k2_screen32m_lines.txt); 44 MB are 6.8 us at the HBM "
+                "regime": "latency / issue-bound at 1 M particles: 3 pipeline tiles per CTA, "
+                          "~540 warp instructions per 128 particles at 6 warps per scheduler "
+                          "(profiles/r2u_screen32m_lines.txt); 44 MB are 6.8 us at the HBM "
                           "peak.  The same kernel at 32 M particles: extras.at_scale_screen_24B"}
     line = {
         "metric": "particle_element_updates_per_s", "value": value,
