@@ -13,7 +13,7 @@ import torch
 import bench
 from lynx_b200 import _lib as L
 
-mode = sys.argv[1] if len(sys.argv) > 1 else "screen1m"
+mode = sys.argv[1] if len(sys.argv) > 1 else "screen1m"  # screen1m | screen1m_persistent | cfg4 | screen32m
 cta = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 dev = torch.device("cuda:0")
 torch.cuda.set_device(0)
@@ -21,7 +21,7 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 lib = L.lib()
 fn = lib.lynx_dbg_k2_trace
 fn.argtypes = [C.POINTER(C.c_uint64), C.c_int]
-if mode == "screen1m":
+if mode.startswith("screen1m"):
     w = bench.ParticleWorkload(1_000_000, dev, 1002)
 elif mode == "cfg4":
     w = bench.ParticleWorkload(12_500_000, dev, 1004, lattice="cfg4")
@@ -37,7 +37,10 @@ rows = []
 for i in range(60):
     if not os.environ.get('LYNX_NOFLUSH'):
         flush.zero_()
-    w.step()
+    if mode.endswith("_persistent"):
+        w.persistent_step()
+    else:
+        w.step()
     torch.cuda.synchronize()
     fn(buf, cta)
     t = np.array(list(buf), dtype=np.float64)
