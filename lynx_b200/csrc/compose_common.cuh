@@ -23,6 +23,17 @@ struct RecordSinkT {
     for (int i = 0; i < 6; ++i)
 #pragma unroll
       for (int j = 0; j < 7; ++j) d[i * 7 + j] = M.m[i][j];
+    // slot 42 of the 44-float record: 1 if the map is three 2x2 blocks on (x, xp), (y, yp),
+    // (s, p) with a zero kick column -- drifts, untilted and aligned quadrupoles, a cavity's own
+    // map -- which the particle kernels apply with 24 instead of 42 operations
+    // (track_common.cuh apply_block2, the same bits).  -0 counts as zero: 0 * v + acc == acc.
+    bool blocks = true;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = 0; j < 7; ++j)
+        if ((i >> 1) != (j >> 1) && map_live<LT>(i, j)) blocks = blocks && (M.m[i][j] == 0.f);
+    d[kMapFloats] = blocks ? 1.f : 0.f;
     if (WITH_MAPS && maps_out) {
       float* o = maps_out + idx * 49;
 #pragma unroll

@@ -101,12 +101,15 @@ __device__ __forceinline__ void apply_affine_xy(const float* __restrict__ m, con
   }
 }
 
-// The linear map of an active cavity (cavity.py:248-325, maps.cuh cavity_setting) is three
-// 2x2 blocks on (x, xp), (y, yp), (s, p) with a zero kick column: 12 of the 42 entries.  Same
-// order of operations as apply_affine on the non-zero entries, so the result is bit-identical
-// for finite coordinates (fma(0, v, acc) == acc).  A dense product also turns EVERY coordinate
-// of a particle into NaN as soon as one of them is not finite (0 * inf, 0 * NaN); the term z
-// (0 for a finite particle, NaN otherwise) reproduces that.  24 instead of 42 operations.
+// A map that is three 2x2 blocks on (x, xp), (y, yp), (s, p) with a zero kick column: 12 of the
+// 42 entries -- the linear map of an active cavity (cavity.py:248-325, maps.cuh cavity_setting)
+// and every stage K1 flags (compose_common.cuh write_map).  Same order of operations as
+// apply_affine on the non-zero entries, so the result is bit-identical for finite coordinates
+// (fma(0, v, acc) == acc).  A dense product also multiplies every coordinate OUTSIDE a row's
+// block by zero: one that is not finite turns the row into NaN (0 * inf, 0 * NaN), while inside
+// its own block an infinity stays an infinity.  The terms t (0 for a finite pair, NaN otherwise)
+// reproduce exactly that: row block b gets the t of the other two blocks.  27 instead of 42
+// operations.
 template <int NP>
 __device__ __forceinline__ void apply_block2(const float* __restrict__ m, float (&v)[6][NP]) {
   float a[3][4];
@@ -119,11 +122,12 @@ __device__ __forceinline__ void apply_block2(const float* __restrict__ m, float 
   }
 #pragma unroll
   for (int j = 0; j < NP; ++j) {
-    float z = 0.f;
+    float t[3];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) z = fmaf(v[k][j], 0.f, z);
+    for (int b = 0; b < 3; ++b) t[b] = fmaf(v[2 * b + 1][j], 0.f, fmaf(v[2 * b][j], 0.f, 0.f));
 #pragma unroll
     for (int b = 0; b < 3; ++b) {
+      const float z = t[(b + 1) % 3] + t[(b + 2) % 3];
       const float u = v[2 * b][j], w = v[2 * b + 1][j];
       v[2 * b][j] = fmaf(a[b][1], w, fmaf(a[b][0], u, 0.f)) + z;
       v[2 * b + 1][j] = fmaf(a[b][3], w, fmaf(a[b][2], u, 0.f)) + z;

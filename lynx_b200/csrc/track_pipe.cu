@@ -498,7 +498,10 @@ track_pipe_kernel(TrackArgs a, uint32_t win_words) {
               break;
             }
           }
-          apply_affine(rec + p.a, v);
+          if (rec[p.a + kMapFloats] != 0.f)  // K1 found three 2x2 blocks (compose_common.cuh write_map)
+            apply_block2(rec + p.a, v);
+          else
+            apply_affine(rec + p.a, v);
         } else if (p.kind == P_CAVITY) {
           float s0[4], q0[4];
 #pragma unroll

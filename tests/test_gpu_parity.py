@@ -799,3 +799,61 @@ def test_non_finite_particles_propagate_like_a_dense_product():
     spec2 = F.cavity_dipole_line(screen_active=False)[3:5]
     got2 = F.build_segment(spec2).track(_gpu_beam(soa, F.CFG4_ENERGY)).soa[0, :, :n].cpu().numpy()
     assert np.isnan(got2[:, [17, 123]]).all() and np.isfinite(got2[:, ok]).all()
+
+
+@pytest.mark.gpu
+def test_block_structured_stage_maps_match_the_dense_product():
+    """K1 flags a stage map that is three 2x2 blocks with a zero kick column (drifts, untilted
+    aligned quadrupoles: compose_common.cuh write_map) and K2 applies it with apply_block2.  The
+    result must be what the dense product gives: within tolerance of the oracle, and for
+    particles with a non-finite coordinate the oracle's pattern of NaN and +-inf (0 * inf in the
+    rows outside the coordinate's block, an infinity inside it) with nobody else touched -- the
+    finite particles' bits do not depend on their neighbours.  The same line with a corrector in
+    it has a kick column and takes the dense path: same properties."""
+    n = 5003
+    base = [("drift", "D0", {"length": 0.5}), ("quadrupole", "Q1", {"length": 0.2, "k1": 4.2}),
+            ("drift", "D1", {"length": 0.3}), ("quadrupole", "Q2", {"length": 0.2, "k1": -3.1}),
+            ("drift", "D2", {"length": 0.7})]
+    kicked = base[:2] + [("hcor", "H1", {"length": 0.02, "angle": 1.5e-4})] + base[2:]
+    clean = F.cfg4_beam_soa(n, seed=11)
+    dirty = clean.copy()
+    bad = [40, 77, 4001, 4500]
+    dirty[5, 40] = np.inf     # p: s', p' stay infinite, the transverse rows become NaN
+    dirty[0, 77] = -np.inf    # x: x', xp' stay infinite, the other rows become NaN
+    dirty[2, 4001] = np.nan   # y: everything NaN
+    dirty[4, 4500] = np.inf   # s: s' infinite, p' = 0 * inf + p = NaN, the rest NaN
+    ok = np.ones(n, dtype=bool)
+    ok[bad] = False
+    for spec in (base, kicked):
+        _, t64 = _oracle_track(spec, clean, F.CFG4_ENERGY, torch.float64)
+        _, t32 = _oracle_track(spec, clean, F.CFG4_ENERGY, torch.float32)
+        ref = F.build_segment(spec).track(_gpu_beam(clean, F.CFG4_ENERGY)).soa[0, :, :n].cpu().numpy()
+        assert_close_scaled(ref, _planes(t64), _planes(t32), what="block / dense stage")
+        got = F.build_segment(spec).track(_gpu_beam(dirty, F.CFG4_ENERGY)).soa[0, :, :n].cpu().numpy()
+        # the dense product of the SAME merged map (K1's), row by row in fp32
+        M = F.build_segment(spec).transfer_map(torch.tensor([F.CFG4_ENERGY]).cuda())[0].cpu().numpy()
+        hom = np.concatenate([dirty[:6, bad], np.ones((1, len(bad)), np.float32)]).astype(np.float32)
+        with np.errstate(invalid="ignore", over="ignore"):
+            want = np.zeros((6, len(bad)), np.float32)
+            for i in range(6):
+                acc = np.full(len(bad), M[i, 6], np.float32)
+                for k in range(6):
+                    acc = (M[i, k] * hom[k] + acc).astype(np.float32)
+                want[i] = acc
+        np.testing.assert_array_equal(np.isnan(got[:, bad]), np.isnan(want))
+        np.testing.assert_array_equal(np.where(np.isinf(got[:, bad]), np.sign(got[:, bad]), 0.0),
+                                      np.where(np.isinf(want), np.sign(want), 0.0))
+        assert np.isinf(got[:, bad]).any() and np.isnan(got[:, bad]).any()
+        np.testing.assert_array_equal(got[:, ok], ref[:, ok])
+    # and through the screen: the two poisoned particles are not counted, everybody else is where
+    # the clean beam puts them
+    scr = dict(F.ARES_SCREEN)
+    scr["is_active"] = True
+    seg = F.build_segment(base + [("screen", "SCR", scr)])
+    seg.track(_gpu_beam(clean, F.CFG4_ENERGY))
+    img_clean = seg.SCR.reading.clone()
+    seg2 = F.build_segment(base + [("screen", "SCR", scr)])
+    seg2.track(_gpu_beam(dirty, F.CFG4_ENERGY))
+    img_dirty = seg2.SCR.reading
+    assert 0.0 <= float(img_clean.sum() - img_dirty.sum()) <= 4.0
+    assert int((img_clean != img_dirty).sum()) <= 4
