@@ -154,9 +154,14 @@ static __device__ __noinline__ int find_bin_slow(float x, const float* __restric
 // Regular tables (every screen the reference builds: torch.linspace), exact.
 // t = x * inv + off = (x - e0) * n / (en - e0).  margin = d + delta (hist_axis_setup): d < 0.2 is
 // the MEASURED deviation of the table from the ideal linspace through its end points, in bins;
-// delta >= |t - t*| bounds the fp32 error of t (0.75 n 2^-21 for |e0|, |en| <= en - e0: the
-// relative errors 2^-23 of inv, 1.5 * 2^-23 of off and 2^-24 of the final rounding, acting on
-// magnitudes <= n; n 2^-21 is used).
+// delta >= |t - t*| bounds the fp32 error of t for x in [e0, en] and |e0|, |en| <= en - e0.  With
+// inv_f = (n / D)(1 + a), |a| <= 2^-23 (the rounded difference D_f, then the rounded quotient),
+// off_f = -e0 inv_f (1 + b), |b| <= 2^-24, and one rounding c of the fma:
+//   t = ((x - e0) inv_f - e0 inv_f b)(1 + c) = u (1 + a) - (e0 n / D)(1 + a) b + t c,
+// the error of inv is common to both terms and acts on u = (x - e0) n / D <= n, not on x inv and
+// e0 inv separately: |t - u| <= n (2^-23 + 2^-24 + 2^-24) = n 2^-22 (second order: < 2^-30 for
+// n < 2^15; the margin carries 2^-20 of slack for it, for frac(t) - 0.5 and 0.5 - margin being
+// rounded, and 0.25 d for d being a rounded fp64 measurement).
 //   frac(t) in (margin, 1 - margin): the particle lies in bin floor(t) of the TABLE.
 //   otherwise it is within margin + delta < 0.26 bins of the ideal edge j = round(t), hence more
 //   than 0.49 bins from the ideal edges j - 1 and j + 1, whose table values are off by < 0.2:
@@ -232,7 +237,7 @@ __device__ __forceinline__ void hist_axis_setup(const float* __restrict__ e, int
     h->e0 = fe0;
     h->en = fen;
     h->inv = (float)n / (fen - fe0);
-    const float m = 1.25f * d + (float)n * (1.f / 2097152.f) + (1.f / 1048576.f);
+    const float m = 1.25f * d + (float)n * (1.f / 4194304.f) + (1.f / 1048576.f);
     const bool ok = d < 0.2f && m < 0.25f && step > 0.0 && fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
     // margin >= 0.5 means: irregular table, always searched
     h->margin = ok ? m : 1.f;
@@ -301,7 +306,7 @@ __device__ __forceinline__ void hist_axis_setup_staged(const float* __restrict__
     r.e0 = f0;
     r.en = fn;
     r.inv = (float)n / (fn - f0);
-    const float m = 1.25f * d + (float)n * (1.f / 2097152.f) + (1.f / 1048576.f);
+    const float m = 1.25f * d + (float)n * (1.f / 4194304.f) + (1.f / 1048576.f);
     const bool ok = d < 0.2f && m < 0.25f && step > 0.0 && fmaxf(fabsf(f0), fabsf(fn)) <= fn - f0;
     r.margin = ok ? m : 1.f;  // margin >= 0.5 means: irregular table, always searched
     *h = r;

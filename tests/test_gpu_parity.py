@@ -857,3 +857,50 @@ def test_block_structured_stage_maps_match_the_dense_product():
     img_dirty = seg2.SCR.reading
     assert 0.0 <= float(img_clean.sum() - img_dirty.sum()) <= 4.0
     assert int((img_clean != img_dirty).sum()) <= 4
+
+
+def test_bins_of_particles_placed_on_and_around_every_edge_are_exact():
+    """The fast bin lookup trusts floor(t) only where frac(t) is farther than a margin from 0 and 1
+    (track_common.cuh: n 2^-22 + the measured deviation of the table); everything closer is
+    decided by the edge table.  Adversarial beam: a screen alone (identity map, coordinates reach
+    the screen bit for bit), particles ON every edge of both axes, a few ulp to either side, and
+    around the margin itself (edge +- 0.05 ... 2 margins) where the fast path takes over.  The
+    image must equal torch.histogramdd's exactly.  (Every fp32 coordinate within 7 ulp of an edge
+    is in the beam; that the margin bounds the rounding error of t for ANY table is the
+    derivation in track_common.cuh, not something a test can show.)"""
+    scr = dict(F.ARES_SCREEN)
+    scr["is_active"] = True
+    ex, ey = screen_bin_edges(scr["resolution"], scr["pixel_size"], scr.get("binning", 1))
+    ex64, ey64 = ex.double().numpy(), ey.double().numpy()
+
+    def around(e):
+        e32 = e.astype(np.float32)
+        n = len(e) - 1
+        step = (e[-1] - e[0]) / n
+        m = n * 2.0 ** -22 + 2.0 ** -20
+        pts = [e32]
+        for k in (1, 2, 3, 4, 5, 6, 7):
+            up, dn = e32.copy(), e32.copy()
+            for _ in range(k):
+                up, dn = np.nextafter(up, np.float32(np.inf)), np.nextafter(dn, np.float32(-np.inf))
+            pts += [up, dn]
+        for f in (0.05, 0.1, 0.2, 0.3, 0.5, 0.9, 0.99, 1.0, 1.01, 1.1, 1.5, 2.0):
+            pts += [(e + f * m * step).astype(np.float32), (e - f * m * step).astype(np.float32)]
+        return np.concatenate(pts)
+
+    xs, ys = around(ex64), around(ey64)
+    rng = np.random.default_rng(5)
+    # pair every x candidate with a random interior y and the other way round
+    x = np.concatenate([xs, rng.uniform(ex64[3], ex64[-4], len(ys)).astype(np.float32)])
+    y = np.concatenate([rng.uniform(ey64[3], ey64[-4], len(xs)).astype(np.float32), ys])
+    n = len(x)
+    soa = np.zeros((6, n), np.float32)
+    soa[0], soa[2] = x, y
+    seg = F.build_segment([("screen", "SCR", scr)])
+    seg.track(_gpu_beam(soa, F.ASTRA_ENERGY))
+    got = seg.SCR.reading[0].cpu()
+    want = screen_reading_particles(torch.from_numpy(x)[None], torch.from_numpy(y)[None], ex, ey)[0]
+    assert got.shape == want.shape
+    assert float(want.sum()) > 0.9 * n
+    diff = (got != want)
+    assert int(diff.sum()) == 0, f"{int(diff.sum())} pixels differ, counts {float(got.sum())} vs {float(want.sum())}"
