@@ -696,8 +696,8 @@ static int launch_track_pipe_cw(const TrackArgs& a, int moment_mode, bool has_ou
   const uint32_t cap = 227 * 1024 - 4096 - 1024;  // static shared memory takes the rest
   const bool hist = a.img != nullptr && !has_out;
   if (a.img && (a.W >= 32768 || a.H >= 32768)) return 1;  // bins travel as two 15-bit lanes
-  // grid: every CTA of a row gets the same number of tiles (1 M particles on 148 CTAs: 4 x 1696
-  // each instead of 3 or 4 x 2048 -- the longest CTA sets the kernel time)
+  // grid: every CTA of a row gets the same number of tiles (1 M particles on 148 CTAs with 24
+  // consumer warps: 3 x 2272 each instead of 2 or 3 x 3072 -- the longest CTA sets the kernel time)
   int64_t per_b = (sm_count + a.B - 1) / a.B;
   if (per_b < 1) per_b = 1;
   const int64_t full_tiles = (a.N + kPipeTile - 1) / kPipeTile;
