@@ -159,9 +159,8 @@ static __device__ __noinline__ int find_bin_slow(float x, const float* __restric
 // off_f = -e0 inv_f (1 + b), |b| <= 2^-24, and one rounding c of the fma:
 //   t = ((x - e0) inv_f - e0 inv_f b)(1 + c) = u (1 + a) - (e0 n / D)(1 + a) b + t c,
 // the error of inv is common to both terms and acts on u = (x - e0) n / D <= n, not on x inv and
-// e0 inv separately: |t - u| <= n (2^-23 + 2^-24 + 2^-24) = n 2^-22 (second order: < 2^-30 for
-// n < 2^15; the margin carries 2^-20 of slack for it, for frac(t) - 0.5 and 0.5 - margin being
-// rounded, and 0.25 d for d being a rounded fp64 measurement).
+// e0 inv separately: |t - u| <= n (2^-23 + 2^-24 + 2^-24) = n 2^-22 in the worst case.
+// hist_axis_finish evaluates the first two terms for the table at hand instead of bounding them.
 //   frac(t) in (margin, 1 - margin): the particle lies in bin floor(t) of the TABLE.
 //   otherwise it is within margin + delta < 0.26 bins of the ideal edge j = round(t), hence more
 //   than 0.49 bins from the ideal edges j - 1 and j + 1, whose table values are off by < 0.2:
@@ -205,12 +204,37 @@ __device__ __forceinline__ int find_bin_regular(float x, const float* __restrict
 // Any table: irregular ones (margin >= 0.5) are searched.
 __device__ __forceinline__ int find_bin(float x, const float* __restrict__ e, int n,
                                         const HistAxis& h) {
-  const float off = -h.e0 * h.inv;
+  const float off = __fmul_rn(-h.e0, h.inv);  // the value whose error hist_axis_finish measured
   if (h.margin >= 0.5f) {
     const float t = fmaf(x, h.inv, off);
     return find_bin_slow(x, e, n, (t >= 0.f && t < (float)n) ? (int)t : 0, h.e0, h.en);
   }
   return find_bin_regular(x, e, n, h.inv, off, h.margin, h.e0, h.en);
+}
+
+// Geometry of one axis from its end points and the measured deviation d of the table (bins).
+// The rounding error of t is bounded with THIS table's numbers instead of their worst case:
+//   t = fl(x inv_f + off_f),  x inv_f + off_f = u (inv_f / inv) + (off_f + e0 inv_f),
+// so |t - u| <= n a + b + (n + 1) 2^-24 with a = |inv_f / inv - 1| (<= 2^-23) and
+// b = |off_f + e0 inv_f| (<= n 2^-24), both evaluated here in fp64 from the very fp32 values the
+// particle kernel uses (it forms off_f = -e0 * inv_f with one fp32 multiplication, as below).
+// Worst case n 2^-22; the reference's 2448 x 2040 screens come out at 0.35 - 0.6 of that, and
+// with them the share of lookups the table has to decide.  2^-20 of slack covers the rounding of
+// this evaluation, of frac(t) - 0.5 and of 0.5 - margin; 0.25 d that d is a rounded measurement.
+__device__ __forceinline__ void hist_axis_finish(HistAxis* h, float fe0, float fen, int n, float d,
+                                                 double step) {
+  const float inv_f = (float)n / (fen - fe0);
+  const float off_f = __fmul_rn(-fe0, inv_f);
+  const double inv = (double)n / ((double)fen - (double)fe0);
+  const double a = fabs((double)inv_f - inv) / inv;
+  const double b = fabs((double)off_f + (double)fe0 * (double)inv_f);
+  const float eps = (float)((double)n * a + b + (double)(n + 1) * 5.9604644775390625e-08);
+  const float m = 1.25f * d + 1.001f * eps + (1.f / 1048576.f);
+  const bool ok = d < 0.2f && m < 0.25f && step > 0.0 && fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
+  h->e0 = fe0;
+  h->en = fen;
+  h->inv = inv_f;
+  h->margin = ok ? m : 1.f;  // margin >= 0.5 means: irregular table, always searched
 }
 
 // Cooperative (whole CTA) measurement of how far edge table `e` (n+1 values) deviates from the
@@ -232,15 +256,7 @@ __device__ __forceinline__ void hist_axis_setup(const float* __restrict__ e, int
   atomicMax(&s_dev, __float_as_uint(dev));
   __syncthreads();
   if (tid == 0) {
-    const float d = __uint_as_float(s_dev);
-    const float fe0 = (float)e0, fen = (float)en;
-    h->e0 = fe0;
-    h->en = fen;
-    h->inv = (float)n / (fen - fe0);
-    const float m = 1.25f * d + (float)n * (1.f / 4194304.f) + (1.f / 1048576.f);
-    const bool ok = d < 0.2f && m < 0.25f && step > 0.0 && fmaxf(fabsf(fe0), fabsf(fen)) <= fen - fe0;
-    // margin >= 0.5 means: irregular table, always searched
-    h->margin = ok ? m : 1.f;
+    hist_axis_finish(h, (float)e0, (float)en, n, __uint_as_float(s_dev), step);
   }
   __syncthreads();
 }
@@ -301,14 +317,8 @@ __device__ __forceinline__ void hist_axis_setup_staged(const float* __restrict__
   atomicMax(&s_dev, __float_as_uint(dev));
   __syncthreads();
   if (tid == 0) {
-    const float d = __uint_as_float(s_dev);
     HistAxis r;
-    r.e0 = f0;
-    r.en = fn;
-    r.inv = (float)n / (fn - f0);
-    const float m = 1.25f * d + (float)n * (1.f / 4194304.f) + (1.f / 1048576.f);
-    const bool ok = d < 0.2f && m < 0.25f && step > 0.0 && fmaxf(fabsf(f0), fabsf(fn)) <= fn - f0;
-    r.margin = ok ? m : 1.f;  // margin >= 0.5 means: irregular table, always searched
+    hist_axis_finish(&r, f0, fn, n, __uint_as_float(s_dev), step);
     *h = r;
   }
 }

@@ -304,7 +304,8 @@ track_pipe_kernel(TrackArgs a, uint32_t win_words) {
       const float mx = rec[p.a], my = rec[p.a + 1];
       const bool yfix = (p.c & LYNX_F_SCREEN_Y_FIX) != 0;
       const HistAxis hx = s_hist[0], hy = s_hist[1];
-      const float offx = -hx.e0 * hx.inv, offy = -hy.e0 * hy.inv;
+      // one fp32 multiplication each: hist_axis_finish measured the error of exactly this value
+      const float offx = __fmul_rn(-hx.e0, hx.inv), offy = __fmul_rn(-hy.e0, hy.inv);
       const bool regular = hx.margin < 0.5f && hy.margin < 0.5f;  // warp-uniform
       int pk[4];  // ix | iy << 16, or -1 (dead lane / outside the screen)
       if (regular) {

@@ -3,9 +3,10 @@ same fp32 operations restated in numpy, checked against a search of the edge tab
 (torch.histogramdd's rule: left-closed bins, the last one right-closed).
 
 The kernel trusts floor(t), t = fma(x, inv, off), wherever frac(t) is farther than
-    margin = 1.25 d + n 2^-22 + 2^-20
+    margin = 1.25 d + 1.001 eps + 2^-20,   eps = n a + b + (n + 1) 2^-24 <= n 2^-22
 from 0 and 1 (d: measured deviation of the table from the ideal grid through its end points, in
-bins) and lets the table decide everywhere else.  The derivation of n 2^-22 is in the header;
+bins; a, b: the measured errors of inv and off for the table at hand) and lets the table decide
+everywhere else.  The derivation is in the header;
 this test throws tables at it for which the bound is tight -- one end of the screen at zero, so
 that |e0| or |en| equals the extent and u = n at the far end -- and coordinates that sit a few
 ulp to a few margins from every edge."""
@@ -16,16 +17,23 @@ F32 = np.float32
 
 
 def _setup(e):
-    """hist_axis_setup_staged: e0, en, inv, margin from the fp32 table e (n + 1 entries)."""
+    """hist_axis_setup_staged + hist_axis_finish: e0, en, inv, margin, ok, eps from the fp32 table
+    e (n + 1 entries).  eps = n a + b + (n + 1) 2^-24 with a, b the measured errors of inv and
+    off for THIS table."""
     n = len(e) - 1
     f0, fn = e[0], e[-1]
     step = (np.float64(fn) - np.float64(f0)) / n
     ideal = np.float64(f0) + step * np.arange(n + 1, dtype=np.float64)
     d = F32(np.max(np.abs(e.astype(np.float64) - ideal)) / step)
     inv = F32(F32(n) / F32(fn - f0))
-    m = F32(F32(1.25) * d + F32(n) * F32(2.0 ** -22) + F32(2.0 ** -20))
+    off = F32(-f0 * inv)
+    inv_true = np.float64(n) / (np.float64(fn) - np.float64(f0))
+    a = abs(np.float64(inv) - inv_true) / inv_true
+    b = abs(np.float64(off) + np.float64(f0) * np.float64(inv))
+    eps = F32(n * a + b + (n + 1) * 2.0 ** -24)
+    m = F32(F32(1.25) * d + F32(1.001) * eps + F32(2.0 ** -20))
     ok = d < 0.2 and m < 0.25 and step > 0 and max(abs(f0), abs(fn)) <= F32(fn - f0)
-    return f0, fn, inv, m, ok
+    return f0, fn, inv, m, ok, eps
 
 
 def _fast_bins(x, f0, fn, inv, m):
@@ -77,7 +85,7 @@ TABLES = [
 def test_fast_path_never_disagrees_with_the_table(n, lo, hi):
     rng = np.random.default_rng(n)
     e = np.linspace(np.float64(lo), np.float64(hi), n + 1).astype(F32)  # torch.linspace-like
-    f0, fn, inv, m, ok = _setup(e)
+    f0, fn, inv, m, ok, _ = _setup(e)
     if not ok:
         pytest.skip("table takes the searched path in the kernel")
     x = _candidates(e, rng)
@@ -99,7 +107,7 @@ def test_the_candidates_reach_the_error_zone():
     for n, lo, hi in [(32767, -0.37, 0.63), (2448, -4.3437e-3, 4.3437e-3), (32767, 0.0, 1.0),
                       (30011, -0.911, 0.0893), (20000, -0.0131, 0.9771)]:
         e = np.linspace(np.float64(lo), np.float64(hi), n + 1).astype(F32)
-        f0, fn, inv, _, ok = _setup(e)
+        f0, fn, inv, _, ok, _ = _setup(e)
         assert ok
         x = _candidates(e, np.random.default_rng(1))
         fast, _ = _fast_bins(x, f0, fn, inv, F32(0.0))
@@ -108,10 +116,11 @@ def test_the_candidates_reach_the_error_zone():
 
 @pytest.mark.parametrize("n,lo,hi", TABLES)
 def test_error_of_t_stays_below_the_bound(n, lo, hi):
-    """|t - u| <= n 2^-22 for every coordinate inside the table (u: the exact position on the
-    ideal grid) -- the inequality the margin is built on, checked directly."""
+    """|t - u| <= eps = n a + b + (n + 1) 2^-24 <= n 2^-22 for every coordinate inside the table
+    (u: the exact position on the ideal grid; a, b: this table's errors of inv and off) -- the
+    inequality the margin is built on, checked directly."""
     e = np.linspace(np.float64(lo), np.float64(hi), n + 1).astype(F32)
-    f0, fn, inv, _, ok = _setup(e)
+    f0, fn, inv, _, ok, eps = _setup(e)
     if not ok:
         pytest.skip("table takes the searched path in the kernel")
     x = _candidates(e, np.random.default_rng(2))
@@ -120,4 +129,5 @@ def test_error_of_t_stays_below_the_bound(n, lo, hi):
     t = (x.astype(np.float64) * np.float64(inv) + np.float64(off)).astype(F32)
     step = (np.float64(fn) - np.float64(f0)) / n
     u = (x.astype(np.float64) - np.float64(f0)) / step
-    assert np.max(np.abs(t.astype(np.float64) - u)) <= n * 2.0 ** -22
+    err = np.max(np.abs(t.astype(np.float64) - u))
+    assert err <= float(eps) <= 1.001 * n * 2.0 ** -22 + 2.0 ** -23
